@@ -1,0 +1,330 @@
+// BatchNorm for NHWC bf16 activations: batch statistics, finalize (+ running stats), fused
+// apply (+ residual + ReLU), and the two backward passes.
+//
+// Replaces torch's SyncBatchNorm autograd function and its ATen kernels (ref:main.py:43;
+// torch/nn/modules/_functions.py:39-179).  Cross-GPU exchange of the
+// per-channel partials is done by comm.cu (peer loads over NVLink); these kernels take pointer
+// tables so that one code path serves 1..8 ranks and rank-order-fixed summation keeps every rank
+// bitwise identical.
+#include "common.cuh"
+#include "../include/pmdist.h"
+
+namespace pmd {
+namespace {
+
+constexpr int kBlock = 256;
+
+// Generic per-channel two-value reduction over rows of a [rows, C] bf16 tensor.  A thread owns a
+// group of 8 consecutive channels (one 16-byte load) and walks rows with stride (threads / groups).
+template <typename F>
+__device__ __forceinline__ void column_reduce2(F f, long long rows, int C, float* out0, float* out1) {
+  extern __shared__ float red[];          // [2][rows_per_iter][C] would be large; reduce in two steps
+  const int groups = C / 8;
+  const int g = threadIdx.x % groups;
+  const int rl = threadIdx.x / groups;
+  const int rows_per_iter = blockDim.x / groups;
+  float a0[8], a1[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) a0[i] = a1[i] = 0.f;
+  if (rl < rows_per_iter) {
+    for (long long r = static_cast<long long>(blockIdx.x) * rows_per_iter + rl; r < rows;
+         r += static_cast<long long>(gridDim.x) * rows_per_iter)
+      f(r, g * 8, a0, a1);
+  }
+  // cross-thread reduction: red[rl][c] for each of the two values
+  float* r0 = red;
+  float* r1 = red + rows_per_iter * C;
+  if (rl < rows_per_iter) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      r0[rl * C + g * 8 + i] = a0[i];
+      r1[rl * C + g * 8 + i] = a1[i];
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s0 = 0.f, s1 = 0.f;
+    for (int j = 0; j < rows_per_iter; ++j) {
+      s0 += r0[j * C + c];
+      s1 += r1[j * C + c];
+    }
+    red_add_f32(out0 + c, s0);
+    red_add_f32(out1 + c, s1);
+  }
+}
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = unpack_bf16x2(w[i]);
+    v[2 * i] = f.x;
+    v[2 * i + 1] = f.y;
+  }
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
+  *reinterpret_cast<uint4*>(p) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                            pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+}
+
+__global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ y, long long rows, int C, float* stats) {
+  column_reduce2(
+      [&](long long r, int c0, float(&a0)[8], float(&a1)[8]) {
+        float v[8];
+        load8(y + r * C + c0, v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          a0[i] += v[i];
+          a1[i] += v[i] * v[i];
+        }
+      },
+      rows, C, stats, stats + C);
+}
+
+__global__ void bn_finalize_kernel(const float* const* __restrict__ stats_ranks, int world, float count_per_rank,
+                                   int C, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                   float* running_mean, float* running_var, long long* num_batches, float momentum,
+                                   float eps, float* scale, float* shift, float* save_mean, float* save_invstd) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0 && num_batches != nullptr) *num_batches += 1;
+  if (c >= C) return;
+  float s1 = 0.f, s2 = 0.f;
+  for (int w = 0; w < world; ++w) {            // fixed rank order -> identical result on every rank
+    const volatile float* st = stats_ranks[w];
+    s1 += st[c];
+    s2 += st[C + c];
+  }
+  const float n = count_per_rank * world;
+  const float mean = s1 / n;
+  const float var = fmaxf(s2 / n - mean * mean, 0.f);
+  const float invstd = rsqrtf(var + eps);
+  const float a = gamma[c] * invstd;
+  scale[c] = a;
+  shift[c] = beta[c] - mean * a;
+  save_mean[c] = mean;
+  save_invstd[c] = invstd;
+  if (running_mean != nullptr) {
+    const float unbiased = var * (n / fmaxf(n - 1.f, 1.f));
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+  }
+}
+
+__global__ void bn_eval_affine_kernel(int C, const float* gamma, const float* beta, const float* rm, const float* rv,
+                                      float eps, float* scale, float* shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float a = gamma[c] * rsqrtf(rv[c] + eps);
+  scale[c] = a;
+  shift[c] = beta[c] - rm[c] * a;
+}
+
+template <int RES>   // 0: none, 1: plain residual, 2: residual with its own affine
+__global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ scale,
+                                const float* __restrict__ shift, const __nv_bfloat16* __restrict__ res,
+                                const float* __restrict__ rscale, const float* __restrict__ rshift, int relu,
+                                __nv_bfloat16* __restrict__ z, long long total8, int C) {
+  const int groups = C / 8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total8;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c0 = static_cast<int>(i % groups) * 8;
+    float v[8], o[8];
+    load8(y + i * 8, v);
+    const float4 sa = __ldg(reinterpret_cast<const float4*>(scale + c0));
+    const float4 sb = __ldg(reinterpret_cast<const float4*>(scale + c0 + 4));
+    const float4 ha = __ldg(reinterpret_cast<const float4*>(shift + c0));
+    const float4 hb = __ldg(reinterpret_cast<const float4*>(shift + c0 + 4));
+    const float sc[8] = {sa.x, sa.y, sa.z, sa.w, sb.x, sb.y, sb.z, sb.w};
+    const float sh[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = fmaf(v[j], sc[j], sh[j]);
+    if (RES != 0) {
+      float rv[8];
+      load8(res + i * 8, rv);
+      if (RES == 2) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], __ldg(rscale + c0 + j), __ldg(rshift + c0 + j));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += rv[j];
+      }
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], 0.f);
+    }
+    store8(z + i * 8, o);
+  }
+}
+
+__global__ void bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
+                                     const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+                                     const float* __restrict__ invstd, int relu, float* sum_g, float* sum_gx,
+                                     long long rows, int C) {
+  column_reduce2(
+      [&](long long r, int c0, float(&a0)[8], float(&a1)[8]) {
+        float g[8], yv[8];
+        load8(dz + r * C + c0, g);
+        load8(y + r * C + c0, yv);
+        if (relu) {
+          float zv[8];
+          load8(z + r * C + c0, zv);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) g[i] = zv[i] > 0.f ? g[i] : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          a0[i] += g[i];
+          a1[i] += g[i] * (yv[i] - __ldg(mean + c0 + i)) * __ldg(invstd + c0 + i);
+        }
+      },
+      rows, C, sum_g, sum_gx);
+}
+
+__global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
+                                    const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+                                    const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                    const float* const* __restrict__ sums_ranks, int world, int my_rank,
+                                    float count_total, int relu, __nv_bfloat16* __restrict__ dy, float* dgamma,
+                                    float* dbeta, long long total8, int C) {
+  extern __shared__ float coef[];      // [3][C]: a = gamma*invstd, mean_g, mean_gx*invstd
+  float* ca = coef;
+  float* cg = coef + C;
+  float* cx = coef + 2 * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float sg = 0.f, sgx = 0.f;
+    for (int w = 0; w < world; ++w) {
+      const volatile float* st = sums_ranks[w];
+      sg += st[c];
+      sgx += st[C + c];
+    }
+    if (blockIdx.x == 0 && dgamma != nullptr) {
+      const volatile float* mine = sums_ranks[my_rank];
+      dbeta[c] += mine[c];
+      dgamma[c] += mine[C + c];
+    }
+    const float is = invstd[c];
+    ca[c] = gamma[c] * is;
+    cg[c] = sg / count_total;
+    cx[c] = sgx / count_total;
+  }
+  __syncthreads();
+  const int groups = C / 8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total8;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c0 = static_cast<int>(i % groups) * 8;
+    float g[8], yv[8], o[8];
+    load8(dz + i * 8, g);
+    load8(y + i * 8, yv);
+    if (relu) {
+      float zv[8];
+      load8(z + i * 8, zv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = zv[j] > 0.f ? g[j] : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = c0 + j;
+      const float xhat = (yv[j] - __ldg(mean + c)) * __ldg(invstd + c);
+      o[j] = ca[c] * (g[j] - cg[c] - xhat * cx[c]);
+    }
+    store8(dy + i * 8, o);
+  }
+}
+
+int grid_for(long long work_items, int per_block) {
+  long long b = ceil_div_ll(work_items, per_block);
+  const long long cap = 148LL * 8;
+  return static_cast<int>(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace
+}  // namespace pmd
+
+using namespace pmd;
+
+#define BN_CHECK_C(C) PMD_REQUIRE((C) % 8 == 0 && (C) >= 8 && (C) <= 2048, "BatchNorm channel count must be a multiple of 8 in [8, 2048]")
+
+extern "C" PMD_API int pmd_bn_stats(const void* d_y, long long rows, int C, float* d_stats, void* stream) {
+  BN_CHECK_C(C);
+  const int groups = C / 8, rpi = kBlock / groups > 0 ? kBlock / groups : 1;
+  PMD_REQUIRE(groups <= kBlock, "C too large for bn_stats");
+  const int smem = 2 * rpi * C * 4;
+  bn_stats_kernel<<<grid_for(rows, rpi * 4), kBlock, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(d_y), rows, C, d_stats);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_bn_finalize(const float* const* d_stats_ranks, int world, float count_per_rank, int C,
+                               const float* d_gamma, const float* d_beta, float* d_running_mean, float* d_running_var,
+                               long long* d_num_batches, float momentum, float eps, float* d_scale, float* d_shift,
+                               float* d_mean, float* d_invstd, void* stream) {
+  bn_finalize_kernel<<<ceil_div(C, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      d_stats_ranks, world, count_per_rank, C, d_gamma, d_beta, d_running_mean, d_running_var, d_num_batches, momentum,
+      eps, d_scale, d_shift, d_mean, d_invstd);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_bn_eval_affine(int C, const float* d_gamma, const float* d_beta, const float* d_running_mean,
+                                  const float* d_running_var, float eps, float* d_scale, float* d_shift, void* stream) {
+  bn_eval_affine_kernel<<<ceil_div(C, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      C, d_gamma, d_beta, d_running_mean, d_running_var, eps, d_scale, d_shift);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_bn_apply(const void* d_y, const float* d_scale, const float* d_shift, const void* d_res,
+                            const float* d_res_scale, const float* d_res_shift, int relu, void* d_z, long long rows,
+                            int C, void* stream) {
+  BN_CHECK_C(C);
+  const long long total8 = rows * C / 8;
+  const int grid = grid_for(total8, kBlock * 2);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* y = static_cast<const __nv_bfloat16*>(d_y);
+  const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(d_res);
+  __nv_bfloat16* z = static_cast<__nv_bfloat16*>(d_z);
+  if (d_res == nullptr)
+    bn_apply_kernel<0><<<grid, kBlock, 0, st>>>(y, d_scale, d_shift, nullptr, nullptr, nullptr, relu, z, total8, C);
+  else if (d_res_scale == nullptr)
+    bn_apply_kernel<1><<<grid, kBlock, 0, st>>>(y, d_scale, d_shift, res, nullptr, nullptr, relu, z, total8, C);
+  else
+    bn_apply_kernel<2><<<grid, kBlock, 0, st>>>(y, d_scale, d_shift, res, d_res_scale, d_res_shift, relu, z, total8, C);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_bn_bwd_reduce(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
+                                 const float* d_invstd, int relu, float* d_sums, long long rows, int C, void* stream) {
+  BN_CHECK_C(C);
+  const int groups = C / 8, rpi = kBlock / groups > 0 ? kBlock / groups : 1;
+  PMD_REQUIRE(groups <= kBlock, "C too large for bn_bwd_reduce");
+  const int smem = 2 * rpi * C * 4;
+  bn_bwd_reduce_kernel<<<grid_for(rows, rpi * 4), kBlock, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(d_dz), static_cast<const __nv_bfloat16*>(d_z),
+      static_cast<const __nv_bfloat16*>(d_y), d_mean, d_invstd, relu, d_sums, d_sums + C, rows, C);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
+                                const float* d_invstd, const float* d_gamma, const float* const* d_sums_ranks, int world,
+                                int my_rank, float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta,
+                                long long rows, int C, void* stream) {
+  BN_CHECK_C(C);
+  const long long total8 = rows * C / 8;
+  bn_bwd_apply_kernel<<<grid_for(total8, kBlock * 2), kBlock, 3 * C * 4, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(d_dz), static_cast<const __nv_bfloat16*>(d_z),
+      static_cast<const __nv_bfloat16*>(d_y), d_mean, d_invstd, d_gamma, d_sums_ranks, world, my_rank, count_total,
+      relu, static_cast<__nv_bfloat16*>(d_dy), d_dgamma, d_dbeta, total8, C);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}

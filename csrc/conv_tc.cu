@@ -1,0 +1,691 @@
+// Implicit-GEMM convolution for sm_100a: tcgen05.mma with TMEM accumulators, operands staged into
+// 128B-swizzled shared memory by TMA, warp-specialised (1 TMA thread, 1 MMA thread, 4 epilogue warps).
+//
+// Replaces cuDNN's fprop / dgrad / wgrad under nn.Conv2d (ref:model/resnet.py:20-31, 48-61, 79;
+// ref:main.py:45 cudnn.benchmark).
+//
+// fprop / dgrad  -- "gather GEMM":  Out[pixel, n] = sum over k-blocks  A_kb[pixel, 64] * B_kb[n, 64]
+//   * a CTA owns a tile of 128 output pixels (a w_box x h_box x n_box brick of the NHWC grid) and
+//     BN in {64,128} output channels; the accumulator is a 128-lane x BN-column fp32 TMEM tile;
+//   * a k-block is (filter tap, 64-channel chunk).  Its A operand is the same brick shifted by the
+//     tap offset, fetched with ONE 4-D TMA box -- zero padding is the TMA out-of-bounds fill, stride-2
+//     convolutions read one of four parity views of the input (separate tensor maps), and stride-2
+//     dgrad runs one output-parity class per blockIdx.z.  No im2col buffer ever exists;
+//   * fprop epilogue: bf16 round, per-channel sum / sum-of-squares for BatchNorm and a
+//     TMA store; dgrad epilogue can fold in a second convolution's k-blocks (projection shortcut) and an
+//     addend tensor (identity shortcut), so the branch sum of a residual block needs no extra pass.
+// wgrad -- dW[(tap,c), k] = sum over pixels X_tap[pixel, c] * dY[pixel, k]
+//   * both operands are "MN-major" (the reduction dim, pixels, is the slow dim of NHWC), which
+//     tcgen05 consumes directly from the TMA-written tiles: no transposes;
+//   * M = 128 = two (tap, 64-channel) boxes of X, N = up to 256 output channels, reduction split over
+//     gridDim.z CTAs; partial tiles go straight into the fp32 gradient slab with red.global.add.f32.
+#include "conv_tc.cuh"
+#include "ptx.cuh"
+
+namespace pmd {
+
+using namespace ptx;
+
+namespace {
+
+constexpr int kThreads = 192;      // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2..5: epilogue
+constexpr int kABytes = 16384;     // 128 rows x 128 B (fprop/dgrad A; wgrad: two 64-pixel boxes)
+
+__device__ __forceinline__ void tma_load_3d(const CUtensorMap* m, uint64_t* bar, void* dst, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
+template <int STAGES>
+struct PipeBars {
+  uint64_t full[STAGES];
+  uint64_t empty[STAGES];
+  uint64_t tmem_full;
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* raw) {
+  const uint32_t s = smem_u32(raw);
+  return raw + ((1024u - (s & 1023u)) & 1023u);
+}
+
+// ============================================================================ fprop / dgrad
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
+  constexpr int kStageBytes = kABytes + BN * 128;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  PipeBars<STAGES>* bars = reinterpret_cast<PipeBars<STAGES>*>(smem + STAGES * kStageBytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cls = blockIdx.z, ntile = blockIdx.y;
+  int t = blockIdx.x;
+  const int tw = t % p.tiles_w;
+  t /= p.tiles_w;
+  const int th = t % p.tiles_h;
+  const int tn = t / p.tiles_h;
+  const int w0 = tw * p.w_box, h0 = th * p.h_box, n0 = tn * p.n_box;
+  const int kb0 = p.kb_begin[cls], nkb = p.kb_count[cls];
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&bars->full[s], 1);
+      mbar_init(&bars->empty[s], 1);
+    }
+    mbar_init(&bars->tmem_full, 1);
+    fence_mbar_init();
+    prefetch_tmap(&p.a[0]);
+    prefetch_tmap(&p.b[0]);
+    prefetch_tmap(&p.out[cls]);
+  }
+  if (warp == 1) tmem_alloc<BN>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&bars->empty[s], ph ^ 1u);
+        const KBlock kb = p.kb[kb0 + i];
+        uint8_t* sa = smem + s * kStageBytes;
+        uint8_t* sb = sa + kABytes;
+        mbar_expect_tx(&bars->full[s], kStageBytes);
+        tma_load_4d(&p.a[kb.a_map], &bars->full[s], sa, kb.a_ch, w0 + kb.dw, h0 + kb.dh, n0);
+        if (p.b_tap_last)
+          tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, ntile * BN, kb.tap);
+        else
+          tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, kb.tap, ntile * BN);
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, false);
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&bars->full[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
+        const uint32_t b_addr = a_addr + kABytes;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {   // 64-channel chunk = 4 x (K = 16)
+          umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 32, 16, 1024),
+                    make_smem_desc_sw128(b_addr + k * 32, 16, 1024), idesc, (i | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&bars->empty[s]);   // frees the smem slot once these MMAs have read it
+      }
+      if (nkb > 0) umma_commit(&bars->tmem_full);
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (128 threads)
+    const int q = warp & 3;              // TMEM lane quarter this warp may read
+    const int row = q * 32 + lane;       // accumulator row == pixel inside the brick
+    const int wi = row % p.w_box;
+    const int hi = (row / p.w_box) % p.h_box;
+    const int ni = row / (p.w_box * p.h_box);
+    const bool valid = (w0 + wi < p.GW[cls]) && (h0 + hi < p.GH[cls]) && (n0 + ni < p.N);
+    const __nv_bfloat16* add_row = nullptr;
+    if (p.addend != nullptr && valid) {
+      const long long pix = (static_cast<long long>(n0 + ni) * p.GH[cls] + (h0 + hi)) * p.GW[cls] + (w0 + wi);
+      add_row = p.addend + pix * p.out_channels + ntile * BN;
+    }
+    if (nkb > 0) {
+      mbar_wait(&bars->tmem_full, 0);
+      tc_fence_after();
+    }
+    uint8_t* stage_out = smem;           // pipeline buffers are idle now: reuse them as the store staging
+#pragma unroll
+    for (int hf = 0; hf < BN / 64; ++hf) {
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        uint32_t v[32];
+        if (nkb > 0) {
+          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + hf * 64 + cc * 32, v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        uint32_t packed[16];
+        if (add_row != nullptr) {
+          const uint4* ap = reinterpret_cast<const uint4*>(add_row + hf * 64 + cc * 32);
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const uint4 a4 = __ldg(ap + jj);
+            const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 af = unpack_bf16x2(aw[e]);
+              packed[jj * 4 + e] = pack_bf16x2(__uint_as_float(v[jj * 8 + e * 2]) + af.x,
+                                               __uint_as_float(v[jj * 8 + e * 2 + 1]) + af.y);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            packed[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+        }
+        if (!valid) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) packed[j] = 0u;
+        }
+        uint8_t* rowp = stage_out + hf * kABytes + row * 128;
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          const int chunk = (cc * 4 + jj) ^ (row & 7);     // SWIZZLE_128B, as the output tensor map expects
+          *reinterpret_cast<uint4*>(rowp + chunk * 16) =
+              make_uint4(packed[jj * 4], packed[jj * 4 + 1], packed[jj * 4 + 2], packed[jj * 4 + 3]);
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    const int et = threadIdx.x - 64;
+    if (et == 0) {
+#pragma unroll
+      for (int hf = 0; hf < BN / 64; ++hf)
+        tma_store_4d(&p.out[cls], stage_out + hf * kABytes, ntile * BN + hf * 64, w0, h0, n0);
+      tma_store_commit();
+    }
+    if (p.stats != nullptr) {
+      // per-channel sum and sum of squares of the bf16-rounded tile: thread -> (channel, half of the rows)
+      const int c = et & 63, rh = et >> 6;
+#pragma unroll
+      for (int hf = 0; hf < BN / 64; ++hf) {
+        float s1 = 0.f, s2 = 0.f;
+        const uint8_t* base = stage_out + hf * kABytes;
+#pragma unroll 8
+        for (int r = rh * 64; r < rh * 64 + 64; ++r) {
+          const __nv_bfloat16 hv =
+              *reinterpret_cast<const __nv_bfloat16*>(base + r * 128 + (((c >> 3) ^ (r & 7)) << 4) + (c & 7) * 2);
+          const float f = __bfloat162float(hv);
+          s1 += f;
+          s2 += f * f;
+        }
+        red_add_f32(p.stats + ntile * BN + hf * 64 + c, s1);
+        red_add_f32(p.stats + p.out_channels + ntile * BN + hf * 64 + c, s2);
+      }
+    }
+    if (et == 0) tma_store_wait_read0();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<BN>(tmem_base);
+}
+
+// ============================================================================ wgrad
+template <int BNW, int STAGES>
+__global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_constant__ WgradParams p) {
+  constexpr int kBoxBytes = 8192;                       // 64 pixels x 128 B
+  constexpr int kStageBytes = 2 * kBoxBytes + (BNW / 64) * kBoxBytes;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  PipeBars<STAGES>* bars = reinterpret_cast<PipeBars<STAGES>*>(smem + STAGES * kStageBytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int box0 = 2 * blockIdx.x;
+  const int box1 = min(box0 + 1, p.n_boxes - 1);
+  const int k0 = blockIdx.y * BNW;
+  const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_n;
+  const int per = (tiles_total + gridDim.z - 1) / gridDim.z;
+  const int pt_begin = blockIdx.z * per;
+  const int pt_end = min(pt_begin + per, tiles_total);
+  const int niter = max(pt_end - pt_begin, 0);
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&bars->full[s], 1);
+      mbar_init(&bars->empty[s], 1);
+    }
+    mbar_init(&bars->tmem_full, 1);
+    fence_mbar_init();
+    prefetch_tmap(&p.dy);
+    prefetch_tmap(&p.x[0]);
+  }
+  if (warp == 1) tmem_alloc<BNW>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const WBox b0 = p.box[box0], b1 = p.box[box1];
+      for (int i = 0; i < niter; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        int t = pt_begin + i;
+        const int w0 = (t % p.tiles_w) * p.w_box;
+        t /= p.tiles_w;
+        const int h0 = (t % p.tiles_h) * p.h_box;
+        const int n0 = (t / p.tiles_h) * p.n_box;
+        mbar_wait(&bars->empty[s], ph ^ 1u);
+        uint8_t* sa = smem + s * kStageBytes;
+        uint8_t* sb = sa + 2 * kBoxBytes;
+        mbar_expect_tx(&bars->full[s], kStageBytes);
+        tma_load_4d(&p.x[b0.a_map], &bars->full[s], sa, b0.a_ch, w0 + b0.dw, h0 + b0.dh, n0);
+        tma_load_4d(&p.x[b1.a_map], &bars->full[s], sa + kBoxBytes, b1.a_ch, w0 + b1.dw, h0 + b1.dh, n0);
+#pragma unroll
+        for (int j = 0; j < BNW / 64; ++j)
+          tma_load_4d(&p.dy, &bars->full[s], sb + j * kBoxBytes, k0 + j * 64, w0, h0, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BNW, true, true);
+      for (int i = 0; i < niter; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&bars->full[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
+        const uint32_t b_addr = a_addr + 2 * kBoxBytes;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {   // 64 pixels = 4 x (K = 16 rows of 128 B)
+          umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 2048, kBoxBytes, 1024),
+                    make_smem_desc_sw128(b_addr + k * 2048, kBoxBytes, 1024), idesc, (i | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&bars->empty[s]);
+      }
+      if (niter > 0) umma_commit(&bars->tmem_full);
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int bx = row >> 6, c = row & 63;
+    const bool live = (niter > 0) && (box0 + bx < p.n_boxes);
+    if (niter > 0) {
+      mbar_wait(&bars->tmem_full, 0);
+      tc_fence_after();
+    }
+    const int out_col = p.box[min(box0 + bx, p.n_boxes - 1)].out_col + c;
+    if (niter > 0) {
+#pragma unroll 1
+      for (int cc = 0; cc < BNW / 32; ++cc) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cc * 32, v);
+        tmem_ld_wait();
+        if (live) {
+          float* dst = p.dw + static_cast<long long>(k0 + cc * 32) * p.RSC + out_col;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) red_add_f32(dst + static_cast<long long>(j) * p.RSC, __uint_as_float(v[j]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<BNW>(tmem_base);
+}
+
+// ============================================================================ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+int encode_map(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+               const uint32_t* box) {
+  EncodeTiledFn fn = get_encode_fn();
+  PMD_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  cuuint64_t gd[5], gs[5];
+  cuuint32_t bx[5];
+  for (int i = 0; i < rank; ++i) {
+    gd[i] = dims[i];
+    bx[i] = box[i];
+  }
+  for (int i = 0; i + 1 < rank; ++i) gs[i] = strides_bytes[i];
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gd, gs, bx, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(r)));
+    return -1;
+  }
+  return 0;
+}
+
+// NHWC bf16 activation [N,H,W,C]; view = every `step`-th row/column starting at (ph, pw).
+int act_map(CUtensorMap* m, const void* base, int N, int H, int W, int C, int step, int ph, int pw, int w_box,
+            int h_box, int n_box) {
+  const int Hv = (H - ph + step - 1) / step, Wv = (W - pw + step - 1) / step;
+  const char* b = static_cast<const char*>(base) + (static_cast<long long>(ph) * W + pw) * C * 2;
+  const uint64_t dims[4] = {(uint64_t)C, (uint64_t)Wv, (uint64_t)Hv, (uint64_t)N};
+  const uint64_t strides[3] = {(uint64_t)step * C * 2, (uint64_t)step * W * C * 2, (uint64_t)H * W * C * 2};
+  const uint32_t box[4] = {64u, (uint32_t)w_box, (uint32_t)h_box, (uint32_t)n_box};
+  return encode_map(m, b, 4, dims, strides, box);
+}
+
+int largest_pow2_le(int x) {
+  int p = 1;
+  while (p * 2 <= x) p *= 2;
+  return p;
+}
+
+// Split P (= 64 or 128) pixels into a w x h x n brick; prefer box sides that divide the grid.
+void choose_brick(int P, int GW, int GH, int* w_box, int* h_box, int* n_box) {
+  auto pick = [](int limit, int extent) {
+    int best = 1;
+    for (int c = 1; c <= limit; c *= 2)
+      if (extent % c == 0) best = c;
+    if (best < 4 && extent >= 4) best = largest_pow2_le(extent < limit ? extent : limit);   // awkward extent: accept OOB waste
+    return best;
+  };
+  *w_box = pick(P < 32 ? P : 32, GW);
+  *h_box = pick(P / *w_box, GH);
+  *n_box = P / (*w_box * *h_box);
+}
+
+}  // namespace
+
+int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
+                       ConvGemmParams* out) {
+  PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
+  ConvGemmParams& p = *out;
+  memset(&p, 0, sizeof(p));
+  const int pad = s.R / 2, RS = s.R * s.R;
+  const int Ho = conv_out_dim(s.H, s.R, s.stride), Wo = conv_out_dim(s.W, s.R, s.stride);
+  choose_brick(128, Wo, Ho, &p.w_box, &p.h_box, &p.n_box);
+  p.tiles_w = ceil_div(Wo, p.w_box);
+  p.tiles_h = ceil_div(Ho, p.h_box);
+  p.tiles_n = ceil_div(s.N, p.n_box);
+  p.N = s.N;
+  p.n_classes = 1;
+  p.GW[0] = Wo;
+  p.GH[0] = Ho;
+  p.b_tap_last = 0;
+  p.out_channels = s.K;
+  p.bn_tile = (s.K % 128 == 0) ? 128 : 64;
+  p.stats = stats;
+  p.addend = nullptr;
+  if (s.stride == 1) {
+    if (act_map(&p.a[0], x, s.N, s.H, s.W, s.C, 1, 0, 0, p.w_box, p.h_box, p.n_box)) return -1;
+  } else {
+    for (int ph = 0; ph < 2; ++ph)
+      for (int pw = 0; pw < 2; ++pw)
+        if (act_map(&p.a[ph * 2 + pw], x, s.N, s.H, s.W, s.C, 2, ph, pw, p.w_box, p.h_box, p.n_box)) return -1;
+  }
+  {
+    const uint64_t dims[3] = {(uint64_t)s.C, (uint64_t)RS, (uint64_t)s.K};
+    const uint64_t strides[2] = {(uint64_t)s.C * 2, (uint64_t)RS * s.C * 2};
+    const uint32_t box[3] = {64u, 1u, (uint32_t)p.bn_tile};
+    if (encode_map(&p.b[0], w_krsc, 3, dims, strides, box)) return -1;
+  }
+  if (act_map(&p.out[0], y, s.N, Ho, Wo, s.K, 1, 0, 0, p.w_box, p.h_box, p.n_box)) return -1;
+  int n = 0;
+  for (int r = 0; r < s.R; ++r)
+    for (int q = 0; q < s.R; ++q) {
+      int a_map = 0, dh, dw;
+      if (s.stride == 1) {
+        dh = r - pad;
+        dw = q - pad;
+      } else {   // input row = 2*ho - pad + r = 2*(ho + dh) + ph
+        const int oh = r - pad, ow = q - pad;
+        const int ph = ((oh % 2) + 2) % 2, pw = ((ow % 2) + 2) % 2;
+        dh = (oh - ph) / 2;
+        dw = (ow - pw) / 2;
+        a_map = ph * 2 + pw;
+      }
+      for (int c0 = 0; c0 < s.C; c0 += 64) {
+        PMD_REQUIRE(n < kMaxKBlocks, "too many k-blocks for one convolution");
+        KBlock& kb = p.kb[n++];
+        kb.dh = (int8_t)dh;
+        kb.dw = (int8_t)dw;
+        kb.a_map = (uint8_t)a_map;
+        kb.b_map = 0;
+        kb.a_ch = (uint16_t)c0;
+        kb.b_c0 = (uint16_t)c0;
+        kb.tap = (uint8_t)(r * s.R + q);
+      }
+    }
+  p.kb_begin[0] = 0;
+  p.kb_count[0] = n;
+  return 0;
+}
+
+int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const PmdConvShape* s2,
+                       const void* dy2, const void* w2_rsck, const void* addend, void* dx, ConvGemmParams* out) {
+  PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
+  ConvGemmParams& p = *out;
+  memset(&p, 0, sizeof(p));
+  const int Ho = conv_out_dim(s.H, s.R, s.stride), Wo = conv_out_dim(s.W, s.R, s.stride);
+  if (s2 != nullptr) {
+    PMD_REQUIRE(conv_tc_supported(*s2) && s2->N == s.N && s2->H == s.H && s2->W == s.W && s2->C == s.C &&
+                    s2->stride == s.stride && conv_out_dim(s2->H, s2->R, s2->stride) == Ho,
+                "fused second dgrad must consume the same input tensor with the same stride");
+  }
+  PMD_REQUIRE(addend == nullptr || s.stride == 1, "addend is only supported for stride-1 dgrad");
+  const int st = s.stride;
+  p.n_classes = st * st;
+  int maxGW = 0, maxGH = 0;
+  for (int ph = 0; ph < st; ++ph)
+    for (int pw = 0; pw < st; ++pw) {
+      const int cls = ph * st + pw;
+      p.GH[cls] = (s.H - ph + st - 1) / st;
+      p.GW[cls] = (s.W - pw + st - 1) / st;
+      maxGW = p.GW[cls] > maxGW ? p.GW[cls] : maxGW;
+      maxGH = p.GH[cls] > maxGH ? p.GH[cls] : maxGH;
+    }
+  choose_brick(128, maxGW, maxGH, &p.w_box, &p.h_box, &p.n_box);
+  p.tiles_w = ceil_div(maxGW, p.w_box);
+  p.tiles_h = ceil_div(maxGH, p.h_box);
+  p.tiles_n = ceil_div(s.N, p.n_box);
+  p.N = s.N;
+  p.b_tap_last = 1;
+  p.out_channels = s.C;
+  p.bn_tile = (s.C % 128 == 0) ? 128 : 64;
+  p.stats = nullptr;
+  p.addend = static_cast<const __nv_bfloat16*>(addend);
+  // A operands: the output-gradient tensors on the (Ho, Wo) grid
+  if (act_map(&p.a[0], dy, s.N, Ho, Wo, s.K, 1, 0, 0, p.w_box, p.h_box, p.n_box)) return -1;
+  if (s2 != nullptr && act_map(&p.a[1], dy2, s.N, Ho, Wo, s2->K, 1, 0, 0, p.w_box, p.h_box, p.n_box)) return -1;
+  // B operands: RSCK weights as (k inner, c rows, tap)
+  auto wmap = [&](CUtensorMap* m, const void* w, const PmdConvShape& cs) {
+    const uint64_t dims[3] = {(uint64_t)cs.K, (uint64_t)cs.C, (uint64_t)(cs.R * cs.R)};
+    const uint64_t strides[2] = {(uint64_t)cs.K * 2, (uint64_t)cs.C * cs.K * 2};
+    const uint32_t box[3] = {64u, (uint32_t)p.bn_tile, 1u};
+    return encode_map(m, w, 3, dims, strides, box);
+  };
+  if (wmap(&p.b[0], w_rsck, s)) return -1;
+  if (s2 != nullptr && wmap(&p.b[1], w2_rsck, *s2)) return -1;
+  // outputs: one parity view of dx per class
+  for (int ph = 0; ph < st; ++ph)
+    for (int pw = 0; pw < st; ++pw)
+      if (act_map(&p.out[ph * st + pw], dx, s.N, s.H, s.W, s.C, st, ph, pw, p.w_box, p.h_box, p.n_box)) return -1;
+  int n = 0;
+  for (int ph = 0; ph < st; ++ph)
+    for (int pw = 0; pw < st; ++pw) {
+      const int cls = ph * st + pw;
+      p.kb_begin[cls] = n;
+      for (int which = 0; which < (s2 != nullptr ? 2 : 1); ++which) {
+        const PmdConvShape& cs = which == 0 ? s : *s2;
+        const int pad = cs.R / 2;
+        for (int r = 0; r < cs.R; ++r)
+          for (int q = 0; q < cs.R; ++q) {
+            // input row h = st*ho - pad + r  ->  ho = (h + pad - r)/st with h = st*a + ph
+            const int nh = ph + pad - r, nw = pw + pad - q;
+            if (((nh % st) + st) % st != 0 || ((nw % st) + st) % st != 0) continue;
+            const int dh = nh / st, dw = nw / st;    // exact (checked above), may be negative
+            for (int k0 = 0; k0 < cs.K; k0 += 64) {
+              PMD_REQUIRE(n < kMaxKBlocks, "too many k-blocks for one dgrad");
+              KBlock& kb = p.kb[n++];
+              kb.dh = (int8_t)dh;
+              kb.dw = (int8_t)dw;
+              kb.a_map = (uint8_t)which;
+              kb.b_map = (uint8_t)which;
+              kb.a_ch = (uint16_t)k0;
+              kb.b_c0 = (uint16_t)k0;
+              kb.tap = (uint8_t)(r * cs.R + q);
+            }
+          }
+      }
+      p.kb_count[cls] = n - p.kb_begin[cls];
+    }
+  return 0;
+}
+
+int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, float* dw, int split, int sm_count,
+                       WgradParams* out) {
+  PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
+  WgradParams& p = *out;
+  memset(&p, 0, sizeof(p));
+  const int pad = s.R / 2, RS = s.R * s.R;
+  const int Ho = conv_out_dim(s.H, s.R, s.stride), Wo = conv_out_dim(s.W, s.R, s.stride);
+  choose_brick(64, Wo, Ho, &p.w_box, &p.h_box, &p.n_box);
+  p.tiles_w = ceil_div(Wo, p.w_box);
+  p.tiles_h = ceil_div(Ho, p.h_box);
+  p.tiles_n = ceil_div(s.N, p.n_box);
+  p.K = s.K;
+  p.RSC = RS * s.C;
+  p.dw = dw;
+  p.bn_tile = (s.K % 256 == 0) ? 256 : (s.K % 128 == 0 ? 128 : 64);
+  if (s.stride == 1) {
+    if (act_map(&p.x[0], x, s.N, s.H, s.W, s.C, 1, 0, 0, p.w_box, p.h_box, p.n_box)) return -1;
+  } else {
+    for (int ph = 0; ph < 2; ++ph)
+      for (int pw = 0; pw < 2; ++pw)
+        if (act_map(&p.x[ph * 2 + pw], x, s.N, s.H, s.W, s.C, 2, ph, pw, p.w_box, p.h_box, p.n_box)) return -1;
+  }
+  if (act_map(&p.dy, dy, s.N, Ho, Wo, s.K, 1, 0, 0, p.w_box, p.h_box, p.n_box)) return -1;
+  int n = 0;
+  for (int r = 0; r < s.R; ++r)
+    for (int q = 0; q < s.R; ++q) {
+      int a_map = 0, dh, dw_;
+      if (s.stride == 1) {
+        dh = r - pad;
+        dw_ = q - pad;
+      } else {
+        const int oh = r - pad, ow = q - pad;
+        const int ph = ((oh % 2) + 2) % 2, pw = ((ow % 2) + 2) % 2;
+        dh = (oh - ph) / 2;
+        dw_ = (ow - pw) / 2;
+        a_map = ph * 2 + pw;
+      }
+      for (int c0 = 0; c0 < s.C; c0 += 64) {
+        PMD_REQUIRE(n < kMaxWBoxes, "too many operand boxes for one wgrad");
+        WBox& b = p.box[n++];
+        b.dh = (int8_t)dh;
+        b.dw = (int8_t)dw_;
+        b.a_map = (uint8_t)a_map;
+        b.a_ch = (uint16_t)c0;
+        b.out_col = (r * s.R + q) * s.C + c0;
+      }
+    }
+  p.n_boxes = n;
+  const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_n;
+  if (split <= 0) {
+    const int ctas = ceil_div(n, 2) * (s.K / p.bn_tile);
+    split = ceil_div(3 * (sm_count > 0 ? sm_count : 148), ctas);
+    const int max_split = ceil_div(tiles_total, 8);     // keep >= 8 pipeline iterations per CTA
+    if (split > max_split) split = max_split;
+  }
+  if (split > tiles_total) split = tiles_total;
+  if (split < 1) split = 1;
+  p.split = split;
+  return 0;
+}
+
+template <typename Kernel>
+static int set_smem(Kernel k, int bytes) {
+  PMD_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  return 0;
+}
+
+int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream) {
+  const dim3 grid(p.tiles_w * p.tiles_h * p.tiles_n, p.out_channels / p.bn_tile, p.n_classes);
+  if (p.bn_tile == 64) {
+    constexpr int ST = 4;
+    constexpr int smem = ST * (kABytes + 64 * 128) + sizeof(PipeBars<ST>) + 1024;
+    static bool once = false;
+    if (!once) {
+      if (set_smem(conv_gemm_kernel<64, ST>, smem)) return -1;
+      once = true;
+    }
+    conv_gemm_kernel<64, ST><<<grid, kThreads, smem, stream>>>(p);
+  } else {
+    constexpr int ST = 3;
+    constexpr int smem = ST * (kABytes + 128 * 128) + sizeof(PipeBars<ST>) + 1024;
+    static bool once = false;
+    if (!once) {
+      if (set_smem(conv_gemm_kernel<128, ST>, smem)) return -1;
+      once = true;
+    }
+    conv_gemm_kernel<128, ST><<<grid, kThreads, smem, stream>>>(p);
+  }
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int BNW, int ST>
+static int launch_wgrad_t(const WgradParams& p, cudaStream_t stream) {
+  constexpr int smem = ST * (2 * 8192 + (BNW / 64) * 8192) + sizeof(PipeBars<ST>) + 1024;
+  static bool once = false;
+  if (!once) {
+    if (set_smem(conv_wgrad_kernel<BNW, ST>, smem)) return -1;
+    once = true;
+  }
+  const dim3 grid(ceil_div(p.n_boxes, 2), p.K / BNW, p.split);
+  conv_wgrad_kernel<BNW, ST><<<grid, kThreads, smem, stream>>>(p);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_wgrad(const WgradParams& p, cudaStream_t stream) {
+  if (p.bn_tile == 256) return launch_wgrad_t<256, 4>(p, stream);
+  if (p.bn_tile == 128) return launch_wgrad_t<128, 4>(p, stream);
+  return launch_wgrad_t<64, 4>(p, stream);
+}
+
+}  // namespace pmd
+
+// ============================================================================ C ABI
+using namespace pmd;
+
+extern "C" PMD_API int pmd_conv_fprop(const PmdConvShape* s, const void* d_x, const void* d_w_krsc, void* d_y, float* d_stats,
+                              void* stream) {
+  ConvGemmParams p;
+  if (build_fprop_params(*s, d_x, d_w_krsc, d_y, d_stats, &p)) return -1;
+  return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" PMD_API int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, const void* d_w_rsck, const PmdConvShape* s2,
+                              const void* d_dy2, const void* d_w2_rsck, const void* d_addend, void* d_dx,
+                              void* stream) {
+  ConvGemmParams p;
+  if (build_dgrad_params(*s, d_dy, d_w_rsck, s2, d_dy2, d_w2_rsck, d_addend, d_dx, &p)) return -1;
+  return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" PMD_API int pmd_conv_wgrad(const PmdConvShape* s, const void* d_x, const void* d_dy, float* d_dw_krsc, int split_k,
+                              void* stream) {
+  WgradParams p;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (build_wgrad_params(*s, d_x, d_dy, d_dw_krsc, split_k, sms, &p)) return -1;
+  return launch_wgrad(p, static_cast<cudaStream_t>(stream));
+}

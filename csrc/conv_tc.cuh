@@ -1,0 +1,76 @@
+// Internal interface of the tensor-core convolution kernels (conv_tc.cu): parameter blocks that
+// are built once per layer (tensor maps + k-block tables) and launched every step by the engine.
+#pragma once
+
+#include "common.cuh"
+#include "../include/pmdist.h"
+
+namespace pmd {
+
+constexpr int kMaxKBlocks = 96;
+constexpr int kMaxWBoxes = 96;
+
+// One pipeline stage of the fprop/dgrad implicit GEMM: which activation window and which weight
+// slice to fetch.  (dh, dw) shift the 128-pixel box inside activation map `a_map`; zero padding
+// is TMA out-of-bounds fill.
+struct KBlock {
+  int8_t dh, dw;
+  uint8_t a_map, b_map;
+  uint16_t a_ch;   // first channel of the 64-wide chunk in the activation tensor
+  uint16_t b_c0;   // first reduction-dim element of the 64-wide chunk in the weight tensor
+  uint8_t tap;     // r*S + s
+  uint8_t pad_[3];
+};
+
+struct ConvGemmParams {
+  CUtensorMap a[4];
+  CUtensorMap b[2];
+  CUtensorMap out[4];
+  KBlock kb[kMaxKBlocks];
+  int kb_begin[4], kb_count[4];
+  int GW[4], GH[4];          // valid pixel grid per class (blockIdx.z)
+  int N;
+  int w_box, h_box, n_box, tiles_w, tiles_h, tiles_n;
+  int n_classes;
+  int b_tap_last;            // weight-map coordinate order: 0 = (c, tap, n) [KRSC], 1 = (c, n, tap) [RSCK]
+  int out_channels;          // total channels of the output tensor
+  int bn_tile;               // 64 or 128
+  float* stats;              // optional [2 * out_channels]
+  const __nv_bfloat16* addend;  // optional NHWC tensor shaped like the (single-class) output
+};
+
+struct WBox {
+  int8_t dh, dw;
+  uint8_t a_map, pad0_;
+  uint16_t a_ch, pad1_;
+  int32_t out_col;           // tap * C + first channel: column of dW's [K][R*S*C] matrix
+};
+
+struct WgradParams {
+  CUtensorMap x[4];
+  CUtensorMap dy;
+  WBox box[kMaxWBoxes];
+  int n_boxes;
+  int w_box, h_box, n_box, tiles_w, tiles_h, tiles_n;
+  int K, RSC;
+  int bn_tile;               // 64, 128 or 256 output-channel columns per CTA
+  int split;
+  float* dw;
+};
+
+// Builders return 0 / -1 (error text via pmd_last_error()).
+int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
+                       ConvGemmParams* out);
+int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const PmdConvShape* s2,
+                       const void* dy2, const void* w2_rsck, const void* addend, void* dx, ConvGemmParams* out);
+int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, float* dw, int split, int sm_count,
+                       WgradParams* out);
+int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream);
+int launch_wgrad(const WgradParams& p, cudaStream_t stream);
+
+inline int conv_out_dim(int in, int R, int stride) { return (in + 2 * (R / 2) - R) / stride + 1; }
+inline bool conv_tc_supported(const PmdConvShape& s) {
+  return s.C % 64 == 0 && s.K % 64 == 0 && (s.R == 1 || s.R == 3) && (s.stride == 1 || s.stride == 2);
+}
+
+}  // namespace pmd

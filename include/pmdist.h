@@ -1,0 +1,132 @@
+/* libpmdist -- C ABI of the B200-native (sm_100a) data-parallel training runtime.
+ *
+ * Every entry point returns 0 on success and -1 on failure (pmd_last_error() has the text).
+ * Pointers named d_* are device pointers; `stream` is a cudaStream_t passed as void*.
+ * Activations are NHWC bf16; convolution weights are KRSC (fprop/wgrad) or RSCK (dgrad) bf16;
+ * master parameters, gradients and momentum are fp32.
+ *
+ * The Python package binds this header with ctypes (pmdist/ops/_lib.py).  "ref:" citations name
+ * the place in the reference (MOONJOOYOUNG/pytorch_multiprocessing-distributed) whose behaviour
+ * the entry point replaces; the reference itself ships no native code.
+ */
+#ifndef PMDIST_H_
+#define PMDIST_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* pmd_last_error(void);
+/* Number of kernels this library has launched in this process (bench.py "gpu_launches"). */
+unsigned long long pmd_launch_count(void);
+int pmd_version(void);
+
+/* ------------------------------------------------------------------ convolution (conv_tc.cu)
+ * Implicit-GEMM convolution on tcgen05 tensor cores with TMEM accumulators, operands staged by
+ * TMA.  Replaces cuDNN fprop/dgrad/wgrad under nn.Conv2d (ref:model/resnet.py:20-31, 48-61, 79;
+ * SURVEY.md K1-K3).  R == S in {1, 3}, pad = R/2, stride in {1, 2}; C and K multiples of 64. */
+typedef struct {
+  int N, H, W, C; /* input  [N, H, W, C] */
+  int K;          /* output [N, Ho, Wo, K], Ho = (H + 2*(R/2) - R)/stride + 1 */
+  int R;          /* square filter size: 1 or 3 */
+  int stride;     /* 1 or 2 */
+} PmdConvShape;
+
+/* y = conv(x, w).  If d_stats != NULL, the epilogue also accumulates per-output-channel
+ * sum(y) into d_stats[0..K) and sum(y*y) into d_stats[K..2K) (of the bf16-rounded outputs): the
+ * BatchNorm batch statistics at no extra pass.  d_stats must be zeroed by the caller. */
+int pmd_conv_fprop(const PmdConvShape* s, const void* d_x, const void* d_w_krsc, void* d_y, float* d_stats,
+                   void* stream);
+/* dx = conv_transpose(dy, w) [+ conv_transpose(dy2, w2)] [+ addend].  The optional second
+ * convolution (s2 != NULL) must consume the same input tensor (a residual block's projection
+ * shortcut); it is accumulated in the same TMEM tile, so the branch sum costs no extra pass.
+ * d_addend (may be NULL) is an NHWC bf16 tensor shaped like dx (identity-shortcut gradient). */
+int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, const void* d_w_rsck, const PmdConvShape* s2,
+                   const void* d_dy2, const void* d_w2_rsck, const void* d_addend, void* d_dx, void* stream);
+/* dw (fp32, KRSC) += x^T * dy, reduction over all N*Ho*Wo pixels split over `split_k` CTAs per
+ * output tile (0 = choose); partial tiles are added with red.global.add.f32, so d_dw is an
+ * accumulator the caller zeroes (it is a slice of the flat gradient bucket slab). */
+int pmd_conv_wgrad(const PmdConvShape* s, const void* d_x, const void* d_dy, float* d_dw_krsc, int split_k,
+                   void* stream);
+
+/* Direct (SIMT) convolution for shapes the tensor-core path does not take (the C=3 stem) and as
+ * an in-library cross-check.  Same layouts; C, K arbitrary.  x may carry `x_cstride` >= C channels
+ * per pixel (the augmentation kernel pads RGB to 4). */
+int pmd_conv_fprop_direct(const PmdConvShape* s, int x_cstride, const void* d_x, const void* d_w_krsc, void* d_y,
+                          void* stream);
+int pmd_conv_dgrad_direct(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, void* d_dx, void* stream);
+int pmd_conv_wgrad_direct(const PmdConvShape* s, int x_cstride, const void* d_x, const void* d_dy,
+                          float* d_dw_krsc, void* stream);
+
+/* ------------------------------------------------------------------ BatchNorm (bn.cu)
+ * Replaces torch's SyncBatchNorm kernels (ref:main.py:43). */
+/* per-channel sum / sum-of-squares of a bf16 [rows, C] tensor -> d_stats[2C] (accumulates). */
+int pmd_bn_stats(const void* d_y, long long rows, int C, float* d_stats, void* stream);
+/* Combine statistics and produce the affine the apply kernel uses.
+ *   d_stats_ranks: `world` pointers (device array of float*) to each rank's [2C] sums -- with
+ *   world == 1 pass a 1-element table.  count_per_rank = rows each rank contributed.
+ *   Writes scale[c] = gamma*invstd, shift[c] = beta - mean*scale, save_mean, save_invstd; updates
+ *   running_mean/var (momentum, unbiased variance) and num_batches_tracked like torch. */
+int pmd_bn_finalize(const float* const* d_stats_ranks, int world, float count_per_rank, int C, const float* d_gamma,
+                    const float* d_beta, float* d_running_mean, float* d_running_var, long long* d_num_batches,
+                    float momentum, float eps, float* d_scale, float* d_shift, float* d_mean, float* d_invstd,
+                    void* stream);
+/* eval mode: scale/shift from running statistics. */
+int pmd_bn_eval_affine(int C, const float* d_gamma, const float* d_beta, const float* d_running_mean,
+                       const float* d_running_var, float eps, float* d_scale, float* d_shift, void* stream);
+/* z = act(scale*y + shift [+ (res_scale*res + res_shift | res)]); relu != 0 applies max(.,0). */
+int pmd_bn_apply(const void* d_y, const float* d_scale, const float* d_shift, const void* d_res,
+                 const float* d_res_scale, const float* d_res_shift, int relu, void* d_z, long long rows, int C,
+                 void* stream);
+/* backward reduce: g = dz * (z > 0 if relu); d_sums[0..C) += sum(g), d_sums[C..2C) += sum(g * xhat),
+ * xhat = (y - mean) * invstd. */
+int pmd_bn_bwd_reduce(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean, const float* d_invstd,
+                      int relu, float* d_sums, long long rows, int C, void* stream);
+/* backward elementwise: dy = gamma*invstd * (g - sum_g/Ntot - xhat * sum_gx/Ntot); sums come from
+ * `world` ranks (summed in rank order); also writes dgamma = local sum_gx, dbeta = local sum_g. */
+int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean, const float* d_invstd,
+                     const float* d_gamma, const float* const* d_sums_ranks, int world, int my_rank,
+                     float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta, long long rows,
+                     int C, void* stream);
+
+/* ------------------------------------------------------------------ head + loss (head.cu)
+ * Global average pool + Linear, cross-entropy with top-1/top-5 counters (ref:model/resnet.py:102-104,
+ * ref:main.py:48,105, ref:utils.py:64-77). */
+int pmd_pool_fc_fwd(const void* d_z, int N, int HW, int C, const float* d_w, const float* d_b, int classes,
+                    float* d_feat, float* d_logits, void* stream);
+/* metrics (double[4]) += {sum loss, top-1 hits, top-5 hits, samples} over samples with valid != 0;
+ * d_dlogits = (softmax - onehot) * grad_scale (NULL for evaluation). */
+int pmd_ce_fwd_bwd(const float* d_logits, const long long* d_labels, const unsigned char* d_valid, int N,
+                   int classes, float grad_scale, float* d_dlogits, double* d_metrics, void* stream);
+int pmd_pool_fc_bwd(const float* d_dlogits, const float* d_feat, const float* d_w, int N, int HW, int C,
+                    int classes, float* d_dw, float* d_db, void* d_dz, void* stream);
+
+/* ------------------------------------------------------------------ optimiser (optim.cu)
+ * SGD with weight decay, momentum and Nesterov on flat fp32 slabs; writes the bf16 working copy
+ * in the same pass (ref:main.py:51-55,110; math = torch/optim/sgd.py). */
+int pmd_sgd_step(float* d_param, const float* d_grad, float* d_mom, void* d_param_bf16, long long n, float lr,
+                 float momentum, float weight_decay, int nesterov, float grad_scale, void* stream);
+/* bf16 KRSC -> bf16 RSCK repack of every conv weight in one launch (table of {src, dst, K, RS, C}). */
+typedef struct {
+  long long src_off; /* element offset in the bf16 working slab (KRSC) */
+  long long dst_off; /* element offset in the dgrad weight slab (RSCK) */
+  int K, RS, C;
+  int pad_;
+} PmdRepackEntry;
+int pmd_repack_dgrad_weights(const void* d_w_bf16, void* d_wt_bf16, const PmdRepackEntry* d_table, int n_entries,
+                             long long max_elems, void* stream);
+int pmd_cast_f32_to_bf16(const float* d_src, void* d_dst, long long n, void* stream);
+
+/* ------------------------------------------------------------------ input pipeline (data_aug.cu)
+ * uint8 NHWC RGB -> zero-pad crop + horizontal flip + ToTensor + Normalize(0.5, 0.5) -> NHWC bf16
+ * with `c_out` >= 3 channels (extra channels zero) (ref:data.py:11-19).
+ * aug = int32 [N,3] = (x offset, y offset, flip), offsets in [0, 2*pad]. */
+int pmd_augment(const unsigned char* d_u8, const int* d_aug, int N, int H, int W, int pad, int c_out, void* d_out,
+                void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PMDIST_H_ */

@@ -1,0 +1,71 @@
+"""ctypes binding of libpmdist.so (C ABI declared in include/pmdist.h).
+
+The library is built in-tree by tools/build_native.py (``__graft_entry__.build()`` calls it).  On a
+machine with a GPU a missing or unloadable library is a hard error -- there is no silent PyTorch
+fallback for the native ops.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import sys
+from typing import Optional
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), '_lib', 'libpmdist.so')
+REPO_ROOT = os.path.dirname(os.path.dirname(_HERE))
+_lib: Optional[C.CDLL] = None
+
+
+class PmdConvShape(C.Structure):
+    _fields_ = [('N', C.c_int), ('H', C.c_int), ('W', C.c_int), ('C', C.c_int), ('K', C.c_int),
+                ('R', C.c_int), ('stride', C.c_int)]
+
+
+class PmdRepackEntry(C.Structure):
+    _fields_ = [('src_off', C.c_longlong), ('dst_off', C.c_longlong), ('K', C.c_int), ('RS', C.c_int),
+                ('C', C.c_int), ('pad_', C.c_int)]
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def build(force: bool = False) -> str:
+    sys.path.insert(0, os.path.join(REPO_ROOT, 'tools'))
+    try:
+        import build_native
+        return build_native.build(force=force)
+    finally:
+        sys.path.pop(0)
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        _lib = C.CDLL(LIB_PATH)
+        _lib.pmd_last_error.restype = C.c_char_p
+        _lib.pmd_launch_count.restype = C.c_ulonglong
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise NativeError(lib().pmd_last_error().decode('utf-8', 'replace'))
+
+
+def launch_count() -> int:
+    return int(lib().pmd_launch_count())
+
+
+def ptr(t) -> C.c_void_p:
+    """Device (or host) pointer of a torch tensor, or NULL for None."""
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def stream_ptr(stream=None) -> C.c_void_p:
+    import torch
+    s = torch.cuda.current_stream() if stream is None else stream
+    return C.c_void_p(s.cuda_stream)

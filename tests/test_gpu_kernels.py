@@ -1,0 +1,26 @@
+"""Kernel tier: every hand-written sm_100a kernel against a plain PyTorch fp32
+reference of the same op.  Cases live in tools/gpu_cases.py (shared with tools/gpu_probe.py)."""
+import os
+import sys
+
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tools'))
+import gpu_cases  # noqa: E402
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', sorted(gpu_cases.CASES))
+def test_kernel_matches_torch_reference(name):
+    res = gpu_cases.CASES[name]()
+    assert res['ok'], res
+
+
+@pytest.mark.gpu
+def test_native_library_is_loaded_and_counts_launches():
+    import torch
+    from pmdist.ops import _lib, nn as nk
+    before = _lib.launch_count()
+    nk.bn_stats(torch.zeros(8, 8, 8, 64, dtype=torch.bfloat16, device='cuda'))
+    assert _lib.launch_count() == before + 1
+    assert any('libpmdist.so' in ln for ln in open('/proc/self/maps'))

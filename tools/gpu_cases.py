@@ -1,0 +1,331 @@
+"""GPU numerics cases shared by tests/test_gpu_*.py and tools/gpu_probe.py.
+
+Every case compares one native sm_100a kernel against a plain PyTorch fp32 reference of the same op
+on bf16-rounded inputs and returns a dict with error statistics and a pass flag.
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Dict
+
+import torch
+import torch.nn.functional as F
+
+CASES: Dict[str, Callable[[], dict]] = {}
+
+
+def case(name):
+    def deco(fn):
+        CASES[name] = fn
+        return fn
+    return deco
+
+
+def _cmp(got: torch.Tensor, ref: torch.Tensor, rel_tol: float) -> dict:
+    got, ref = got.float(), ref.float()
+    scale = ref.abs().max().item() + 1e-12
+    err = (got - ref).abs()
+    out = {'max_abs_err': err.max().item(), 'ref_max': scale, 'rel_to_max': err.max().item() / scale,
+           'mean_abs_err': err.mean().item(), 'nan': bool(torch.isnan(got).any().item())}
+    out['ok'] = (not out['nan']) and out['rel_to_max'] <= rel_tol
+    return out
+
+
+def _rand_bf16(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device='cuda').manual_seed(seed)
+    return (torch.randn(*shape, device='cuda', generator=g) * scale).to(torch.bfloat16)
+
+
+def _nchw(x_nhwc):
+    return x_nhwc.float().permute(0, 3, 1, 2).contiguous()
+
+
+def _conv_ref(x_nhwc, w_kcrs, stride):
+    R = w_kcrs.shape[-1]
+    y = F.conv2d(_nchw(x_nhwc), w_kcrs.float(), stride=stride, padding=R // 2)
+    return y.permute(0, 2, 3, 1).contiguous()
+
+
+# ------------------------------------------------------------------ fprop
+def _fprop_case(N, H, C, K, R, stride, stats=True, direct=False, W=None):
+    from pmdist.ops import conv as cv
+    W = W or H
+    x = _rand_bf16(N, H, W, C, seed=1)
+    w = _rand_bf16(K, C, R, R, scale=1.0 / math.sqrt(C * R * R), seed=2)
+    st = torch.zeros(2 * K, dtype=torch.float32, device='cuda') if (stats and not direct) else None
+    y = cv.conv_fprop(x, cv.krsc_from_torch(w), stride, st, direct=direct)
+    torch.cuda.synchronize()
+    ref = _conv_ref(x, w, stride)
+    res = _cmp(y, ref, 2e-2)
+    if st is not None:
+        yb = y.float()
+        s1, s2 = yb.sum((0, 1, 2)), (yb * yb).sum((0, 1, 2))
+        r1 = _cmp(st[:K], s1, 1e-3)
+        r2 = _cmp(st[K:], s2, 1e-3)
+        res['stats_sum_rel'] = r1['rel_to_max']
+        res['stats_sq_rel'] = r2['rel_to_max']
+        res['ok'] = res['ok'] and r1['ok'] and r2['ok']
+    return res
+
+
+for _name, _args in {
+    'fprop_3x3_s1_c64_k64_h32': (4, 32, 64, 64, 3, 1),
+    'fprop_3x3_s1_c128_k128_h16': (4, 16, 128, 128, 3, 1),
+    'fprop_3x3_s2_c64_k128_h32': (4, 32, 64, 128, 3, 2),
+    'fprop_1x1_s2_c64_k128_h32': (4, 32, 64, 128, 1, 2),
+    'fprop_1x1_s1_c256_k64_h8': (8, 8, 256, 64, 1, 1),
+    'fprop_3x3_s1_c512_k512_h4': (16, 4, 512, 512, 3, 1),
+    'fprop_3x3_s1_c64_k64_h32_n3_tail': (3, 32, 64, 64, 3, 1),
+    'fprop_3x3_s2_c256_k512_h8_n3': (3, 8, 256, 512, 3, 2),
+    'fprop_3x3_s1_c64_k64_h28_imagenetish': (2, 28, 64, 64, 3, 1),
+}.items():
+    CASES[_name] = (lambda a=_args: _fprop_case(*a))
+CASES['fprop_direct_stem_c3'] = lambda: _fprop_case(4, 32, 3, 64, 3, 1, direct=True)
+CASES['fprop_direct_c16_s2'] = lambda: _fprop_case(2, 8, 16, 24, 3, 2, direct=True)
+
+
+# ------------------------------------------------------------------ dgrad
+def _dgrad_ref(dy_nhwc, w_kcrs, x_shape_nhwc, stride):
+    N, H, W, C = x_shape_nhwc
+    R = w_kcrs.shape[-1]
+    dx = torch.nn.grad.conv2d_input((N, C, H, W), w_kcrs.float(), _nchw(dy_nhwc), stride=stride, padding=R // 2)
+    return dx.permute(0, 2, 3, 1).contiguous()
+
+
+def _dgrad_case(N, H, C, K, R, stride, shortcut_K=0, addend=False, direct=False):
+    from pmdist.ops import conv as cv
+    Ho = cv.out_dim(H, R, stride)
+    dy = _rand_bf16(N, Ho, Ho, K, seed=3)
+    w = _rand_bf16(K, C, R, R, scale=1.0 / math.sqrt(K * R * R), seed=4)
+    ref = _dgrad_ref(dy, w, (N, H, H, C), stride)
+    second = None
+    if shortcut_K:
+        dy2 = _rand_bf16(N, Ho, Ho, shortcut_K, seed=5)
+        w2 = _rand_bf16(shortcut_K, C, 1, 1, scale=1.0 / math.sqrt(shortcut_K), seed=6)
+        ref = ref + _dgrad_ref(dy2, w2, (N, H, H, C), stride)
+        second = (dy2, cv.rsck_from_torch(w2), 1)
+    add = None
+    if addend:
+        add = _rand_bf16(N, H, H, C, seed=7)
+        ref = ref + add.float()
+    if direct:
+        dx = cv.conv_dgrad(dy, cv.krsc_from_torch(w), (N, H, H, C), R, stride, direct=True)
+    else:
+        dx = cv.conv_dgrad(dy, cv.rsck_from_torch(w), (N, H, H, C), R, stride, second=second, addend=add)
+    torch.cuda.synchronize()
+    return _cmp(dx, ref, 2e-2)
+
+
+for _name, _args in {
+    'dgrad_3x3_s1_c64_k64_h32': (4, 32, 64, 64, 3, 1),
+    'dgrad_3x3_s1_c128_k128_h16_addend': (4, 16, 128, 128, 3, 1, 0, True),
+    'dgrad_3x3_s2_c64_k128_h32': (4, 32, 64, 128, 3, 2),
+    'dgrad_3x3_s2_c64_k128_h32_shortcut': (4, 32, 64, 128, 3, 2, 128),
+    'dgrad_1x1_s2_c64_k128_h32': (4, 32, 64, 128, 1, 2),
+    'dgrad_1x1_s1_c256_k64_h8_shortcut': (8, 8, 256, 64, 1, 1, 256),
+    'dgrad_3x3_s1_c512_k512_h4': (16, 4, 512, 512, 3, 1),
+    'dgrad_3x3_s2_c256_k512_h8_n3_shortcut': (3, 8, 256, 512, 3, 2, 512),
+}.items():
+    CASES[_name] = (lambda a=_args: _dgrad_case(*a))
+CASES['dgrad_direct_c16_s2'] = lambda: _dgrad_case(2, 8, 16, 24, 3, 2, direct=True)
+
+
+# ------------------------------------------------------------------ wgrad
+def _wgrad_case(N, H, C, K, R, stride, split=0, direct=False):
+    from pmdist.ops import conv as cv
+    Ho = cv.out_dim(H, R, stride)
+    x = _rand_bf16(N, H, H, C, seed=8)
+    dy = _rand_bf16(N, Ho, Ho, K, seed=9)
+    dw = cv.conv_wgrad(x, dy, R, stride, split_k=split, direct=direct)
+    torch.cuda.synchronize()
+    ref = torch.nn.grad.conv2d_weight(_nchw(x), (K, C, R, R), _nchw(dy), stride=stride, padding=R // 2)
+    return _cmp(dw, ref.permute(0, 2, 3, 1).contiguous(), 2e-3)
+
+
+for _name, _args in {
+    'wgrad_3x3_s1_c64_k64_h32': (4, 32, 64, 64, 3, 1),
+    'wgrad_3x3_s1_c64_k64_h32_split1': (2, 32, 64, 64, 3, 1, 1),
+    'wgrad_3x3_s1_c128_k128_h16': (4, 16, 128, 128, 3, 1),
+    'wgrad_3x3_s2_c64_k128_h32': (4, 32, 64, 128, 3, 2),
+    'wgrad_1x1_s2_c64_k128_h32': (4, 32, 64, 128, 1, 2),
+    'wgrad_1x1_s1_c256_k64_h8': (8, 8, 256, 64, 1, 1),
+    'wgrad_3x3_s1_c512_k512_h4': (16, 4, 512, 512, 3, 1),
+    'wgrad_3x3_s1_c256_k256_h8_n3': (3, 8, 256, 256, 3, 1),
+}.items():
+    CASES[_name] = (lambda a=_args: _wgrad_case(*a))
+CASES['wgrad_direct_stem_c3'] = lambda: _wgrad_case(4, 32, 3, 64, 3, 1, direct=True)
+CASES['wgrad_direct_generic_c16'] = lambda: _wgrad_case(2, 8, 16, 24, 3, 2, direct=True)
+
+
+# ------------------------------------------------------------------ BatchNorm
+@case('bn_train_forward_backward_c64')
+def _bn_case(C=64, N=8, H=16, relu=True, with_res=True):
+    from pmdist.ops import nn as nk
+    y = _rand_bf16(N, H, H, C, seed=10) * 1.5 + 0.25
+    y = y.to(torch.bfloat16)
+    res = _rand_bf16(N, H, H, C, seed=11) if with_res else None
+    gamma = torch.rand(C, device='cuda') + 0.5
+    beta = torch.randn(C, device='cuda') * 0.1
+    rm, rv = torch.zeros(C, device='cuda'), torch.ones(C, device='cuda')
+    nb = torch.zeros(1, dtype=torch.int64, device='cuda')
+    rows = N * H * H
+    stats = nk.bn_stats(y)
+    scale, shift, mean, invstd = nk.bn_finalize([stats], float(rows), gamma, beta, rm, rv, nb)
+    z = nk.bn_apply(y, scale, shift, relu, res)
+    dz = _rand_bf16(N, H, H, C, seed=12)
+    sums = nk.bn_bwd_reduce(dz, z, y, mean, invstd, relu)
+    dgamma, dbeta = torch.zeros(C, device='cuda'), torch.zeros(C, device='cuda')
+    dy = nk.bn_bwd_apply(dz, z, y, mean, invstd, gamma, [sums], 0, float(rows), relu, dgamma, dbeta)
+    torch.cuda.synchronize()
+    # reference in fp32 autograd
+    yr = y.float().requires_grad_(True)
+    g_, b_ = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rm2, rv2 = torch.zeros(C, device='cuda'), torch.ones(C, device='cuda')
+    out = F.batch_norm(yr.permute(0, 3, 1, 2), rm2, rv2, g_, b_, True, 0.1, 1e-5).permute(0, 2, 3, 1)
+    if with_res:
+        out = out + res.float()
+    if relu:
+        out = F.relu(out)
+    # use the kernel's own relu mask (z > 0) so bf16 rounding at the threshold cannot flip a sample
+    mask = (z.float() > 0).float() if relu else torch.ones_like(out)
+    pre = out if not relu else None
+    gsrc = dz.float() * mask
+    lin = F.batch_norm(yr.permute(0, 3, 1, 2), None, None, g_, b_, True, 0.0, 1e-5).permute(0, 2, 3, 1)
+    lin.backward(gsrc)
+    r = {}
+    r['z'] = _cmp(z, out.detach(), 1e-2)
+    r['dy'] = _cmp(dy, yr.grad, 2e-2)
+    r['dgamma'] = _cmp(dgamma, g_.grad, 2e-3)
+    r['dbeta'] = _cmp(dbeta, b_.grad, 2e-3)
+    r['running_mean'] = _cmp(rm, rm2, 1e-3)
+    r['running_var'] = _cmp(rv, rv2, 1e-3)
+    r['ok'] = all(v['ok'] for v in r.values()) and int(nb.item()) == 1
+    return r
+
+
+CASES['bn_train_forward_backward_c512_norelu'] = lambda: _bn_case(512, 16, 4, False, False)
+CASES['bn_train_forward_backward_c2048'] = lambda: _bn_case(2048, 4, 4, True, True)
+
+
+@case('bn_two_rank_tables_sum_in_rank_order')
+def _bn_two_rank():
+    """world=2 pointer tables on one GPU: statistics of two half-batches must combine to the
+    statistics of the whole batch (the SyncBN contract, torch/nn/modules/_functions.py:102-115)."""
+    from pmdist.ops import nn as nk
+    C, N, H = 64, 8, 8
+    y = (_rand_bf16(N, H, H, C, seed=13) * 2 + 1).to(torch.bfloat16)
+    gamma, beta = torch.rand(C, device='cuda') + 0.5, torch.randn(C, device='cuda')
+    halves = [y[:N // 2].contiguous(), y[N // 2:].contiguous()]
+    st = [nk.bn_stats(h) for h in halves]
+    rows_half = (N // 2) * H * H
+    sc2, sh2, m2, i2 = nk.bn_finalize(st, float(rows_half), gamma, beta, None, None, None)
+    sc1, sh1, m1, i1 = nk.bn_finalize([nk.bn_stats(y)], float(2 * rows_half), gamma, beta, None, None, None)
+    torch.cuda.synchronize()
+    r = {'scale': _cmp(sc2, sc1, 1e-5), 'shift': _cmp(sh2, sh1, 1e-4), 'mean': _cmp(m2, m1, 1e-5)}
+    r['ok'] = all(v['ok'] for v in r.values())
+    return r
+
+
+@case('bn_eval_affine')
+def _bn_eval():
+    from pmdist.ops import nn as nk
+    C = 128
+    gamma, beta = torch.rand(C, device='cuda') + 0.5, torch.randn(C, device='cuda')
+    rm, rv = torch.randn(C, device='cuda'), torch.rand(C, device='cuda') + 0.5
+    y = _rand_bf16(4, 8, 8, C, seed=14)
+    sc, sh = nk.bn_eval_affine(gamma, beta, rm, rv)
+    z = nk.bn_apply(y, sc, sh, True)
+    torch.cuda.synchronize()
+    ref = F.relu(F.batch_norm(_nchw(y), rm, rv, gamma, beta, False, 0.1, 1e-5)).permute(0, 2, 3, 1)
+    return _cmp(z, ref, 1e-2)
+
+
+@case('bn_apply_residual_with_affine')
+def _bn_res_affine():
+    from pmdist.ops import nn as nk
+    C = 128
+    y, r_ = _rand_bf16(4, 8, 8, C, seed=15), _rand_bf16(4, 8, 8, C, seed=16)
+    a, b, ra, rb = (torch.randn(C, device='cuda') for _ in range(4))
+    z = nk.bn_apply(y, a, b, True, r_, ra, rb)
+    torch.cuda.synchronize()
+    ref = F.relu(y.float() * a + b + r_.float() * ra + rb)
+    return _cmp(z, ref, 1e-2)
+
+
+# ------------------------------------------------------------------ head / loss / optimiser / aug
+@case('pool_fc_ce_forward_backward')
+def _head_case():
+    from pmdist.ops import nn as nk
+    N, H, C, classes = 32, 4, 512, 10
+    z = _rand_bf16(N, H, H, C, seed=17).abs().to(torch.bfloat16)
+    w = torch.randn(classes, C, device='cuda') * 0.05
+    b = torch.randn(classes, device='cuda') * 0.1
+    labels = torch.randint(0, classes, (N,), device='cuda')
+    feat, logits = nk.pool_fc_fwd(z, w, b)
+    dl, metrics = nk.ce_fwd_bwd(logits, labels, None, 1.0 / N)
+    dw, db, dz = nk.pool_fc_bwd(dl, feat, w, (H, H))
+    torch.cuda.synchronize()
+    zr = z.float().requires_grad_(True)
+    wr, br = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    lg = F.linear(zr.mean((1, 2)), wr, br)
+    loss = F.cross_entropy(lg, labels)
+    loss.backward()
+    top = lg.topk(5, 1).indices.eq(labels.view(-1, 1))
+    r = {'logits': _cmp(logits, lg.detach(), 1e-4), 'dw': _cmp(dw, wr.grad, 1e-3), 'db': _cmp(db, br.grad, 1e-3),
+         'dz': _cmp(dz, zr.grad, 1e-2)}
+    m = metrics.tolist()
+    r['metrics'] = {'got': m, 'want': [loss.item() * N, float(top[:, :1].sum()), float(top.sum()), float(N)]}
+    r['metrics']['ok'] = (abs(m[0] - loss.item() * N) < 1e-2 * N and m[1] == float(top[:, :1].sum())
+                          and m[2] == float(top.sum()) and m[3] == N)
+    r['ok'] = all(v['ok'] for v in r.values())
+    return r
+
+
+@case('ce_valid_mask_excludes_padding')
+def _ce_valid():
+    from pmdist.ops import nn as nk
+    N, classes = 16, 10
+    logits = torch.randn(N, classes, device='cuda')
+    labels = torch.randint(0, classes, (N,), device='cuda')
+    valid = torch.ones(N, dtype=torch.uint8, device='cuda')
+    valid[-3:] = 0
+    _, m = nk.ce_fwd_bwd(logits, labels, valid, want_grad=False)
+    torch.cuda.synchronize()
+    want = F.cross_entropy(logits[:-3], labels[:-3], reduction='sum').item()
+    ok = abs(m[0].item() - want) < 1e-3 * N and m[3].item() == N - 3
+    return {'ok': ok, 'got': m.tolist(), 'want_loss_sum': want}
+
+
+@case('sgd_nesterov_matches_torch_three_steps')
+def _sgd_case():
+    from pmdist.ops import nn as nk
+    n = 100003
+    p0 = torch.randn(n, device='cuda')
+    p, m = p0.clone(), torch.zeros(n, device='cuda')
+    pb = torch.empty(n, dtype=torch.bfloat16, device='cuda')
+    pt = p0.clone().requires_grad_(True)
+    opt = torch.optim.SGD([pt], lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=True)
+    for step in range(3):
+        g = torch.randn(n, device='cuda', generator=torch.Generator(device='cuda').manual_seed(step))
+        nk.sgd_step(p, g * 4.0, m, pb, 0.1, grad_scale=0.25)      # grad_scale folds the 1/world_size
+        pt.grad = g.clone()
+        opt.step()
+    torch.cuda.synchronize()
+    r = {'param': _cmp(p, pt.detach(), 1e-5), 'bf16_copy': _cmp(pb, p, 1e-2)}
+    r['ok'] = all(v['ok'] for v in r.values())
+    return r
+
+
+@case('augment_matches_cpu_path_bitwise')
+def _aug_case():
+    from pmdist.data.loader import augment_cpu, draw_aug_params
+    from pmdist.data.sources import synthetic_source
+    from pmdist.ops import nn as nk
+    src = synthetic_source(64, 32, seed=5)
+    aug = draw_aug_params(64, True, torch.Generator().manual_seed(1))
+    ref = augment_cpu(src.images, aug).to(torch.bfloat16)            # NCHW
+    out = nk.augment(src.images.cuda(), aug.cuda(), 8, 4)
+    torch.cuda.synchronize()
+    got = out[..., :3].permute(0, 3, 1, 2).cpu()
+    ok = torch.equal(got, ref) and bool((out[..., 3] == 0).all())
+    return {'ok': ok, 'max_abs_err': (got.float() - ref.float()).abs().max().item()}
