@@ -1,0 +1,273 @@
+"""Headline benchmark: ResNet training images/sec on N B200s of one node.
+
+    python bench.py --gpus 1 --steps 50 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus 8 --steps 50 --warmup 5
+    python bench.py --impl reference --gpus 1 --steps 20 --warmup 5      # the unmodified reference
+
+Metric / config (BASELINE.json): "ResNet images/sec at 1/2/4/8 B200 (device-timed, max over ranks)",
+config 3 = weak scaling, the reference's CIFAR ResNet18 ([1,1,1,1], ref:model/resnet.py:108-109),
+synthetic 32x32 data, 512 images per GPU, SGD-Nesterov + SyncBN + data-parallel gradient averaging,
+i.e. one full training step (forward, loss, backward, gradient all-reduce, optimizer) per "step".
+
+Two numbers are measured on the own arm:
+  value  -- device-timed (CUDA events around exactly K steps, barrier + synchronize on both sides,
+            max over ranks) with the step's inputs already in device memory;
+  e2e    -- the same K steps through the public API (BatchLoader -> engine.train_step -> read_metrics):
+            every step copies its uint8 batch + labels + augmentation parameters from pinned host memory
+            and reads the loss/accuracy accumulators back to the host.
+One training step touches ~1.4 GB of activations per 512 images, far more than the 126 MB L2, so no
+explicit L2 flush is needed between iterations (stated in "config").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BASELINE_PUBLISHED = None      # BASELINE.json: "published": {} -> vs_baseline is null
+
+
+# ----------------------------------------------------------------------------- clocks sampler
+class ClockSampler:
+    """Samples SM clock and throttle reasons with NVML while the timed region runs."""
+    REASONS = {0x0000000000000004: 'sw_power_cap', 0x0000000000000008: 'hw_slowdown',
+               0x0000000000000020: 'sw_thermal_slowdown', 0x0000000000000040: 'hw_thermal_slowdown',
+               0x0000000000000080: 'hw_power_brake_slowdown', 0x0000000000000002: 'applications_clocks_setting',
+               0x0000000000000010: 'sync_boost', 0x0000000000000100: 'display_clock_setting'}
+
+    def __init__(self, index: int, period: float = 0.1) -> None:
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self) -> None:
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._t = threading.Thread(target=self._loop, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._t is not None:
+            self._t.join()
+
+    def summary(self) -> dict:
+        s = sorted(self.samples)
+        return {'sm_mhz': (s[len(s) // 2] if s else None), 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons),
+                'samples': len(s)}
+
+
+# ----------------------------------------------------------------------------- own arm
+def run_native(a) -> None:
+    import torch
+    from pmdist.data.loader import BatchLoader
+    from pmdist.data.sampler import ShardSampler
+    from pmdist.data.sources import synthetic_source
+    from pmdist.models.resnet import MODEL_ALIASES, build_resnet, resnet_spec
+    from pmdist.ops import _lib
+    from pmdist.parallel.engine import NativeEngine, heap_bytes_for
+    from pmdist.parallel.peer import PeerComm
+    from pmdist.utils.schedule import SGDConfig
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', str(rank)))
+    if world != a.gpus:
+        raise SystemExit(f'--gpus {a.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {a.gpus}')
+    torch.cuda.set_device(local)
+    device = torch.device('cuda', local)
+    depth = MODEL_ALIASES[a.model]
+    spec = resnet_spec(depth)
+    comm = PeerComm(rank, world, device, heap_bytes_for(spec.num_parameters()))
+    torch.manual_seed(0)
+    model = build_resnet(depth)
+    B = a.per_gpu_batch
+    eng = NativeEngine(model, comm, SGDConfig(), device, B, a.image_size, sync_bn=True, use_graph=not a.no_graph,
+                       bucket_mb=a.bucket_mb, algo=a.algo)
+    src = synthetic_source(B * 8, a.image_size, seed=rank).pin()
+    loader = BatchLoader(src, ShardSampler(len(src), 1, 0, True, rank), B, True, seed=rank, pin=True)
+    lr = 0.1
+
+    def batches():
+        ep = 0
+        while True:
+            loader.set_epoch(ep)
+            ep += 1
+            for b in loader:
+                if b.n == B:
+                    yield b
+
+    it = batches()
+    # ---- warm-up (first call per batch size is eager, the second captures the CUDA graph)
+    for _ in range(max(a.warmup, 3)):
+        eng.train_step(next(it), lr)
+    eng.read_metrics()
+    torch.cuda.synchronize()
+
+    # ---- device-timed region: inputs resident in device memory
+    comm.barrier()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = _lib.launch_count()
+    with ClockSampler(local) as clk:
+        start.record()
+        for _ in range(a.steps):
+            eng.train_step_staged(B, lr)
+        stop.record()
+        torch.cuda.synchronize()
+    launches = _lib.launch_count() - launches0
+    comm.barrier()
+    dev_ms = start.elapsed_time(stop)
+    loss_dev = eng.read_metrics()
+
+    # ---- end-to-end region: public API, H2D of every batch from pinned memory, D2H of the metrics
+    comm.barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        eng.train_step(next(it), lr)
+        m = eng.read_metrics()                   # device -> host read of the step's loss / accuracy
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    comm.barrier()
+
+    import struct
+    gathered = comm.all_gather_bytes(struct.pack('dd', dev_ms, e2e_ms))
+    dev_max = max(struct.unpack('dd', g)[0] for g in gathered)
+    e2e_max = max(struct.unpack('dd', g)[1] for g in gathered)
+    if rank == 0:
+        gb = B * world
+        value = gb * a.steps / (dev_max / 1e3)
+        out = {
+            'metric': 'ResNet training images/sec (device-timed, max over ranks)', 'value': round(value, 1),
+            'unit': 'images/s', 'n_gpus': world, 'steps': a.steps, 'warmup': max(a.warmup, 3),
+            'ms_per_step': round(dev_max / a.steps, 4), 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': BASELINE_PUBLISHED, 'dtype': 'bf16', 'data': 'synthetic', 'impl': 'pmdist-native',
+            'config': {'model': f'CIFAR ResNet{depth} from model/resnet.py (ResNet18 = [1,1,1,1] blocks)',
+                       'global_batch': gb, 'per_gpu_batch': B, 'seq_len': None, 'image': f'{a.image_size}x{a.image_size}',
+                       'parallelism': f'dp{world}', 'sync_bn': True, 'optimizer': 'SGD-Nesterov lr0.1 m0.9 wd1e-4',
+                       'grad_allreduce': eng.algo, 'transport': comm.describe(), 'cuda_graph': not a.no_graph,
+                       'l2': 'no flush: per-step working set (~2.7 MB/image of activations+gradients) exceeds the 126 MB L2',
+                       'weights': 'random init'},
+            'clocks': clk.summary(),
+            'e2e': {'value': round(gb * a.steps / (e2e_max / 1e3), 1), 'unit': 'images/s',
+                    'ms_per_step': round(e2e_max / a.steps, 4),
+                    'h2d_bytes_per_step': eng.h2d_bytes(B), 'd2h_bytes_per_step': 32,
+                    'path': 'BatchLoader(pinned) -> NativeEngine.train_step -> read_metrics'},
+            'gpu_launches': int(launches), 'launches_per_step': eng.launches_per_step(B),
+            'loss_after_bench': (m[0] / m[3]) if m[3] else None,
+            'achieved_tflops_per_gpu': round(spec.train_flops_per_image(a.image_size) * B * a.steps / (dev_max / 1e3) / 1e12, 2),
+        }
+        print(json.dumps(out), flush=True)
+    eng.close()
+    comm.close()
+
+
+# ----------------------------------------------------------------------------- reference arm
+def run_reference(a) -> None:
+    """Runs baseline/_ref/main.py (the unmodified reference) through its own CLI; under torchrun only
+    rank 0 launches it -- the reference spawns its own world_size processes (ref:main.py:185-188)."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    ref_main = os.path.join(ROOT, 'baseline', '_ref', 'main.py')
+    if not os.path.exists(ref_main):
+        print(json.dumps({'impl': 'reference', 'unavailable': 'baseline/_ref missing: run baseline/install_reference.sh'}))
+        return
+    try:
+        import torch
+        ngpu = torch.cuda.device_count()
+    except Exception:
+        ngpu = 0
+    if ngpu < a.gpus:
+        print(json.dumps({'impl': 'reference', 'unavailable': f'needs {a.gpus} CUDA devices, found {ngpu}'}))
+        return
+    import tempfile
+    W, K, N, B = max(a.warmup, 3), a.steps, a.gpus, a.per_gpu_batch
+    work = tempfile.mkdtemp(prefix='ref_bench_')
+    gb = B * N
+    env = {k: v for k, v in os.environ.items()
+           if k not in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE', 'MASTER_ADDR', 'MASTER_PORT', 'TORCHELASTIC_RUN_ID',
+                        'GROUP_RANK', 'ROLE_RANK', 'LOCAL_WORLD_SIZE', 'ROLE_WORLD_SIZE')}
+    env.update({'REF_SHIM': '1', 'PYTHONPATH': os.path.join(ROOT, 'baseline', 'shim') + os.pathsep + env.get('PYTHONPATH', ''),
+                'REF_TRAIN_SIZE': str(gb * (W + K)), 'REF_TEST_SIZE': str(gb), 'REF_IMAGE_SIZE': str(a.image_size),
+                'REF_TIMING_OUT': os.path.join(work, 'timing')})
+    cmd = [sys.executable, ref_main, '--batch_size', str(gb), '--epochs', '1', '--world_size', str(N),
+           '--save_path', os.path.join(work, 'out') + '/', '--print-freq', '1000']
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    with ClockSampler(local) as clk:
+        r = subprocess.run(cmd, cwd=work, env=env, capture_output=True, text=True, timeout=3000)
+    if r.returncode != 0:
+        print(json.dumps({'impl': 'reference', 'unavailable': 'reference run failed: ' + (r.stderr or r.stdout)[-300:].replace('\n', ' ')}))
+        return
+    dev, wall, flags = [], [], {}
+    for rk in range(N):
+        with open(os.path.join(work, f'timing.rank{rk}.json')) as f:
+            t = json.load(f)
+        dev.append(sum(t['device_ms'][W:W + K]))
+        wall.append(sum(t['iter_wall_ms'][W:W + K - 1]) * K / max(K - 1, 1))
+        flags = t['flags']
+    dev_max, e2e_max = max(dev), max(wall)
+    out = {'metric': 'ResNet training images/sec (device-timed, max over ranks)', 'value': round(gb * K / (dev_max / 1e3), 1),
+           'unit': 'images/s', 'n_gpus': N, 'steps': K, 'warmup': W, 'ms_per_step': round(dev_max / K, 4),
+           'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'fp32 (cuDNN TF32 convs allowed)',
+           'data': 'synthetic', 'impl': 'reference',
+           'config': {'model': 'reference ResNet18 ([1,1,1,1]) via baseline/_ref/main.py, unmodified', 'global_batch': gb,
+                      'per_gpu_batch': B, 'seq_len': None, 'parallelism': f'dp{N} (torch DDP + SyncBatchNorm over NCCL)',
+                      'torch_flags': flags, 'timing': 'CUDA events DDP.forward..SGD.step from baseline/shim/sitecustomize.py'},
+           'clocks': clk.summary(),
+           'e2e': {'value': round(gb * K / (e2e_max / 1e3), 1), 'unit': 'images/s', 'ms_per_step': round(e2e_max / K, 4),
+                   'h2d_bytes_per_step': B * (3 * a.image_size * a.image_size * 4 + 8), 'd2h_bytes_per_step': 8,
+                   'path': "reference's own loop: DataLoader(4 workers, PIL transforms) -> .cuda() -> step -> 2x .item()"},
+           'gpu_launches': None}
+    print(json.dumps(out), flush=True)
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=30)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='native', choices=['native', 'reference'])
+    ap.add_argument('--model', default='res18')
+    ap.add_argument('--per-gpu-batch', type=int, default=512)
+    ap.add_argument('--image-size', type=int, default=32)
+    ap.add_argument('--algo', default='auto')
+    ap.add_argument('--bucket-mb', type=float, default=0.0)
+    ap.add_argument('--no-graph', action='store_true')
+    a = ap.parse_args()
+    if a.impl == 'reference':
+        run_reference(a)
+    else:
+        run_native(a)
+
+
+if __name__ == '__main__':
+    main()

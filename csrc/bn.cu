@@ -185,9 +185,9 @@ __global__ void bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dz, const
 __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
                                     const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
                                     const float* __restrict__ invstd, const float* __restrict__ gamma,
-                                    const float* const* __restrict__ sums_ranks, int world, int my_rank,
+                                    const float* const* __restrict__ sums_ranks, int world, const float* __restrict__ local_sums,
                                     float count_total, int relu, __nv_bfloat16* __restrict__ dy, float* dgamma,
-                                    float* dbeta, long long total8, int C) {
+                                    float* dbeta, __nv_bfloat16* __restrict__ g_out, long long total8, int C) {
   extern __shared__ float coef[];      // [3][C]: a = gamma*invstd, mean_g, mean_gx*invstd
   float* ca = coef;
   float* cg = coef + C;
@@ -200,9 +200,8 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const 
       sgx += st[C + c];
     }
     if (blockIdx.x == 0 && dgamma != nullptr) {
-      const volatile float* mine = sums_ranks[my_rank];
-      dbeta[c] += mine[c];
-      dgamma[c] += mine[C + c];
+      dbeta[c] += local_sums[c];
+      dgamma[c] += local_sums[C + c];
     }
     const float is = invstd[c];
     ca[c] = gamma[c] * is;
@@ -223,6 +222,7 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const 
 #pragma unroll
       for (int j = 0; j < 8; ++j) g[j] = zv[j] > 0.f ? g[j] : 0.f;
     }
+    if (g_out != nullptr) store8(g_out + i * 8, g);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int c = c0 + j;
@@ -316,14 +316,14 @@ extern "C" PMD_API int pmd_bn_bwd_reduce(const void* d_dz, const void* d_z, cons
 
 extern "C" PMD_API int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
                                 const float* d_invstd, const float* d_gamma, const float* const* d_sums_ranks, int world,
-                                int my_rank, float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta,
-                                long long rows, int C, void* stream) {
+                                const float* d_local_sums, float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta,
+                                void* d_g_out, long long rows, int C, void* stream) {
   BN_CHECK_C(C);
   const long long total8 = rows * C / 8;
   bn_bwd_apply_kernel<<<grid_for(total8, kBlock * 2), kBlock, 3 * C * 4, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(d_dz), static_cast<const __nv_bfloat16*>(d_z),
-      static_cast<const __nv_bfloat16*>(d_y), d_mean, d_invstd, d_gamma, d_sums_ranks, world, my_rank, count_total,
-      relu, static_cast<__nv_bfloat16*>(d_dy), d_dgamma, d_dbeta, total8, C);
+      static_cast<const __nv_bfloat16*>(d_y), d_mean, d_invstd, d_gamma, d_sums_ranks, world, d_local_sums, count_total,
+      relu, static_cast<__nv_bfloat16*>(d_dy), d_dgamma, d_dbeta, static_cast<__nv_bfloat16*>(d_g_out), total8, C);
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

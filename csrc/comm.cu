@@ -106,7 +106,7 @@ __global__ void barrier_kernel(PmdSym s, int slot) { rank_barrier(s, slot, false
 template <int ALGO>
 __global__ void __launch_bounds__(512) allreduce_sgd_kernel(PmdSym s, PmdAllreduceSgd a, int slot0) {
   const int slot = slot0 + blockIdx.x;
-  const SgdHyper h{a.lr, a.momentum, a.weight_decay, 1.0f / s.world, a.nesterov};
+  const SgdHyper h{a.d_lr != nullptr ? *a.d_lr : a.lr, a.momentum, a.weight_decay, 1.0f / s.world, a.nesterov};
   rank_barrier(s, slot, false);   // every rank's backward has produced this range
   const long long n4 = a.n / 4, first4 = a.first / 4;
   long long lo = 0, hi = n4;

@@ -1,0 +1,681 @@
+// The step engine: builds a static launch plan for one ResNet training / evaluation step over
+// preallocated buffers and replays it (as a CUDA graph after the first call).
+//
+// Replaces torch autograd + DDP Reducer + optimizer for the GPU path (ref:main.py:87-171; SURVEY.md
+// 3.3, 3.4, W10, W25).  What runs per training step, all on the device:
+//   memset(grad slab, BN partials) -> augment -> [conv fprop (+BN partials) -> BN finalize (peer
+//   exchange when SyncBN) -> BN apply (+residual, ReLU)]* -> pool+FC -> CE (+metrics) -> backward
+//   (BN reduce / exchange / apply, wgrad straight into the bucket slab, dgrad with the shortcut
+//   branch fused) -> per bucket, as soon as its last gradient exists: fused all-reduce + SGD on a
+//   side stream -> repack dgrad weights.
+#include <map>
+#include <memory>
+#include <vector>
+
+#include "common.cuh"
+#include "conv_tc.cuh"
+#include "../include/pmdist.h"
+#include "../include/pmdist_engine.h"
+
+using namespace pmd;
+typedef __nv_bfloat16 bf16;
+
+#define E_CHECK(expr)          \
+  do {                         \
+    if ((expr) != 0) return -1; \
+  } while (0)
+
+namespace {
+
+struct Conv {
+  PmdConvShape s{};      // s.N filled per plan
+  int Ho = 0, Wo = 0;
+  bool tc = false;
+  long long w_off = 0, g_off = 0, b_off = 0;
+  int w_bkt = 0, g_bkt = 0, b_bkt = 0;
+  float *rm = nullptr, *rv = nullptr;
+  long long* nb = nullptr;
+  int x_cstride = 0;
+  const bf16* x = nullptr;
+  bf16 *y = nullptr, *dy = nullptr;
+  float *scale = nullptr, *shift = nullptr, *mean = nullptr, *invstd = nullptr;
+  float *stats = nullptr, *sums = nullptr, *sums_total = nullptr;
+  unsigned long long stats_off = 0, sums_off = 0;
+  const float** tab_stats = nullptr;   // device: 1-entry pointer tables for the local-statistics path
+  const float** tab_sums = nullptr;
+  const float** tab_total = nullptr;
+};
+
+struct Block {
+  int main[3] = {-1, -1, -1};
+  int n_main = 0;
+  int sc = -1;
+  bf16 *z_in = nullptr, *dz_in = nullptr;
+  bf16* z_mid[2] = {nullptr, nullptr};
+  bf16* dz_mid[2] = {nullptr, nullptr};
+  bf16 *z_out = nullptr, *dz_out = nullptr, *g_out = nullptr;
+  int Hin = 0, Hout = 0, Cin = 0, Cout = 0;
+};
+
+struct ConvPlan {
+  ConvGemmParams fprop, fprop_eval;
+  WgradParams wgrad;
+};
+
+struct Plan {
+  int n = 0;
+  std::vector<ConvPlan> conv;
+  std::vector<ConvGemmParams> block_dgrad;   // one per block (conv0 + fused shortcut / addend)
+  std::vector<ConvGemmParams> inner_dgrad;   // per conv index (main[j], j >= 1)
+  cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
+  int train_launches = 0, eval_launches = 0;
+  bool train_warm = false, eval_warm = false;
+};
+
+}  // namespace
+
+struct PmdEngine {
+  PmdEngineConfig cfg{};
+  PmdComm* comm = nullptr;
+  PmdCommInfo info{};
+  PmdSym sym{};
+  std::vector<Conv> convs;
+  std::vector<Block> blocks;
+  std::vector<long long> bucket_start, bucket_numel;
+  std::vector<int> bucket_params;     // number of parameter tensors per bucket
+  int sm_count = 148;
+  // slabs (symmetric heap)
+  unsigned long long param_off = 0, grad_off = 0, mom_off = 0, bf16_off = 0, metrics_off = 0, bnpart_off = 0;
+  long long bnpart_bytes = 0;
+  float *param = nullptr, *grad = nullptr, *mom = nullptr;
+  bf16* wbf16 = nullptr;
+  double* metrics = nullptr;
+  // local buffers
+  std::vector<void*> owned;
+  bf16* wt = nullptr;                 // RSCK copies for dgrad (same element offsets as the slab)
+  PmdRepackEntry* d_repack = nullptr;
+  int n_repack = 0;
+  long long repack_max = 0;
+  bf16* x0 = nullptr;
+  unsigned char *in_u8 = nullptr, *in_valid = nullptr;
+  int* in_aug = nullptr;
+  long long* in_labels = nullptr;
+  float *feat = nullptr, *logits = nullptr, *dlogits = nullptr, *d_lr = nullptr;
+  double* metrics_total = nullptr;
+  bf16 *z_stem = nullptr, *dz_stem = nullptr;
+  long long activation_bytes = 0;
+  cudaStream_t comm_stream = nullptr;
+  std::vector<cudaEvent_t> events;
+  cudaEvent_t ev_join = nullptr;
+  std::map<int, std::unique_ptr<Plan>> plans;
+  float last_lr = -1.f;
+
+  template <typename T>
+  int dalloc(T** p, long long count) {
+    void* q = nullptr;
+    const size_t bytes = static_cast<size_t>(count) * sizeof(T);
+    PMD_CHECK_CUDA(cudaMalloc(&q, bytes > 0 ? bytes : 16));
+    PMD_CHECK_CUDA(cudaMemset(q, 0, bytes > 0 ? bytes : 16));
+    owned.push_back(q);
+    activation_bytes += static_cast<long long>(bytes);
+    *p = static_cast<T*>(q);
+    return 0;
+  }
+  int halloc(unsigned long long* off, unsigned long long bytes) {
+    const long long o = pmd_comm_alloc(comm, bytes, 1024);
+    if (o < 0) return -1;
+    *off = static_cast<unsigned long long>(o);
+    return 0;
+  }
+  template <typename T>
+  T* hptr(unsigned long long off) { return reinterpret_cast<T*>(info.local_base + off); }
+};
+
+namespace {
+
+int build_topology(PmdEngine* e) {
+  const PmdEngineConfig& c = e->cfg;
+  const int B = c.max_batch, HW = c.image_hw;
+  const int expansion = c.bottleneck ? 4 : 1;
+  const int planes[4] = {64, 128, 256, 512}, strides[4] = {1, 2, 2, 2};
+  auto add_conv = [&](int H, int Cin, int K, int R, int stride) {
+    Conv cv;
+    cv.s = PmdConvShape{B, H, H, Cin, K, R, stride};
+    cv.Ho = conv_out_dim(H, R, stride);
+    cv.Wo = cv.Ho;
+    cv.tc = conv_tc_supported(cv.s);
+    cv.x_cstride = Cin;
+    e->convs.push_back(cv);
+    return static_cast<int>(e->convs.size()) - 1;
+  };
+  const int stem = add_conv(HW, 3, 64, 3, 1);
+  e->convs[stem].x_cstride = 4;
+  int H = HW, Cin = 64;
+  for (int si = 0; si < 4; ++si)
+    for (int bi = 0; bi < c.blocks[si]; ++bi) {
+      Block b;
+      const int stride = bi == 0 ? strides[si] : 1;
+      const int P = planes[si], Cout = P * expansion;
+      b.Hin = H;
+      b.Cin = Cin;
+      b.Cout = Cout;
+      if (!c.bottleneck) {
+        b.n_main = 2;
+        b.main[0] = add_conv(H, Cin, P, 3, stride);
+        b.main[1] = add_conv(e->convs[b.main[0]].Ho, P, P, 3, 1);
+      } else {
+        b.n_main = 3;
+        b.main[0] = add_conv(H, Cin, P, 1, 1);
+        b.main[1] = add_conv(H, P, P, 3, stride);
+        b.main[2] = add_conv(e->convs[b.main[1]].Ho, P, Cout, 1, 1);
+      }
+      if (stride != 1 || Cin != Cout) b.sc = add_conv(H, Cin, Cout, 1, stride);
+      b.Hout = e->convs[b.main[b.n_main - 1]].Ho;
+      H = b.Hout;
+      Cin = Cout;
+      e->blocks.push_back(b);
+    }
+  PMD_REQUIRE(static_cast<int>(e->convs.size()) == c.n_convs, "conv count disagrees with the Python model spec");
+  return 0;
+}
+
+int allocate(PmdEngine* e) {
+  const PmdEngineConfig& c = e->cfg;
+  const long long S = c.slab_elems;
+  const int B = c.max_batch;
+  E_CHECK(e->halloc(&e->param_off, S * 4));
+  E_CHECK(e->halloc(&e->grad_off, S * 4));
+  E_CHECK(e->halloc(&e->mom_off, S * 4));
+  E_CHECK(e->halloc(&e->bf16_off, S * 2));
+  E_CHECK(e->halloc(&e->metrics_off, 64));
+  long long part = 0;
+  for (Conv& cv : e->convs) part += 4LL * cv.s.K * 4;   // stats[2K] + sums[2K]
+  e->bnpart_bytes = part;
+  E_CHECK(e->halloc(&e->bnpart_off, part));
+  e->param = e->hptr<float>(e->param_off);
+  e->grad = e->hptr<float>(e->grad_off);
+  e->mom = e->hptr<float>(e->mom_off);
+  e->wbf16 = e->hptr<bf16>(e->bf16_off);
+  e->metrics = e->hptr<double>(e->metrics_off);
+  PMD_CHECK_CUDA(cudaMemset(e->param, 0, S * 4));
+  PMD_CHECK_CUDA(cudaMemset(e->grad, 0, S * 4));
+  PMD_CHECK_CUDA(cudaMemset(e->mom, 0, S * 4));
+  PMD_CHECK_CUDA(cudaMemset(e->wbf16, 0, S * 2));
+  PMD_CHECK_CUDA(cudaMemset(e->metrics, 0, 64));
+  PMD_CHECK_CUDA(cudaMemset(e->hptr<char>(e->bnpart_off), 0, part));
+
+  E_CHECK(e->dalloc(&e->wt, S));
+  E_CHECK(e->dalloc(&e->x0, 1LL * B * c.image_hw * c.image_hw * 4));
+  E_CHECK(e->dalloc(&e->in_u8, 1LL * B * c.image_hw * c.image_hw * 3));
+  E_CHECK(e->dalloc(&e->in_aug, 3LL * B));
+  E_CHECK(e->dalloc(&e->in_labels, B));
+  E_CHECK(e->dalloc(&e->in_valid, B));
+  E_CHECK(e->dalloc(&e->feat, 1LL * B * 512 * (c.bottleneck ? 4 : 1)));
+  E_CHECK(e->dalloc(&e->logits, 1LL * B * c.num_classes));
+  E_CHECK(e->dalloc(&e->dlogits, 1LL * B * c.num_classes));
+  E_CHECK(e->dalloc(&e->d_lr, 4));
+  E_CHECK(e->dalloc(&e->metrics_total, 4));
+
+  unsigned long long poff = e->bnpart_off;
+  std::vector<PmdRepackEntry> rep;
+  for (size_t i = 0; i < e->convs.size(); ++i) {
+    Conv& cv = e->convs[i];
+    const long long out_elems = 1LL * B * cv.Ho * cv.Wo * cv.s.K;
+    E_CHECK(e->dalloc(&cv.y, out_elems));
+    E_CHECK(e->dalloc(&cv.dy, out_elems));
+    float* f = nullptr;
+    E_CHECK(e->dalloc(&f, 6LL * cv.s.K));
+    cv.scale = f;
+    cv.shift = f + cv.s.K;
+    cv.mean = f + 2 * cv.s.K;
+    cv.invstd = f + 3 * cv.s.K;
+    cv.sums_total = f + 4 * cv.s.K;
+    cv.stats_off = poff;
+    cv.sums_off = poff + 2ULL * cv.s.K * 4;
+    poff += 4ULL * cv.s.K * 4;
+    cv.stats = e->hptr<float>(cv.stats_off);
+    cv.sums = e->hptr<float>(cv.sums_off);
+    const float** tabs = nullptr;
+    E_CHECK(e->dalloc(&tabs, 4));
+    const float* host_tab[3] = {cv.stats, cv.sums, cv.sums_total};
+    PMD_CHECK_CUDA(cudaMemcpy(tabs, host_tab, sizeof(host_tab), cudaMemcpyHostToDevice));
+    cv.tab_stats = tabs;
+    cv.tab_sums = tabs + 1;
+    cv.tab_total = tabs + 2;
+    cv.w_off = c.conv_w_off[i];
+    cv.g_off = c.bn_g_off[i];
+    cv.b_off = c.bn_b_off[i];
+    cv.w_bkt = c.conv_w_bucket[i];
+    cv.g_bkt = c.bn_g_bucket[i];
+    cv.b_bkt = c.bn_b_bucket[i];
+    cv.rm = c.d_bn_float + c.bn_rm_off[i];
+    cv.rv = c.d_bn_float + c.bn_rv_off[i];
+    cv.nb = c.d_bn_nbt + i;
+    if (cv.tc && i > 0) {
+      PmdRepackEntry r{cv.w_off, cv.w_off, cv.s.K, cv.s.R * cv.s.R, cv.s.C, 0};
+      rep.push_back(r);
+      const long long el = 1LL * cv.s.K * cv.s.R * cv.s.R * cv.s.C;
+      e->repack_max = el > e->repack_max ? el : e->repack_max;
+    }
+  }
+  e->n_repack = static_cast<int>(rep.size());
+  if (e->n_repack > 0) {
+    E_CHECK(e->dalloc(&e->d_repack, e->n_repack));
+    PMD_CHECK_CUDA(cudaMemcpy(e->d_repack, rep.data(), rep.size() * sizeof(PmdRepackEntry), cudaMemcpyHostToDevice));
+  }
+  // activations between convs
+  Conv& st = e->convs[0];
+  E_CHECK(e->dalloc(&e->z_stem, 1LL * B * st.Ho * st.Wo * st.s.K));
+  E_CHECK(e->dalloc(&e->dz_stem, 1LL * B * st.Ho * st.Wo * st.s.K));
+  st.x = e->x0;
+  bf16 *z_prev = e->z_stem, *dz_prev = e->dz_stem;
+  for (Block& b : e->blocks) {
+    b.z_in = z_prev;
+    b.dz_in = dz_prev;
+    const bf16* x = b.z_in;
+    for (int j = 0; j < b.n_main; ++j) {
+      Conv& cv = e->convs[b.main[j]];
+      cv.x = x;
+      if (j < b.n_main - 1) {
+        const long long el = 1LL * B * cv.Ho * cv.Wo * cv.s.K;
+        E_CHECK(e->dalloc(&b.z_mid[j], el));
+        E_CHECK(e->dalloc(&b.dz_mid[j], el));
+        x = b.z_mid[j];
+      }
+    }
+    if (b.sc >= 0) e->convs[b.sc].x = b.z_in;
+    const long long oel = 1LL * B * b.Hout * b.Hout * b.Cout;
+    E_CHECK(e->dalloc(&b.z_out, oel));
+    E_CHECK(e->dalloc(&b.dz_out, oel));
+    if (b.sc < 0) E_CHECK(e->dalloc(&b.g_out, oel));
+    z_prev = b.z_out;
+    dz_prev = b.dz_out;
+  }
+  return 0;
+}
+
+Plan* get_plan(PmdEngine* e, int n) {
+  auto it = e->plans.find(n);
+  if (it != e->plans.end()) return it->second.get();
+  std::unique_ptr<Plan> pl(new Plan());
+  pl->n = n;
+  pl->conv.resize(e->convs.size());
+  pl->inner_dgrad.resize(e->convs.size());
+  pl->block_dgrad.resize(e->blocks.size());
+  for (size_t i = 0; i < e->convs.size(); ++i) {
+    Conv& cv = e->convs[i];
+    if (!cv.tc) continue;
+    PmdConvShape s = cv.s;
+    s.N = n;
+    if (build_fprop_params(s, cv.x, e->wbf16 + cv.w_off, cv.y, cv.stats, &pl->conv[i].fprop)) return nullptr;
+    pl->conv[i].fprop_eval = pl->conv[i].fprop;
+    pl->conv[i].fprop_eval.stats = nullptr;
+    if (build_wgrad_params(s, cv.x, cv.dy, e->grad + cv.w_off, 0, e->sm_count, &pl->conv[i].wgrad)) return nullptr;
+  }
+  for (size_t bi = 0; bi < e->blocks.size(); ++bi) {
+    Block& b = e->blocks[bi];
+    for (int j = 1; j < b.n_main; ++j) {
+      Conv& cv = e->convs[b.main[j]];
+      PmdConvShape s = cv.s;
+      s.N = n;
+      if (build_dgrad_params(s, cv.dy, e->wt + cv.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_mid[j - 1],
+                             &pl->inner_dgrad[b.main[j]]))
+        return nullptr;
+    }
+    Conv& c0 = e->convs[b.main[0]];
+    PmdConvShape s0 = c0.s;
+    s0.N = n;
+    if (b.sc >= 0) {
+      Conv& cs = e->convs[b.sc];
+      PmdConvShape ss = cs.s;
+      ss.N = n;
+      if (build_dgrad_params(s0, c0.dy, e->wt + c0.w_off, &ss, cs.dy, e->wt + cs.w_off, nullptr, b.dz_in,
+                             &pl->block_dgrad[bi]))
+        return nullptr;
+    } else {
+      if (build_dgrad_params(s0, c0.dy, e->wt + c0.w_off, nullptr, nullptr, nullptr, b.g_out, b.dz_in,
+                             &pl->block_dgrad[bi]))
+        return nullptr;
+    }
+  }
+  Plan* raw = pl.get();
+  e->plans[n] = std::move(pl);
+  return raw;
+}
+
+// ---------------------------------------------------------------------------------- step bodies
+struct BucketTracker {
+  PmdEngine* e;
+  cudaStream_t main;
+  std::vector<int> pending;
+  int launched = 0;
+  float lr;
+  int done(int bkt) {
+    if (--pending[bkt] != 0) return 0;
+    // bucket complete: hand it to the comm stream
+    cudaEvent_t ev = e->events[launched % e->events.size()];
+    PMD_CHECK_CUDA(cudaEventRecord(ev, main));
+    PMD_CHECK_CUDA(cudaStreamWaitEvent(e->comm_stream, ev, 0));
+    PmdAllreduceSgd a{};
+    a.param_off = e->param_off;
+    a.grad_off = e->grad_off;
+    a.mom_off = e->mom_off;
+    a.bf16_off = e->bf16_off;
+    a.first = e->bucket_start[bkt];
+    a.n = e->bucket_numel[bkt];
+    a.lr = lr;
+    a.momentum = e->cfg.momentum;
+    a.weight_decay = e->cfg.weight_decay;
+    a.nesterov = e->cfg.nesterov;
+    a.algo = e->cfg.algo;
+    a.blocks = e->cfg.comm_blocks;
+    a.d_lr = e->d_lr;
+    const int slot = 2 * static_cast<int>(e->convs.size()) + 8 + bkt * 128;
+    E_CHECK(pmd_allreduce_sgd(&e->sym, &a, slot, e->comm_stream));
+    ++launched;
+    return 0;
+  }
+};
+
+int bn_forward(PmdEngine* e, int ci, long long rows, cudaStream_t st) {
+  Conv& cv = e->convs[ci];
+  const PmdEngineConfig& c = e->cfg;
+  if (e->sym.world > 1 && c.sync_bn)
+    return pmd_bn_finalize_sync(&e->sym, ci, cv.stats_off, static_cast<float>(rows), cv.s.K, e->param + cv.g_off,
+                                e->param + cv.b_off, cv.rm, cv.rv, cv.nb, c.bn_momentum, c.bn_eps, cv.scale, cv.shift,
+                                cv.mean, cv.invstd, st);
+  return pmd_bn_finalize(cv.tab_stats, 1, static_cast<float>(rows), cv.s.K, e->param + cv.g_off, e->param + cv.b_off,
+                         cv.rm, cv.rv, cv.nb, c.bn_momentum, c.bn_eps, cv.scale, cv.shift, cv.mean, cv.invstd, st);
+}
+
+// BatchNorm backward of conv `ci`: dz (grad wrt the activation that followed it), mask source z.
+int bn_backward(PmdEngine* e, int ci, const bf16* dz, const bf16* z, long long rows, bf16* g_out, cudaStream_t st) {
+  Conv& cv = e->convs[ci];
+  E_CHECK(pmd_bn_bwd_reduce(dz, z, cv.y, cv.mean, cv.invstd, 1, cv.sums, rows, cv.s.K, st));
+  const bool sync = e->sym.world > 1 && e->cfg.sync_bn;
+  float total_rows = static_cast<float>(rows);
+  const float* const* tab = cv.tab_sums;
+  if (sync) {
+    E_CHECK(pmd_small_allreduce_sync(&e->sym, static_cast<int>(e->convs.size()) + ci, cv.sums_off, 2 * cv.s.K,
+                                     cv.sums_total, st));
+    tab = cv.tab_total;
+    total_rows *= e->sym.world;
+  }
+  return pmd_bn_bwd_apply(dz, z, cv.y, cv.mean, cv.invstd, e->param + cv.g_off, tab, 1, cv.sums, total_rows, 1, cv.dy,
+                          e->grad + cv.g_off, e->grad + cv.b_off, g_out, rows, cv.s.K, st);
+}
+
+int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
+  const PmdEngineConfig& c = e->cfg;
+  const int n = pl->n;
+  E_CHECK(pmd_augment(e->in_u8, e->in_aug, n, c.image_hw, c.image_hw, 8, 4, e->x0, st));
+  auto conv_fwd = [&](int ci) -> int {
+    Conv& cv = e->convs[ci];
+    const long long rows = 1LL * n * cv.Ho * cv.Wo;
+    if (cv.tc) {
+      E_CHECK(launch_conv_gemm(train ? pl->conv[ci].fprop : pl->conv[ci].fprop_eval, st));
+    } else {
+      PmdConvShape s = cv.s;
+      s.N = n;
+      E_CHECK(pmd_conv_fprop_direct(&s, cv.x_cstride, cv.x, e->wbf16 + cv.w_off, cv.y, st));
+      if (train) E_CHECK(pmd_bn_stats(cv.y, rows, cv.s.K, cv.stats, st));
+    }
+    if (train) return bn_forward(e, ci, rows, st);
+    return pmd_bn_eval_affine(cv.s.K, e->param + cv.g_off, e->param + cv.b_off, cv.rm, cv.rv, c.bn_eps, cv.scale,
+                              cv.shift, st);
+  };
+  E_CHECK(conv_fwd(0));
+  {
+    Conv& cv = e->convs[0];
+    E_CHECK(pmd_bn_apply(cv.y, cv.scale, cv.shift, nullptr, nullptr, nullptr, 1, e->z_stem, 1LL * n * cv.Ho * cv.Wo,
+                         cv.s.K, st));
+  }
+  for (Block& b : e->blocks) {
+    for (int j = 0; j < b.n_main; ++j) {
+      E_CHECK(conv_fwd(b.main[j]));
+      if (j < b.n_main - 1) {
+        Conv& cv = e->convs[b.main[j]];
+        E_CHECK(pmd_bn_apply(cv.y, cv.scale, cv.shift, nullptr, nullptr, nullptr, 1, b.z_mid[j],
+                             1LL * n * cv.Ho * cv.Wo, cv.s.K, st));
+      }
+    }
+    if (b.sc >= 0) E_CHECK(conv_fwd(b.sc));
+    Conv& last = e->convs[b.main[b.n_main - 1]];
+    const long long rows = 1LL * n * last.Ho * last.Wo;
+    if (b.sc >= 0) {
+      Conv& cs = e->convs[b.sc];
+      E_CHECK(pmd_bn_apply(last.y, last.scale, last.shift, cs.y, cs.scale, cs.shift, 1, b.z_out, rows, last.s.K, st));
+    } else {
+      E_CHECK(pmd_bn_apply(last.y, last.scale, last.shift, b.z_in, nullptr, nullptr, 1, b.z_out, rows, last.s.K, st));
+    }
+  }
+  Block& lb = e->blocks.back();
+  E_CHECK(pmd_pool_fc_fwd(lb.z_out, n, lb.Hout * lb.Hout, lb.Cout, e->param + c.fc_w_off, e->param + c.fc_b_off,
+                          c.num_classes, e->feat, e->logits, st));
+  return 0;
+}
+
+int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
+  const PmdEngineConfig& c = e->cfg;
+  const int n = pl->n;
+  PMD_CHECK_CUDA(cudaMemsetAsync(e->grad, 0, c.slab_elems * 4, st));
+  PMD_CHECK_CUDA(cudaMemsetAsync(e->hptr<char>(e->bnpart_off), 0, e->bnpart_bytes, st));
+  E_CHECK(run_forward(e, pl, true, st));
+  E_CHECK(pmd_ce_fwd_bwd(e->logits, e->in_labels, nullptr, n, c.num_classes, 1.0f / n, e->dlogits, e->metrics, st));
+  BucketTracker bt{e, st, e->bucket_params, 0, lr};
+  Block& lb = e->blocks.back();
+  E_CHECK(pmd_pool_fc_bwd(e->dlogits, e->feat, e->param + c.fc_w_off, n, lb.Hout * lb.Hout, lb.Cout, c.num_classes,
+                          e->grad + c.fc_w_off, e->grad + c.fc_b_off, lb.dz_out, st));
+  E_CHECK(bt.done(c.fc_b_bucket));
+  E_CHECK(bt.done(c.fc_w_bucket));
+  auto bn_done = [&](int ci) -> int {
+    E_CHECK(bt.done(e->convs[ci].g_bkt));
+    return bt.done(e->convs[ci].b_bkt);
+  };
+  auto wgrad = [&](int ci) -> int {
+    Conv& cv = e->convs[ci];
+    if (cv.tc) {
+      E_CHECK(launch_wgrad(pl->conv[ci].wgrad, st));
+    } else {
+      PmdConvShape s = cv.s;
+      s.N = n;
+      E_CHECK(pmd_conv_wgrad_direct(&s, cv.x_cstride, cv.x, cv.dy, e->grad + cv.w_off, st));
+    }
+    return bt.done(cv.w_bkt);
+  };
+  for (int bi = static_cast<int>(e->blocks.size()) - 1; bi >= 0; --bi) {
+    Block& b = e->blocks[bi];
+    const int last = b.main[b.n_main - 1];
+    const long long rows_out = 1LL * n * b.Hout * b.Hout;
+    E_CHECK(bn_backward(e, last, b.dz_out, b.z_out, rows_out, b.g_out, st));
+    E_CHECK(bn_done(last));
+    if (b.sc >= 0) {
+      E_CHECK(bn_backward(e, b.sc, b.dz_out, b.z_out, rows_out, nullptr, st));
+      E_CHECK(bn_done(b.sc));
+    }
+    for (int j = b.n_main - 1; j >= 1; --j) {
+      const int ci = b.main[j], prev = b.main[j - 1];
+      E_CHECK(wgrad(ci));
+      E_CHECK(launch_conv_gemm(pl->inner_dgrad[ci], st));
+      Conv& pv = e->convs[prev];
+      E_CHECK(bn_backward(e, prev, b.dz_mid[j - 1], b.z_mid[j - 1], 1LL * n * pv.Ho * pv.Wo, nullptr, st));
+      E_CHECK(bn_done(prev));
+    }
+    E_CHECK(wgrad(b.main[0]));
+    if (b.sc >= 0) E_CHECK(wgrad(b.sc));
+    E_CHECK(launch_conv_gemm(pl->block_dgrad[bi], st));
+  }
+  {
+    Conv& cv = e->convs[0];
+    E_CHECK(bn_backward(e, 0, e->dz_stem, e->z_stem, 1LL * n * cv.Ho * cv.Wo, nullptr, st));
+    E_CHECK(bn_done(0));
+    E_CHECK(wgrad(0));
+  }
+  PMD_REQUIRE(bt.launched == c.n_buckets, "internal: not every gradient bucket was launched");
+  PMD_CHECK_CUDA(cudaEventRecord(e->ev_join, e->comm_stream));
+  PMD_CHECK_CUDA(cudaStreamWaitEvent(st, e->ev_join, 0));
+  if (e->n_repack > 0) E_CHECK(pmd_repack_dgrad_weights(e->wbf16, e->wt, e->d_repack, e->n_repack, e->repack_max, st));
+  return 0;
+}
+
+int run_eval(PmdEngine* e, Plan* pl, cudaStream_t st) {
+  E_CHECK(run_forward(e, pl, false, st));
+  return pmd_ce_fwd_bwd(e->logits, e->in_labels, e->in_valid, pl->n, e->cfg.num_classes, 0.f, nullptr, e->metrics, st);
+}
+
+template <typename Body>
+int run_or_replay(PmdEngine* e, cudaGraphExec_t* graph, bool* warm, int* launches, cudaStream_t st, Body body) {
+  if (!e->cfg.use_graph || !*warm) {
+    // first call for this batch size runs eagerly: surfaces errors, sets function attributes, counts launches
+    const unsigned long long before = g_launch_count;
+    E_CHECK(body());
+    *launches = static_cast<int>(g_launch_count - before);
+    *warm = true;
+    return 0;
+  }
+  if (*graph == nullptr) {
+    cudaGraph_t g = nullptr;
+    PMD_CHECK_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    const unsigned long long before = g_launch_count;
+    const int rc = body();
+    g_launch_count = before;   // capture records nodes, nothing ran
+    const cudaError_t ce = cudaStreamEndCapture(st, &g);
+    if (rc != 0) {
+      if (g != nullptr) cudaGraphDestroy(g);
+      return -1;
+    }
+    PMD_CHECK_CUDA(ce);
+    PMD_CHECK_CUDA(cudaGraphInstantiate(graph, g, 0));
+    cudaGraphDestroy(g);
+  }
+  PMD_CHECK_CUDA(cudaGraphLaunch(*graph, st));
+  count_launch(*launches);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" PMD_API int pmd_engine_create(const PmdEngineConfig* cfg, PmdComm* comm, PmdEngine** out) {
+  PMD_REQUIRE(cfg != nullptr && comm != nullptr, "engine needs a config and a communicator");
+  PmdEngine* e = new PmdEngine();
+  *out = e;
+  e->cfg = *cfg;
+  e->comm = comm;
+  E_CHECK(pmd_comm_info(comm, &e->info));
+  e->sym.rank = e->info.rank;
+  e->sym.world = e->info.world;
+  e->sym.d_bases = reinterpret_cast<const unsigned long long*>(e->info.d_bases);
+  e->sym.mc_base = e->info.mc_base;
+  cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, e->info.device);
+  e->bucket_start.assign(cfg->bucket_start, cfg->bucket_start + cfg->n_buckets);
+  e->bucket_numel.assign(cfg->bucket_numel, cfg->bucket_numel + cfg->n_buckets);
+  PMD_REQUIRE(cfg->n_buckets >= 1 && 2 * cfg->n_convs + 8 + cfg->n_buckets * 128 + 200 < PMD_MAX_SLOTS,
+              "too many gradient buckets for the signal pad (raise --bucket-mb)");
+  E_CHECK(build_topology(e));
+  E_CHECK(allocate(e));
+  e->bucket_params.assign(cfg->n_buckets, 0);
+  for (Conv& cv : e->convs) {
+    e->bucket_params[cv.w_bkt]++;
+    e->bucket_params[cv.g_bkt]++;
+    e->bucket_params[cv.b_bkt]++;
+  }
+  e->bucket_params[cfg->fc_w_bucket]++;
+  e->bucket_params[cfg->fc_b_bucket]++;
+  // copy the offset tables: the caller's arrays need not outlive this call
+  e->cfg.conv_w_off = e->cfg.bn_g_off = e->cfg.bn_b_off = nullptr;
+  e->cfg.bucket_start = e->cfg.bucket_numel = nullptr;
+  PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
+  e->events.resize(cfg->n_buckets + 1);
+  for (auto& ev : e->events) PMD_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  PMD_CHECK_CUDA(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+  PMD_CHECK_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+extern "C" PMD_API int pmd_engine_destroy(PmdEngine* e) {
+  if (e == nullptr) return 0;
+  cudaDeviceSynchronize();
+  for (auto& kv : e->plans) {
+    if (kv.second->train_graph) cudaGraphExecDestroy(kv.second->train_graph);
+    if (kv.second->eval_graph) cudaGraphExecDestroy(kv.second->eval_graph);
+  }
+  for (void* p : e->owned) cudaFree(p);
+  for (auto& ev : e->events) cudaEventDestroy(ev);
+  if (e->ev_join) cudaEventDestroy(e->ev_join);
+  if (e->comm_stream) cudaStreamDestroy(e->comm_stream);
+  delete e;
+  return 0;
+}
+
+extern "C" PMD_API int pmd_engine_buffers(PmdEngine* e, PmdEngineBuffers* o) {
+  memset(o, 0, sizeof(*o));
+  o->param = reinterpret_cast<unsigned long long>(e->param);
+  o->grad = reinterpret_cast<unsigned long long>(e->grad);
+  o->mom = reinterpret_cast<unsigned long long>(e->mom);
+  o->bf16 = reinterpret_cast<unsigned long long>(e->wbf16);
+  o->in_u8 = reinterpret_cast<unsigned long long>(e->in_u8);
+  o->in_aug = reinterpret_cast<unsigned long long>(e->in_aug);
+  o->in_labels = reinterpret_cast<unsigned long long>(e->in_labels);
+  o->in_valid = reinterpret_cast<unsigned long long>(e->in_valid);
+  o->logits = reinterpret_cast<unsigned long long>(e->logits);
+  o->metrics = reinterpret_cast<unsigned long long>(e->metrics);
+  o->slab_elems = e->cfg.slab_elems;
+  o->activation_bytes = e->activation_bytes;
+  o->heap_bytes_used = static_cast<long long>(e->bnpart_off + e->bnpart_bytes);
+  return 0;
+}
+
+extern "C" PMD_API int pmd_engine_sync_params(PmdEngine* e, int broadcast_from_rank0, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (broadcast_from_rank0 && e->sym.world > 1) {
+    E_CHECK(pmd_broadcast(&e->sym, e->param_off, static_cast<unsigned long long>(e->cfg.slab_elems) * 4, 0, 64,
+                          PMD_MAX_SLOTS - 128, st));
+    E_CHECK(pmd_broadcast(&e->sym, e->mom_off, static_cast<unsigned long long>(e->cfg.slab_elems) * 4, 0, 64,
+                          PMD_MAX_SLOTS - 128, st));
+  }
+  E_CHECK(pmd_cast_f32_to_bf16(e->param, e->wbf16, e->cfg.slab_elems, st));
+  if (e->n_repack > 0) E_CHECK(pmd_repack_dgrad_weights(e->wbf16, e->wt, e->d_repack, e->n_repack, e->repack_max, st));
+  PMD_CHECK_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" PMD_API int pmd_engine_train_step(PmdEngine* e, int n, float lr, void* stream) {
+  PMD_REQUIRE(n >= 1 && n <= e->cfg.max_batch, "batch size outside [1, max_batch]");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Plan* pl = get_plan(e, n);
+  if (pl == nullptr) return -1;
+  if (lr != e->last_lr) {
+    PMD_CHECK_CUDA(cudaMemcpyAsync(e->d_lr, &lr, sizeof(float), cudaMemcpyHostToDevice, st));
+    e->last_lr = lr;
+  }
+  return run_or_replay(e, &pl->train_graph, &pl->train_warm, &pl->train_launches, st,
+                       [&]() { return run_train(e, pl, lr, st); });
+}
+
+extern "C" PMD_API int pmd_engine_eval_step(PmdEngine* e, int n, void* stream) {
+  PMD_REQUIRE(n >= 1 && n <= e->cfg.max_batch, "batch size outside [1, max_batch]");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Plan* pl = get_plan(e, n);
+  if (pl == nullptr) return -1;
+  return run_or_replay(e, &pl->eval_graph, &pl->eval_warm, &pl->eval_launches, st,
+                       [&]() { return run_eval(e, pl, st); });
+}
+
+extern "C" PMD_API int pmd_engine_read_metrics(PmdEngine* e, int reduce_over_ranks, int reset, double* out4,
+                                               void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const double* src = e->metrics;
+  if (reduce_over_ranks && e->sym.world > 1) {
+    E_CHECK(pmd_metric_allreduce(&e->sym, PMD_MAX_SLOTS - 160, e->metrics_off, e->metrics_total, st));
+    src = e->metrics_total;
+  }
+  PMD_CHECK_CUDA(cudaMemcpyAsync(out4, src, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (reset) PMD_CHECK_CUDA(cudaMemsetAsync(e->metrics, 0, 4 * sizeof(double), st));
+  PMD_CHECK_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" PMD_API int pmd_engine_launches_per_step(PmdEngine* e, int n) {
+  auto it = e->plans.find(n);
+  return it == e->plans.end() ? 0 : it->second->train_launches;
+}

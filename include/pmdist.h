@@ -85,11 +85,12 @@ int pmd_bn_apply(const void* d_y, const float* d_scale, const float* d_shift, co
 int pmd_bn_bwd_reduce(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean, const float* d_invstd,
                       int relu, float* d_sums, long long rows, int C, void* stream);
 /* backward elementwise: dy = gamma*invstd * (g - sum_g/Ntot - xhat * sum_gx/Ntot); sums come from
- * `world` ranks (summed in rank order); also writes dgamma = local sum_gx, dbeta = local sum_g. */
+ * `world` ranks (summed in rank order); also adds dgamma += d_local_sums[C..2C), dbeta += d_local_sums[0..C).
+ * d_g_out (may be NULL) receives g itself: the gradient an identity shortcut carries past the block. */
 int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean, const float* d_invstd,
-                     const float* d_gamma, const float* const* d_sums_ranks, int world, int my_rank,
-                     float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta, long long rows,
-                     int C, void* stream);
+                     const float* d_gamma, const float* const* d_sums_ranks, int world, const float* d_local_sums,
+                     float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta, void* d_g_out,
+                     long long rows, int C, void* stream);
 
 /* ------------------------------------------------------------------ head + loss (head.cu)
  * Global average pool + Linear, cross-entropy with top-1/top-5 counters (ref:model/resnet.py:102-104,

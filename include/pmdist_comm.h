@@ -92,6 +92,7 @@ typedef struct {
   int nesterov;
   int algo;   /* PMD_ALGO_* (AUTO resolved by the caller) */
   int blocks; /* CTAs (== flag slots used) */
+  const float* d_lr; /* if non-NULL the learning rate is read from device memory (CUDA-graph replays) */
 } PmdAllreduceSgd;
 int pmd_allreduce_sgd(const PmdSym* sym, const PmdAllreduceSgd* a, int slot, void* stream);
 

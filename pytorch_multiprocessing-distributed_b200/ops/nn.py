@@ -66,13 +66,14 @@ def bn_bwd_reduce(dz, z, y, mean, invstd, relu: bool, sums: Optional[torch.Tenso
 
 
 def bn_bwd_apply(dz, z, y, mean, invstd, gamma, sums_ranks: Sequence[torch.Tensor], my_rank: int, count_total: float,
-                 relu: bool, dgamma=None, dbeta=None) -> torch.Tensor:
+                 relu: bool, dgamma=None, dbeta=None, g_out=None) -> torch.Tensor:
     Cc = y.shape[-1]
     dy = torch.empty_like(y)
     table = _ptr_table(sums_ranks)
     check(_lib.lib().pmd_bn_bwd_apply(ptr(dz), ptr(z), ptr(y), ptr(mean), ptr(invstd), ptr(gamma), ptr(table),
-                                      C.c_int(len(sums_ranks)), C.c_int(my_rank), _F(count_total), C.c_int(int(relu)),
-                                      ptr(dy), ptr(dgamma), ptr(dbeta), _LL(y.numel() // Cc), C.c_int(Cc), stream_ptr()))
+                                      C.c_int(len(sums_ranks)), ptr(sums_ranks[my_rank]), _F(count_total), C.c_int(int(relu)),
+                                      ptr(dy), ptr(dgamma), ptr(dbeta), ptr(g_out), _LL(y.numel() // Cc), C.c_int(Cc),
+                                      stream_ptr()))
     return dy
 
 

@@ -66,8 +66,11 @@ def _make_comm(args, rank, world_size, device):
     if backend == 'auto':
         backend = ('p2p' if device.type == 'cuda' else 'gloo') if world_size > 1 else 'single'
     if backend == 'p2p':
+        from .models.resnet import MODEL_ALIASES, resnet_spec
+        from .parallel.engine import heap_bytes_for
         from .parallel.peer import PeerComm
-        return PeerComm(rank, world_size, device)
+        depth = MODEL_ALIASES.get(args.model.lower(), 18)
+        return PeerComm(rank, world_size, device, heap_bytes_for(resnet_spec(depth, args.num_classes).num_parameters()))
     if world_size == 1 and backend in ('gloo', 'single'):
         backend = 'single'
     return make_comm(rank, world_size, backend, device)
@@ -208,10 +211,12 @@ def worker(rank: int, world_size: int, args) -> None:
             train_epoch(engine, train_loader, epoch, lr, args, rank, train_logger, comm)
             validate(engine, test_loader, epoch, args, rank, test_logger, comm, 'test')
             last = epoch == int(args.epochs)
-            if rank == 0 and (last or (args.save_every and epoch % args.save_every == 0)):
-                ckpt.save_model(args.save_path, epoch, engine.model_state())
-                ckpt.save_train_state(args.save_path, epoch, engine.optimizer_state(),
-                                      {'args': {k: v for k, v in vars(args).items()}})
+            if last or (args.save_every and epoch % args.save_every == 0):
+                opt_state = engine.optimizer_state()       # collective: momentum slices live on their owner rank
+                if rank == 0:
+                    ckpt.save_model(args.save_path, epoch, engine.model_state())
+                    ckpt.save_train_state(args.save_path, epoch, opt_state,
+                                          {'args': {k: v for k, v in vars(args).items()}})
         if rank == 0 and not args.no_plot and args.epochs >= start_epoch:
             from .utils import plot_curves
             plot_curves.draw_plot(args.save_path)

@@ -329,3 +329,142 @@ def _aug_case():
     got = out[..., :3].permute(0, 3, 1, 2).cpu()
     ok = torch.equal(got, ref) and bool((out[..., 3] == 0).all())
     return {'ok': ok, 'max_abs_err': (got.float() - ref.float()).abs().max().item()}
+
+
+# ------------------------------------------------------------------ step engine (single GPU)
+def _mk_engine(depth=18, batch=32, hw=32, graph=True, seed=0):
+    from pmdist.models.resnet import build_resnet
+    from pmdist.parallel.comm import SingleComm
+    from pmdist.parallel.engine import NativeEngine
+    from pmdist.utils.schedule import SGDConfig
+    torch.manual_seed(seed)
+    model = build_resnet(depth)
+    eng = NativeEngine(model, SingleComm(), SGDConfig(), torch.device('cuda', 0), batch, hw, use_graph=graph)
+    return model, eng
+
+
+def _mk_batch(n, hw=32, train=True, seed=0):
+    from pmdist.data.loader import Batch, draw_aug_params
+    from pmdist.data.sources import synthetic_source
+    src = synthetic_source(n, hw, seed=seed)
+    aug = draw_aug_params(n, train, torch.Generator().manual_seed(seed))
+    return Batch(src.images, src.labels, torch.ones(n, dtype=torch.bool), aug, train)
+
+
+def _torch_twin(model):
+    """An ordinary fp32 torch copy (contiguous NCHW weights) of an engine-bound model."""
+    from pmdist.models.resnet import build_resnet
+    twin = build_resnet(model.spec.depth, model.spec.num_classes).cuda()
+    twin.load_state_dict({k: v.detach().clone().contiguous() for k, v in model.state_dict().items()})
+    return twin
+
+
+def _engine_forward_case(depth):
+    from pmdist.data.loader import augment_cpu
+    model, eng = _mk_engine(depth, 16)
+    b = _mk_batch(16, train=False)
+    twin = _torch_twin(model).eval()
+    eng.eval_step(b)
+    eng.synchronize()
+    with torch.no_grad():
+        ref = twin(augment_cpu(b.u8, b.aug).cuda())
+    r = _cmp(eng.logits[:16], ref, 5e-2)
+    m = eng.read_metrics()
+    r['metrics'] = m
+    r['ok'] = r['ok'] and m[3] == 16
+    eng.close()
+    return r
+
+
+CASES['engine_eval_logits_resnet18'] = lambda: _engine_forward_case(18)
+CASES['engine_eval_logits_resnet50'] = lambda: _engine_forward_case(50)
+CASES['engine_eval_logits_resnet34'] = lambda: _engine_forward_case(34)
+
+
+def _engine_train_case(depth, steps=1, graph=True):
+    from pmdist.data.loader import augment_cpu
+    model, eng = _mk_engine(depth, 32, graph=graph)
+    twin = _torch_twin(model).train()
+    opt = torch.optim.SGD(twin.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=True)
+    before = {k: v.detach().clone() for k, v in twin.state_dict().items()}
+    losses_ref, losses = [], []
+    for s in range(steps):
+        b = _mk_batch(32, train=True, seed=s)
+        eng.train_step(b, 0.1)
+        losses.append(eng.read_metrics()[0] / 32)
+        x, y = augment_cpu(b.u8, b.aug).cuda(), b.labels.cuda()
+        loss = F.cross_entropy(twin(x), y)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        losses_ref.append(loss.item())
+    eng.synchronize()
+    got, want = model.state_dict(), twin.state_dict()
+    worst_cos, worst_name = 1.0, ''
+    num = den_a = den_b = 0.0
+    for k in want:
+        if 'num_batches' in k or 'running' in k:
+            continue
+        da = (got[k].float() - before[k]).flatten().double()
+        db = (want[k].float() - before[k]).flatten().double()
+        num += float(da @ db)
+        den_a += float(da @ da)
+        den_b += float(db @ db)
+        cos = float(da @ db) / (float(da.norm() * db.norm()) + 1e-30)
+        if cos < worst_cos:
+            worst_cos, worst_name = cos, k
+    total_cos = num / (math.sqrt(den_a * den_b) + 1e-30)
+    rm = _cmp(got['bn1.running_mean'], want['bn1.running_mean'], 2e-2)
+    rv = _cmp(got['layer4.0.bn2.running_var'], want['layer4.0.bn2.running_var'], 5e-2)
+    r = {'loss': losses, 'loss_ref': losses_ref, 'update_cosine_total': total_cos, 'worst_tensor_cosine': worst_cos,
+         'worst_tensor': worst_name, 'running_mean': rm, 'running_var': rv,
+         'nbt': int(got['bn1.num_batches_tracked']), 'launches_per_step': eng.launches_per_step(32)}
+    r['ok'] = (total_cos > 0.98 and worst_cos > 0.9 and abs(losses[0] - losses_ref[0]) < 0.05 and rm['ok'] and rv['ok']
+               and r['nbt'] == steps)
+    eng.close()
+    return r
+
+
+CASES['engine_train_step_resnet18_matches_torch'] = lambda: _engine_train_case(18, 1)
+CASES['engine_train_3steps_resnet18_graph'] = lambda: _engine_train_case(18, 3)
+CASES['engine_train_step_resnet50_matches_torch'] = lambda: _engine_train_case(50, 1)
+CASES['engine_train_step_resnet34_identity_shortcuts'] = lambda: _engine_train_case(34, 1)
+
+
+@case('engine_loss_decreases_and_tail_batch')
+def _engine_learns():
+    model, eng = _mk_engine(18, 64)
+    from pmdist.data.loader import BatchLoader
+    from pmdist.data.sampler import ShardSampler
+    from pmdist.data.sources import synthetic_source
+    src = synthetic_source(64 * 6 + 20, 32, seed=3).pin()       # last batch has 20 samples
+    ld = BatchLoader(src, ShardSampler(len(src), 1, 0, True, 0), 64, True, pin=True)
+    hist = []
+    for ep in range(4):
+        ld.set_epoch(ep)
+        for b in ld:
+            eng.train_step(b, 0.05)
+        m = eng.read_metrics()
+        hist.append(m[0] / m[3])
+    sizes = [b.n for b in ld]
+    ok = hist[-1] < hist[0] - 0.1 and all(math.isfinite(h) for h in hist) and sizes[-1] == 20
+    eng.close()
+    return {'ok': ok, 'loss_per_epoch': hist, 'batch_sizes': sizes}
+
+
+@case('engine_checkpoint_roundtrip')
+def _engine_ckpt():
+    model, eng = _mk_engine(18, 16)
+    eng.train_step(_mk_batch(16, seed=1), 0.1)
+    sd = eng.model_state()
+    opt = eng.optimizer_state()
+    fp = eng.weights_fingerprint()
+    eng.close()
+    model2, eng2 = _mk_engine(18, 16, seed=5)
+    eng2.load_model_state(sd)
+    eng2.load_optimizer_state(opt)
+    ok = abs(eng2.weights_fingerprint() - fp) < 1e-6 * max(1.0, abs(fp))
+    keys_ok = len(sd) == 74 and all(v.is_contiguous() and v.device.type == 'cpu' for v in sd.values())
+    mom_ok = all(torch.equal(a, b) for a, b in zip(opt['momentum'].values(), eng2.optimizer_state()['momentum'].values()))
+    eng2.close()
+    return {'ok': ok and keys_ok and mom_ok, 'fingerprint': fp, 'keys_ok': keys_ok, 'momentum_ok': mom_ok}
