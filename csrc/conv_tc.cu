@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
           const uint4* ap = reinterpret_cast<const uint4*>(add_row + hf * 64 + cc * 32);
 #pragma unroll
           for (int jj = 0; jj < 4; ++jj) {
-            const uint4 a4 = __ldg(ap + jj);
+            const uint4 a4 = ap[jj];   // plain load: the addend may alias the output (in-place accumulate)
             const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {

@@ -66,6 +66,7 @@ struct Plan {
   int n = 0;
   std::vector<ConvPlan> conv;
   std::vector<ConvGemmParams> block_dgrad;   // one per block (conv0 + fused shortcut / addend)
+  std::vector<ConvGemmParams> sc_dgrad;      // per block: shortcut alone, when it cannot share conv0's tile grid
   std::vector<ConvGemmParams> inner_dgrad;   // per conv index (main[j], j >= 1)
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_launches = 0, eval_launches = 0;
@@ -104,7 +105,8 @@ struct PmdEngine {
   double* metrics_total = nullptr;
   bf16 *z_stem = nullptr, *dz_stem = nullptr;
   long long activation_bytes = 0;
-  cudaStream_t comm_stream = nullptr;
+  cudaStream_t comm_stream = nullptr, main_stream = nullptr;
+  cudaEvent_t ev_in = nullptr, ev_out = nullptr;
   std::vector<cudaEvent_t> events;
   cudaEvent_t ev_join = nullptr;
   std::map<int, std::unique_ptr<Plan>> plans;
@@ -302,6 +304,7 @@ Plan* get_plan(PmdEngine* e, int n) {
   pl->conv.resize(e->convs.size());
   pl->inner_dgrad.resize(e->convs.size());
   pl->block_dgrad.resize(e->blocks.size());
+  pl->sc_dgrad.resize(e->blocks.size());
   for (size_t i = 0; i < e->convs.size(); ++i) {
     Conv& cv = e->convs[i];
     if (!cv.tc) continue;
@@ -325,11 +328,23 @@ Plan* get_plan(PmdEngine* e, int n) {
     Conv& c0 = e->convs[b.main[0]];
     PmdConvShape s0 = c0.s;
     s0.N = n;
-    if (b.sc >= 0) {
+    if (b.sc >= 0 && e->convs[b.sc].s.stride == c0.s.stride) {
       Conv& cs = e->convs[b.sc];
       PmdConvShape ss = cs.s;
       ss.N = n;
       if (build_dgrad_params(s0, c0.dy, e->wt + c0.w_off, &ss, cs.dy, e->wt + cs.w_off, nullptr, b.dz_in,
+                             &pl->block_dgrad[bi]))
+        return nullptr;
+    } else if (b.sc >= 0) {
+      // Bottleneck stage entry: conv0 is 1x1 stride 1 but the projection is 1x1 stride 2.  The shortcut's
+      // dgrad fills dz_in first (zeros at the positions it skips), conv0's dgrad then adds onto it in place.
+      Conv& cs = e->convs[b.sc];
+      PmdConvShape ss = cs.s;
+      ss.N = n;
+      if (build_dgrad_params(ss, cs.dy, e->wt + cs.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_in,
+                             &pl->sc_dgrad[bi]))
+        return nullptr;
+      if (build_dgrad_params(s0, c0.dy, e->wt + c0.w_off, nullptr, nullptr, nullptr, b.dz_in, b.dz_in,
                              &pl->block_dgrad[bi]))
         return nullptr;
     } else {
@@ -503,6 +518,8 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     }
     E_CHECK(wgrad(b.main[0]));
     if (b.sc >= 0) E_CHECK(wgrad(b.sc));
+    if (b.sc >= 0 && e->convs[b.sc].s.stride != e->convs[b.main[0]].s.stride)
+      E_CHECK(launch_conv_gemm(pl->sc_dgrad[bi], st));
     E_CHECK(launch_conv_gemm(pl->block_dgrad[bi], st));
   }
   {
@@ -585,6 +602,9 @@ extern "C" PMD_API int pmd_engine_create(const PmdEngineConfig* cfg, PmdComm* co
   e->cfg.conv_w_off = e->cfg.bn_g_off = e->cfg.bn_b_off = nullptr;
   e->cfg.bucket_start = e->cfg.bucket_numel = nullptr;
   PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
+  PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->main_stream, cudaStreamNonBlocking));
+  PMD_CHECK_CUDA(cudaEventCreateWithFlags(&e->ev_in, cudaEventDisableTiming));
+  PMD_CHECK_CUDA(cudaEventCreateWithFlags(&e->ev_out, cudaEventDisableTiming));
   e->events.resize(cfg->n_buckets + 1);
   for (auto& ev : e->events) PMD_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   PMD_CHECK_CUDA(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
@@ -603,6 +623,9 @@ extern "C" PMD_API int pmd_engine_destroy(PmdEngine* e) {
   for (auto& ev : e->events) cudaEventDestroy(ev);
   if (e->ev_join) cudaEventDestroy(e->ev_join);
   if (e->comm_stream) cudaStreamDestroy(e->comm_stream);
+  if (e->main_stream) cudaStreamDestroy(e->main_stream);
+  if (e->ev_in) cudaEventDestroy(e->ev_in);
+  if (e->ev_out) cudaEventDestroy(e->ev_out);
   delete e;
   return 0;
 }
@@ -639,26 +662,44 @@ extern "C" PMD_API int pmd_engine_sync_params(PmdEngine* e, int broadcast_from_r
   return 0;
 }
 
+// The step runs on the engine's own stream (the caller's may be the legacy default stream, which
+// cannot be captured); events order it after the caller's pending work (the H2D copies of this
+// step's inputs) and order the caller's later work (metric reads) after it.
+static int enter(PmdEngine* e, cudaStream_t user) {
+  PMD_CHECK_CUDA(cudaEventRecord(e->ev_in, user));
+  PMD_CHECK_CUDA(cudaStreamWaitEvent(e->main_stream, e->ev_in, 0));
+  return 0;
+}
+static int leave(PmdEngine* e, cudaStream_t user) {
+  PMD_CHECK_CUDA(cudaEventRecord(e->ev_out, e->main_stream));
+  PMD_CHECK_CUDA(cudaStreamWaitEvent(user, e->ev_out, 0));
+  return 0;
+}
+
 extern "C" PMD_API int pmd_engine_train_step(PmdEngine* e, int n, float lr, void* stream) {
   PMD_REQUIRE(n >= 1 && n <= e->cfg.max_batch, "batch size outside [1, max_batch]");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaStream_t user = static_cast<cudaStream_t>(stream), st = e->main_stream;
   Plan* pl = get_plan(e, n);
   if (pl == nullptr) return -1;
+  E_CHECK(enter(e, user));
   if (lr != e->last_lr) {
     PMD_CHECK_CUDA(cudaMemcpyAsync(e->d_lr, &lr, sizeof(float), cudaMemcpyHostToDevice, st));
     e->last_lr = lr;
   }
-  return run_or_replay(e, &pl->train_graph, &pl->train_warm, &pl->train_launches, st,
-                       [&]() { return run_train(e, pl, lr, st); });
+  E_CHECK(run_or_replay(e, &pl->train_graph, &pl->train_warm, &pl->train_launches, st,
+                        [&]() { return run_train(e, pl, lr, st); }));
+  return leave(e, user);
 }
 
 extern "C" PMD_API int pmd_engine_eval_step(PmdEngine* e, int n, void* stream) {
   PMD_REQUIRE(n >= 1 && n <= e->cfg.max_batch, "batch size outside [1, max_batch]");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaStream_t user = static_cast<cudaStream_t>(stream), st = e->main_stream;
   Plan* pl = get_plan(e, n);
   if (pl == nullptr) return -1;
-  return run_or_replay(e, &pl->eval_graph, &pl->eval_warm, &pl->eval_launches, st,
-                       [&]() { return run_eval(e, pl, st); });
+  E_CHECK(enter(e, user));
+  E_CHECK(run_or_replay(e, &pl->eval_graph, &pl->eval_warm, &pl->eval_launches, st,
+                        [&]() { return run_eval(e, pl, st); }));
+  return leave(e, user);
 }
 
 extern "C" PMD_API int pmd_engine_read_metrics(PmdEngine* e, int reduce_over_ranks, int reset, double* out4,
