@@ -1,0 +1,104 @@
+"""Gradient all-reduce bucket-size sweep (BASELINE.json config 5): hand-written P2P kernels
+(one-shot / two-shot / NVLS multimem) vs NCCL on the same box, 1 KB .. 256 MB plus the real sizes of
+the reference model (SyncBN 512 B - 4 KB, DDP buckets 9.6 / 10.0 / 19.6 MB).
+
+Timing: CUDA events on the launching stream around `iters` back-to-back calls after warm-up, device
+barrier before, max over ranks.  Bus bandwidth = 2*(W-1)/W * bytes / time (NCCL's convention).
+
+    python tools/allreduce_sweep.py --gpus 8 --out gpurun_out/sweep8.json
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import struct
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+SIZES = [1 << 10, 4 << 10, 16 << 10, 64 << 10, 256 << 10, 1 << 20, 4 << 20, 9_622_784, 9_990_184, 16 << 20,
+         19_612_968, 64 << 20, 256 << 20]
+
+
+def _worker(rank: int, world: int, out: str, max_bytes: int) -> None:
+    import torch
+    import torch.distributed as dist
+    from pmdist.ops import _lib
+    from pmdist.ops._lib import check
+    from pmdist.parallel.peer import ALGOS, PeerComm
+    torch.cuda.set_device(rank)
+    dev = torch.device('cuda', rank)
+    sizes = [s for s in SIZES if s <= max_bytes]
+    big = max(sizes)
+    comm = PeerComm(rank, world, dev, heap_bytes=2 * big + (64 << 20))
+    lib = _lib.lib()
+    in_off = comm.alloc(big + 64)
+    out_off = comm.alloc(big + 64)
+    comm.view(in_off, (big // 4,), torch.float32).normal_()
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
+    nccl_buf = torch.randn(big // 4, device=dev)
+    algos = ['oneshot', 'twoshot'] + (['nvls'] if comm.info.multicast_mapped else [])
+    rows = []
+    for nbytes in sizes:
+        n = nbytes // 4 // 4 * 4
+        iters = 200 if nbytes <= (1 << 20) else (50 if nbytes <= (32 << 20) else 10)
+        row = {'bytes': n * 4}
+
+        def time_it(fn):
+            for _ in range(5):
+                fn()
+            torch.cuda.synchronize()
+            comm.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(iters):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            us = a.elapsed_time(b) * 1e3 / iters
+            allv = comm.all_gather_bytes(struct.pack('d', us))
+            return max(struct.unpack('d', v)[0] for v in allv)
+
+        for algo in algos:
+            for blocks in ((8, 32) if nbytes <= (1 << 20) else (32, 96)):
+                def fn(algo=algo, blocks=blocks):
+                    check(lib.pmd_allreduce_f32(C.byref(comm.sym), C.c_ulonglong(in_off), C.c_ulonglong(out_off),
+                                                C.c_longlong(n), C.c_int(ALGOS[algo]), C.c_int(blocks), C.c_int(2000),
+                                                _lib.stream_ptr()))
+                us = time_it(fn)
+                key = f'{algo}_b{blocks}'
+                row[key + '_us'] = round(us, 2)
+                row[key + '_busbw_GBs'] = round(2 * (world - 1) / world * n * 4 / us / 1e3, 1)
+        view = nccl_buf[:n]
+        us = time_it(lambda: dist.all_reduce(view))
+        row['nccl_us'] = round(us, 2)
+        row['nccl_busbw_GBs'] = round(2 * (world - 1) / world * n * 4 / us / 1e3, 1)
+        best = min((v, k) for k, v in row.items() if k.endswith('_us') and not k.startswith('nccl'))
+        row['best_p2p'] = best[1][:-3]
+        row['speedup_vs_nccl'] = round(row['nccl_us'] / best[0], 2)
+        rows.append(row)
+        if rank == 0:
+            print(json.dumps(row), flush=True)
+    if rank == 0:
+        with open(out, 'w') as f:
+            json.dump({'world': world, 'transport': comm.describe(), 'rows': rows}, f, indent=1)
+    dist.destroy_process_group()
+    comm.close()
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=2)
+    ap.add_argument('--max-mb', type=int, default=256)
+    ap.add_argument('--out', default=os.path.join(ROOT, 'gpurun_out', 'allreduce_sweep.json'))
+    a = ap.parse_args()
+    os.makedirs(os.path.dirname(a.out), exist_ok=True)
+    from pmdist.parallel import launch
+    launch.spawn(_worker, a.gpus, args=(a.out, a.max_mb << 20), timeout=1200)
+
+
+if __name__ == '__main__':
+    main()
