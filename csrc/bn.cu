@@ -158,78 +158,159 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float
   }
 }
 
-__global__ void bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
-                                     const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
-                                     const float* __restrict__ invstd, int relu, float* sum_g, float* sum_gx,
-                                     long long rows, int C) {
-  column_reduce2(
-      [&](long long r, int c0, float(&a0)[8], float(&a1)[8]) {
-        float g[8], yv[8];
-        load8(dz + r * C + c0, g);
-        load8(y + r * C + c0, yv);
-        if (relu) {
-          float zv[8];
-          load8(z + r * C + c0, zv);
+// ---------------------------------------------------------------- backward, 1 or 2 branches
+// A residual block's output gradient dz feeds the last main-path BatchNorm AND (projection blocks) the
+// shortcut's BatchNorm through the same ReLU mask; handling both in one pass reads dz and the mask
+// source once instead of twice.  MASK: 0 none, 1 z > 0, 2 recomputed from branch 0's own forward
+// affine (scale*y + shift > 0; valid when that BatchNorm had no residual), which skips reading z at all.
+struct BnBranchDev {
+  const __nv_bfloat16* y;
+  const float* mean;
+  const float* invstd;
+  const float* gamma;
+  float* sums;          // [2C] local sums: accumulated by reduce, read by apply
+  const float* totals;  // [2C] sums over all ranks (== sums on one rank)
+  __nv_bfloat16* dy;
+  float* dgamma;
+  float* dbeta;
+};
+
+template <int NB, int MASK>
+__global__ void bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
+                                           const float* __restrict__ mscale, const float* __restrict__ mshift,
+                                           BnBranchDev b0, BnBranchDev b1, long long rows, int C) {
+  extern __shared__ float red[];
+  const int groups = C / 8;
+  const int g = threadIdx.x % groups;
+  const int rl = threadIdx.x / groups;
+  const int rpi = blockDim.x / groups;
+  const int c0 = g * 8;
+  float acc[NB][2][8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) g[i] = zv[i] > 0.f ? g[i] : 0.f;
-        }
+  for (int b = 0; b < NB; ++b)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[b][0][i] = acc[b][1][i] = 0.f;
+  float mean0[8], is0[8], mean1[8], is1[8], ms[8], mh[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    mean0[i] = b0.mean[c0 + i];
+    is0[i] = b0.invstd[c0 + i];
+    if (NB == 2) {
+      mean1[i] = b1.mean[c0 + i];
+      is1[i] = b1.invstd[c0 + i];
+    }
+    if (MASK == 2) {
+      ms[i] = mscale[c0 + i];
+      mh[i] = mshift[c0 + i];
+    }
+  }
+  if (rl < rpi) {
+    for (long long r = static_cast<long long>(blockIdx.x) * rpi + rl; r < rows;
+         r += static_cast<long long>(gridDim.x) * rpi) {
+      float gv[8], y0[8];
+      load8(dz + r * C + c0, gv);
+      load8(b0.y + r * C + c0, y0);
+      if (MASK == 1) {
+        float zv[8];
+        load8(z + r * C + c0, zv);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) gv[i] = zv[i] > 0.f ? gv[i] : 0.f;
+      } else if (MASK == 2) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) gv[i] = fmaf(y0[i], ms[i], mh[i]) > 0.f ? gv[i] : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        acc[0][0][i] += gv[i];
+        acc[0][1][i] += gv[i] * (y0[i] - mean0[i]) * is0[i];
+      }
+      if (NB == 2) {
+        float y1[8];
+        load8(b1.y + r * C + c0, y1);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          a0[i] += g[i];
-          a1[i] += g[i] * (yv[i] - __ldg(mean + c0 + i)) * __ldg(invstd + c0 + i);
+          acc[1][0][i] += gv[i];
+          acc[1][1][i] += gv[i] * (y1[i] - mean1[i]) * is1[i];
         }
-      },
-      rows, C, sum_g, sum_gx);
+      }
+    }
+  }
+  // block reduction: red[b][v][rl][c]
+  if (rl < rpi) {
+#pragma unroll
+    for (int b = 0; b < NB; ++b)
+#pragma unroll
+      for (int v = 0; v < 2; ++v)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) red[((b * 2 + v) * rpi + rl) * C + c0 + i] = acc[b][v][i];
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < NB * 2 * C; idx += blockDim.x) {
+    const int c = idx % C, bv = idx / C;
+    float sum = 0.f;
+    for (int j = 0; j < rpi; ++j) sum += red[(bv * rpi + j) * C + c];
+    float* dst = (bv / 2 == 0 ? b0.sums : b1.sums) + (bv % 2) * C + c;
+    red_add_f32(dst, sum);
+  }
 }
 
-__global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
-                                    const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
-                                    const float* __restrict__ invstd, const float* __restrict__ gamma,
-                                    const float* const* __restrict__ sums_ranks, int world, const float* __restrict__ local_sums,
-                                    float count_total, int relu, __nv_bfloat16* __restrict__ dy, float* dgamma,
-                                    float* dbeta, __nv_bfloat16* __restrict__ g_out, long long total8, int C) {
-  extern __shared__ float coef[];      // [3][C]: a = gamma*invstd, mean_g, mean_gx*invstd
-  float* ca = coef;
-  float* cg = coef + C;
-  float* cx = coef + 2 * C;
+template <int NB, int MASK>
+__global__ void bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
+                                          const float* __restrict__ mscale, const float* __restrict__ mshift,
+                                          BnBranchDev b0, BnBranchDev b1, float count_total,
+                                          __nv_bfloat16* __restrict__ g_out, long long total8, int C) {
+  extern __shared__ float coef[];      // per branch [4][C]: a = gamma*invstd, mean_g, mean_gx, (mean, invstd packed later)
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    float sg = 0.f, sgx = 0.f;
-    for (int w = 0; w < world; ++w) {
-      const volatile float* st = sums_ranks[w];
-      sg += st[c];
-      sgx += st[C + c];
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      const BnBranchDev& br = b == 0 ? b0 : b1;
+      float* cf = coef + b * 3 * C;
+      cf[c] = br.gamma[c] * br.invstd[c];
+      cf[C + c] = br.totals[c] / count_total;
+      cf[2 * C + c] = br.totals[C + c] / count_total;
+      if (blockIdx.x == 0 && br.dgamma != nullptr) {
+        br.dbeta[c] += br.sums[c];
+        br.dgamma[c] += br.sums[C + c];
+      }
     }
-    if (blockIdx.x == 0 && dgamma != nullptr) {
-      dbeta[c] += local_sums[c];
-      dgamma[c] += local_sums[C + c];
-    }
-    const float is = invstd[c];
-    ca[c] = gamma[c] * is;
-    cg[c] = sg / count_total;
-    cx[c] = sgx / count_total;
   }
   __syncthreads();
   const int groups = C / 8;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total8;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int c0 = static_cast<int>(i % groups) * 8;
-    float g[8], yv[8], o[8];
-    load8(dz + i * 8, g);
-    load8(y + i * 8, yv);
-    if (relu) {
+    float gv[8], y0[8], o[8];
+    load8(dz + i * 8, gv);
+    load8(b0.y + i * 8, y0);
+    if (MASK == 1) {
       float zv[8];
       load8(z + i * 8, zv);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = zv[j] > 0.f ? g[j] : 0.f;
+      for (int j = 0; j < 8; ++j) gv[j] = zv[j] > 0.f ? gv[j] : 0.f;
+    } else if (MASK == 2) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) gv[j] = fmaf(y0[j], __ldg(mscale + c0 + j), __ldg(mshift + c0 + j)) > 0.f ? gv[j] : 0.f;
     }
-    if (g_out != nullptr) store8(g_out + i * 8, g);
+    if (g_out != nullptr) store8(g_out + i * 8, gv);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int c = c0 + j;
-      const float xhat = (yv[j] - __ldg(mean + c)) * __ldg(invstd + c);
-      o[j] = ca[c] * (g[j] - cg[c] - xhat * cx[c]);
+      const float xhat = (y0[j] - __ldg(b0.mean + c)) * __ldg(b0.invstd + c);
+      o[j] = coef[c] * (gv[j] - coef[C + c] - xhat * coef[2 * C + c]);
     }
-    store8(dy + i * 8, o);
+    store8(b0.dy + i * 8, o);
+    if (NB == 2) {
+      float y1[8];
+      load8(b1.y + i * 8, y1);
+      const float* cf = coef + 3 * C;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int c = c0 + j;
+        const float xhat = (y1[j] - __ldg(b1.mean + c)) * __ldg(b1.invstd + c);
+        o[j] = cf[c] * (gv[j] - cf[C + c] - xhat * cf[2 * C + c]);
+      }
+      store8(b1.dy + i * 8, o);
+    }
   }
 }
 
@@ -300,31 +381,126 @@ extern "C" PMD_API int pmd_bn_apply(const void* d_y, const float* d_scale, const
   return 0;
 }
 
-extern "C" PMD_API int pmd_bn_bwd_reduce(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
-                                 const float* d_invstd, int relu, float* d_sums, long long rows, int C, void* stream) {
+static BnBranchDev to_dev(const PmdBnBranch& b) {
+  BnBranchDev d;
+  d.y = static_cast<const __nv_bfloat16*>(b.y);
+  d.mean = b.mean;
+  d.invstd = b.invstd;
+  d.gamma = b.gamma;
+  d.sums = b.sums;
+  d.totals = b.totals != nullptr ? b.totals : b.sums;
+  d.dy = static_cast<__nv_bfloat16*>(b.dy);
+  d.dgamma = b.dgamma;
+  d.dbeta = b.dbeta;
+  return d;
+}
+
+template <int NB>
+static void launch_reduce(int mask, int grid, int smem, cudaStream_t st, const __nv_bfloat16* dz, const __nv_bfloat16* z,
+                          const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, long long rows, int C) {
+  if (mask == 0) bn_bwd_reduce_multi_kernel<NB, 0><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
+  if (mask == 1) bn_bwd_reduce_multi_kernel<NB, 1><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
+  if (mask == 2) bn_bwd_reduce_multi_kernel<NB, 2><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
+}
+template <int NB>
+static void launch_apply(int mask, int grid, int smem, cudaStream_t st, const __nv_bfloat16* dz, const __nv_bfloat16* z,
+                         const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, float count,
+                         __nv_bfloat16* g_out, long long total8, int C) {
+  if (mask == 0) bn_bwd_apply_multi_kernel<NB, 0><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, count, g_out, total8, C);
+  if (mask == 1) bn_bwd_apply_multi_kernel<NB, 1><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, count, g_out, total8, C);
+  if (mask == 2) bn_bwd_apply_multi_kernel<NB, 2><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, count, g_out, total8, C);
+}
+
+extern "C" PMD_API int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
+                                               const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
+                                               long long rows, int C, void* stream) {
   BN_CHECK_C(C);
+  PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
+  PMD_REQUIRE(mask_mode != 1 || d_z != nullptr, "mask mode 1 needs z");
+  PMD_REQUIRE(mask_mode != 2 || (d_mask_scale != nullptr && d_mask_shift != nullptr), "mask mode 2 needs the forward affine");
   const int groups = C / 8, rpi = kBlock / groups > 0 ? kBlock / groups : 1;
   PMD_REQUIRE(groups <= kBlock, "C too large for bn_bwd_reduce");
-  const int smem = 2 * rpi * C * 4;
-  bn_bwd_reduce_kernel<<<grid_for(rows, rpi * 4), kBlock, smem, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(d_dz), static_cast<const __nv_bfloat16*>(d_z),
-      static_cast<const __nv_bfloat16*>(d_y), d_mean, d_invstd, relu, d_sums, d_sums + C, rows, C);
+  const int smem = nb * 2 * rpi * C * 4;
+  const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
+  const int grid = grid_for(rows, rpi * 4);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
+  const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);
+  if (nb == 1)
+    launch_reduce<1>(mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C);
+  else
+    launch_reduce<2>(mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C);
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
 }
 
-extern "C" PMD_API int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
-                                const float* d_invstd, const float* d_gamma, const float* const* d_sums_ranks, int world,
-                                const float* d_local_sums, float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta,
-                                void* d_g_out, long long rows, int C, void* stream) {
+extern "C" PMD_API int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
+                                              const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
+                                              float count_total, void* d_g_out, long long rows, int C, void* stream) {
   BN_CHECK_C(C);
+  PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
   const long long total8 = rows * C / 8;
-  bn_bwd_apply_kernel<<<grid_for(total8, kBlock * 2), kBlock, 3 * C * 4, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(d_dz), static_cast<const __nv_bfloat16*>(d_z),
-      static_cast<const __nv_bfloat16*>(d_y), d_mean, d_invstd, d_gamma, d_sums_ranks, world, d_local_sums, count_total,
-      relu, static_cast<__nv_bfloat16*>(d_dy), d_dgamma, d_dbeta, static_cast<__nv_bfloat16*>(d_g_out), total8, C);
+  const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
+  const int grid = grid_for(total8, kBlock * 2);
+  const int smem = nb * 3 * C * 4;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
+  const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);
+  __nv_bfloat16* g = static_cast<__nv_bfloat16*>(d_g_out);
+  if (nb == 1)
+    launch_apply<1>(mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
+  else
+    launch_apply<2>(mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
+}
+
+// single-branch forms kept for callers that have one BatchNorm at a time
+extern "C" PMD_API int pmd_bn_bwd_reduce(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
+                                         const float* d_invstd, int relu, float* d_sums, long long rows, int C,
+                                         void* stream) {
+  PmdBnBranch b{};
+  b.y = d_y;
+  b.mean = d_mean;
+  b.invstd = d_invstd;
+  b.sums = d_sums;
+  return pmd_bn_bwd_reduce_multi(d_dz, d_z, nullptr, nullptr, relu ? 1 : 0, &b, 1, rows, C, stream);
+}
+
+// Totals over `world` ranks are summed on the fly from a pointer table (kept for the 1-GPU multi-table tests).
+namespace pmd {
+namespace {
+__global__ void sum_tables_kernel(const float* const* tabs, int world, int n, float* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float acc = 0.f;
+  for (int w = 0; w < world; ++w) acc += tabs[w][i];
+  out[i] = acc;
+}
+}  // namespace
+}  // namespace pmd
+
+extern "C" PMD_API int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
+                                        const float* d_invstd, const float* d_gamma, const float* const* d_sums_ranks,
+                                        int world, const float* d_local_sums, float count_total, int relu, void* d_dy,
+                                        float* d_dgamma, float* d_dbeta, void* d_g_out, long long rows, int C,
+                                        void* stream) {
+  BN_CHECK_C(C);
+  static float* totals = nullptr;      // [2 * 2048] scratch for the table sum
+  if (totals == nullptr) PMD_CHECK_CUDA(cudaMalloc(&totals, 2 * 2048 * sizeof(float)));
+  sum_tables_kernel<<<ceil_div(2 * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_sums_ranks, world, 2 * C, totals);
+  count_launch();
+  PmdBnBranch b{};
+  b.y = d_y;
+  b.mean = d_mean;
+  b.invstd = d_invstd;
+  b.gamma = d_gamma;
+  b.sums = const_cast<float*>(d_local_sums);
+  b.totals = totals;
+  b.dy = d_dy;
+  b.dgamma = d_dgamma;
+  b.dbeta = d_dbeta;
+  return pmd_bn_bwd_apply_multi(d_dz, d_z, nullptr, nullptr, relu ? 1 : 0, &b, 1, count_total, d_g_out, rows, C, stream);
 }

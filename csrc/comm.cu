@@ -266,7 +266,7 @@ int clamp_blocks(int blocks, long long work4) {
   if (blocks <= 0) blocks = 32;
   const long long need = ceil_div_ll(work4 > 0 ? work4 : 1, 512);
   if (blocks > need) blocks = static_cast<int>(need);
-  if (blocks > 128) blocks = 128;
+  if (blocks > 1024) blocks = 1024;
   return blocks < 1 ? 1 : blocks;
 }
 
@@ -295,6 +295,7 @@ extern "C" PMD_API int pmd_allreduce_sgd(const PmdSym* sym, const PmdAllreduceSg
   const long long work4 = algo == PMD_ALGO_ONESHOT ? a->n / 4 : ceil_div_ll(a->n / 4, sym->world);
   PmdAllreduceSgd aa = *a;
   aa.blocks = clamp_blocks(a->blocks, work4);
+  if (sym->world > 1 && aa.blocks > 128) aa.blocks = 128;   // one flag slot per CTA; the engine reserves 128 per bucket
   PMD_REQUIRE(slot + aa.blocks <= PMD_MAX_SLOTS, "flag slots exhausted");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (algo == PMD_ALGO_ONESHOT)

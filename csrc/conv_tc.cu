@@ -303,7 +303,7 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
     const int q = warp & 3;
     const int row = q * 32 + lane;
     const int bx = row >> 6, c = row & 63;
-    const bool live = (niter > 0) && (box0 + bx < p.n_boxes);
+    const bool live = (niter > 0) && (box0 + bx < p.n_boxes) && (c < p.c_valid);
     if (niter > 0) {
       mbar_wait(&bars->tmem_full, 0);
       tc_fence_after();
@@ -547,7 +547,7 @@ int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck
 }
 
 int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, float* dw, int split, int sm_count,
-                       WgradParams* out) {
+                       WgradParams* out, int rsc_override, int c_valid) {
   PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
   WgradParams& p = *out;
   memset(&p, 0, sizeof(p));
@@ -558,7 +558,8 @@ int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, flo
   p.tiles_h = ceil_div(Ho, p.h_box);
   p.tiles_n = ceil_div(s.N, p.n_box);
   p.K = s.K;
-  p.RSC = RS * s.C;
+  p.RSC = rsc_override > 0 ? rsc_override : RS * s.C;
+  p.c_valid = c_valid;
   p.dw = dw;
   p.bn_tile = (s.K % 256 == 0) ? 256 : (s.K % 128 == 0 ? 128 : 64);
   if (s.stride == 1) {

@@ -55,6 +55,7 @@ struct WgradParams {
   int K, RSC;
   int bn_tile;               // 64, 128 or 256 output-channel columns per CTA
   int split;
+  int c_valid;                 // rows (channels within a box) >= c_valid are not written (stem: 27 of 64)
   float* dw;
 };
 
@@ -64,7 +65,7 @@ int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc,
 int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const PmdConvShape* s2,
                        const void* dy2, const void* w2_rsck, const void* addend, void* dx, ConvGemmParams* out);
 int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, float* dw, int split, int sm_count,
-                       WgradParams* out);
+                       WgradParams* out, int rsc_override = 0, int c_valid = 64);
 int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream);
 int launch_wgrad(const WgradParams& p, cudaStream_t stream);
 

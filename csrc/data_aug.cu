@@ -34,10 +34,95 @@ __global__ void augment_kernel(const unsigned char* __restrict__ u8, const int* 
   }
 }
 
+// Augmentation fused with the stem convolution's im2col: every output pixel carries the 3x3x3
+// neighbourhood of the AUGMENTED image (tap-major, channel-minor: column = (r*3+s)*3 + c, the KRSC order
+// of the stem weight) padded with zeros to 64 columns.  The stem conv (ref:model/resnet.py:79-80) then is
+// a 64-wide 1x1 convolution the tcgen05 path handles, and so is its weight gradient.  Positions outside
+// the image are the convolution's zero padding (0), positions inside the image but outside the crop are
+// torchvision's pre-normalisation zero pad (-1 after Normalize).
+__global__ void augment_im2col_kernel(const unsigned char* __restrict__ u8, const int* __restrict__ aug, int N, int H,
+                                      int W, int pad, __nv_bfloat16* __restrict__ out) {
+  const long long total = static_cast<long long>(N) * H * W;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int x = static_cast<int>(i % W);
+    const int y = static_cast<int>((i / W) % H);
+    const int n = static_cast<int>(i / (static_cast<long long>(W) * H));
+    const int ox = aug[n * 3], oy = aug[n * 3 + 1], fl = aug[n * 3 + 2];
+    const unsigned char* img = u8 + static_cast<long long>(n) * H * W * 3;
+    float v[28];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+      for (int q = 0; q < 3; ++q) {
+        const int ay = y + r - 1, ax = x + q - 1;            // position in the augmented image
+        float t0 = 0.f, t1 = 0.f, t2 = 0.f;
+        if (ay >= 0 && ay < H && ax >= 0 && ax < W) {
+          const int xc = fl ? (W - 1 - ax) : ax;
+          const int sx = xc + ox - pad, sy = ay + oy - pad;   // position in the stored image
+          t0 = t1 = t2 = -1.f;
+          if (sx >= 0 && sx < W && sy >= 0 && sy < H) {
+            const unsigned char* p = img + (static_cast<long long>(sy) * W + sx) * 3;
+            t0 = (p[0] / 255.0f - 0.5f) / 0.5f;
+            t1 = (p[1] / 255.0f - 0.5f) / 0.5f;
+            t2 = (p[2] / 255.0f - 0.5f) / 0.5f;
+          }
+        }
+        v[(r * 3 + q) * 3] = t0;
+        v[(r * 3 + q) * 3 + 1] = t1;
+        v[(r * 3 + q) * 3 + 2] = t2;
+      }
+    }
+    v[27] = 0.f;
+    uint4* o = reinterpret_cast<uint4*>(out + i * 64);
+    o[0] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+    o[1] = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]),
+                      pack_bf16x2(v[14], v[15]));
+    o[2] = make_uint4(pack_bf16x2(v[16], v[17]), pack_bf16x2(v[18], v[19]), pack_bf16x2(v[20], v[21]),
+                      pack_bf16x2(v[22], v[23]));
+    o[3] = make_uint4(pack_bf16x2(v[24], v[25]), pack_bf16x2(v[26], v[27]), 0u, 0u);
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    o[4] = z;
+    o[5] = z;
+    o[6] = z;
+    o[7] = z;
+  }
+}
+
+// [K][27] bf16 (KRSC stem weight) -> [K][64] bf16, zero padded.
+__global__ void pad_stem_weight_kernel(const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ wp, int K,
+                                       int rsc) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= K * 64) return;
+  const int k = i / 64, c = i % 64;
+  wp[i] = c < rsc ? w[k * rsc + c] : __float2bfloat16_rn(0.f);
+}
+
 }  // namespace
 }  // namespace pmd
 
 using namespace pmd;
+
+extern "C" PMD_API int pmd_augment_im2col(const unsigned char* d_u8, const int* d_aug, int N, int H, int W, int pad,
+                                          void* d_out, void* stream) {
+  const long long total = static_cast<long long>(N) * H * W;
+  long long blocks = ceil_div_ll(total, 128);
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  augment_im2col_kernel<<<static_cast<int>(blocks), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      d_u8, d_aug, N, H, W, pad, static_cast<__nv_bfloat16*>(d_out));
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_pad_stem_weight(const void* d_w, void* d_w_padded, int K, int rsc, void* stream) {
+  PMD_REQUIRE(rsc <= 64, "stem filter has more than 64 taps*channels");
+  pad_stem_weight_kernel<<<ceil_div(K * 64, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(d_w), static_cast<__nv_bfloat16*>(d_w_padded), K, rsc);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" PMD_API int pmd_augment(const unsigned char* d_u8, const int* d_aug, int N, int H, int W, int pad, int c_out,
                            void* d_out, void* stream) {

@@ -31,6 +31,8 @@ struct Conv {
   PmdConvShape s{};      // s.N filled per plan
   int Ho = 0, Wo = 0;
   bool tc = false;
+  bool stem_col = false;   // 3->64 stem run as a 64-wide 1x1 conv over the im2col'ed augmented input
+  int real_rsc = 0;        // R*S*C of the parameter as stored in the slab (27 for the stem)
   long long w_off = 0, g_off = 0, b_off = 0;
   int w_bkt = 0, g_bkt = 0, b_bkt = 0;
   float *rm = nullptr, *rv = nullptr;
@@ -98,6 +100,7 @@ struct PmdEngine {
   int n_repack = 0;
   long long repack_max = 0;
   bf16* x0 = nullptr;
+  bf16* stem_w_pad = nullptr;         // [64][64] zero-padded stem weight
   unsigned char *in_u8 = nullptr, *in_valid = nullptr;
   int* in_aug = nullptr;
   long long* in_labels = nullptr;
@@ -150,8 +153,9 @@ int build_topology(PmdEngine* e) {
     e->convs.push_back(cv);
     return static_cast<int>(e->convs.size()) - 1;
   };
-  const int stem = add_conv(HW, 3, 64, 3, 1);
-  e->convs[stem].x_cstride = 4;
+  const int stem = add_conv(HW, 64, 64, 1, 1);   // see data_aug.cu: augmentation emits the 27-column im2col, padded to 64
+  e->convs[stem].stem_col = true;
+  e->convs[stem].real_rsc = 27;
   int H = HW, Cin = 64;
   for (int si = 0; si < 4; ++si)
     for (int bi = 0; bi < c.blocks[si]; ++bi) {
@@ -207,7 +211,8 @@ int allocate(PmdEngine* e) {
   PMD_CHECK_CUDA(cudaMemset(e->hptr<char>(e->bnpart_off), 0, part));
 
   E_CHECK(e->dalloc(&e->wt, S));
-  E_CHECK(e->dalloc(&e->x0, 1LL * B * c.image_hw * c.image_hw * 4));
+  E_CHECK(e->dalloc(&e->x0, 1LL * B * c.image_hw * c.image_hw * 64));
+  E_CHECK(e->dalloc(&e->stem_w_pad, 64 * 64));
   E_CHECK(e->dalloc(&e->in_u8, 1LL * B * c.image_hw * c.image_hw * 3));
   E_CHECK(e->dalloc(&e->in_aug, 3LL * B));
   E_CHECK(e->dalloc(&e->in_labels, B));
@@ -310,10 +315,13 @@ Plan* get_plan(PmdEngine* e, int n) {
     if (!cv.tc) continue;
     PmdConvShape s = cv.s;
     s.N = n;
-    if (build_fprop_params(s, cv.x, e->wbf16 + cv.w_off, cv.y, cv.stats, &pl->conv[i].fprop)) return nullptr;
+    const bf16* w = cv.stem_col ? e->stem_w_pad : e->wbf16 + cv.w_off;
+    if (build_fprop_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop)) return nullptr;
     pl->conv[i].fprop_eval = pl->conv[i].fprop;
     pl->conv[i].fprop_eval.stats = nullptr;
-    if (build_wgrad_params(s, cv.x, cv.dy, e->grad + cv.w_off, 0, e->sm_count, &pl->conv[i].wgrad)) return nullptr;
+    if (build_wgrad_params(s, cv.x, cv.dy, e->grad + cv.w_off, 0, e->sm_count, &pl->conv[i].wgrad,
+                           cv.stem_col ? cv.real_rsc : 0, cv.stem_col ? cv.real_rsc : 64))
+      return nullptr;
   }
   for (size_t bi = 0; bi < e->blocks.size(); ++bi) {
     Block& b = e->blocks[bi];
@@ -383,7 +391,7 @@ struct BucketTracker {
     a.weight_decay = e->cfg.weight_decay;
     a.nesterov = e->cfg.nesterov;
     a.algo = e->cfg.algo;
-    a.blocks = e->cfg.comm_blocks;
+    a.blocks = e->sym.world == 1 ? 4 * e->sm_count : e->cfg.comm_blocks;
     a.d_lr = e->d_lr;
     const int slot = 2 * static_cast<int>(e->convs.size()) + 8 + bkt * 128;
     E_CHECK(pmd_allreduce_sgd(&e->sym, &a, slot, e->comm_stream));
@@ -403,27 +411,46 @@ int bn_forward(PmdEngine* e, int ci, long long rows, cudaStream_t st) {
                          cv.rm, cv.rv, cv.nb, c.bn_momentum, c.bn_eps, cv.scale, cv.shift, cv.mean, cv.invstd, st);
 }
 
-// BatchNorm backward of conv `ci`: dz (grad wrt the activation that followed it), mask source z.
-int bn_backward(PmdEngine* e, int ci, const bf16* dz, const bf16* z, long long rows, bf16* g_out, cudaStream_t st) {
-  Conv& cv = e->convs[ci];
-  E_CHECK(pmd_bn_bwd_reduce(dz, z, cv.y, cv.mean, cv.invstd, 1, cv.sums, rows, cv.s.K, st));
+// BatchNorm backward of conv `ci` (and, for a projection block's output, of the shortcut conv `cj`
+// in the same two passes).  dz = gradient wrt the activation that followed; the ReLU mask comes from z
+// (block outputs, where a residual was added before the ReLU) or is recomputed from y (z == nullptr).
+int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, long long rows, bf16* g_out,
+                cudaStream_t st) {
   const bool sync = e->sym.world > 1 && e->cfg.sync_bn;
+  const int nb = cj >= 0 ? 2 : 1;
+  PmdBnBranch br[2];
+  const int idx[2] = {ci, cj};
+  for (int b = 0; b < nb; ++b) {
+    Conv& cv = e->convs[idx[b]];
+    br[b].y = cv.y;
+    br[b].mean = cv.mean;
+    br[b].invstd = cv.invstd;
+    br[b].gamma = e->param + cv.g_off;
+    br[b].sums = cv.sums;
+    br[b].totals = sync ? cv.sums_total : nullptr;
+    br[b].dy = cv.dy;
+    br[b].dgamma = e->grad + cv.g_off;
+    br[b].dbeta = e->grad + cv.b_off;
+  }
+  Conv& c0 = e->convs[ci];
+  const int mask = z != nullptr ? 1 : 2;
+  E_CHECK(pmd_bn_bwd_reduce_multi(dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
   float total_rows = static_cast<float>(rows);
-  const float* const* tab = cv.tab_sums;
   if (sync) {
-    E_CHECK(pmd_small_allreduce_sync(&e->sym, static_cast<int>(e->convs.size()) + ci, cv.sums_off, 2 * cv.s.K,
-                                     cv.sums_total, st));
-    tab = cv.tab_total;
+    for (int b = 0; b < nb; ++b) {
+      Conv& cv = e->convs[idx[b]];
+      E_CHECK(pmd_small_allreduce_sync(&e->sym, static_cast<int>(e->convs.size()) + idx[b], cv.sums_off, 2 * cv.s.K,
+                                       cv.sums_total, st));
+    }
     total_rows *= e->sym.world;
   }
-  return pmd_bn_bwd_apply(dz, z, cv.y, cv.mean, cv.invstd, e->param + cv.g_off, tab, 1, cv.sums, total_rows, 1, cv.dy,
-                          e->grad + cv.g_off, e->grad + cv.b_off, g_out, rows, cv.s.K, st);
+  return pmd_bn_bwd_apply_multi(dz, z, c0.scale, c0.shift, mask, br, nb, total_rows, g_out, rows, c0.s.K, st);
 }
 
 int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
   const PmdEngineConfig& c = e->cfg;
   const int n = pl->n;
-  E_CHECK(pmd_augment(e->in_u8, e->in_aug, n, c.image_hw, c.image_hw, 8, 4, e->x0, st));
+  E_CHECK(pmd_augment_im2col(e->in_u8, e->in_aug, n, c.image_hw, c.image_hw, 8, e->x0, st));
   auto conv_fwd = [&](int ci) -> int {
     Conv& cv = e->convs[ci];
     const long long rows = 1LL * n * cv.Ho * cv.Wo;
@@ -502,18 +529,15 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     Block& b = e->blocks[bi];
     const int last = b.main[b.n_main - 1];
     const long long rows_out = 1LL * n * b.Hout * b.Hout;
-    E_CHECK(bn_backward(e, last, b.dz_out, b.z_out, rows_out, b.g_out, st));
+    E_CHECK(bn_backward(e, last, b.sc, b.dz_out, b.z_out, rows_out, b.g_out, st));
     E_CHECK(bn_done(last));
-    if (b.sc >= 0) {
-      E_CHECK(bn_backward(e, b.sc, b.dz_out, b.z_out, rows_out, nullptr, st));
-      E_CHECK(bn_done(b.sc));
-    }
+    if (b.sc >= 0) E_CHECK(bn_done(b.sc));
     for (int j = b.n_main - 1; j >= 1; --j) {
       const int ci = b.main[j], prev = b.main[j - 1];
       E_CHECK(wgrad(ci));
       E_CHECK(launch_conv_gemm(pl->inner_dgrad[ci], st));
       Conv& pv = e->convs[prev];
-      E_CHECK(bn_backward(e, prev, b.dz_mid[j - 1], b.z_mid[j - 1], 1LL * n * pv.Ho * pv.Wo, nullptr, st));
+      E_CHECK(bn_backward(e, prev, -1, b.dz_mid[j - 1], nullptr, 1LL * n * pv.Ho * pv.Wo, nullptr, st));
       E_CHECK(bn_done(prev));
     }
     E_CHECK(wgrad(b.main[0]));
@@ -524,7 +548,7 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
   }
   {
     Conv& cv = e->convs[0];
-    E_CHECK(bn_backward(e, 0, e->dz_stem, e->z_stem, 1LL * n * cv.Ho * cv.Wo, nullptr, st));
+    E_CHECK(bn_backward(e, 0, -1, e->dz_stem, nullptr, 1LL * n * cv.Ho * cv.Wo, nullptr, st));
     E_CHECK(bn_done(0));
     E_CHECK(wgrad(0));
   }
@@ -532,6 +556,7 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
   PMD_CHECK_CUDA(cudaEventRecord(e->ev_join, e->comm_stream));
   PMD_CHECK_CUDA(cudaStreamWaitEvent(st, e->ev_join, 0));
   if (e->n_repack > 0) E_CHECK(pmd_repack_dgrad_weights(e->wbf16, e->wt, e->d_repack, e->n_repack, e->repack_max, st));
+  E_CHECK(pmd_pad_stem_weight(e->wbf16 + e->convs[0].w_off, e->stem_w_pad, 64, e->convs[0].real_rsc, st));
   return 0;
 }
 
@@ -658,6 +683,7 @@ extern "C" PMD_API int pmd_engine_sync_params(PmdEngine* e, int broadcast_from_r
   }
   E_CHECK(pmd_cast_f32_to_bf16(e->param, e->wbf16, e->cfg.slab_elems, st));
   if (e->n_repack > 0) E_CHECK(pmd_repack_dgrad_weights(e->wbf16, e->wt, e->d_repack, e->n_repack, e->repack_max, st));
+  E_CHECK(pmd_pad_stem_weight(e->wbf16 + e->convs[0].w_off, e->stem_w_pad, 64, e->convs[0].real_rsc, st));
   PMD_CHECK_CUDA(cudaStreamSynchronize(st));
   return 0;
 }

@@ -9,6 +9,8 @@
 namespace pmd {
 namespace {
 
+constexpr int kFcSplit = 16;
+
 __global__ void pool_fc_fwd_kernel(const __nv_bfloat16* __restrict__ z, int HW, int C, const float* __restrict__ w,
                                    const float* __restrict__ b, int classes, float* __restrict__ feat,
                                    float* __restrict__ logits) {
@@ -102,17 +104,23 @@ __global__ void pool_fc_bwd_kernel(const float* __restrict__ dlogits, const floa
         *reinterpret_cast<uint32_t*>(dz + (static_cast<long long>(n) * HW + p) * C + 2 * c2) = pk;
     }
   } else {
-    const long long o = static_cast<long long>(blockIdx.x - N) * blockDim.x + threadIdx.x;
+    // dW[j][c] = sum_n dlogits[n][j] * feat[n][c]; the sample range is split kFcSplit ways for parallelism
+    const int bid = blockIdx.x - N;
+    const int chunk = bid / kFcSplit, part = bid % kFcSplit;
+    const long long o = static_cast<long long>(chunk) * blockDim.x + threadIdx.x;
     if (o >= static_cast<long long>(classes) * C) return;
     const int j = static_cast<int>(o / C), c = static_cast<int>(o % C);
+    const int per = (N + kFcSplit - 1) / kFcSplit;
+    const int n0 = part * per, n1 = min(n0 + per, N);
     float acc = 0.f, accb = 0.f;
-    for (int n = 0; n < N; ++n) {
+#pragma unroll 4
+    for (int n = n0; n < n1; ++n) {
       const float d = dlogits[static_cast<long long>(n) * classes + j];
       acc += d * feat[static_cast<long long>(n) * C + c];
       accb += d;
     }
-    dw[o] += acc;
-    if (c == 0) db[j] += accb;
+    atomicAdd(dw + o, acc);
+    if (c == 0) atomicAdd(db + j, accb);
   }
 }
 
@@ -144,7 +152,7 @@ extern "C" PMD_API int pmd_ce_fwd_bwd(const float* d_logits, const long long* d_
 extern "C" PMD_API int pmd_pool_fc_bwd(const float* d_dlogits, const float* d_feat, const float* d_w, int N, int HW, int C,
                                int classes, float* d_dw, float* d_db, void* d_dz, void* stream) {
   PMD_REQUIRE(C % 2 == 0, "feature width must be even");
-  const int extra = ceil_div(classes * C, 256);
+  const int extra = ceil_div(classes * C, 256) * kFcSplit;
   pool_fc_bwd_kernel<<<N + extra, 256, classes * 4, static_cast<cudaStream_t>(stream)>>>(
       d_dlogits, d_feat, d_w, N, HW, C, classes, d_dw, d_db, static_cast<__nv_bfloat16*>(d_dz));
   count_launch();

@@ -92,6 +92,26 @@ int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const void* d_y, const f
                      float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta, void* d_g_out,
                      long long rows, int C, void* stream);
 
+/* One or two BatchNorms that share the incoming gradient dz and its ReLU mask (a residual block's last
+ * main-path BN and its projection-shortcut BN) handled in one pass each.  mask_mode: 0 none, 1 z > 0,
+ * 2 recomputed as mask_scale*y0 + mask_shift > 0 from branch 0's forward affine (no read of z). */
+typedef struct {
+  const void* y;        /* conv output this BN normalised (bf16 NHWC) */
+  const float* mean;
+  const float* invstd;
+  const float* gamma;   /* apply only */
+  float* sums;          /* [2C] local sums: += by reduce, read by apply (dgamma/dbeta) */
+  const float* totals;  /* [2C] totals over ranks; NULL = sums */
+  void* dy;             /* apply only */
+  float* dgamma;        /* apply only, may be NULL; += */
+  float* dbeta;
+} PmdBnBranch;
+int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale, const float* d_mask_shift,
+                            int mask_mode, const PmdBnBranch* br, int nb, long long rows, int C, void* stream);
+int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z, const float* d_mask_scale, const float* d_mask_shift,
+                           int mask_mode, const PmdBnBranch* br, int nb, float count_total, void* d_g_out,
+                           long long rows, int C, void* stream);
+
 /* ------------------------------------------------------------------ head + loss (head.cu)
  * Global average pool + Linear, cross-entropy with top-1/top-5 counters (ref:model/resnet.py:102-104,
  * ref:main.py:48,105, ref:utils.py:64-77). */
@@ -126,6 +146,13 @@ int pmd_cast_f32_to_bf16(const float* d_src, void* d_dst, long long n, void* str
  * aug = int32 [N,3] = (x offset, y offset, flip), offsets in [0, 2*pad]. */
 int pmd_augment(const unsigned char* d_u8, const int* d_aug, int N, int H, int W, int pad, int c_out, void* d_out,
                 void* stream);
+/* Same augmentation fused with the stem convolution's im2col: out is [N, H, W, 64] bf16 whose first 27
+ * columns are the 3x3x3 neighbourhood ((r*3+s)*3 + c order, zero outside the image), the rest zero.  The
+ * 3->64 stem conv (ref:model/resnet.py:79-80) and its weight gradient then run as 64-wide 1x1
+ * convolutions on the tensor-core path; pmd_pad_stem_weight makes the matching [K][64] weight. */
+int pmd_augment_im2col(const unsigned char* d_u8, const int* d_aug, int N, int H, int W, int pad, void* d_out,
+                       void* stream);
+int pmd_pad_stem_weight(const void* d_w_k_rsc, void* d_w_padded_k64, int K, int rsc, void* stream);
 
 #ifdef __cplusplus
 }

@@ -487,3 +487,100 @@ def _engine_ckpt():
     mom_ok = all(torch.equal(a, b) for a, b in zip(opt['momentum'].values(), eng2.optimizer_state()['momentum'].values()))
     eng2.close()
     return {'ok': ok and keys_ok and mom_ok, 'fingerprint': fp, 'keys_ok': keys_ok, 'momentum_ok': mom_ok}
+
+
+# ------------------------------------------------------------------ v2 kernels: im2col stem, two-branch BN backward
+@case('stem_im2col_conv_matches_conv3x3')
+def _stem_im2col():
+    """augment_im2col + 64-wide 1x1 tensor-core conv == augment + 3x3 conv (pad 1) of the RGB image;
+    its tensor-core wgrad lands in the [K][27] KRSC stem gradient."""
+    import ctypes as C
+    from pmdist.data.loader import augment_cpu, draw_aug_params
+    from pmdist.data.sources import synthetic_source
+    from pmdist.ops import _lib, conv as cv
+    from pmdist.ops._lib import check, ptr, stream_ptr, PmdConvShape
+    N, H = 8, 32
+    src = synthetic_source(N, H, seed=21)
+    aug = draw_aug_params(N, True, torch.Generator().manual_seed(2))
+    x = augment_cpu(src.images, aug).cuda().to(torch.bfloat16).float()                # NCHW, bf16-rounded
+    w = _rand_bf16(64, 3, 3, 3, scale=0.2, seed=22)
+    col = torch.empty((N, H, H, 64), dtype=torch.bfloat16, device='cuda')
+    lib = _lib.lib()
+    check(lib.pmd_augment_im2col(ptr(src.images.cuda()), ptr(aug.cuda()), C.c_int(N), C.c_int(H), C.c_int(H), C.c_int(8),
+                                 ptr(col), stream_ptr()))
+    wk = cv.krsc_from_torch(w).reshape(64, 27).contiguous()
+    wp = torch.empty((64, 64), dtype=torch.bfloat16, device='cuda')
+    check(lib.pmd_pad_stem_weight(ptr(wk), ptr(wp), C.c_int(64), C.c_int(27), stream_ptr()))
+    y = cv.conv_fprop(col, wp.view(64, 1, 1, 64), 1)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x, w.float(), padding=1).permute(0, 2, 3, 1)
+    r = {'fprop': _cmp(y, ref, 2e-2)}
+    # wgrad through the engine-internal row mask is exercised by the engine cases; here: plain 64-col wgrad
+    dy = _rand_bf16(N, H, H, 64, seed=23)
+    dw = cv.conv_wgrad(col, dy, 1, 1)                                               # [64,1,1,64]
+    torch.cuda.synchronize()
+    refw = torch.nn.grad.conv2d_weight(x, (64, 3, 3, 3), _nchw(dy), padding=1).permute(0, 2, 3, 1).reshape(64, 27)
+    r['wgrad'] = _cmp(dw.view(64, 64)[:, :27], refw, 2e-3)
+    r['wgrad_pad_cols_zero'] = {'ok': bool((dw.view(64, 64)[:, 27:] == 0).all())}
+    r['ok'] = all(v['ok'] for v in r.values())
+    return r
+
+
+@case('bn_bwd_two_branch_and_mask_from_y')
+def _bn_multi():
+    import ctypes as C
+    from pmdist.ops import _lib, nn as nk
+    from pmdist.ops._lib import check, ptr, stream_ptr
+
+    class Br(C.Structure):
+        _fields_ = [('y', C.c_void_p), ('mean', C.c_void_p), ('invstd', C.c_void_p), ('gamma', C.c_void_p),
+                    ('sums', C.c_void_p), ('totals', C.c_void_p), ('dy', C.c_void_p), ('dgamma', C.c_void_p),
+                    ('dbeta', C.c_void_p)]
+    lib = _lib.lib()
+    Cc, N, H = 128, 8, 8
+    rows = N * H * H
+    ys = [(_rand_bf16(N, H, H, Cc, seed=30 + i) * 1.3 + 0.2).to(torch.bfloat16) for i in range(2)]
+    gam = [torch.rand(Cc, device='cuda') + 0.5 for _ in range(2)]
+    bet = [torch.randn(Cc, device='cuda') * 0.1 for _ in range(2)]
+    fin = [nk.bn_finalize([nk.bn_stats(y)], float(rows), g, b, None, None, None) for y, g, b in zip(ys, gam, bet)]
+    z = nk.bn_apply(ys[0], fin[0][0], fin[0][1], True, ys[1], fin[1][0], fin[1][1])      # relu(bn0(y0) + bn1(y1))
+    dz = _rand_bf16(N, H, H, Cc, seed=33)
+    # two-branch pass
+    sums = [torch.zeros(2 * Cc, device='cuda') for _ in range(2)]
+    dys = [torch.empty_like(ys[0]) for _ in range(2)]
+    dgs = [torch.zeros(Cc, device='cuda') for _ in range(4)]
+    brs = (Br * 2)()
+    for i in range(2):
+        brs[i] = Br(ys[i].data_ptr(), fin[i][2].data_ptr(), fin[i][3].data_ptr(), gam[i].data_ptr(), sums[i].data_ptr(), 0,
+                    dys[i].data_ptr(), dgs[2 * i].data_ptr(), dgs[2 * i + 1].data_ptr())
+    check(lib.pmd_bn_bwd_reduce_multi(ptr(dz), ptr(z), None, None, C.c_int(1), brs, C.c_int(2), C.c_longlong(rows),
+                                      C.c_int(Cc), stream_ptr()))
+    check(lib.pmd_bn_bwd_apply_multi(ptr(dz), ptr(z), None, None, C.c_int(1), brs, C.c_int(2), C.c_float(rows), None,
+                                     C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
+    torch.cuda.synchronize()
+    r = {}
+    for i in range(2):   # oracle: the single-branch kernels
+        s1 = nk.bn_bwd_reduce(dz, z, ys[i], fin[i][2], fin[i][3], True)
+        dg, db = torch.zeros(Cc, device='cuda'), torch.zeros(Cc, device='cuda')
+        d1 = nk.bn_bwd_apply(dz, z, ys[i], fin[i][2], fin[i][3], gam[i], [s1], 0, float(rows), True, dg, db)
+        torch.cuda.synchronize()
+        r[f'dy{i}'] = _cmp(dys[i], d1, 1e-6)
+        r[f'sums{i}'] = _cmp(sums[i], s1, 1e-4)
+        r[f'dgamma{i}'] = _cmp(dgs[2 * i], dg, 1e-4)
+    # mask recomputed from y (no residual): must equal the z-based mask
+    z1 = nk.bn_apply(ys[0], fin[0][0], fin[0][1], True)
+    sA, sB = torch.zeros(2 * Cc, device='cuda'), torch.zeros(2 * Cc, device='cuda')
+    dyA, dyB = torch.empty_like(z1), torch.empty_like(z1)
+    for mode, zz, ss, dd in ((1, z1, sA, dyA), (2, None, sB, dyB)):
+        b1 = (Br * 1)()
+        b1[0] = Br(ys[0].data_ptr(), fin[0][2].data_ptr(), fin[0][3].data_ptr(), gam[0].data_ptr(), ss.data_ptr(), 0,
+                   dd.data_ptr(), 0, 0)
+        check(lib.pmd_bn_bwd_reduce_multi(ptr(dz), ptr(zz), ptr(fin[0][0]), ptr(fin[0][1]), C.c_int(mode), b1, C.c_int(1),
+                                          C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
+        check(lib.pmd_bn_bwd_apply_multi(ptr(dz), ptr(zz), ptr(fin[0][0]), ptr(fin[0][1]), C.c_int(mode), b1, C.c_int(1),
+                                         C.c_float(rows), None, C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
+    torch.cuda.synchronize()
+    r['mask_from_y_dy'] = _cmp(dyB, dyA, 1e-6)
+    r['mask_from_y_sums'] = _cmp(sB, sA, 1e-5)
+    r['ok'] = all(v['ok'] for v in r.values())
+    return r

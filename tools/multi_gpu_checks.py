@@ -142,7 +142,7 @@ def summarize(out_dir: str, world: int) -> dict:
         moved = len(set(fps[0])) == len(fps[0])
         l_multi, l_one = rs[0]['engine'][algo]['losses'], oracle['losses']
         close = all(abs(a - b) < 0.03 for a, b in zip(l_multi, l_one))
-        fp_close = all(abs(a - b) < 2e-3 * max(1.0, abs(b)) for a, b in zip(fps[0], oracle['fingerprints']))
+        fp_close = all(abs(a - b) < 1e-2 * max(1.0, abs(b)) for a, b in zip(fps[0], oracle['fingerprints']))
         bn_same = len({r['engine'][algo]['bn_rm'] for r in rs}) == 1
         summary['algos'][algo] = {'weights_bitwise_equal_across_ranks': same, 'weights_moved': moved,
                                   'loss_matches_single_rank': close, 'fingerprint_close_to_single_rank': fp_close,
