@@ -506,7 +506,8 @@ def _stem_im2col():
     w = _rand_bf16(64, 3, 3, 3, scale=0.2, seed=22)
     col = torch.empty((N, H, H, 64), dtype=torch.bfloat16, device='cuda')
     lib = _lib.lib()
-    check(lib.pmd_augment_im2col(ptr(src.images.cuda()), ptr(aug.cuda()), C.c_int(N), C.c_int(H), C.c_int(H), C.c_int(8),
+    u8_dev, aug_dev = src.images.cuda(), aug.cuda()      # keep both alive: a freed temporary's block is reused at once
+    check(lib.pmd_augment_im2col(ptr(u8_dev), ptr(aug_dev), C.c_int(N), C.c_int(H), C.c_int(H), C.c_int(8),
                                  ptr(col), stream_ptr()))
     wk = cv.krsc_from_torch(w).reshape(64, 27).contiguous()
     wp = torch.empty((64, 64), dtype=torch.bfloat16, device='cuda')
@@ -564,7 +565,7 @@ def _bn_multi():
         dg, db = torch.zeros(Cc, device='cuda'), torch.zeros(Cc, device='cuda')
         d1 = nk.bn_bwd_apply(dz, z, ys[i], fin[i][2], fin[i][3], gam[i], [s1], 0, float(rows), True, dg, db)
         torch.cuda.synchronize()
-        r[f'dy{i}'] = _cmp(dys[i], d1, 1e-6)
+        r[f'dy{i}'] = _cmp(dys[i], d1, 1e-3)     # one bf16 ulp where the atomically-summed totals differ in the last bit
         r[f'sums{i}'] = _cmp(sums[i], s1, 1e-4)
         r[f'dgamma{i}'] = _cmp(dgs[2 * i], dg, 1e-4)
     # mask recomputed from y (no residual): must equal the z-based mask
@@ -580,7 +581,7 @@ def _bn_multi():
         check(lib.pmd_bn_bwd_apply_multi(ptr(dz), ptr(zz), ptr(fin[0][0]), ptr(fin[0][1]), C.c_int(mode), b1, C.c_int(1),
                                          C.c_float(rows), None, C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
     torch.cuda.synchronize()
-    r['mask_from_y_dy'] = _cmp(dyB, dyA, 1e-6)
+    r['mask_from_y_dy'] = _cmp(dyB, dyA, 1e-3)
     r['mask_from_y_sums'] = _cmp(sB, sA, 1e-5)
     r['ok'] = all(v['ok'] for v in r.values())
     return r
