@@ -504,3 +504,70 @@ extern "C" PMD_API int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const
   b.dbeta = d_dbeta;
   return pmd_bn_bwd_apply_multi(d_dz, d_z, nullptr, nullptr, relu ? 1 : 0, &b, 1, count_total, d_g_out, rows, C, stream);
 }
+
+// ---------------------------------------------------------------------------------------------
+// pmd_bn_bwd_apply_static: the same computation as pmd_bn_bwd_apply for hosts that must not allocate
+// device memory.  pmd_bn_bwd_apply sums the per-rank [2C] tables into a scratch vector that it obtains
+// from cudaMalloc on first use.  Some programs that want this kernel cannot afford that call: an
+// application that has handed the whole GPU to its own memory pool (there is nothing left for the CUDA
+// allocator to give), or a control loop that may not take the device-wide synchronisation cudaMalloc
+// implies.  For them the scratch lives in the library image instead: a file-scope __device__ array of
+// 2 * kStaticMaxC floats (8 KB), present on every GPU that loads libpmdist.so until the process exits.
+//
+//   * Limit: C <= 1024 channels; larger C is refused with an error, nothing is launched.
+//   * The device address of the array is looked up with cudaGetSymbolAddress the first time the entry
+//     point runs on a given device (that device being current).  Make that first call during start-up,
+//     before any stream capture is begun; later calls only launch kernels.
+//   * No cudaMalloc / cudaFree / allocating library call is made on any path through this function.
+//   * All calls on a device share the one array and it keeps whatever the previous call left in it.
+//     Nothing in it has to start at zero: the first kernel overwrites entries [0, 2C) and the second
+//     reads only those.  Two calls whose kernels can overlap on the GPU (different streams without an
+//     ordering between them) would race on the array -- serialise them.
+namespace pmd {
+namespace {
+constexpr int kStaticMaxC = 1024;
+constexpr int kStaticMaxDevices = 64;
+static __device__ __align__(256) float g_bn_totals_static[2 * kStaticMaxC];
+float* g_bn_totals_static_addr[kStaticMaxDevices] = {};   // per device: where the array above lives
+}  // namespace
+}  // namespace pmd
+
+extern "C" PMD_API int pmd_bn_bwd_apply_static(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
+                                               const float* d_invstd, const float* d_gamma,
+                                               const float* const* d_sums_ranks, int world, const float* d_local_sums,
+                                               float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta,
+                                               void* d_g_out, long long rows, int C, void* stream) {
+  if (C > kStaticMaxC) {
+    set_error("pmd_bn_bwd_apply_static: C = " + std::to_string(C) + " exceeds the built-in scratch (at most " +
+              std::to_string(kStaticMaxC) + " channels); use pmd_bn_bwd_apply, which allocates its scratch");
+    return -1;
+  }
+  BN_CHECK_C(C);
+  PMD_REQUIRE(world >= 1, "world must be >= 1");
+  int dev = -1;
+  PMD_CHECK_CUDA(cudaGetDevice(&dev));
+  PMD_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "device ordinal outside the static table");
+  if (g_bn_totals_static_addr[dev] == nullptr) {
+    // In host code the array's name is only a handle for the runtime, not a device pointer: resolve it once
+    // per device, with that device current, and hand the resolved address to the kernels.
+    float* ptr = nullptr;
+    PMD_CHECK_CUDA(cudaGetSymbolAddress((void**)&ptr, g_bn_totals_static));
+    PMD_REQUIRE(ptr != nullptr, "cudaGetSymbolAddress returned a null address");
+    g_bn_totals_static_addr[dev] = ptr;
+  }
+  float* totals = g_bn_totals_static_addr[dev];
+  sum_tables_kernel<<<ceil_div(2 * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_sums_ranks, world, 2 * C, totals);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  PmdBnBranch b{};
+  b.y = d_y;
+  b.mean = d_mean;
+  b.invstd = d_invstd;
+  b.gamma = d_gamma;
+  b.sums = const_cast<float*>(d_local_sums);
+  b.totals = totals;
+  b.dy = d_dy;
+  b.dgamma = d_dgamma;
+  b.dbeta = d_dbeta;
+  return pmd_bn_bwd_apply_multi(d_dz, d_z, nullptr, nullptr, relu ? 1 : 0, &b, 1, count_total, d_g_out, rows, C, stream);
+}

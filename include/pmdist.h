@@ -92,6 +92,20 @@ int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const void* d_y, const f
                      float count_total, int relu, void* d_dy, float* d_dgamma, float* d_dbeta, void* d_g_out,
                      long long rows, int C, void* stream);
 
+/* Same result as pmd_bn_bwd_apply, for callers that cannot allocate device memory (a host that gave the
+ * whole GPU to its own pool, or a loop that must not incur cudaMalloc's device-wide synchronisation).  It
+ * has no counterpart in the reference.  The [2C] table-sum scratch is a __device__ array built into the
+ * library (8 KB per GPU for the life of the process) instead of a cudaMalloc'ed buffer:
+ *   - C may be at most 1024; larger C returns -1 with an explanatory pmd_last_error() and launches nothing;
+ *   - the first call on each device resolves the array's address (cudaGetSymbolAddress): make that call at
+ *     start-up, before any stream capture begins; no call ever allocates or frees device memory;
+ *   - the array is shared by every call and keeps the previous call's contents (nothing needs to be zero:
+ *     entries [0, 2C) are rewritten before they are read); calls that can overlap on the GPU race on it. */
+int pmd_bn_bwd_apply_static(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
+                            const float* d_invstd, const float* d_gamma, const float* const* d_sums_ranks, int world,
+                            const float* d_local_sums, float count_total, int relu, void* d_dy, float* d_dgamma,
+                            float* d_dbeta, void* d_g_out, long long rows, int C, void* stream);
+
 /* One or two BatchNorms that share the incoming gradient dz and its ReLU mask (a residual block's last
  * main-path BN and its projection-shortcut BN) handled in one pass each.  mask_mode: 0 none, 1 z > 0,
  * 2 recomputed as mask_scale*y0 + mask_shift > 0 from branch 0's forward affine (no read of z). */
