@@ -213,9 +213,13 @@ def run_reference(a) -> None:
     W, K, N, B = max(a.warmup, 3), a.steps, a.gpus, a.per_gpu_batch
     work = tempfile.mkdtemp(prefix='ref_bench_')
     gb = B * N
-    env = {k: v for k, v in os.environ.items()
-           if k not in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE', 'MASTER_ADDR', 'MASTER_PORT', 'TORCHELASTIC_RUN_ID',
-                        'GROUP_RANK', 'ROLE_RANK', 'LOCAL_WORLD_SIZE', 'ROLE_WORLD_SIZE')}
+    # Scrub everything torchrun exported: in particular TORCHELASTIC_USE_AGENT_STORE=True would make the
+    # reference's own init_process_group (ref:main.py:193) look for the agent's TCPStore on ITS port 20080
+    # instead of hosting one, and every rank would wait for a store nobody serves.
+    torchrun_vars = {'RANK', 'LOCAL_RANK', 'WORLD_SIZE', 'MASTER_ADDR', 'MASTER_PORT', 'GROUP_RANK', 'ROLE_RANK',
+                     'LOCAL_WORLD_SIZE', 'ROLE_WORLD_SIZE', 'GROUP_WORLD_SIZE', 'ROLE_NAME', 'OMP_NUM_THREADS',
+                     'NCCL_ASYNC_ERROR_HANDLING', 'TORCH_NCCL_ASYNC_ERROR_HANDLING'}
+    env = {k: v for k, v in os.environ.items() if k not in torchrun_vars and not k.startswith('TORCHELASTIC_')}
     env.update({'REF_SHIM': '1', 'PYTHONPATH': os.path.join(ROOT, 'baseline', 'shim') + os.pathsep + env.get('PYTHONPATH', ''),
                 'REF_TRAIN_SIZE': str(gb * (W + K)), 'REF_TEST_SIZE': str(gb), 'REF_IMAGE_SIZE': str(a.image_size),
                 'REF_TIMING_OUT': os.path.join(work, 'timing')})
@@ -223,7 +227,7 @@ def run_reference(a) -> None:
            '--save_path', os.path.join(work, 'out') + '/', '--print-freq', '1000']
     local = int(os.environ.get('LOCAL_RANK', '0'))
     with ClockSampler(local) as clk:
-        r = subprocess.run(cmd, cwd=work, env=env, capture_output=True, text=True, timeout=3000)
+        r = subprocess.run(cmd, cwd=work, env=env, capture_output=True, text=True, timeout=1500)
     if r.returncode != 0:
         print(json.dumps({'impl': 'reference', 'unavailable': 'reference run failed: ' + (r.stderr or r.stdout)[-300:].replace('\n', ' ')}))
         return

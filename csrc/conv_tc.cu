@@ -19,6 +19,8 @@
 //     tcgen05 consumes directly from the TMA-written tiles: no transposes;
 //   * M = 128 = two (tap, 64-channel) boxes of X, N = up to 256 output channels, reduction split over
 //     gridDim.z CTAs; partial tiles go straight into the fp32 gradient slab with red.global.add.f32.
+#include <cstdlib>
+
 #include "conv_tc.cuh"
 #include "ptx.cuh"
 
@@ -220,6 +222,242 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<BN>(tmem_base);
+}
+
+// ============================================================================ fprop / dgrad, persistent
+// Same math as conv_gemm_kernel, restructured so that the fixed per-CTA costs (barrier init, TMEM
+// allocation, first-load latency, epilogue) are paid once per SM instead of once per tile: each CTA loops
+// over tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...; the TMA ring runs continuously across tile
+// boundaries; the accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile j
+// (tcgen05.ld -> bf16 -> smem -> TMA store + BN statistics) overlaps the MMAs of tile j+1.
+template <int STAGES>
+struct PersistBars {
+  uint64_t full[STAGES];
+  uint64_t empty[STAGES];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+};
+
+struct TileCoord {
+  int cls, ntile, w0, h0, n0, kb0, nkb;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const ConvGemmParams& p, int t, int bn) {
+  TileCoord c;
+  const int ntiles_n = p.out_channels / bn;
+  const int pix_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
+  c.ntile = t % ntiles_n;          // channel tiles of one pixel brick are adjacent: they share the A loads in L2
+  int r = t / ntiles_n;
+  const int pt = r % pix_tiles;
+  c.cls = r / pix_tiles;
+  const int tw = pt % p.tiles_w;
+  const int th = (pt / p.tiles_w) % p.tiles_h;
+  const int tn = pt / (p.tiles_w * p.tiles_h);
+  c.w0 = tw * p.w_box;
+  c.h0 = th * p.h_box;
+  c.n0 = tn * p.n_box;
+  c.kb0 = p.kb_begin[c.cls];
+  c.nkb = p.kb_count[c.cls];
+  return c;
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __grid_constant__ ConvGemmParams p,
+                                                                       int total_tiles) {
+  constexpr int kStageBytes = kABytes + BN * 128;
+  constexpr int kStagingBytes = (BN / 64) * kABytes;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  uint8_t* stage_out = smem + STAGES * kStageBytes;
+  PersistBars<STAGES>* bars = reinterpret_cast<PersistBars<STAGES>*>(stage_out + kStagingBytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&bars->full[s], 1);
+      mbar_init(&bars->empty[s], 1);
+    }
+    mbar_init(&bars->tmem_full[0], 1);
+    mbar_init(&bars->tmem_full[1], 1);
+    mbar_init(&bars->tmem_empty[0], 128);
+    mbar_init(&bars->tmem_empty[1], 128);
+    fence_mbar_init();
+    prefetch_tmap(&p.a[0]);
+    prefetch_tmap(&p.b[0]);
+    prefetch_tmap(&p.out[0]);
+  }
+  if (warp == 1) tmem_alloc<2 * BN>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const TileCoord c = decode_tile(p, t, BN);
+        for (int i = 0; i < c.nkb; ++i, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(&bars->empty[s], ph ^ 1u);
+          const KBlock kb = p.kb[c.kb0 + i];
+          uint8_t* sa = smem + s * kStageBytes;
+          uint8_t* sb = sa + kABytes;
+          mbar_expect_tx(&bars->full[s], kStageBytes);
+          tma_load_4d(&p.a[kb.a_map], &bars->full[s], sa, kb.a_ch, c.w0 + kb.dw, c.h0 + kb.dh, c.n0);
+          if (p.b_tap_last)
+            tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, c.ntile * BN, kb.tap);
+          else
+            tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, kb.tap, c.ntile * BN);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, false);
+      uint32_t it = 0, jm = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const TileCoord c = decode_tile(p, t, BN);
+        if (c.nkb == 0) continue;
+        const uint32_t acc = jm & 1, use = jm >> 1;
+        mbar_wait(&bars->tmem_empty[acc], (use & 1) ^ 1u);     // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_addr = tmem_base + acc * BN;
+        for (int i = 0; i < c.nkb; ++i, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(&bars->full[s], ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
+          const uint32_t b_addr = a_addr + kABytes;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            umma_bf16(d_addr, make_smem_desc_sw128(a_addr + k * 32, 16, 1024),
+                      make_smem_desc_sw128(b_addr + k * 32, 16, 1024), idesc, (i | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&bars->empty[s]);
+        }
+        umma_commit(&bars->tmem_full[acc]);
+        ++jm;
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (128 threads)
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int wi = row % p.w_box;
+    const int hi = (row / p.w_box) % p.h_box;
+    const int ni = row / (p.w_box * p.h_box);
+    const int et = threadIdx.x - 64;
+    uint32_t jm = 0;
+    bool store_pending = false;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const TileCoord c = decode_tile(p, t, BN);
+      const bool valid = (c.w0 + wi < p.GW[c.cls]) && (c.h0 + hi < p.GH[c.cls]) && (c.n0 + ni < p.N);
+      const __nv_bfloat16* add_row = nullptr;
+      if (p.addend != nullptr && valid) {
+        const long long pix =
+            (static_cast<long long>(c.n0 + ni) * p.GH[c.cls] + (c.h0 + hi)) * p.GW[c.cls] + (c.w0 + wi);
+        add_row = p.addend + pix * p.out_channels + c.ntile * BN;
+      }
+      const uint32_t acc = jm & 1, use = jm >> 1;
+      if (c.nkb > 0) {
+        mbar_wait(&bars->tmem_full[acc], use & 1);
+        tc_fence_after();
+      }
+      // the previous tile's TMA store must have finished reading the staging buffer (and every thread must
+      // have finished its statistics pass over it) before anybody overwrites it
+      if (et == 0 && store_pending) tma_store_wait_read0();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+      for (int hf = 0; hf < BN / 64; ++hf) {
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          uint32_t v[32];
+          if (c.nkb > 0) {
+            tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + hf * 64 + cc * 32, v);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = 0u;
+          }
+          uint32_t packed[16];
+          if (add_row != nullptr) {
+            const uint4* ap = reinterpret_cast<const uint4*>(add_row + hf * 64 + cc * 32);
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+              const uint4 a4 = ap[jj];
+              const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 af = unpack_bf16x2(aw[e]);
+                packed[jj * 4 + e] = pack_bf16x2(__uint_as_float(v[jj * 8 + e * 2]) + af.x,
+                                                 __uint_as_float(v[jj * 8 + e * 2 + 1]) + af.y);
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              packed[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+          }
+          if (!valid) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) packed[j] = 0u;
+          }
+          uint8_t* rowp = stage_out + hf * kABytes + row * 128;
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const int chunk = (cc * 4 + jj) ^ (row & 7);
+            *reinterpret_cast<uint4*>(rowp + chunk * 16) =
+                make_uint4(packed[jj * 4], packed[jj * 4 + 1], packed[jj * 4 + 2], packed[jj * 4 + 3]);
+          }
+        }
+      }
+      if (c.nkb > 0) {
+        // all of this thread's TMEM reads have completed (tcgen05.wait::ld above): release the accumulator
+        tc_fence_before();
+        mbar_arrive(&bars->tmem_empty[acc]);
+        ++jm;
+      }
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (et == 0) {
+#pragma unroll
+        for (int hf = 0; hf < BN / 64; ++hf)
+          tma_store_4d(&p.out[c.cls], stage_out + hf * kABytes, c.ntile * BN + hf * 64, c.w0, c.h0, c.n0);
+        tma_store_commit();
+      }
+      store_pending = true;
+      if (p.stats != nullptr) {
+        const int ch = et & 63, rh = et >> 6;
+#pragma unroll
+        for (int hf = 0; hf < BN / 64; ++hf) {
+          float s1 = 0.f, s2 = 0.f;
+          const uint8_t* base = stage_out + hf * kABytes;
+#pragma unroll 8
+          for (int r = rh * 64; r < rh * 64 + 64; ++r) {
+            const __nv_bfloat16 hv =
+                *reinterpret_cast<const __nv_bfloat16*>(base + r * 128 + (((ch >> 3) ^ (r & 7)) << 4) + (ch & 7) * 2);
+            const float f = __bfloat162float(hv);
+            s1 += f;
+            s2 += f * f;
+          }
+          red_add_f32(p.stats + c.ntile * BN + hf * 64 + ch, s1);
+          red_add_f32(p.stats + p.out_channels + c.ntile * BN + hf * 64 + ch, s2);
+        }
+      }
+    }
+    if (et == 0 && store_pending) tma_store_wait_read0();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
 }
 
 // ============================================================================ wgrad
@@ -614,27 +852,70 @@ static int set_smem(Kernel k, int bytes) {
   return 0;
 }
 
+template <int BN, int ST>
+static int launch_conv_gemm_t(const ConvGemmParams& p, const dim3& grid, cudaStream_t stream) {
+  constexpr int smem = ST * (kABytes + BN * 128) + sizeof(PipeBars<ST>) + 1024;
+  static bool once = false;
+  if (!once) {
+    if (set_smem(conv_gemm_kernel<BN, ST>, smem)) return -1;
+    once = true;
+  }
+  conv_gemm_kernel<BN, ST><<<grid, kThreads, smem, stream>>>(p);
+  return 0;
+}
+
+// Pipeline depth trades smem per CTA against resident CTAs per SM (the epilogue of one CTA overlaps the
+// main loop of its neighbours).  Tunable for experiments: PMD_GEMM64_STAGES / PMD_GEMM128_STAGES in {2,3,4}.
+static int stages_from_env(const char* name, int dflt) {
+  const char* v = getenv(name);
+  if (v == nullptr) return dflt;
+  const int s = atoi(v);
+  return (s >= 2 && s <= 4) ? s : dflt;
+}
+
+template <int BN, int ST>
+static int launch_conv_gemm_persistent_t(const ConvGemmParams& p, cudaStream_t stream) {
+  constexpr int smem = ST * (kABytes + BN * 128) + (BN / 64) * kABytes + sizeof(PersistBars<ST>) + 1024;
+  static int ctas_per_sm = 0, sms = 0;
+  if (ctas_per_sm == 0) {
+    if (set_smem(conv_gemm_persistent_kernel<BN, ST>, smem)) return -1;
+    int dev = 0;
+    PMD_CHECK_CUDA(cudaGetDevice(&dev));
+    PMD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    int occ = 0;
+    PMD_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_gemm_persistent_kernel<BN, ST>, kThreads, smem));
+    const int by_tmem = 512 / (2 * BN);          // each CTA owns 2*BN TMEM columns of the SM's 512
+    ctas_per_sm = occ < by_tmem ? occ : by_tmem;
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+  }
+  const int total = p.tiles_w * p.tiles_h * p.tiles_n * (p.out_channels / BN) * p.n_classes;
+  const int grid = total < ctas_per_sm * sms ? total : ctas_per_sm * sms;
+  conv_gemm_persistent_kernel<BN, ST><<<grid, kThreads, smem, stream>>>(p, total);
+  return 0;
+}
+
 int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream) {
   const dim3 grid(p.tiles_w * p.tiles_h * p.tiles_n, p.out_channels / p.bn_tile, p.n_classes);
-  if (p.bn_tile == 64) {
-    constexpr int ST = 4;
-    constexpr int smem = ST * (kABytes + 64 * 128) + sizeof(PipeBars<ST>) + 1024;
-    static bool once = false;
-    if (!once) {
-      if (set_smem(conv_gemm_kernel<64, ST>, smem)) return -1;
-      once = true;
-    }
-    conv_gemm_kernel<64, ST><<<grid, kThreads, smem, stream>>>(p);
+  static const int st64 = stages_from_env("PMD_GEMM64_STAGES", 3), st128 = stages_from_env("PMD_GEMM128_STAGES", 2);
+  static const bool persistent = getenv("PMD_GEMM_PERSISTENT") == nullptr || atoi(getenv("PMD_GEMM_PERSISTENT")) != 0;
+  int rc;
+  if (persistent) {
+    if (p.bn_tile == 64)
+      rc = st64 == 2 ? launch_conv_gemm_persistent_t<64, 2>(p, stream)
+                     : (st64 == 4 ? launch_conv_gemm_persistent_t<64, 4>(p, stream)
+                                  : launch_conv_gemm_persistent_t<64, 3>(p, stream));
+    else
+      rc = st128 == 4 ? launch_conv_gemm_persistent_t<128, 4>(p, stream)
+                      : (st128 == 3 ? launch_conv_gemm_persistent_t<128, 3>(p, stream)
+                                    : launch_conv_gemm_persistent_t<128, 2>(p, stream));
+  } else if (p.bn_tile == 64) {
+    rc = st64 == 2 ? launch_conv_gemm_t<64, 2>(p, grid, stream)
+                   : (st64 == 3 ? launch_conv_gemm_t<64, 3>(p, grid, stream) : launch_conv_gemm_t<64, 4>(p, grid, stream));
   } else {
-    constexpr int ST = 3;
-    constexpr int smem = ST * (kABytes + 128 * 128) + sizeof(PipeBars<ST>) + 1024;
-    static bool once = false;
-    if (!once) {
-      if (set_smem(conv_gemm_kernel<128, ST>, smem)) return -1;
-      once = true;
-    }
-    conv_gemm_kernel<128, ST><<<grid, kThreads, smem, stream>>>(p);
+    rc = st128 == 2 ? launch_conv_gemm_t<128, 2>(p, grid, stream)
+                    : (st128 == 4 ? launch_conv_gemm_t<128, 4>(p, grid, stream) : launch_conv_gemm_t<128, 3>(p, grid, stream));
   }
+  if (rc != 0) return -1;
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

@@ -108,7 +108,9 @@ struct PmdEngine {
   double* metrics_total = nullptr;
   bf16 *z_stem = nullptr, *dz_stem = nullptr;
   long long activation_bytes = 0;
-  cudaStream_t comm_stream = nullptr, main_stream = nullptr;
+  cudaStream_t comm_stream = nullptr, main_stream = nullptr, wg_stream = nullptr;
+  std::vector<cudaEvent_t> wg_events;
+  int wg_event_next = 0;
   cudaEvent_t ev_in = nullptr, ev_out = nullptr;
   std::vector<cudaEvent_t> events;
   cudaEvent_t ev_join = nullptr;
@@ -376,9 +378,13 @@ struct BucketTracker {
   int done(int bkt) {
     if (--pending[bkt] != 0) return 0;
     // bucket complete: hand it to the comm stream
+    // gradients of this bucket were produced on the main stream (BN, FC) and on the wgrad stream
     cudaEvent_t ev = e->events[launched % e->events.size()];
     PMD_CHECK_CUDA(cudaEventRecord(ev, main));
     PMD_CHECK_CUDA(cudaStreamWaitEvent(e->comm_stream, ev, 0));
+    cudaEvent_t ev2 = e->wg_events[(e->wg_event_next++) % e->wg_events.size()];
+    PMD_CHECK_CUDA(cudaEventRecord(ev2, e->wg_stream));
+    PMD_CHECK_CUDA(cudaStreamWaitEvent(e->comm_stream, ev2, 0));
     PmdAllreduceSgd a{};
     a.param_off = e->param_off;
     a.grad_off = e->grad_off;
@@ -514,17 +520,27 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     E_CHECK(bt.done(e->convs[ci].g_bkt));
     return bt.done(e->convs[ci].b_bkt);
   };
+  // Weight gradients are off the critical path (nothing in backward consumes them), so they run on a
+  // side stream: the L2-bound wgrad GEMMs overlap the DRAM-bound BatchNorm passes of the layer below.
   auto wgrad = [&](int ci) -> int {
     Conv& cv = e->convs[ci];
+    cudaEvent_t ev = e->wg_events[(e->wg_event_next++) % e->wg_events.size()];
+    PMD_CHECK_CUDA(cudaEventRecord(ev, st));                       // dy of this conv is ready
+    PMD_CHECK_CUDA(cudaStreamWaitEvent(e->wg_stream, ev, 0));
     if (cv.tc) {
-      E_CHECK(launch_wgrad(pl->conv[ci].wgrad, st));
+      E_CHECK(launch_wgrad(pl->conv[ci].wgrad, e->wg_stream));
     } else {
       PmdConvShape s = cv.s;
       s.N = n;
-      E_CHECK(pmd_conv_wgrad_direct(&s, cv.x_cstride, cv.x, cv.dy, e->grad + cv.w_off, st));
+      E_CHECK(pmd_conv_wgrad_direct(&s, cv.x_cstride, cv.x, cv.dy, e->grad + cv.w_off, e->wg_stream));
     }
     return bt.done(cv.w_bkt);
   };
+  {   // the wgrad stream joins the step after the gradient slab was cleared
+    cudaEvent_t ev = e->wg_events[(e->wg_event_next++) % e->wg_events.size()];
+    PMD_CHECK_CUDA(cudaEventRecord(ev, st));
+    PMD_CHECK_CUDA(cudaStreamWaitEvent(e->wg_stream, ev, 0));
+  }
   for (int bi = static_cast<int>(e->blocks.size()) - 1; bi >= 0; --bi) {
     Block& b = e->blocks[bi];
     const int last = b.main[b.n_main - 1];
@@ -555,6 +571,11 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
   PMD_REQUIRE(bt.launched == c.n_buckets, "internal: not every gradient bucket was launched");
   PMD_CHECK_CUDA(cudaEventRecord(e->ev_join, e->comm_stream));
   PMD_CHECK_CUDA(cudaStreamWaitEvent(st, e->ev_join, 0));
+  {
+    cudaEvent_t ev = e->wg_events[(e->wg_event_next++) % e->wg_events.size()];
+    PMD_CHECK_CUDA(cudaEventRecord(ev, e->wg_stream));
+    PMD_CHECK_CUDA(cudaStreamWaitEvent(st, ev, 0));
+  }
   if (e->n_repack > 0) E_CHECK(pmd_repack_dgrad_weights(e->wbf16, e->wt, e->d_repack, e->n_repack, e->repack_max, st));
   E_CHECK(pmd_pad_stem_weight(e->wbf16 + e->convs[0].w_off, e->stem_w_pad, 64, e->convs[0].real_rsc, st));
   return 0;
@@ -628,6 +649,9 @@ extern "C" PMD_API int pmd_engine_create(const PmdEngineConfig* cfg, PmdComm* co
   e->cfg.bucket_start = e->cfg.bucket_numel = nullptr;
   PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
   PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->main_stream, cudaStreamNonBlocking));
+  PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->wg_stream, cudaStreamNonBlocking));
+  e->wg_events.resize(2 * (cfg->n_convs + cfg->n_buckets) + 8);
+  for (auto& ev : e->wg_events) PMD_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   PMD_CHECK_CUDA(cudaEventCreateWithFlags(&e->ev_in, cudaEventDisableTiming));
   PMD_CHECK_CUDA(cudaEventCreateWithFlags(&e->ev_out, cudaEventDisableTiming));
   e->events.resize(cfg->n_buckets + 1);
@@ -649,6 +673,8 @@ extern "C" PMD_API int pmd_engine_destroy(PmdEngine* e) {
   if (e->ev_join) cudaEventDestroy(e->ev_join);
   if (e->comm_stream) cudaStreamDestroy(e->comm_stream);
   if (e->main_stream) cudaStreamDestroy(e->main_stream);
+  if (e->wg_stream) cudaStreamDestroy(e->wg_stream);
+  for (auto& ev : e->wg_events) cudaEventDestroy(ev);
   if (e->ev_in) cudaEventDestroy(e->ev_in);
   if (e->ev_out) cudaEventDestroy(e->ev_out);
   delete e;
