@@ -120,31 +120,46 @@ __global__ void bn_eval_affine_kernel(int C, const float* gamma, const float* be
   shift[c] = beta[c] - rm[c] * a;
 }
 
+__device__ __forceinline__ void lds8(const float* p, float (&v)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
 template <int RES>   // 0: none, 1: plain residual, 2: residual with its own affine
 __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ scale,
                                 const float* __restrict__ shift, const __nv_bfloat16* __restrict__ res,
                                 const float* __restrict__ rscale, const float* __restrict__ rshift, int relu,
                                 __nv_bfloat16* __restrict__ z, long long total8, int C) {
+  extern __shared__ float aff[];     // [scale | shift | rscale | rshift], C floats each: 2-4 wide shared loads per
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {   // 8 elements instead of 16-32 scalar global loads
+    aff[c] = scale[c];
+    aff[C + c] = shift[c];
+    if (RES == 2) {
+      aff[2 * C + c] = rscale[c];
+      aff[3 * C + c] = rshift[c] ;
+    }
+  }
+  __syncthreads();
   const int groups = C / 8;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total8;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int c0 = static_cast<int>(i % groups) * 8;
-    float v[8], o[8];
+    float v[8], o[8], sc[8], sh[8];
     load8(y + i * 8, v);
-    const float4 sa = __ldg(reinterpret_cast<const float4*>(scale + c0));
-    const float4 sb = __ldg(reinterpret_cast<const float4*>(scale + c0 + 4));
-    const float4 ha = __ldg(reinterpret_cast<const float4*>(shift + c0));
-    const float4 hb = __ldg(reinterpret_cast<const float4*>(shift + c0 + 4));
-    const float sc[8] = {sa.x, sa.y, sa.z, sa.w, sb.x, sb.y, sb.z, sb.w};
-    const float sh[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+    lds8(aff + c0, sc);
+    lds8(aff + C + c0, sh);
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = fmaf(v[j], sc[j], sh[j]);
     if (RES != 0) {
       float rv[8];
       load8(res + i * 8, rv);
       if (RES == 2) {
+        lds8(aff + 2 * C + c0, sc);
+        lds8(aff + 3 * C + c0, sh);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], __ldg(rscale + c0 + j), __ldg(rshift + c0 + j));
+        for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], sc[j], sh[j]);
       } else {
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] += rv[j];
@@ -205,34 +220,49 @@ __global__ void bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz,
     }
   }
   if (rl < rpi) {
-    for (long long r = static_cast<long long>(blockIdx.x) * rpi + rl; r < rows;
-         r += static_cast<long long>(gridDim.x) * rpi) {
-      float gv[8], y0[8];
-      load8(dz + r * C + c0, gv);
-      load8(b0.y + r * C + c0, y0);
-      if (MASK == 1) {
-        float zv[8];
-        load8(z + r * C + c0, zv);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) gv[i] = zv[i] > 0.f ? gv[i] : 0.f;
-      } else if (MASK == 2) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) gv[i] = fmaf(y0[i], ms[i], mh[i]) > 0.f ? gv[i] : 0.f;
-      }
+    const long long stride = static_cast<long long>(gridDim.x) * rpi;
+    auto body = [&](long long r, const float (&gin)[8], const float (&y0)[8], const float (&zin)[8],
+                    const float (&y1)[8]) {
+      float gv[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
+        gv[i] = gin[i];
+        if (MASK == 1) gv[i] = zin[i] > 0.f ? gv[i] : 0.f;
+        if (MASK == 2) gv[i] = fmaf(y0[i], ms[i], mh[i]) > 0.f ? gv[i] : 0.f;
         acc[0][0][i] += gv[i];
         acc[0][1][i] += gv[i] * (y0[i] - mean0[i]) * is0[i];
-      }
-      if (NB == 2) {
-        float y1[8];
-        load8(b1.y + r * C + c0, y1);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        if (NB == 2) {
           acc[1][0][i] += gv[i];
           acc[1][1][i] += gv[i] * (y1[i] - mean1[i]) * is1[i];
         }
       }
+    };
+    long long r = static_cast<long long>(blockIdx.x) * rpi + rl;
+    // two rows per iteration: all loads of both rows are issued before either is consumed
+    for (; r + stride < rows; r += 2 * stride) {
+      float ga[8], gb[8], ya[8], yb[8], za[8], zb[8], y1a[8], y1b[8];
+      load8(dz + r * C + c0, ga);
+      load8(dz + (r + stride) * C + c0, gb);
+      load8(b0.y + r * C + c0, ya);
+      load8(b0.y + (r + stride) * C + c0, yb);
+      if (MASK == 1) {
+        load8(z + r * C + c0, za);
+        load8(z + (r + stride) * C + c0, zb);
+      }
+      if (NB == 2) {
+        load8(b1.y + r * C + c0, y1a);
+        load8(b1.y + (r + stride) * C + c0, y1b);
+      }
+      body(r, ga, ya, za, y1a);
+      body(r + stride, gb, yb, zb, y1b);
+    }
+    for (; r < rows; r += stride) {
+      float ga[8], ya[8], za[8], y1a[8];
+      load8(dz + r * C + c0, ga);
+      load8(b0.y + r * C + c0, ya);
+      if (MASK == 1) load8(z + r * C + c0, za);
+      if (NB == 2) load8(b1.y + r * C + c0, y1a);
+      body(r, ga, ya, za, y1a);
     }
   }
   // block reduction: red[b][v][rl][c]
@@ -259,19 +289,28 @@ __global__ void bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz, 
                                           const float* __restrict__ mscale, const float* __restrict__ mshift,
                                           BnBranchDev b0, BnBranchDev b1, float count_total,
                                           __nv_bfloat16* __restrict__ g_out, long long total8, int C) {
-  extern __shared__ float coef[];      // per branch [4][C]: a = gamma*invstd, mean_g, mean_gx, (mean, invstd packed later)
+  // dy = gamma*invstd * (g - mean_g - xhat*mean_gx), xhat = (y - mean)*invstd, folded per channel into
+  // dy = a*g + k1*y + k0.  Shared layout: per branch [a | k1 | k0] (C floats each), then [mscale | mshift].
+  extern __shared__ float coef[];
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
       const BnBranchDev& br = b == 0 ? b0 : b1;
       float* cf = coef + b * 3 * C;
-      cf[c] = br.gamma[c] * br.invstd[c];
-      cf[C + c] = br.totals[c] / count_total;
-      cf[2 * C + c] = br.totals[C + c] / count_total;
+      const float is = br.invstd[c], mu = br.mean[c];
+      const float a = br.gamma[c] * is;
+      const float mg = br.totals[c] / count_total, mgx = br.totals[C + c] / count_total;
+      cf[c] = a;
+      cf[C + c] = -a * mgx * is;
+      cf[2 * C + c] = a * (mgx * is * mu - mg);
       if (blockIdx.x == 0 && br.dgamma != nullptr) {
         br.dbeta[c] += br.sums[c];
         br.dgamma[c] += br.sums[C + c];
       }
+    }
+    if (MASK == 2) {
+      coef[NB * 3 * C + c] = mscale[c];
+      coef[NB * 3 * C + C + c] = mshift[c];
     }
   }
   __syncthreads();
@@ -279,7 +318,7 @@ __global__ void bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz, 
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total8;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int c0 = static_cast<int>(i % groups) * 8;
-    float gv[8], y0[8], o[8];
+    float gv[8], y0[8], o[8], ka[8], k1[8], k0[8];
     load8(dz + i * 8, gv);
     load8(b0.y + i * 8, y0);
     if (MASK == 1) {
@@ -288,27 +327,26 @@ __global__ void bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz, 
 #pragma unroll
       for (int j = 0; j < 8; ++j) gv[j] = zv[j] > 0.f ? gv[j] : 0.f;
     } else if (MASK == 2) {
+      lds8(coef + NB * 3 * C + c0, ka);
+      lds8(coef + NB * 3 * C + C + c0, k1);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) gv[j] = fmaf(y0[j], __ldg(mscale + c0 + j), __ldg(mshift + c0 + j)) > 0.f ? gv[j] : 0.f;
+      for (int j = 0; j < 8; ++j) gv[j] = fmaf(y0[j], ka[j], k1[j]) > 0.f ? gv[j] : 0.f;
     }
     if (g_out != nullptr) store8(g_out + i * 8, gv);
+    lds8(coef + c0, ka);
+    lds8(coef + C + c0, k1);
+    lds8(coef + 2 * C + c0, k0);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = c0 + j;
-      const float xhat = (y0[j] - __ldg(b0.mean + c)) * __ldg(b0.invstd + c);
-      o[j] = coef[c] * (gv[j] - coef[C + c] - xhat * coef[2 * C + c]);
-    }
+    for (int j = 0; j < 8; ++j) o[j] = fmaf(ka[j], gv[j], fmaf(k1[j], y0[j], k0[j]));
     store8(b0.dy + i * 8, o);
     if (NB == 2) {
       float y1[8];
       load8(b1.y + i * 8, y1);
-      const float* cf = coef + 3 * C;
+      lds8(coef + 3 * C + c0, ka);
+      lds8(coef + 4 * C + c0, k1);
+      lds8(coef + 5 * C + c0, k0);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int c = c0 + j;
-        const float xhat = (y1[j] - __ldg(b1.mean + c)) * __ldg(b1.invstd + c);
-        o[j] = cf[c] * (gv[j] - cf[C + c] - xhat * cf[2 * C + c]);
-      }
+      for (int j = 0; j < 8; ++j) o[j] = fmaf(ka[j], gv[j], fmaf(k1[j], y1[j], k0[j]));
       store8(b1.dy + i * 8, o);
     }
   }
@@ -371,11 +409,11 @@ extern "C" PMD_API int pmd_bn_apply(const void* d_y, const float* d_scale, const
   const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(d_res);
   __nv_bfloat16* z = static_cast<__nv_bfloat16*>(d_z);
   if (d_res == nullptr)
-    bn_apply_kernel<0><<<grid, kBlock, 0, st>>>(y, d_scale, d_shift, nullptr, nullptr, nullptr, relu, z, total8, C);
+    bn_apply_kernel<0><<<grid, kBlock, 2 * C * 4, st>>>(y, d_scale, d_shift, nullptr, nullptr, nullptr, relu, z, total8, C);
   else if (d_res_scale == nullptr)
-    bn_apply_kernel<1><<<grid, kBlock, 0, st>>>(y, d_scale, d_shift, res, nullptr, nullptr, relu, z, total8, C);
+    bn_apply_kernel<1><<<grid, kBlock, 2 * C * 4, st>>>(y, d_scale, d_shift, res, nullptr, nullptr, relu, z, total8, C);
   else
-    bn_apply_kernel<2><<<grid, kBlock, 0, st>>>(y, d_scale, d_shift, res, d_res_scale, d_res_shift, relu, z, total8, C);
+    bn_apply_kernel<2><<<grid, kBlock, 4 * C * 4, st>>>(y, d_scale, d_shift, res, d_res_scale, d_res_shift, relu, z, total8, C);
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
@@ -402,10 +440,24 @@ static void launch_reduce(int mask, int grid, int smem, cudaStream_t st, const _
   if (mask == 1) bn_bwd_reduce_multi_kernel<NB, 1><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
   if (mask == 2) bn_bwd_reduce_multi_kernel<NB, 2><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
 }
+template <int NB, int MASK>
+static void allow_big_smem() {
+  static bool once = false;
+  if (!once) {
+    cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, MASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    once = true;
+  }
+}
+
 template <int NB>
 static void launch_apply(int mask, int grid, int smem, cudaStream_t st, const __nv_bfloat16* dz, const __nv_bfloat16* z,
                          const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, float count,
                          __nv_bfloat16* g_out, long long total8, int C) {
+  if (smem > 48 * 1024) {
+    allow_big_smem<NB, 0>();
+    allow_big_smem<NB, 1>();
+    allow_big_smem<NB, 2>();
+  }
   if (mask == 0) bn_bwd_apply_multi_kernel<NB, 0><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, count, g_out, total8, C);
   if (mask == 1) bn_bwd_apply_multi_kernel<NB, 1><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, count, g_out, total8, C);
   if (mask == 2) bn_bwd_apply_multi_kernel<NB, 2><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, count, g_out, total8, C);
@@ -443,7 +495,7 @@ extern "C" PMD_API int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z,
   const long long total8 = rows * C / 8;
   const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
   const int grid = grid_for(total8, kBlock * 2);
-  const int smem = nb * 3 * C * 4;
+  const int smem = (nb * 3 + 2) * C * 4;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
   const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);

@@ -240,6 +240,96 @@ __global__ void bn_finalize_sync_kernel(PmdSym s, int slot, unsigned long long s
   }
 }
 
+// ------------------------------------------------------------------ push ("LL") exchange for tiny vectors
+// The flag-barrier + peer-load exchange above costs two NVLink round trips.  For the <= 16 KB SyncBatchNorm
+// vectors a push protocol needs one one-way trip: every rank STORES its n floats into every peer's receive
+// area as 8-byte words {value, epoch}; a word is valid exactly when its epoch half matches, so data and flag
+// arrive in one transaction and receivers poll local memory only.  Receive area (per exchange, in every
+// heap): uint2 [2 parities][world][n]; the parity alternates per use, so a fast rank that is already one use
+// ahead never overwrites words a slow rank is still waiting for.
+__device__ __forceinline__ void st_ll(uint2* p, float v, uint32_t epoch) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
+}
+__device__ __forceinline__ float poll_ll(const uint2* p, uint32_t epoch, int rank, int src, int slot) {
+  uint32_t v, f;
+  const unsigned long long t0 = globaltimer_ns();
+  uint32_t spins = 0;
+  for (;;) {
+    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(f) : "l"(p) : "memory");
+    if (f == epoch) break;
+    if (((++spins) & 0xfff) == 0 && globaltimer_ns() - t0 > 30000000000ULL) {
+      printf("pmdist: rank %d timed out waiting for rank %d's data (slot %d, epoch %u, saw %u)\n", rank, src, slot, epoch,
+             f);
+      __trap();
+    }
+  }
+  return __uint_as_float(v);
+}
+
+// Every thread of the (single) block calls this; returns with sum_s[0..n) = rank-ordered total in shared memory.
+__device__ void ll_exchange_sum(const PmdSym& s, int slot, const float* local, int n, unsigned long long recv_off,
+                                float* sum_s) {
+  __shared__ uint32_t epoch_s;
+  if (threadIdx.x == 0) {
+    uint32_t* ep = epoch_ptr(s, slot);
+    const uint32_t e = *ep + 1;
+    *ep = e;
+    epoch_s = e;
+  }
+  __syncthreads();
+  const uint32_t epoch = epoch_s;
+  const int parity = epoch & 1;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float v = local[i];
+    for (int w = 0; w < s.world; ++w) {
+      if (w == s.rank) continue;
+      uint2* dst = heap_ptr<uint2>(s, w, recv_off) + (static_cast<long long>(parity) * s.world + s.rank) * n + i;
+      st_ll(dst, v, epoch);
+    }
+  }
+  const uint2* mine = heap_ptr<const uint2>(s, s.rank, recv_off) + static_cast<long long>(parity) * s.world * n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    float acc = 0.f;
+    for (int w = 0; w < s.world; ++w)      // rank order: identical bits on every rank
+      acc += (w == s.rank) ? local[i] : poll_ll(mine + static_cast<long long>(w) * n + i, epoch, s.rank, w, slot);
+    sum_s[i] = acc;
+  }
+  __syncthreads();
+}
+
+__global__ void bn_finalize_push_kernel(PmdSym s, int slot, const float* __restrict__ stats, unsigned long long recv_off,
+                                        float count_per_rank, int C, const float* __restrict__ gamma,
+                                        const float* __restrict__ beta, float* running_mean, float* running_var,
+                                        long long* num_batches, float momentum, float eps, float* scale, float* shift,
+                                        float* save_mean, float* save_invstd) {
+  extern __shared__ float tot[];     // [2C]
+  ll_exchange_sum(s, slot, stats, 2 * C, recv_off, tot);
+  if (threadIdx.x == 0 && num_batches != nullptr) *num_batches += 1;
+  const float n = count_per_rank * s.world;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float mean = tot[c] / n;
+    const float var = fmaxf(tot[C + c] / n - mean * mean, 0.f);
+    const float invstd = rsqrtf(var + eps);
+    const float a = gamma[c] * invstd;
+    scale[c] = a;
+    shift[c] = beta[c] - mean * a;
+    save_mean[c] = mean;
+    save_invstd[c] = invstd;
+    if (running_mean != nullptr) {
+      const float unbiased = var * (n / fmaxf(n - 1.f, 1.f));
+      running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+    }
+  }
+}
+
+__global__ void small_allreduce_push_kernel(PmdSym s, int slot, const float* __restrict__ local, int n,
+                                            unsigned long long recv_off, float* total) {
+  extern __shared__ float tot[];
+  ll_exchange_sum(s, slot, local, n, recv_off, tot);
+  for (int i = threadIdx.x; i < n; i += blockDim.x) total[i] = tot[i];
+}
+
 __global__ void small_allreduce_sync_kernel(PmdSym s, int slot, unsigned long long off, int n, float* total) {
   rank_barrier(s, slot, false);
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
@@ -370,6 +460,32 @@ extern "C" PMD_API int pmd_metric_allreduce(const PmdSym* sym, int slot, unsigne
                                             void* stream) {
   SYM_CHECK(sym);
   metric_allreduce_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(*sym, slot, off, d_total);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_bn_finalize_push(const PmdSym* sym, int slot, const float* d_stats, unsigned long long recv_off,
+                                            float count_per_rank, int C, const float* d_gamma, const float* d_beta,
+                                            float* d_running_mean, float* d_running_var, long long* d_num_batches,
+                                            float momentum, float eps, float* d_scale, float* d_shift, float* d_mean,
+                                            float* d_invstd, void* stream) {
+  SYM_CHECK(sym);
+  PMD_REQUIRE(2 * C * 4 <= 48 * 1024, "too many channels for the push exchange");
+  bn_finalize_push_kernel<<<1, 512, 2 * C * 4, static_cast<cudaStream_t>(stream)>>>(
+      *sym, slot, d_stats, recv_off, count_per_rank, C, d_gamma, d_beta, d_running_mean, d_running_var, d_num_batches,
+      momentum, eps, d_scale, d_shift, d_mean, d_invstd);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_small_allreduce_push(const PmdSym* sym, int slot, const float* d_local, int n,
+                                                unsigned long long recv_off, float* d_total, void* stream) {
+  SYM_CHECK(sym);
+  PMD_REQUIRE(n * 4 <= 48 * 1024, "vector too long for the push exchange");
+  small_allreduce_push_kernel<<<1, 512, n * 4, static_cast<cudaStream_t>(stream)>>>(*sym, slot, d_local, n, recv_off,
+                                                                                  d_total);
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

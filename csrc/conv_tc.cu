@@ -896,8 +896,10 @@ static int launch_conv_gemm_persistent_t(const ConvGemmParams& p, cudaStream_t s
 
 int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream) {
   const dim3 grid(p.tiles_w * p.tiles_h * p.tiles_n, p.out_channels / p.bn_tile, p.n_classes);
-  static const int st64 = stages_from_env("PMD_GEMM64_STAGES", 3), st128 = stages_from_env("PMD_GEMM128_STAGES", 2);
-  static const bool persistent = getenv("PMD_GEMM_PERSISTENT") == nullptr || atoi(getenv("PMD_GEMM_PERSISTENT")) != 0;
+  // Measured on B200 (profiles/r1_conv_variants.md): one tile per CTA with 2 resident CTAs per SM beats the
+  // persistent double-buffered variant on these shapes, so the latter is opt-in (PMD_GEMM_PERSISTENT=1).
+  static const int st64 = stages_from_env("PMD_GEMM64_STAGES", 2), st128 = stages_from_env("PMD_GEMM128_STAGES", 3);
+  static const bool persistent = getenv("PMD_GEMM_PERSISTENT") != nullptr && atoi(getenv("PMD_GEMM_PERSISTENT")) != 0;
   int rc;
   if (persistent) {
     if (p.bn_tile == 64)

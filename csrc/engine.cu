@@ -43,6 +43,7 @@ struct Conv {
   float *scale = nullptr, *shift = nullptr, *mean = nullptr, *invstd = nullptr;
   float *stats = nullptr, *sums = nullptr, *sums_total = nullptr;
   unsigned long long stats_off = 0, sums_off = 0;
+  unsigned long long recv_fwd_off = 0, recv_bwd_off = 0;   // push-exchange receive areas (multi-rank SyncBN)
   const float** tab_stats = nullptr;   // device: 1-entry pointer tables for the local-statistics path
   const float** tab_sums = nullptr;
   const float** tab_total = nullptr;
@@ -200,6 +201,15 @@ int allocate(PmdEngine* e) {
   for (Conv& cv : e->convs) part += 4LL * cv.s.K * 4;   // stats[2K] + sums[2K]
   e->bnpart_bytes = part;
   E_CHECK(e->halloc(&e->bnpart_off, part));
+  if (e->sym.world > 1 && c.sync_bn) {
+    for (Conv& cv : e->convs) {
+      const unsigned long long bytes = PMD_LL_RECV_BYTES(e->sym.world, 2 * cv.s.K);
+      E_CHECK(e->halloc(&cv.recv_fwd_off, bytes));
+      E_CHECK(e->halloc(&cv.recv_bwd_off, bytes));
+      PMD_CHECK_CUDA(cudaMemset(e->hptr<char>(cv.recv_fwd_off), 0, bytes));
+      PMD_CHECK_CUDA(cudaMemset(e->hptr<char>(cv.recv_bwd_off), 0, bytes));
+    }
+  }
   e->param = e->hptr<float>(e->param_off);
   e->grad = e->hptr<float>(e->grad_off);
   e->mom = e->hptr<float>(e->mom_off);
@@ -410,9 +420,9 @@ int bn_forward(PmdEngine* e, int ci, long long rows, cudaStream_t st) {
   Conv& cv = e->convs[ci];
   const PmdEngineConfig& c = e->cfg;
   if (e->sym.world > 1 && c.sync_bn)
-    return pmd_bn_finalize_sync(&e->sym, ci, cv.stats_off, static_cast<float>(rows), cv.s.K, e->param + cv.g_off,
-                                e->param + cv.b_off, cv.rm, cv.rv, cv.nb, c.bn_momentum, c.bn_eps, cv.scale, cv.shift,
-                                cv.mean, cv.invstd, st);
+    return pmd_bn_finalize_push(&e->sym, ci, cv.stats, cv.recv_fwd_off, static_cast<float>(rows), cv.s.K,
+                                e->param + cv.g_off, e->param + cv.b_off, cv.rm, cv.rv, cv.nb, c.bn_momentum, c.bn_eps,
+                                cv.scale, cv.shift, cv.mean, cv.invstd, st);
   return pmd_bn_finalize(cv.tab_stats, 1, static_cast<float>(rows), cv.s.K, e->param + cv.g_off, e->param + cv.b_off,
                          cv.rm, cv.rv, cv.nb, c.bn_momentum, c.bn_eps, cv.scale, cv.shift, cv.mean, cv.invstd, st);
 }
@@ -445,8 +455,8 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
   if (sync) {
     for (int b = 0; b < nb; ++b) {
       Conv& cv = e->convs[idx[b]];
-      E_CHECK(pmd_small_allreduce_sync(&e->sym, static_cast<int>(e->convs.size()) + idx[b], cv.sums_off, 2 * cv.s.K,
-                                       cv.sums_total, st));
+      E_CHECK(pmd_small_allreduce_push(&e->sym, static_cast<int>(e->convs.size()) + idx[b], cv.sums, 2 * cv.s.K,
+                                       cv.recv_bwd_off, cv.sums_total, st));
     }
     total_rows *= e->sym.world;
   }

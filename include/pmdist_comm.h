@@ -115,6 +115,17 @@ int pmd_bn_finalize_sync(const PmdSym* sym, int slot, unsigned long long stats_o
                          float* d_mean, float* d_invstd, void* stream);
 int pmd_small_allreduce_sync(const PmdSym* sym, int slot, unsigned long long off, int n, float* d_total,
                              void* stream);
+/* Push ("LL") forms of the two exchanges above: one one-way NVLink trip instead of two round trips.  Every rank
+ * stores its vector into every peer's receive area as {value, epoch} words and polls only its own memory.
+ * recv_off: heap offset (same on every rank) of a zero-initialised area of PMD_LL_RECV_BYTES(world, n) bytes
+ * that belongs to this exchange alone; d_stats / d_local may be any device pointer of this rank. */
+#define PMD_LL_RECV_BYTES(world, n) (2ull * (world) * (n) * 8ull)
+int pmd_bn_finalize_push(const PmdSym* sym, int slot, const float* d_stats, unsigned long long recv_off,
+                         float count_per_rank, int C, const float* d_gamma, const float* d_beta, float* d_running_mean,
+                         float* d_running_var, long long* d_num_batches, float momentum, float eps, float* d_scale,
+                         float* d_shift, float* d_mean, float* d_invstd, void* stream);
+int pmd_small_allreduce_push(const PmdSym* sym, int slot, const float* d_local, int n, unsigned long long recv_off,
+                             float* d_total, void* stream);
 /* metrics: double[4] at heap offset `off` on every rank -> d_total (local) = sum over ranks. */
 int pmd_metric_allreduce(const PmdSym* sym, int slot, unsigned long long off, double* d_total, void* stream);
 

@@ -53,8 +53,8 @@ class PmdEngineBuffers(C.Structure):
 
 
 def heap_bytes_for(num_params: int) -> int:
-    """fp32 param + grad + momentum, bf16 copy, BN partials, scratch."""
-    return int(num_params * 14 * 1.02) + 48 * MiB
+    """fp32 param + grad + momentum, bf16 copy, BN partials, SyncBN push-exchange receive areas, scratch."""
+    return int(num_params * 14 * 1.02) + 96 * MiB
 
 
 def _arr(ctype, values):
