@@ -59,6 +59,20 @@ if os.environ.get('REF_SHIM') == '1':
     except Exception as _e:      # torchvision missing: the reference cannot run anyway
         sys.stderr.write('ref shim: could not install the synthetic CIFAR10: %r\n' % (_e,))
 
+    if os.environ.get('REF_GLOBAL_POOL') == '1':
+        # BASELINE.json config 4 (224x224): the reference head is F.avg_pool2d(out, 4) + Linear(512*expansion, 10)
+        # (ref:model/resnet.py:102-104) and raises on anything but a 4x4 final map.  The labelled variant used
+        # for that config only: pool over the whole remaining map (identical at 32x32).  SURVEY.md 7.5.
+        import torch.nn.functional as _F
+        _avg = _F.avg_pool2d
+
+        def _avg_pool2d(x, kernel_size, *a, **k):
+            if kernel_size == 4 and x.dim() == 4 and x.shape[-1] != 4:
+                return _F.adaptive_avg_pool2d(x, 1)
+            return _avg(x, kernel_size, *a, **k)
+
+        _F.avg_pool2d = _avg_pool2d
+
     if os.environ.get('REF_CPU') == '1':
         import torch
         import torch.distributed as dist

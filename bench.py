@@ -43,7 +43,7 @@ class ClockSampler:
                0x0000000000000080: 'hw_power_brake_slowdown', 0x0000000000000002: 'applications_clocks_setting',
                0x0000000000000010: 'sync_boost', 0x0000000000000100: 'display_clock_setting'}
 
-    def __init__(self, index: int, period: float = 0.1) -> None:
+    def __init__(self, index: int, period: float = 0.005) -> None:
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self._stop = threading.Event()
@@ -173,7 +173,7 @@ def run_native(a) -> None:
             'config': {'model': f'CIFAR ResNet{depth} from model/resnet.py (ResNet18 = [1,1,1,1] blocks)',
                        'global_batch': gb, 'per_gpu_batch': B, 'seq_len': None, 'image': f'{a.image_size}x{a.image_size}',
                        'parallelism': f'dp{world}', 'sync_bn': True, 'optimizer': 'SGD-Nesterov lr0.1 m0.9 wd1e-4',
-                       'grad_allreduce': eng.algo, 'transport': comm.describe(), 'cuda_graph': not a.no_graph,
+                       'grad_allreduce': eng.algo, 'grad_allreduce_choice': eng.algo_source, 'transport': comm.describe(), 'cuda_graph': not a.no_graph,
                        'l2': 'no flush: per-step working set (~2.7 MB/image of activations+gradients) exceeds the 126 MB L2',
                        'weights': 'random init'},
             'clocks': clk.summary(),
@@ -223,6 +223,12 @@ def run_reference(a) -> None:
     env.update({'REF_SHIM': '1', 'PYTHONPATH': os.path.join(ROOT, 'baseline', 'shim') + os.pathsep + env.get('PYTHONPATH', ''),
                 'REF_TRAIN_SIZE': str(gb * (W + K)), 'REF_TEST_SIZE': str(gb), 'REF_IMAGE_SIZE': str(a.image_size),
                 'REF_TIMING_OUT': os.path.join(work, 'timing')})
+    if a.image_size != 32:
+        env['REF_GLOBAL_POOL'] = '1'      # labelled variant: the reference head cannot take non-32x32 inputs
+    if a.model not in ('res', 'res18'):
+        print(json.dumps({'impl': 'reference', 'unavailable':
+                          "the reference's main.py only builds ResNet18 (--model res, ref:main.py:39-40)"}))
+        return
     cmd = [sys.executable, ref_main, '--batch_size', str(gb), '--epochs', '1', '--world_size', str(N),
            '--save_path', os.path.join(work, 'out') + '/', '--print-freq', '1000']
     local = int(os.environ.get('LOCAL_RANK', '0'))

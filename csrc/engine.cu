@@ -87,6 +87,7 @@ struct PmdEngine {
   std::vector<Block> blocks;
   std::vector<long long> bucket_start, bucket_numel;
   std::vector<int> bucket_params;     // number of parameter tensors per bucket
+  std::vector<int> bucket_algo, bucket_blocks;
   int sm_count = 148;
   // slabs (symmetric heap)
   unsigned long long param_off = 0, grad_off = 0, mom_off = 0, bf16_off = 0, metrics_off = 0, bnpart_off = 0;
@@ -406,8 +407,8 @@ struct BucketTracker {
     a.momentum = e->cfg.momentum;
     a.weight_decay = e->cfg.weight_decay;
     a.nesterov = e->cfg.nesterov;
-    a.algo = e->cfg.algo;
-    a.blocks = e->sym.world == 1 ? 4 * e->sm_count : e->cfg.comm_blocks;
+    a.algo = e->bucket_algo[bkt];
+    a.blocks = e->sym.world == 1 ? 4 * e->sm_count : e->bucket_blocks[bkt];
     a.d_lr = e->d_lr;
     const int slot = 2 * static_cast<int>(e->convs.size()) + 8 + bkt * 128;
     E_CHECK(pmd_allreduce_sgd(&e->sym, &a, slot, e->comm_stream));
@@ -642,6 +643,10 @@ extern "C" PMD_API int pmd_engine_create(const PmdEngineConfig* cfg, PmdComm* co
   cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, e->info.device);
   e->bucket_start.assign(cfg->bucket_start, cfg->bucket_start + cfg->n_buckets);
   e->bucket_numel.assign(cfg->bucket_numel, cfg->bucket_numel + cfg->n_buckets);
+  e->bucket_algo.assign(cfg->n_buckets, cfg->algo);
+  e->bucket_blocks.assign(cfg->n_buckets, cfg->comm_blocks);
+  if (cfg->bucket_algo != nullptr) e->bucket_algo.assign(cfg->bucket_algo, cfg->bucket_algo + cfg->n_buckets);
+  if (cfg->bucket_blocks != nullptr) e->bucket_blocks.assign(cfg->bucket_blocks, cfg->bucket_blocks + cfg->n_buckets);
   PMD_REQUIRE(cfg->n_buckets >= 1 && 2 * cfg->n_convs + 8 + cfg->n_buckets * 128 + 200 < PMD_MAX_SLOTS,
               "too many gradient buckets for the signal pad (raise --bucket-mb)");
   E_CHECK(build_topology(e));
@@ -657,6 +662,7 @@ extern "C" PMD_API int pmd_engine_create(const PmdEngineConfig* cfg, PmdComm* co
   // copy the offset tables: the caller's arrays need not outlive this call
   e->cfg.conv_w_off = e->cfg.bn_g_off = e->cfg.bn_b_off = nullptr;
   e->cfg.bucket_start = e->cfg.bucket_numel = nullptr;
+  e->cfg.bucket_algo = e->cfg.bucket_blocks = nullptr;
   PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
   PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->main_stream, cudaStreamNonBlocking));
   PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->wg_stream, cudaStreamNonBlocking));

@@ -53,6 +53,9 @@ typedef struct {
   int use_graph; /* capture steps into CUDA graphs */
   int algo;      /* PMD_ALGO_* for the gradient buckets */
   int comm_blocks;
+  /* optional per-bucket overrides chosen from the measured all-reduce table (NULL = algo / comm_blocks) */
+  const int* bucket_algo;
+  const int* bucket_blocks;
 } PmdEngineConfig;
 
 typedef struct {

@@ -42,6 +42,7 @@ class PmdEngineConfig(C.Structure):
         ('momentum', C.c_float), ('weight_decay', C.c_float), ('nesterov', C.c_int),
         ('bn_momentum', C.c_float), ('bn_eps', C.c_float),
         ('sync_bn', C.c_int), ('use_graph', C.c_int), ('algo', C.c_int), ('comm_blocks', C.c_int),
+        ('bucket_algo', C.POINTER(C.c_int)), ('bucket_blocks', C.POINTER(C.c_int)),
     ]
 
 
@@ -145,12 +146,17 @@ class NativeEngine:
         cfg.momentum, cfg.weight_decay, cfg.nesterov = sgd.momentum, sgd.weight_decay, int(sgd.nesterov)
         cfg.bn_momentum, cfg.bn_eps = 0.1, 1e-5
         cfg.sync_bn, cfg.use_graph = int(sync_bn), int(use_graph)
-        if algo == 'auto':
-            algo = 'nvls' if comm.info.multicast_mapped else 'twoshot'
         if algo == 'nccl':
             raise ValueError("--algo nccl belongs to --engine host (the NCCL baseline path)")
-        self.algo = algo
-        cfg.algo, cfg.comm_blocks = ALGOS[algo], comm_blocks
+        if algo == 'nvls' and not comm.info.multicast_mapped:
+            algo = 'twoshot'
+        from .tuning import choose_bucket_algos
+        self.bucket_algos, self.bucket_blocks, self.algo_source = choose_bucket_algos(
+            comm.world_size, [nn_ * 4 for nn_ in numels], bool(comm.info.multicast_mapped), algo, comm_blocks)
+        self.algo = '+'.join(sorted(set(self.bucket_algos)))
+        cfg.algo, cfg.comm_blocks = ALGOS[self.bucket_algos[0]], comm_blocks
+        cfg.bucket_algo = arr(C.c_int, [ALGOS[a_] for a_ in self.bucket_algos])
+        cfg.bucket_blocks = arr(C.c_int, [min(int(b_), 128) for b_ in self.bucket_blocks])
         self._h = C.c_void_p()
         check(self.lib.pmd_engine_create(C.byref(cfg), comm.handle, C.byref(self._h)))
         bufs = PmdEngineBuffers()
@@ -249,11 +255,13 @@ class NativeEngine:
         bucket current; collect the live slices from the peers' heaps (collective: all ranks call)."""
         w = self.comm.world_size
         m = self.flat_m.clone()
-        if w == 1 or self.algo == 'oneshot':
+        if w == 1 or all(a == 'oneshot' for a in self.bucket_algos):
             return m
         self.comm.barrier()
         mom_off = self.bufs.mom - self.comm.info.local_base
-        for b in self.buckets:
+        for b, b_algo in zip(self.buckets, self.bucket_algos):
+            if b_algo == 'oneshot':
+                continue            # every rank updated the whole bucket: momentum is replicated
             n4 = ((b.numel + ALIGN - 1) // ALIGN * ALIGN) // 4
             per = (n4 + w - 1) // w
             for r in range(w):

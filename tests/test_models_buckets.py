@@ -107,3 +107,22 @@ def test_reference_written_checkpoint_loads(tmp_path, ref_modules):
     mpth, spth, e = ckpt.find_resume(str(tmp_path))
     assert e == 20 and spth is None
     ResNet18().load_state_dict(ckpt.load_model(mpth))
+
+
+def test_bucket_algorithm_selector_uses_measured_table(tmp_path, monkeypatch):
+    import json
+    from pmdist.parallel.tuning import AllreduceTable, choose_bucket_algos
+    rows = [{'bytes': 4096, 'oneshot_b8_us': 5.0, 'twoshot_b8_us': 7.0, 'nvls_b8_us': 6.0, 'nccl_us': 20.0},
+            {'bytes': 16 << 20, 'oneshot_b96_us': 90.0, 'twoshot_b96_us': 50.0, 'nvls_b96_us': 40.0, 'nccl_us': 55.0}]
+    path = tmp_path / 'allreduce_w8.json'
+    path.write_text(json.dumps({'world': 8, 'rows': rows}))
+    monkeypatch.setenv('PMDIST_ALLREDUCE_TABLE', str(path))
+    algos, blocks, why = choose_bucket_algos(8, [2048, 10 << 20], multicast=True)
+    assert algos == ['oneshot', 'nvls'] and blocks == [8, 96] and 'measured' in why
+    algos, _, _ = choose_bucket_algos(8, [2048, 10 << 20], multicast=False)        # no NVLS on this host
+    assert algos == ['oneshot', 'twoshot']
+    assert choose_bucket_algos(8, [1 << 20], True, forced='twoshot')[0] == ['twoshot']
+    assert choose_bucket_algos(1, [1 << 20], True)[0] == ['oneshot']
+    monkeypatch.delenv('PMDIST_ALLREDUCE_TABLE')
+    assert AllreduceTable.load(7) is None
+    assert choose_bucket_algos(7, [1024, 64 << 20], True)[0] == ['oneshot', 'nvls']     # heuristic fallback
