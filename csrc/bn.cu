@@ -143,33 +143,46 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float
   }
   __syncthreads();
   const int groups = C / 8;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total8;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+  const long long T = static_cast<long long>(gridDim.x) * blockDim.x;
+  auto one = [&](long long i, const float (&v)[8], const float (&rv)[8]) {
     const int c0 = static_cast<int>(i % groups) * 8;
-    float v[8], o[8], sc[8], sh[8];
-    load8(y + i * 8, v);
+    float o[8], sc[8], sh[8];
     lds8(aff + c0, sc);
     lds8(aff + C + c0, sh);
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = fmaf(v[j], sc[j], sh[j]);
-    if (RES != 0) {
-      float rv[8];
-      load8(res + i * 8, rv);
-      if (RES == 2) {
-        lds8(aff + 2 * C + c0, sc);
-        lds8(aff + 3 * C + c0, sh);
+    if (RES == 2) {
+      lds8(aff + 2 * C + c0, sc);
+      lds8(aff + 3 * C + c0, sh);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], sc[j], sh[j]);
-      } else {
+      for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], sc[j], sh[j]);
+    } else if (RES == 1) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] += rv[j];
-      }
+      for (int j = 0; j < 8; ++j) o[j] += rv[j];
     }
     if (relu) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], 0.f);
     }
     store8(z + i * 8, o);
+  };
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  for (; i + T < total8; i += 2 * T) {
+    float va[8], vb[8], ra[8], rb[8];
+    load8(y + i * 8, va);
+    load8(y + (i + T) * 8, vb);
+    if (RES != 0) {
+      load8(res + i * 8, ra);
+      load8(res + (i + T) * 8, rb);
+    }
+    one(i, va, ra);
+    one(i + T, vb, rb);
+  }
+  for (; i < total8; i += T) {
+    float va[8], ra[8];
+    load8(y + i * 8, va);
+    if (RES != 0) load8(res + i * 8, ra);
+    one(i, va, ra);
   }
 }
 
@@ -191,55 +204,51 @@ struct BnBranchDev {
 };
 
 template <int NB, int MASK>
-__global__ void bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
-                                           const float* __restrict__ mscale, const float* __restrict__ mshift,
-                                           BnBranchDev b0, BnBranchDev b1, long long rows, int C) {
-  extern __shared__ float red[];
+__global__ void __launch_bounds__(kBlock, 4)
+bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
+                           const float* __restrict__ mscale, const float* __restrict__ mshift, BnBranchDev b0,
+                           BnBranchDev b1, long long rows, int C) {
+  // Accumulates S_g = sum(g) and S_gy = sum(g*y) per channel; sum(g*xhat) = (S_gy - mean*S_g)*invstd is formed
+  // once per block at the end, so the streaming loop carries no per-channel statistics in registers (the
+  // register budget decides how many of these DRAM-bound blocks fit on an SM).
+  extern __shared__ float red[];      // [mask consts 2C] + reduction scratch [(1+NB) * rpi * C]
+  float* msm = red;
+  float* scratch = red + 2 * C;
   const int groups = C / 8;
   const int g = threadIdx.x % groups;
   const int rl = threadIdx.x / groups;
   const int rpi = blockDim.x / groups;
   const int c0 = g * 8;
-  float acc[NB][2][8];
-#pragma unroll
-  for (int b = 0; b < NB; ++b)
-#pragma unroll
-    for (int i = 0; i < 8; ++i) acc[b][0][i] = acc[b][1][i] = 0.f;
-  float mean0[8], is0[8], mean1[8], is1[8], ms[8], mh[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    mean0[i] = b0.mean[c0 + i];
-    is0[i] = b0.invstd[c0 + i];
-    if (NB == 2) {
-      mean1[i] = b1.mean[c0 + i];
-      is1[i] = b1.invstd[c0 + i];
+  if (MASK == 2) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      msm[c] = mscale[c];
+      msm[C + c] = mshift[c];
     }
-    if (MASK == 2) {
-      ms[i] = mscale[c0 + i];
-      mh[i] = mshift[c0 + i];
-    }
+    __syncthreads();
   }
+  float sg[8], sgy0[8], sgy1[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) sg[i] = sgy0[i] = sgy1[i] = 0.f;
   if (rl < rpi) {
     const long long stride = static_cast<long long>(gridDim.x) * rpi;
-    auto body = [&](long long r, const float (&gin)[8], const float (&y0)[8], const float (&zin)[8],
-                    const float (&y1)[8]) {
-      float gv[8];
+    auto body = [&](const float (&gin)[8], const float (&y0)[8], const float (&zin)[8], const float (&y1)[8]) {
+      float ms[8], mh[8];
+      if (MASK == 2) {
+        lds8(msm + c0, ms);
+        lds8(msm + C + c0, mh);
+      }
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        gv[i] = gin[i];
-        if (MASK == 1) gv[i] = zin[i] > 0.f ? gv[i] : 0.f;
-        if (MASK == 2) gv[i] = fmaf(y0[i], ms[i], mh[i]) > 0.f ? gv[i] : 0.f;
-        acc[0][0][i] += gv[i];
-        acc[0][1][i] += gv[i] * (y0[i] - mean0[i]) * is0[i];
-        if (NB == 2) {
-          acc[1][0][i] += gv[i];
-          acc[1][1][i] += gv[i] * (y1[i] - mean1[i]) * is1[i];
-        }
+        float gv = gin[i];
+        if (MASK == 1) gv = zin[i] > 0.f ? gv : 0.f;
+        if (MASK == 2) gv = fmaf(y0[i], ms[i], mh[i]) > 0.f ? gv : 0.f;
+        sg[i] += gv;
+        sgy0[i] = fmaf(gv, y0[i], sgy0[i]);
+        if (NB == 2) sgy1[i] = fmaf(gv, y1[i], sgy1[i]);
       }
     };
     long long r = static_cast<long long>(blockIdx.x) * rpi + rl;
-    // two rows per iteration: all loads of both rows are issued before either is consumed
-    for (; r + stride < rows; r += 2 * stride) {
+    for (; r + stride < rows; r += 2 * stride) {   // two rows in flight per thread
       float ga[8], gb[8], ya[8], yb[8], za[8], zb[8], y1a[8], y1b[8];
       load8(dz + r * C + c0, ga);
       load8(dz + (r + stride) * C + c0, gb);
@@ -253,8 +262,8 @@ __global__ void bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz,
         load8(b1.y + r * C + c0, y1a);
         load8(b1.y + (r + stride) * C + c0, y1b);
       }
-      body(r, ga, ya, za, y1a);
-      body(r + stride, gb, yb, zb, y1b);
+      body(ga, ya, za, y1a);
+      body(gb, yb, zb, y1b);
     }
     for (; r < rows; r += stride) {
       float ga[8], ya[8], za[8], y1a[8];
@@ -262,25 +271,30 @@ __global__ void bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz,
       load8(b0.y + r * C + c0, ya);
       if (MASK == 1) load8(z + r * C + c0, za);
       if (NB == 2) load8(b1.y + r * C + c0, y1a);
-      body(r, ga, ya, za, y1a);
+      body(ga, ya, za, y1a);
+    }
+    // block reduction scratch: [v][rl][c], v = 0: S_g, 1: S_gy0, 2: S_gy1
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      scratch[(0 * rpi + rl) * C + c0 + i] = sg[i];
+      scratch[(1 * rpi + rl) * C + c0 + i] = sgy0[i];
+      if (NB == 2) scratch[(2 * rpi + rl) * C + c0 + i] = sgy1[i];
     }
   }
-  // block reduction: red[b][v][rl][c]
-  if (rl < rpi) {
-#pragma unroll
-    for (int b = 0; b < NB; ++b)
-#pragma unroll
-      for (int v = 0; v < 2; ++v)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) red[((b * 2 + v) * rpi + rl) * C + c0 + i] = acc[b][v][i];
-  }
   __syncthreads();
-  for (int idx = threadIdx.x; idx < NB * 2 * C; idx += blockDim.x) {
-    const int c = idx % C, bv = idx / C;
-    float sum = 0.f;
-    for (int j = 0; j < rpi; ++j) sum += red[(bv * rpi + j) * C + c];
-    float* dst = (bv / 2 == 0 ? b0.sums : b1.sums) + (bv % 2) * C + c;
-    red_add_f32(dst, sum);
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float tg = 0.f, t0 = 0.f, t1 = 0.f;
+    for (int j = 0; j < rpi; ++j) {
+      tg += scratch[(0 * rpi + j) * C + c];
+      t0 += scratch[(1 * rpi + j) * C + c];
+      if (NB == 2) t1 += scratch[(2 * rpi + j) * C + c];
+    }
+    red_add_f32(b0.sums + c, tg);
+    red_add_f32(b0.sums + C + c, (t0 - b0.mean[c] * tg) * b0.invstd[c]);
+    if (NB == 2) {
+      red_add_f32(b1.sums + c, tg);
+      red_add_f32(b1.sums + C + c, (t1 - b1.mean[c] * tg) * b1.invstd[c]);
+    }
   }
 }
 
@@ -315,15 +329,11 @@ __global__ void bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz, 
   }
   __syncthreads();
   const int groups = C / 8;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total8;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+  const long long T = static_cast<long long>(gridDim.x) * blockDim.x;
+  auto one = [&](long long i, float (&gv)[8], const float (&y0)[8], const float (&zv)[8], const float (&y1)[8]) {
     const int c0 = static_cast<int>(i % groups) * 8;
-    float gv[8], y0[8], o[8], ka[8], k1[8], k0[8];
-    load8(dz + i * 8, gv);
-    load8(b0.y + i * 8, y0);
+    float o[8], ka[8], k1[8], k0[8];
     if (MASK == 1) {
-      float zv[8];
-      load8(z + i * 8, zv);
 #pragma unroll
       for (int j = 0; j < 8; ++j) gv[j] = zv[j] > 0.f ? gv[j] : 0.f;
     } else if (MASK == 2) {
@@ -340,8 +350,6 @@ __global__ void bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz, 
     for (int j = 0; j < 8; ++j) o[j] = fmaf(ka[j], gv[j], fmaf(k1[j], y0[j], k0[j]));
     store8(b0.dy + i * 8, o);
     if (NB == 2) {
-      float y1[8];
-      load8(b1.y + i * 8, y1);
       lds8(coef + 3 * C + c0, ka);
       lds8(coef + 4 * C + c0, k1);
       lds8(coef + 5 * C + c0, k0);
@@ -349,6 +357,32 @@ __global__ void bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz, 
       for (int j = 0; j < 8; ++j) o[j] = fmaf(ka[j], gv[j], fmaf(k1[j], y1[j], k0[j]));
       store8(b1.dy + i * 8, o);
     }
+  };
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  for (; i + T < total8; i += 2 * T) {     // two 16-byte groups per thread in flight
+    float ga[8], gb[8], ya[8], yb[8], za[8], zb[8], y1a[8], y1b[8];
+    load8(dz + i * 8, ga);
+    load8(dz + (i + T) * 8, gb);
+    load8(b0.y + i * 8, ya);
+    load8(b0.y + (i + T) * 8, yb);
+    if (MASK == 1) {
+      load8(z + i * 8, za);
+      load8(z + (i + T) * 8, zb);
+    }
+    if (NB == 2) {
+      load8(b1.y + i * 8, y1a);
+      load8(b1.y + (i + T) * 8, y1b);
+    }
+    one(i, ga, ya, za, y1a);
+    one(i + T, gb, yb, zb, y1b);
+  }
+  for (; i < total8; i += T) {
+    float ga[8], ya[8], za[8], y1a[8];
+    load8(dz + i * 8, ga);
+    load8(b0.y + i * 8, ya);
+    if (MASK == 1) load8(z + i * 8, za);
+    if (NB == 2) load8(b1.y + i * 8, y1a);
+    one(i, ga, ya, za, y1a);
   }
 }
 
@@ -472,9 +506,9 @@ extern "C" PMD_API int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z
   PMD_REQUIRE(mask_mode != 2 || (d_mask_scale != nullptr && d_mask_shift != nullptr), "mask mode 2 needs the forward affine");
   const int groups = C / 8, rpi = kBlock / groups > 0 ? kBlock / groups : 1;
   PMD_REQUIRE(groups <= kBlock, "C too large for bn_bwd_reduce");
-  const int smem = nb * 2 * rpi * C * 4;
+  const int smem = (2 * C + (1 + nb) * rpi * C) * 4;
   const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
-  const int grid = grid_for(rows, rpi * 4);
+  const int grid = grid_for(rows, rpi * 8);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
   const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);
