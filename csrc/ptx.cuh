@@ -151,10 +151,8 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 //   MN-major operand ([rows = K][64 bf16 of M/N]):  SBO = 1024 B between 8-row (K) groups,
 //            LBO = byte distance between consecutive 64-element chunks along M/N.
 //            One UMMA (K = 16) covers 16 rows: advance the start address by 2048 B per k-step.
-__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
-                                                        uint32_t base_offset = 0) {
-  // base_offset: (start address >> 7) & 7 when the start is not on a 1024-byte swizzle-atom boundary
-  uint64_t d = static_cast<uint64_t>(base_offset & 7u) << 49;
+__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
   d |= static_cast<uint64_t>((saddr >> 4) & 0x3fffu);                 // start address   [0,14)
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3fffu) << 16;       // leading offset  [16,30)
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fffu) << 32;       // stride offset   [32,46)
