@@ -460,6 +460,202 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
   if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
 }
 
+// ============================================================================ fprop / dgrad with column patches
+// For a 3x3 stride-1 convolution the nine per-tap A bricks of a tile overlap almost entirely: fetching each of
+// them separately reads the activations nine times from L2, and ncu shows these kernels sitting at the L2->SM
+// read-bandwidth limit.  Here the CTA's output tile is 8 (w) x 16 (h) pixels and, per 64-channel chunk, THREE TMA
+// boxes of 8 x 18 pixels are loaded -- one per horizontal tap offset s (columns w0+s-1 .. w0+s+6, rows h0-1 ..
+// h0+16).  In such a patch a pixel row is exactly one 8-row swizzle atom (1024 B), so the A operand of tap (r, s)
+// is the ordinary K-major SW128 tile that starts r atoms into patch s: start = patch_s + r * 1024, SBO = 1024.
+// Every start stays 1024-byte aligned (an earlier single-patch variant with 128-byte-shifted starts gave wrong
+// results, see profiles/r1_conv_variants.md).  Activation traffic drops from 9 x 16 KB to 3 x 18 KB per chunk.
+// Weights stream through their own ring, one (chunk, tap) slice per stage.
+template <int A_STAGES, int B_STAGES>
+struct HaloBars {
+  uint64_t a_full[A_STAGES], a_empty[A_STAGES];
+  uint64_t b_full[B_STAGES], b_empty[B_STAGES];
+  uint64_t tmem_full;
+  uint32_t tmem_base;
+};
+constexpr int kColPatchBytes = 8 * 18 * 128;      // 18432: one horizontal offset
+constexpr int kHaloPatchBytes = 3 * kColPatchBytes;  // 55296: all three
+
+template <int BN, int A_STAGES, int B_STAGES>
+__global__ void __launch_bounds__(kThreads) conv_gemm_halo_kernel(const __grid_constant__ ConvHaloParams p) {
+  constexpr int kBBytes = BN * 128;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  uint8_t* smem_b = smem + A_STAGES * kHaloPatchBytes;
+  HaloBars<A_STAGES, B_STAGES>* bars =
+      reinterpret_cast<HaloBars<A_STAGES, B_STAGES>*>(smem_b + B_STAGES * kBBytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ntile = blockIdx.y;
+  int t = blockIdx.x;
+  const int tw = t % p.tiles_w;
+  t /= p.tiles_w;
+  const int th = t % p.tiles_h;
+  const int n0 = t / p.tiles_h;
+  const int w0 = tw * 8, h0 = th * 16;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < A_STAGES; ++s) {
+      mbar_init(&bars->a_full[s], 1);
+      mbar_init(&bars->a_empty[s], 1);
+    }
+#pragma unroll
+    for (int s = 0; s < B_STAGES; ++s) {
+      mbar_init(&bars->b_full[s], 1);
+      mbar_init(&bars->b_empty[s], 1);
+    }
+    mbar_init(&bars->tmem_full, 1);
+    fence_mbar_init();
+    prefetch_tmap(&p.a);
+    prefetch_tmap(&p.b);
+    prefetch_tmap(&p.out);
+  }
+  if (warp == 1) tmem_alloc<BN>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t ib = 0;
+      for (int c = 0; c < p.n_chunks; ++c) {
+        const int sa = c % A_STAGES;
+        mbar_wait(&bars->a_empty[sa], ((c / A_STAGES) & 1) ^ 1u);
+        mbar_expect_tx(&bars->a_full[sa], kHaloPatchBytes);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          tma_load_4d(&p.a, &bars->a_full[sa], smem + sa * kHaloPatchBytes + q * kColPatchBytes, c * 64, w0 + q - 1,
+                      h0 - 1, n0);
+        for (int tap = 0; tap < 9; ++tap, ++ib) {
+          const int sb = ib % B_STAGES;
+          mbar_wait(&bars->b_empty[sb], ((ib / B_STAGES) & 1) ^ 1u);
+          const int wtap = p.flip_taps ? 8 - tap : tap;
+          mbar_expect_tx(&bars->b_full[sb], kBBytes);
+          if (p.b_tap_last)
+            tma_load_3d(&p.b, &bars->b_full[sb], smem_b + sb * kBBytes, c * 64, ntile * BN, wtap);
+          else
+            tma_load_3d(&p.b, &bars->b_full[sb], smem_b + sb * kBBytes, c * 64, wtap, ntile * BN);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, false);
+      uint32_t ib = 0;
+      for (int c = 0; c < p.n_chunks; ++c) {
+        const int sa = c % A_STAGES;
+        mbar_wait(&bars->a_full[sa], (c / A_STAGES) & 1);
+        tc_fence_after();
+        const uint32_t patch = smem_u32(smem + sa * kHaloPatchBytes);
+        for (int tap = 0; tap < 9; ++tap, ++ib) {
+          const int sb = ib % B_STAGES;
+          mbar_wait(&bars->b_full[sb], (ib / B_STAGES) & 1);
+          tc_fence_after();
+          const int r = tap / 3, q = tap % 3;
+          const uint32_t a_addr = patch + q * kColPatchBytes + r * 1024;
+          const uint32_t b_addr = smem_u32(smem_b + sb * kBBytes);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 32, 16, 1024),
+                      make_smem_desc_sw128(b_addr + k * 32, 16, 1024), idesc, (c | tap | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&bars->b_empty[sb]);
+        }
+        umma_commit(&bars->a_empty[sa]);
+      }
+      umma_commit(&bars->tmem_full);
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;          // = h_i * 8 + w_i
+    const int wi = row & 7, hi = row >> 3;
+    const bool valid = (w0 + wi < p.GW) && (h0 + hi < p.GH) && (n0 < p.N);
+    const __nv_bfloat16* add_row = nullptr;
+    if (p.addend != nullptr && valid) {
+      const long long pix = (static_cast<long long>(n0) * p.GH + (h0 + hi)) * p.GW + (w0 + wi);
+      add_row = p.addend + pix * p.out_channels + ntile * BN;
+    }
+    mbar_wait(&bars->tmem_full, 0);
+    tc_fence_after();
+    uint8_t* stage_out = smem;            // the patch ring is idle once every MMA has completed
+#pragma unroll
+    for (int hf = 0; hf < BN / 64; ++hf) {
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + hf * 64 + cc * 32, v);
+        tmem_ld_wait();
+        uint32_t packed[16];
+        if (add_row != nullptr) {
+          const uint4* ap = reinterpret_cast<const uint4*>(add_row + hf * 64 + cc * 32);
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const uint4 a4 = ap[jj];
+            const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 af = unpack_bf16x2(aw[e]);
+              packed[jj * 4 + e] = pack_bf16x2(__uint_as_float(v[jj * 8 + e * 2]) + af.x,
+                                               __uint_as_float(v[jj * 8 + e * 2 + 1]) + af.y);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+        }
+        if (!valid) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) packed[j] = 0u;
+        }
+        uint8_t* rowp = stage_out + hf * kABytes + row * 128;
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          const int chunk = (cc * 4 + jj) ^ (row & 7);
+          *reinterpret_cast<uint4*>(rowp + chunk * 16) =
+              make_uint4(packed[jj * 4], packed[jj * 4 + 1], packed[jj * 4 + 2], packed[jj * 4 + 3]);
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    const int et = threadIdx.x - 64;
+    if (et == 0) {
+#pragma unroll
+      for (int hf = 0; hf < BN / 64; ++hf)
+        tma_store_4d(&p.out, stage_out + hf * kABytes, ntile * BN + hf * 64, w0, h0, n0);
+      tma_store_commit();
+    }
+    if (p.stats != nullptr) {
+      const int ch = et & 63, rh = et >> 6;
+#pragma unroll
+      for (int hf = 0; hf < BN / 64; ++hf) {
+        float s1 = 0.f, s2 = 0.f;
+        const uint8_t* base = stage_out + hf * kABytes;
+#pragma unroll 8
+        for (int r = rh * 64; r < rh * 64 + 64; ++r) {
+          const __nv_bfloat16 hv =
+              *reinterpret_cast<const __nv_bfloat16*>(base + r * 128 + (((ch >> 3) ^ (r & 7)) << 4) + (ch & 7) * 2);
+          const float f = __bfloat162float(hv);
+          s1 += f;
+          s2 += f * f;
+        }
+        red_add_f32(p.stats + ntile * BN + hf * 64 + ch, s1);
+        red_add_f32(p.stats + p.out_channels + ntile * BN + hf * 64 + ch, s2);
+      }
+    }
+    if (et == 0) tma_store_wait_read0();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<BN>(tmem_base);
+}
+
 // ============================================================================ wgrad
 template <int BNW, int STAGES>
 __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_constant__ WgradParams p) {
@@ -852,6 +1048,82 @@ static int set_smem(Kernel k, int bytes) {
   return 0;
 }
 
+// ---------------------------------------------------------------------------- halo variant, host side
+static int build_halo_common(const PmdConvShape& s, int red_channels, int out_channels, const void* in, const void* w,
+                             bool w_rsck, void* outp, ConvHaloParams* o) {
+  PMD_REQUIRE(conv_halo_supported(s), "shape not eligible for the halo kernel");
+  ConvHaloParams& p = *o;
+  memset(&p, 0, sizeof(p));
+  p.n_chunks = red_channels / 64;
+  p.tiles_w = s.W / 8;
+  p.tiles_h = s.H / 16;
+  p.N = s.N;
+  p.GW = s.W;
+  p.GH = s.H;
+  p.out_channels = out_channels;
+  p.bn_tile = (out_channels % 128 == 0) ? 128 : 64;
+  if (act_map(&p.a, in, s.N, s.H, s.W, red_channels, 1, 0, 0, 8, 18, 1)) return -1;
+  if (act_map(&p.out, outp, s.N, s.H, s.W, out_channels, 1, 0, 0, 8, 16, 1)) return -1;
+  if (!w_rsck) {   // KRSC: (c inner, tap, k)
+    const uint64_t dims[3] = {(uint64_t)s.C, 9ull, (uint64_t)s.K};
+    const uint64_t strides[2] = {(uint64_t)s.C * 2, 9ull * s.C * 2};
+    const uint32_t box[3] = {64u, 1u, (uint32_t)p.bn_tile};
+    if (encode_map(&p.b, w, 3, dims, strides, box)) return -1;
+  } else {         // RSCK: (k inner, c rows, tap)
+    const uint64_t dims[3] = {(uint64_t)s.K, (uint64_t)s.C, 9ull};
+    const uint64_t strides[2] = {(uint64_t)s.K * 2, (uint64_t)s.C * s.K * 2};
+    const uint32_t box[3] = {64u, (uint32_t)p.bn_tile, 1u};
+    if (encode_map(&p.b, w, 3, dims, strides, box)) return -1;
+  }
+  return 0;
+}
+
+int build_fprop_halo_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
+                            ConvHaloParams* out) {
+  if (build_halo_common(s, s.C, s.K, x, w_krsc, false, y, out)) return -1;
+  out->b_tap_last = 0;
+  out->flip_taps = 0;
+  out->stats = stats;
+  return 0;
+}
+
+int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const void* addend, void* dx,
+                            ConvHaloParams* out) {
+  // same-size 3x3 stride-1: dx = conv(dy, flipped w), reduction over K, output channels C
+  if (build_halo_common(s, s.K, s.C, dy, w_rsck, true, dx, out)) return -1;
+  out->b_tap_last = 1;
+  out->flip_taps = 1;
+  out->addend = static_cast<const __nv_bfloat16*>(addend);
+  return 0;
+}
+
+template <int BN, int AS, int BS>
+static int launch_conv_halo_t(const ConvHaloParams& p, cudaStream_t stream) {
+  constexpr int smem = AS * kHaloPatchBytes + BS * BN * 128 + sizeof(HaloBars<AS, BS>) + 1024;
+  static bool once = false;
+  if (!once) {
+    if (set_smem(conv_gemm_halo_kernel<BN, AS, BS>, smem)) return -1;
+    once = true;
+  }
+  const dim3 grid(p.tiles_w * p.tiles_h * p.N, p.out_channels / BN, 1);
+  conv_gemm_halo_kernel<BN, AS, BS><<<grid, kThreads, smem, stream>>>(p);
+  return 0;
+}
+
+int launch_conv_halo(const ConvHaloParams& p, cudaStream_t stream) {
+  // one 54 KB patch stage + 32 KB of weight slices = 86 KB -> 2 CTAs per SM (their phases interleave)
+  const int rc = p.bn_tile == 64 ? launch_conv_halo_t<64, 1, 4>(p, stream) : launch_conv_halo_t<128, 1, 2>(p, stream);
+  if (rc != 0) return -1;
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+bool conv_halo_enabled() {
+  static const bool on = getenv("PMD_CONV_HALO") == nullptr || atoi(getenv("PMD_CONV_HALO")) != 0;
+  return on;
+}
+
 template <int BN, int ST>
 static int launch_conv_gemm_t(const ConvGemmParams& p, const dim3& grid, cudaStream_t stream) {
   constexpr int smem = ST * (kABytes + BN * 128) + sizeof(PipeBars<ST>) + 1024;
@@ -951,6 +1223,11 @@ using namespace pmd;
 
 extern "C" PMD_API int pmd_conv_fprop(const PmdConvShape* s, const void* d_x, const void* d_w_krsc, void* d_y, float* d_stats,
                               void* stream) {
+  if (conv_halo_enabled() && conv_halo_supported(*s)) {
+    ConvHaloParams hp;
+    if (build_fprop_halo_params(*s, d_x, d_w_krsc, d_y, d_stats, &hp)) return -1;
+    return launch_conv_halo(hp, static_cast<cudaStream_t>(stream));
+  }
   ConvGemmParams p;
   if (build_fprop_params(*s, d_x, d_w_krsc, d_y, d_stats, &p)) return -1;
   return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
@@ -959,6 +1236,11 @@ extern "C" PMD_API int pmd_conv_fprop(const PmdConvShape* s, const void* d_x, co
 extern "C" PMD_API int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, const void* d_w_rsck, const PmdConvShape* s2,
                               const void* d_dy2, const void* d_w2_rsck, const void* d_addend, void* d_dx,
                               void* stream) {
+  if (conv_halo_enabled() && conv_halo_supported(*s) && s2 == nullptr) {
+    ConvHaloParams hp;
+    if (build_dgrad_halo_params(*s, d_dy, d_w_rsck, d_addend, d_dx, &hp)) return -1;
+    return launch_conv_halo(hp, static_cast<cudaStream_t>(stream));
+  }
   ConvGemmParams p;
   if (build_dgrad_params(*s, d_dy, d_w_rsck, s2, d_dy2, d_w2_rsck, d_addend, d_dx, &p)) return -1;
   return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));

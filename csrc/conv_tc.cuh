@@ -59,6 +59,35 @@ struct WgradParams {
   float* dw;
 };
 
+inline int conv_out_dim(int in, int R, int stride) { return (in + 2 * (R / 2) - R) / stride + 1; }
+inline bool conv_tc_supported(const PmdConvShape& s) {
+  return s.C % 64 == 0 && s.K % 64 == 0 && (s.R == 1 || s.R == 3) && (s.stride == 1 || s.stride == 2);
+}
+
+// 3x3 stride-1 convolutions on maps with W % 8 == 0 and H % 16 == 0: the A operand of all nine taps comes from
+// three column patches per 64-channel chunk (see conv_gemm_halo_kernel), cutting L2->SM activation traffic 2.7x.
+struct ConvHaloParams {
+  CUtensorMap a;       // input, box (64 ch, 8, 18, 1): one column patch
+  CUtensorMap b;       // weights (3-D, as in ConvGemmParams)
+  CUtensorMap out;     // output, box (64 ch, 8, 16, 1)
+  int n_chunks;        // reduction channels / 64
+  int tiles_w, tiles_h, N, GW, GH;
+  int b_tap_last;      // 0: KRSC (fprop), 1: RSCK (dgrad)
+  int flip_taps;       // dgrad: weight tap (2-r, 2-s) pairs with patch offset (r, s)
+  int out_channels, bn_tile;
+  float* stats;
+  const __nv_bfloat16* addend;
+};
+inline bool conv_halo_supported(const PmdConvShape& s) {
+  return conv_tc_supported(s) && s.R == 3 && s.stride == 1 && s.W % 8 == 0 && s.H % 16 == 0;
+}
+int build_fprop_halo_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
+                            ConvHaloParams* out);
+int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const void* addend, void* dx,
+                            ConvHaloParams* out);
+int launch_conv_halo(const ConvHaloParams& p, cudaStream_t stream);
+bool conv_halo_enabled();   // PMD_CONV_HALO=0 switches the engine back to per-tap loads
+
 // Builders return 0 / -1 (error text via pmd_last_error()).
 int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
                        ConvGemmParams* out);
@@ -69,9 +98,5 @@ int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, flo
 int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream);
 int launch_wgrad(const WgradParams& p, cudaStream_t stream);
 
-inline int conv_out_dim(int in, int R, int stride) { return (in + 2 * (R / 2) - R) / stride + 1; }
-inline bool conv_tc_supported(const PmdConvShape& s) {
-  return s.C % 64 == 0 && s.K % 64 == 0 && (s.R == 1 || s.R == 3) && (s.stride == 1 || s.stride == 2);
-}
 
 }  // namespace pmd

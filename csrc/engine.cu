@@ -62,6 +62,8 @@ struct Block {
 
 struct ConvPlan {
   ConvGemmParams fprop, fprop_eval;
+  ConvHaloParams fprop_h, fprop_eval_h;     // used instead when halo == true (3x3 stride-1, large maps)
+  bool halo = false;
   WgradParams wgrad;
 };
 
@@ -71,6 +73,8 @@ struct Plan {
   std::vector<ConvGemmParams> block_dgrad;   // one per block (conv0 + fused shortcut / addend)
   std::vector<ConvGemmParams> sc_dgrad;      // per block: shortcut alone, when it cannot share conv0's tile grid
   std::vector<ConvGemmParams> inner_dgrad;   // per conv index (main[j], j >= 1)
+  std::vector<ConvHaloParams> block_dgrad_h, inner_dgrad_h;
+  std::vector<char> block_halo, inner_halo;
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_launches = 0, eval_launches = 0;
   bool train_warm = false, eval_warm = false;
@@ -323,6 +327,11 @@ Plan* get_plan(PmdEngine* e, int n) {
   pl->inner_dgrad.resize(e->convs.size());
   pl->block_dgrad.resize(e->blocks.size());
   pl->sc_dgrad.resize(e->blocks.size());
+  pl->block_dgrad_h.resize(e->blocks.size());
+  pl->inner_dgrad_h.resize(e->convs.size());
+  pl->block_halo.assign(e->blocks.size(), 0);
+  pl->inner_halo.assign(e->convs.size(), 0);
+  const bool halo_on = conv_halo_enabled();
   for (size_t i = 0; i < e->convs.size(); ++i) {
     Conv& cv = e->convs[i];
     if (!cv.tc) continue;
@@ -332,6 +341,12 @@ Plan* get_plan(PmdEngine* e, int n) {
     if (build_fprop_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop)) return nullptr;
     pl->conv[i].fprop_eval = pl->conv[i].fprop;
     pl->conv[i].fprop_eval.stats = nullptr;
+    if (halo_on && !cv.stem_col && conv_halo_supported(s)) {
+      if (build_fprop_halo_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop_h)) return nullptr;
+      pl->conv[i].fprop_eval_h = pl->conv[i].fprop_h;
+      pl->conv[i].fprop_eval_h.stats = nullptr;
+      pl->conv[i].halo = true;
+    }
     if (build_wgrad_params(s, cv.x, cv.dy, e->grad + cv.w_off, 0, e->sm_count, &pl->conv[i].wgrad,
                            cv.stem_col ? cv.real_rsc : 0, cv.stem_col ? cv.real_rsc : 64))
       return nullptr;
@@ -345,6 +360,11 @@ Plan* get_plan(PmdEngine* e, int n) {
       if (build_dgrad_params(s, cv.dy, e->wt + cv.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_mid[j - 1],
                              &pl->inner_dgrad[b.main[j]]))
         return nullptr;
+      if (halo_on && conv_halo_supported(s)) {
+        if (build_dgrad_halo_params(s, cv.dy, e->wt + cv.w_off, nullptr, b.dz_mid[j - 1], &pl->inner_dgrad_h[b.main[j]]))
+          return nullptr;
+        pl->inner_halo[b.main[j]] = 1;
+      }
     }
     Conv& c0 = e->convs[b.main[0]];
     PmdConvShape s0 = c0.s;
@@ -372,6 +392,10 @@ Plan* get_plan(PmdEngine* e, int n) {
       if (build_dgrad_params(s0, c0.dy, e->wt + c0.w_off, nullptr, nullptr, nullptr, b.g_out, b.dz_in,
                              &pl->block_dgrad[bi]))
         return nullptr;
+      if (halo_on && conv_halo_supported(s0)) {
+        if (build_dgrad_halo_params(s0, c0.dy, e->wt + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_h[bi])) return nullptr;
+        pl->block_halo[bi] = 1;
+      }
     }
   }
   Plan* raw = pl.get();
@@ -471,7 +495,9 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
   auto conv_fwd = [&](int ci) -> int {
     Conv& cv = e->convs[ci];
     const long long rows = 1LL * n * cv.Ho * cv.Wo;
-    if (cv.tc) {
+    if (cv.tc && pl->conv[ci].halo) {
+      E_CHECK(launch_conv_halo(train ? pl->conv[ci].fprop_h : pl->conv[ci].fprop_eval_h, st));
+    } else if (cv.tc) {
       E_CHECK(launch_conv_gemm(train ? pl->conv[ci].fprop : pl->conv[ci].fprop_eval, st));
     } else {
       PmdConvShape s = cv.s;
@@ -562,7 +588,10 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     for (int j = b.n_main - 1; j >= 1; --j) {
       const int ci = b.main[j], prev = b.main[j - 1];
       E_CHECK(wgrad(ci));
-      E_CHECK(launch_conv_gemm(pl->inner_dgrad[ci], st));
+      if (pl->inner_halo[ci])
+        E_CHECK(launch_conv_halo(pl->inner_dgrad_h[ci], st));
+      else
+        E_CHECK(launch_conv_gemm(pl->inner_dgrad[ci], st));
       Conv& pv = e->convs[prev];
       E_CHECK(bn_backward(e, prev, -1, b.dz_mid[j - 1], nullptr, 1LL * n * pv.Ho * pv.Wo, nullptr, st));
       E_CHECK(bn_done(prev));
@@ -571,7 +600,10 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     if (b.sc >= 0) E_CHECK(wgrad(b.sc));
     if (b.sc >= 0 && e->convs[b.sc].s.stride != e->convs[b.main[0]].s.stride)
       E_CHECK(launch_conv_gemm(pl->sc_dgrad[bi], st));
-    E_CHECK(launch_conv_gemm(pl->block_dgrad[bi], st));
+    if (pl->block_halo[bi])
+      E_CHECK(launch_conv_halo(pl->block_dgrad_h[bi], st));
+    else
+      E_CHECK(launch_conv_gemm(pl->block_dgrad[bi], st));
   }
   {
     Conv& cv = e->convs[0];
