@@ -1119,10 +1119,14 @@ int launch_conv_halo(const ConvHaloParams& p, cudaStream_t stream) {
   return 0;
 }
 
-bool conv_halo_enabled() {
-  static const bool on = getenv("PMD_CONV_HALO") == nullptr || atoi(getenv("PMD_CONV_HALO")) != 0;
-  return on;
+// PMD_CONV_HALO: 0 = never (default), 1 = fprop and dgrad, 2 = dgrad only.  The variant is correct but, measured
+// inside the training step, slower than per-tap loads (profiles/r1_conv_variants.md), so it is opt-in.
+int conv_halo_mode() {
+  static const int mode = getenv("PMD_CONV_HALO") == nullptr ? 0 : atoi(getenv("PMD_CONV_HALO"));
+  return mode;
 }
+bool conv_halo_enabled() { return conv_halo_mode() == 1; }
+bool conv_halo_dgrad_enabled() { return conv_halo_mode() >= 1; }
 
 template <int BN, int ST>
 static int launch_conv_gemm_t(const ConvGemmParams& p, const dim3& grid, cudaStream_t stream) {
@@ -1236,7 +1240,7 @@ extern "C" PMD_API int pmd_conv_fprop(const PmdConvShape* s, const void* d_x, co
 extern "C" PMD_API int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, const void* d_w_rsck, const PmdConvShape* s2,
                               const void* d_dy2, const void* d_w2_rsck, const void* d_addend, void* d_dx,
                               void* stream) {
-  if (conv_halo_enabled() && conv_halo_supported(*s) && s2 == nullptr) {
+  if (conv_halo_dgrad_enabled() && conv_halo_supported(*s) && s2 == nullptr) {
     ConvHaloParams hp;
     if (build_dgrad_halo_params(*s, d_dy, d_w_rsck, d_addend, d_dx, &hp)) return -1;
     return launch_conv_halo(hp, static_cast<cudaStream_t>(stream));

@@ -86,7 +86,8 @@ int build_fprop_halo_params(const PmdConvShape& s, const void* x, const void* w_
 int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const void* addend, void* dx,
                             ConvHaloParams* out);
 int launch_conv_halo(const ConvHaloParams& p, cudaStream_t stream);
-bool conv_halo_enabled();   // PMD_CONV_HALO=0 switches the engine back to per-tap loads
+bool conv_halo_enabled();        // column-patch kernel for fprop
+bool conv_halo_dgrad_enabled();  // column-patch kernel for dgrad (PMD_CONV_HALO: 0 never, 1 both, 2 dgrad only)
 
 // Builders return 0 / -1 (error text via pmd_last_error()).
 int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,

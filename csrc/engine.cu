@@ -331,7 +331,7 @@ Plan* get_plan(PmdEngine* e, int n) {
   pl->inner_dgrad_h.resize(e->convs.size());
   pl->block_halo.assign(e->blocks.size(), 0);
   pl->inner_halo.assign(e->convs.size(), 0);
-  const bool halo_on = conv_halo_enabled();
+  const bool halo_on = conv_halo_enabled(), halo_dgrad = conv_halo_dgrad_enabled();
   for (size_t i = 0; i < e->convs.size(); ++i) {
     Conv& cv = e->convs[i];
     if (!cv.tc) continue;
@@ -360,7 +360,7 @@ Plan* get_plan(PmdEngine* e, int n) {
       if (build_dgrad_params(s, cv.dy, e->wt + cv.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_mid[j - 1],
                              &pl->inner_dgrad[b.main[j]]))
         return nullptr;
-      if (halo_on && conv_halo_supported(s)) {
+      if (halo_dgrad && conv_halo_supported(s)) {
         if (build_dgrad_halo_params(s, cv.dy, e->wt + cv.w_off, nullptr, b.dz_mid[j - 1], &pl->inner_dgrad_h[b.main[j]]))
           return nullptr;
         pl->inner_halo[b.main[j]] = 1;
@@ -392,7 +392,7 @@ Plan* get_plan(PmdEngine* e, int n) {
       if (build_dgrad_params(s0, c0.dy, e->wt + c0.w_off, nullptr, nullptr, nullptr, b.g_out, b.dz_in,
                              &pl->block_dgrad[bi]))
         return nullptr;
-      if (halo_on && conv_halo_supported(s0)) {
+      if (halo_dgrad && conv_halo_supported(s0)) {
         if (build_dgrad_halo_params(s0, c0.dy, e->wt + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_h[bi])) return nullptr;
         pl->block_halo[bi] = 1;
       }
