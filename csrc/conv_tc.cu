@@ -1158,10 +1158,13 @@ static int launch_conv_gemm_persistent_t(const ConvGemmParams& p, cudaStream_t s
     int dev = 0;
     PMD_CHECK_CUDA(cudaGetDevice(&dev));
     PMD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    int occ = 0;
-    PMD_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_gemm_persistent_kernel<BN, ST>, kThreads, smem));
+    // (cudaOccupancyMaxActiveBlocksPerMultiprocessor answered 1 here -- it assumes the default carve-out -- which
+    // left two thirds of every SM idle in the first measurements; compute the residency directly.)
+    PMD_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_persistent_kernel<BN, ST>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        cudaSharedmemCarveoutMaxShared));
+    const int by_smem = (227 * 1024) / (smem + 1024);
     const int by_tmem = 512 / (2 * BN);          // each CTA owns 2*BN TMEM columns of the SM's 512
-    ctas_per_sm = occ < by_tmem ? occ : by_tmem;
+    ctas_per_sm = by_smem < by_tmem ? by_smem : by_tmem;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
   }
   const int total = p.tiles_w * p.tiles_h * p.tiles_n * (p.out_channels / BN) * p.n_classes;
