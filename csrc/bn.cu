@@ -7,6 +7,7 @@
 // tables so that one code path serves 1..8 ranks and rank-order-fixed summation keeps every rank
 // bitwise identical.
 #include "common.cuh"
+#include "sym.cuh"
 #include "../include/pmdist.h"
 
 namespace pmd {
@@ -186,12 +187,120 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float
   }
 }
 
+// ---------------------------------------------------------------- finalize + apply in one kernel
+// The statistics of a BatchNorm are complete when its convolution has finished, so the separate finalize launch
+// (a single tiny block between two large kernels, i.e. pure dependency latency) can go: every block of the
+// apply kernel derives scale/shift from the [sum, sumsq] vector itself (2C loads, C rsqrt -- noise next to the
+// activation traffic), and block 0 also stores what backward and the checkpoint need (mean, invstd, scale, shift,
+// running statistics, num_batches_tracked).  Under SyncBatchNorm the cross-GPU exchange happens in the same
+// prologue (ll_exchange_sum_grid: block 0 pushes and polls over NVLink, the other blocks pick the totals up from
+// local memory).  With RES == 2 the projection shortcut's BatchNorm is finalised here too.
+struct BnFinalizeDev {
+  const float* stats;
+  const float* gamma;
+  const float* beta;
+  float* running_mean;
+  float* running_var;
+  long long* nbt;
+  float *scale, *shift, *mean, *invstd;
+  float* totals;                // local scratch [2C] (multi-rank only)
+  unsigned long long recv_off;  // push-exchange receive area (multi-rank only)
+  int slot;
+};
+
+template <int RES, bool SYNC>
+__global__ void bn_finalize_apply_kernel(PmdSym sym, BnFinalizeDev f0, BnFinalizeDev f1, float count_per_rank,
+                                         float momentum, float eps, const __nv_bfloat16* __restrict__ y,
+                                         const __nv_bfloat16* __restrict__ res, int relu, __nv_bfloat16* __restrict__ z,
+                                         long long total8, int C) {
+  extern __shared__ float aff[];     // [scale | shift | rscale | rshift] (C each) + totals scratch [2C]
+  float* tot = aff + 4 * C;
+  const float n = count_per_rank * (SYNC ? sym.world : 1);
+#pragma unroll
+  for (int b = 0; b < (RES == 2 ? 2 : 1); ++b) {
+    const BnFinalizeDev& f = b == 0 ? f0 : f1;
+    if (SYNC) {
+      ll_exchange_sum_grid(sym, f.slot, f.stats, 2 * C, f.recv_off, f.totals, tot);
+    } else {
+      for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) tot[c] = f.stats[c];
+      __syncthreads();
+    }
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      const float mean = tot[c] / n;
+      const float var = fmaxf(tot[C + c] / n - mean * mean, 0.f);
+      const float invstd = rsqrtf(var + eps);
+      const float a = f.gamma[c] * invstd;
+      const float sh = f.beta[c] - mean * a;
+      aff[b * 2 * C + c] = a;
+      aff[b * 2 * C + C + c] = sh;
+      if (blockIdx.x == 0) {
+        f.scale[c] = a;
+        f.shift[c] = sh;
+        f.mean[c] = mean;
+        f.invstd[c] = invstd;
+        if (f.running_mean != nullptr) {
+          const float unbiased = var * (n / fmaxf(n - 1.f, 1.f));
+          f.running_mean[c] = (1.f - momentum) * f.running_mean[c] + momentum * mean;
+          f.running_var[c] = (1.f - momentum) * f.running_var[c] + momentum * unbiased;
+        }
+        if (c == 0 && f.nbt != nullptr) *f.nbt += 1;
+      }
+    }
+    __syncthreads();
+  }
+  const int groups = C / 8;
+  const long long T = static_cast<long long>(gridDim.x) * blockDim.x;
+  auto one = [&](long long i, const float (&v)[8], const float (&rv)[8]) {
+    const int c0 = static_cast<int>(i % groups) * 8;
+    float o[8], sc[8], sh[8];
+    lds8(aff + c0, sc);
+    lds8(aff + C + c0, sh);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = fmaf(v[j], sc[j], sh[j]);
+    if (RES == 2) {
+      lds8(aff + 2 * C + c0, sc);
+      lds8(aff + 3 * C + c0, sh);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], sc[j], sh[j]);
+    } else if (RES == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] += rv[j];
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], 0.f);
+    }
+    store8(z + i * 8, o);
+  };
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  for (; i + T < total8; i += 2 * T) {
+    float va[8], vb[8], ra[8], rb[8];
+    load8(y + i * 8, va);
+    load8(y + (i + T) * 8, vb);
+    if (RES != 0) {
+      load8(res + i * 8, ra);
+      load8(res + (i + T) * 8, rb);
+    }
+    one(i, va, ra);
+    one(i + T, vb, rb);
+  }
+  for (; i < total8; i += T) {
+    float va[8], ra[8];
+    load8(y + i * 8, va);
+    if (RES != 0) load8(res + i * 8, ra);
+    one(i, va, ra);
+  }
+}
+
 // ---------------------------------------------------------------- backward, 1 or 2 branches
 // A residual block's output gradient dz feeds the last main-path BatchNorm AND (projection blocks) the
 // shortcut's BatchNorm through the same ReLU mask; handling both in one pass reads dz and the mask
 // source once instead of twice.  MASK: 0 none, 1 z > 0, 2 recomputed from branch 0's own forward
 // affine (scale*y + shift > 0; valid when that BatchNorm had no residual), which skips reading z at all.
 struct BnBranchDev {
+  unsigned long long recv_off;  // push-exchange receive area (multi-rank fused exchange only)
+  float* totals_scratch;        // local [2C] where block 0 publishes the exchanged totals
+  int slot;
   const __nv_bfloat16* y;
   const float* mean;
   const float* invstd;
@@ -298,14 +407,24 @@ bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bflo
   }
 }
 
-template <int NB, int MASK>
-__global__ void bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
-                                          const float* __restrict__ mscale, const float* __restrict__ mshift,
-                                          BnBranchDev b0, BnBranchDev b1, float count_total,
-                                          __nv_bfloat16* __restrict__ g_out, long long total8, int C) {
+template <int NB, int MASK, bool SYNC>
+__global__ void bn_bwd_apply_multi_kernel(PmdSym sym, const __nv_bfloat16* __restrict__ dz,
+                                          const __nv_bfloat16* __restrict__ z, const float* __restrict__ mscale,
+                                          const float* __restrict__ mshift, BnBranchDev b0, BnBranchDev b1,
+                                          float count_total, __nv_bfloat16* __restrict__ g_out, long long total8,
+                                          int C) {
   // dy = gamma*invstd * (g - mean_g - xhat*mean_gx), xhat = (y - mean)*invstd, folded per channel into
   // dy = a*g + k1*y + k0.  Shared layout: per branch [a | k1 | k0] (C floats each), then [mscale | mshift].
+  // SYNC: the cross-GPU sum of [sum_g, sum_gx] is exchanged right here (block 0 pushes/polls, see sym.cuh)
   extern __shared__ float coef[];
+  float* tot = coef + (NB * 3 + 2) * C;      // [NB][2C], SYNC only
+  if (SYNC) {
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      const BnBranchDev& br = b == 0 ? b0 : b1;
+      ll_exchange_sum_grid(sym, br.slot, br.sums, 2 * C, br.recv_off, br.totals_scratch, tot + b * 2 * C);
+    }
+  }
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
@@ -313,7 +432,9 @@ __global__ void bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz, 
       float* cf = coef + b * 3 * C;
       const float is = br.invstd[c], mu = br.mean[c];
       const float a = br.gamma[c] * is;
-      const float mg = br.totals[c] / count_total, mgx = br.totals[C + c] / count_total;
+      const float tg = SYNC ? tot[b * 2 * C + c] : br.totals[c];
+      const float tgx = SYNC ? tot[b * 2 * C + C + c] : br.totals[C + c];
+      const float mg = tg / count_total, mgx = tgx / count_total;
       cf[c] = a;
       cf[C + c] = -a * mgx * is;
       cf[2 * C + c] = a * (mgx * is * mu - mg);
@@ -455,6 +576,9 @@ extern "C" PMD_API int pmd_bn_apply(const void* d_y, const float* d_scale, const
 
 static BnBranchDev to_dev(const PmdBnBranch& b) {
   BnBranchDev d;
+  d.recv_off = b.recv_off;
+  d.totals_scratch = b.totals_scratch;
+  d.slot = b.slot;
   d.y = static_cast<const __nv_bfloat16*>(b.y);
   d.mean = b.mean;
   d.invstd = b.invstd;
@@ -474,27 +598,30 @@ static void launch_reduce(int mask, int grid, int smem, cudaStream_t st, const _
   if (mask == 1) bn_bwd_reduce_multi_kernel<NB, 1><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
   if (mask == 2) bn_bwd_reduce_multi_kernel<NB, 2><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
 }
-template <int NB, int MASK>
+template <int NB, int MASK, bool SYNC>
 static void allow_big_smem() {
   static bool once = false;
   if (!once) {
-    cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, MASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, MASK, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
     once = true;
   }
 }
 
-template <int NB>
-static void launch_apply(int mask, int grid, int smem, cudaStream_t st, const __nv_bfloat16* dz, const __nv_bfloat16* z,
-                         const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, float count,
-                         __nv_bfloat16* g_out, long long total8, int C) {
+template <int NB, bool SYNC>
+static void launch_apply(const PmdSym& sym, int mask, int grid, int smem, cudaStream_t st, const __nv_bfloat16* dz,
+                         const __nv_bfloat16* z, const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1,
+                         float count, __nv_bfloat16* g_out, long long total8, int C) {
   if (smem > 48 * 1024) {
-    allow_big_smem<NB, 0>();
-    allow_big_smem<NB, 1>();
-    allow_big_smem<NB, 2>();
+    allow_big_smem<NB, 0, SYNC>();
+    allow_big_smem<NB, 1, SYNC>();
+    allow_big_smem<NB, 2, SYNC>();
   }
-  if (mask == 0) bn_bwd_apply_multi_kernel<NB, 0><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, count, g_out, total8, C);
-  if (mask == 1) bn_bwd_apply_multi_kernel<NB, 1><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, count, g_out, total8, C);
-  if (mask == 2) bn_bwd_apply_multi_kernel<NB, 2><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, count, g_out, total8, C);
+  if (mask == 0)
+    bn_bwd_apply_multi_kernel<NB, 0, SYNC><<<grid, kBlock, smem, st>>>(sym, dz, z, ms, mh, b0, b1, count, g_out, total8, C);
+  if (mask == 1)
+    bn_bwd_apply_multi_kernel<NB, 1, SYNC><<<grid, kBlock, smem, st>>>(sym, dz, z, ms, mh, b0, b1, count, g_out, total8, C);
+  if (mask == 2)
+    bn_bwd_apply_multi_kernel<NB, 2, SYNC><<<grid, kBlock, smem, st>>>(sym, dz, z, ms, mh, b0, b1, count, g_out, total8, C);
 }
 
 extern "C" PMD_API int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
@@ -521,23 +648,116 @@ extern "C" PMD_API int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z
   return 0;
 }
 
-extern "C" PMD_API int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
-                                              const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
-                                              float count_total, void* d_g_out, long long rows, int C, void* stream) {
+static int bn_bwd_apply_impl(const PmdSym* sym, const void* d_dz, const void* d_z, const float* d_mask_scale,
+                             const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb, float count_total,
+                             void* d_g_out, long long rows, int C, void* stream) {
   BN_CHECK_C(C);
   PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
+  const bool sync = sym != nullptr && sym->world > 1;
   const long long total8 = rows * C / 8;
   const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
   const int grid = grid_for(total8, kBlock * 2);
-  const int smem = (nb * 3 + 2) * C * 4;
+  const int smem = (nb * 3 + 2 + (sync ? nb * 2 : 0)) * C * 4;
+  PMD_REQUIRE(smem <= 128 * 1024, "too many channels for the fused BatchNorm backward");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
   const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);
   __nv_bfloat16* g = static_cast<__nv_bfloat16*>(d_g_out);
-  if (nb == 1)
-    launch_apply<1>(mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
-  else
-    launch_apply<2>(mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
+  PmdSym none{};
+  none.world = 1;
+  if (!sync) {
+    if (nb == 1)
+      launch_apply<1, false>(none, mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
+    else
+      launch_apply<2, false>(none, mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
+  } else {
+    if (nb == 1)
+      launch_apply<1, true>(*sym, mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
+    else
+      launch_apply<2, true>(*sym, mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
+  }
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
+                                              const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
+                                              float count_total, void* d_g_out, long long rows, int C, void* stream) {
+  return bn_bwd_apply_impl(nullptr, d_dz, d_z, d_mask_scale, d_mask_shift, mask_mode, br, nb, count_total, d_g_out, rows, C,
+                           stream);
+}
+
+// Multi-rank form: the [sum_g, sum_gx] vectors of all ranks are exchanged inside the kernel's prologue
+// (br[i].slot / recv_off / totals_scratch must be set; br[i].totals is ignored).
+extern "C" PMD_API int pmd_bn_bwd_apply_multi_sync(const PmdSym* sym, const void* d_dz, const void* d_z,
+                                                   const float* d_mask_scale, const float* d_mask_shift, int mask_mode,
+                                                   const PmdBnBranch* br, int nb, float count_total, void* d_g_out,
+                                                   long long rows, int C, void* stream) {
+  return bn_bwd_apply_impl(sym, d_dz, d_z, d_mask_scale, d_mask_shift, mask_mode, br, nb, count_total, d_g_out, rows, C,
+                           stream);
+}
+
+// Forward: finalize (+ SyncBatchNorm exchange) + apply in one launch.
+template <int RES, bool SYNC>
+static void launch_finalize_apply(const PmdSym& sym, int grid, int smem, cudaStream_t st, const BnFinalizeDev& f0,
+                                  const BnFinalizeDev& f1, float count, float momentum, float eps, const __nv_bfloat16* y,
+                                  const __nv_bfloat16* res, int relu, __nv_bfloat16* z, long long total8, int C) {
+  static bool once = false;
+  if (!once && smem > 48 * 1024) {
+    cudaFuncSetAttribute(bn_finalize_apply_kernel<RES, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    once = true;
+  }
+  bn_finalize_apply_kernel<RES, SYNC><<<grid, kBlock, smem, st>>>(sym, f0, f1, count, momentum, eps, y, res, relu, z, total8, C);
+}
+
+static BnFinalizeDev to_dev(const PmdBnFinalize& f) {
+  BnFinalizeDev d;
+  d.stats = f.stats;
+  d.gamma = f.gamma;
+  d.beta = f.beta;
+  d.running_mean = f.running_mean;
+  d.running_var = f.running_var;
+  d.nbt = f.num_batches;
+  d.scale = f.scale;
+  d.shift = f.shift;
+  d.mean = f.mean;
+  d.invstd = f.invstd;
+  d.totals = f.totals_scratch;
+  d.recv_off = f.recv_off;
+  d.slot = f.slot;
+  return d;
+}
+
+extern "C" PMD_API int pmd_bn_finalize_apply(const PmdSym* sym, const PmdBnFinalize* f, const PmdBnFinalize* f_res,
+                                             float count_per_rank, float momentum, float eps, const void* d_y,
+                                             const void* d_res, int relu, void* d_z, long long rows, int C, void* stream) {
+  BN_CHECK_C(C);
+  PMD_REQUIRE(f != nullptr, "missing BatchNorm description");
+  PMD_REQUIRE(f_res == nullptr || d_res != nullptr, "a residual BatchNorm needs the residual tensor");
+  const bool sync = sym != nullptr && sym->world > 1;
+  const long long total8 = rows * C / 8;
+  const int grid = grid_for(total8, kBlock * 2);
+  const int smem = 6 * C * 4;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* y = static_cast<const __nv_bfloat16*>(d_y);
+  const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(d_res);
+  __nv_bfloat16* z = static_cast<__nv_bfloat16*>(d_z);
+  const BnFinalizeDev f0 = to_dev(*f), f1 = to_dev(f_res != nullptr ? *f_res : *f);
+  PmdSym none{};
+  none.world = 1;
+  const int resmode = f_res != nullptr ? 2 : (d_res != nullptr ? 1 : 0);
+#define PMD_FA(RES, SYNC, S) launch_finalize_apply<RES, SYNC>(S, grid, smem, st, f0, f1, count_per_rank, momentum, eps, y, res, relu, z, total8, C)
+  if (!sync) {
+    if (resmode == 0) PMD_FA(0, false, none);
+    if (resmode == 1) PMD_FA(1, false, none);
+    if (resmode == 2) PMD_FA(2, false, none);
+  } else {
+    if (resmode == 0) PMD_FA(0, true, *sym);
+    if (resmode == 1) PMD_FA(1, true, *sym);
+    if (resmode == 2) PMD_FA(2, true, *sym);
+  }
+#undef PMD_FA
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

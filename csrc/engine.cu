@@ -41,7 +41,7 @@ struct Conv {
   const bf16* x = nullptr;
   bf16 *y = nullptr, *dy = nullptr;
   float *scale = nullptr, *shift = nullptr, *mean = nullptr, *invstd = nullptr;
-  float *stats = nullptr, *sums = nullptr, *sums_total = nullptr;
+  float *stats = nullptr, *sums = nullptr, *sums_total = nullptr, *stats_total = nullptr;
   unsigned long long stats_off = 0, sums_off = 0;
   unsigned long long recv_fwd_off = 0, recv_bwd_off = 0;   // push-exchange receive areas (multi-rank SyncBN)
   const float** tab_stats = nullptr;   // device: 1-entry pointer tables for the local-statistics path
@@ -248,12 +248,13 @@ int allocate(PmdEngine* e) {
     E_CHECK(e->dalloc(&cv.y, out_elems));
     E_CHECK(e->dalloc(&cv.dy, out_elems));
     float* f = nullptr;
-    E_CHECK(e->dalloc(&f, 6LL * cv.s.K));
+    E_CHECK(e->dalloc(&f, 8LL * cv.s.K));
     cv.scale = f;
     cv.shift = f + cv.s.K;
     cv.mean = f + 2 * cv.s.K;
     cv.invstd = f + 3 * cv.s.K;
     cv.sums_total = f + 4 * cv.s.K;
+    cv.stats_total = f + 6 * cv.s.K;
     cv.stats_off = poff;
     cv.sums_off = poff + 2ULL * cv.s.K * 4;
     poff += 4ULL * cv.s.K * 4;
@@ -441,15 +442,46 @@ struct BucketTracker {
   }
 };
 
-int bn_forward(PmdEngine* e, int ci, long long rows, cudaStream_t st) {
+// Describes conv `ci`'s BatchNorm for the fused finalize+apply kernel.
+PmdBnFinalize bn_desc(PmdEngine* e, int ci) {
+  Conv& cv = e->convs[ci];
+  PmdBnFinalize f{};
+  f.stats = cv.stats;
+  f.gamma = e->param + cv.g_off;
+  f.beta = e->param + cv.b_off;
+  f.running_mean = cv.rm;
+  f.running_var = cv.rv;
+  f.num_batches = cv.nb;
+  f.scale = cv.scale;
+  f.shift = cv.shift;
+  f.mean = cv.mean;
+  f.invstd = cv.invstd;
+  f.totals_scratch = cv.stats_total;
+  f.recv_off = cv.recv_fwd_off;
+  f.slot = ci;
+  return f;
+}
+
+// z = relu(BN_ci(y_ci) [+ res | + BN_cres(y_cres)]): training mode finalises the statistics (and exchanges them
+// with the peers under SyncBatchNorm) inside the same kernel; evaluation mode uses the running statistics.
+int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long long rows, bool train, cudaStream_t st) {
   Conv& cv = e->convs[ci];
   const PmdEngineConfig& c = e->cfg;
-  if (e->sym.world > 1 && c.sync_bn)
-    return pmd_bn_finalize_push(&e->sym, ci, cv.stats, cv.recv_fwd_off, static_cast<float>(rows), cv.s.K,
-                                e->param + cv.g_off, e->param + cv.b_off, cv.rm, cv.rv, cv.nb, c.bn_momentum, c.bn_eps,
-                                cv.scale, cv.shift, cv.mean, cv.invstd, st);
-  return pmd_bn_finalize(cv.tab_stats, 1, static_cast<float>(rows), cv.s.K, e->param + cv.g_off, e->param + cv.b_off,
-                         cv.rm, cv.rv, cv.nb, c.bn_momentum, c.bn_eps, cv.scale, cv.shift, cv.mean, cv.invstd, st);
+  if (train) {
+    const bool sync = e->sym.world > 1 && c.sync_bn;
+    const PmdBnFinalize f = bn_desc(e, ci);
+    PmdBnFinalize fr{};
+    if (cres >= 0) fr = bn_desc(e, cres);
+    return pmd_bn_finalize_apply(sync ? &e->sym : nullptr, &f, cres >= 0 ? &fr : nullptr, static_cast<float>(rows),
+                                 c.bn_momentum, c.bn_eps, cv.y, cres >= 0 ? e->convs[cres].y : res, 1, z, rows, cv.s.K, st);
+  }
+  E_CHECK(pmd_bn_eval_affine(cv.s.K, e->param + cv.g_off, e->param + cv.b_off, cv.rm, cv.rv, c.bn_eps, cv.scale, cv.shift, st));
+  if (cres >= 0) {
+    Conv& cr = e->convs[cres];
+    E_CHECK(pmd_bn_eval_affine(cr.s.K, e->param + cr.g_off, e->param + cr.b_off, cr.rm, cr.rv, c.bn_eps, cr.scale, cr.shift, st));
+    return pmd_bn_apply(cv.y, cv.scale, cv.shift, cr.y, cr.scale, cr.shift, 1, z, rows, cv.s.K, st);
+  }
+  return pmd_bn_apply(cv.y, cv.scale, cv.shift, res, nullptr, nullptr, 1, z, rows, cv.s.K, st);
 }
 
 // BatchNorm backward of conv `ci` (and, for a projection block's output, of the shortcut conv `cj`
@@ -472,20 +504,17 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
     br[b].dy = cv.dy;
     br[b].dgamma = e->grad + cv.g_off;
     br[b].dbeta = e->grad + cv.b_off;
+    br[b].recv_off = cv.recv_bwd_off;
+    br[b].totals_scratch = cv.sums_total;
+    br[b].slot = static_cast<int>(e->convs.size()) + idx[b];
   }
   Conv& c0 = e->convs[ci];
   const int mask = z != nullptr ? 1 : 2;
   E_CHECK(pmd_bn_bwd_reduce_multi(dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
-  float total_rows = static_cast<float>(rows);
-  if (sync) {
-    for (int b = 0; b < nb; ++b) {
-      Conv& cv = e->convs[idx[b]];
-      E_CHECK(pmd_small_allreduce_push(&e->sym, static_cast<int>(e->convs.size()) + idx[b], cv.sums, 2 * cv.s.K,
-                                       cv.recv_bwd_off, cv.sums_total, st));
-    }
-    total_rows *= e->sym.world;
-  }
-  return pmd_bn_bwd_apply_multi(dz, z, c0.scale, c0.shift, mask, br, nb, total_rows, g_out, rows, c0.s.K, st);
+  if (sync)
+    return pmd_bn_bwd_apply_multi_sync(&e->sym, dz, z, c0.scale, c0.shift, mask, br, nb,
+                                       static_cast<float>(rows) * e->sym.world, g_out, rows, c0.s.K, st);
+  return pmd_bn_bwd_apply_multi(dz, z, c0.scale, c0.shift, mask, br, nb, static_cast<float>(rows), g_out, rows, c0.s.K, st);
 }
 
 int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
@@ -494,7 +523,6 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
   E_CHECK(pmd_augment_im2col(e->in_u8, e->in_aug, n, c.image_hw, c.image_hw, 8, e->x0, st));
   auto conv_fwd = [&](int ci) -> int {
     Conv& cv = e->convs[ci];
-    const long long rows = 1LL * n * cv.Ho * cv.Wo;
     if (cv.tc && pl->conv[ci].halo) {
       E_CHECK(launch_conv_halo(train ? pl->conv[ci].fprop_h : pl->conv[ci].fprop_eval_h, st));
     } else if (cv.tc) {
@@ -503,36 +531,27 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
       PmdConvShape s = cv.s;
       s.N = n;
       E_CHECK(pmd_conv_fprop_direct(&s, cv.x_cstride, cv.x, e->wbf16 + cv.w_off, cv.y, st));
-      if (train) E_CHECK(pmd_bn_stats(cv.y, rows, cv.s.K, cv.stats, st));
+      if (train) E_CHECK(pmd_bn_stats(cv.y, 1LL * n * cv.Ho * cv.Wo, cv.s.K, cv.stats, st));
     }
-    if (train) return bn_forward(e, ci, rows, st);
-    return pmd_bn_eval_affine(cv.s.K, e->param + cv.g_off, e->param + cv.b_off, cv.rm, cv.rv, c.bn_eps, cv.scale,
-                              cv.shift, st);
+    return 0;
   };
   E_CHECK(conv_fwd(0));
   {
     Conv& cv = e->convs[0];
-    E_CHECK(pmd_bn_apply(cv.y, cv.scale, cv.shift, nullptr, nullptr, nullptr, 1, e->z_stem, 1LL * n * cv.Ho * cv.Wo,
-                         cv.s.K, st));
+    E_CHECK(bn_apply_step(e, 0, -1, nullptr, e->z_stem, 1LL * n * cv.Ho * cv.Wo, train, st));
   }
   for (Block& b : e->blocks) {
     for (int j = 0; j < b.n_main; ++j) {
       E_CHECK(conv_fwd(b.main[j]));
       if (j < b.n_main - 1) {
         Conv& cv = e->convs[b.main[j]];
-        E_CHECK(pmd_bn_apply(cv.y, cv.scale, cv.shift, nullptr, nullptr, nullptr, 1, b.z_mid[j],
-                             1LL * n * cv.Ho * cv.Wo, cv.s.K, st));
+        E_CHECK(bn_apply_step(e, b.main[j], -1, nullptr, b.z_mid[j], 1LL * n * cv.Ho * cv.Wo, train, st));
       }
     }
     if (b.sc >= 0) E_CHECK(conv_fwd(b.sc));
     Conv& last = e->convs[b.main[b.n_main - 1]];
-    const long long rows = 1LL * n * last.Ho * last.Wo;
-    if (b.sc >= 0) {
-      Conv& cs = e->convs[b.sc];
-      E_CHECK(pmd_bn_apply(last.y, last.scale, last.shift, cs.y, cs.scale, cs.shift, 1, b.z_out, rows, last.s.K, st));
-    } else {
-      E_CHECK(pmd_bn_apply(last.y, last.scale, last.shift, b.z_in, nullptr, nullptr, 1, b.z_out, rows, last.s.K, st));
-    }
+    E_CHECK(bn_apply_step(e, b.main[b.n_main - 1], b.sc, b.sc >= 0 ? nullptr : b.z_in, b.z_out,
+                          1LL * n * last.Ho * last.Wo, train, st));
   }
   Block& lb = e->blocks.back();
   E_CHECK(pmd_pool_fc_fwd(lb.z_out, n, lb.Hout * lb.Hout, lb.Cout, e->param + c.fc_w_off, e->param + c.fc_b_off,

@@ -119,12 +119,38 @@ typedef struct {
   void* dy;             /* apply only */
   float* dgamma;        /* apply only, may be NULL; += */
   float* dbeta;
+  /* pmd_bn_bwd_apply_multi_sync only: where this BatchNorm's cross-GPU exchange lives */
+  unsigned long long recv_off; /* heap offset of a PMD_LL_RECV_BYTES(world, 2C) receive area */
+  float* totals_scratch;       /* local [2C] */
+  int slot;
+  int pad_;
 } PmdBnBranch;
 int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale, const float* d_mask_shift,
                             int mask_mode, const PmdBnBranch* br, int nb, long long rows, int C, void* stream);
 int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z, const float* d_mask_scale, const float* d_mask_shift,
                            int mask_mode, const PmdBnBranch* br, int nb, float count_total, void* d_g_out,
                            long long rows, int C, void* stream);
+
+/* Forward finalize + apply in ONE launch (no separate pmd_bn_finalize between the convolution and the apply):
+ * z = act(BN(y) [+ res | + BN_res(res)]) with the batch statistics taken from `stats` ([sum, sumsq], as left by
+ * pmd_conv_fprop); writes scale/shift/mean/invstd and updates the running statistics exactly like
+ * pmd_bn_finalize.  With sym != NULL and world > 1 the statistics are exchanged across ranks inside the kernel
+ * (SyncBatchNorm; slot / recv_off / totals_scratch required).  f_res describes the projection shortcut's
+ * BatchNorm when the residual needs its own affine (then d_res is that branch's conv output). */
+typedef struct {
+  const float* stats;           /* [2C] local sums */
+  const float* gamma;
+  const float* beta;
+  float* running_mean;          /* may be NULL */
+  float* running_var;
+  long long* num_batches;       /* may be NULL */
+  float *scale, *shift, *mean, *invstd; /* [C] outputs */
+  float* totals_scratch;        /* [2C] local scratch (multi-rank only) */
+  unsigned long long recv_off;  /* push-exchange receive area (multi-rank only) */
+  int slot;
+  int pad_;
+} PmdBnFinalize;
+/* (pmd_bn_finalize_apply and pmd_bn_bwd_apply_multi_sync take a PmdSym and are declared in pmdist_comm.h) */
 
 /* ------------------------------------------------------------------ head + loss (head.cu)
  * Global average pool + Linear, cross-entropy with top-1/top-5 counters (ref:model/resnet.py:102-104,

@@ -15,15 +15,18 @@
 
 #include <stdint.h>
 
+#include "pmdist.h"
+
 #ifdef __cplusplus
 extern "C" {
 #endif
 
 #define PMD_MAX_RANKS 8
 #define PMD_MAX_SLOTS 4096
-/* signal pad: flags uint32 [PMD_MAX_SLOTS][PMD_MAX_RANKS] then epochs uint32 [PMD_MAX_SLOTS] */
+/* signal pad: flags uint32 [PMD_MAX_SLOTS][PMD_MAX_RANKS], then three local uint32 [PMD_MAX_SLOTS] arrays:
+ * epochs, arrival tickets and published-totals markers (the last two serve the grid-wide fused exchanges) */
 #define PMD_FLAGS_BYTES (PMD_MAX_SLOTS * PMD_MAX_RANKS * 4)
-#define PMD_SIGNAL_BYTES (PMD_FLAGS_BYTES + PMD_MAX_SLOTS * 4)
+#define PMD_SIGNAL_BYTES (PMD_FLAGS_BYTES + 3 * PMD_MAX_SLOTS * 4)
 
 enum { PMD_TRANSPORT_SINGLE = 0, PMD_TRANSPORT_VMM = 1, PMD_TRANSPORT_IPC = 2 };
 enum { PMD_COMM_FORCE_IPC = 1, PMD_COMM_NO_MULTICAST = 2 };
@@ -126,6 +129,15 @@ int pmd_bn_finalize_push(const PmdSym* sym, int slot, const float* d_stats, unsi
                          float* d_shift, float* d_mean, float* d_invstd, void* stream);
 int pmd_small_allreduce_push(const PmdSym* sym, int slot, const float* d_local, int n, unsigned long long recv_off,
                              float* d_total, void* stream);
+/* BatchNorm kernels with the SyncBatchNorm exchange INSIDE (bn.cu; structs in pmdist.h): no stand-alone exchange
+ * launch sits between the producer of the partial sums and their consumer any more.  sym may be NULL (or describe
+ * one rank): then these are the plain single-GPU fused kernels. */
+int pmd_bn_finalize_apply(const PmdSym* sym, const PmdBnFinalize* f, const PmdBnFinalize* f_res, float count_per_rank,
+                          float momentum, float eps, const void* d_y, const void* d_res, int relu, void* d_z,
+                          long long rows, int C, void* stream);
+int pmd_bn_bwd_apply_multi_sync(const PmdSym* sym, const void* d_dz, const void* d_z, const float* d_mask_scale,
+                                const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
+                                float count_total, void* d_g_out, long long rows, int C, void* stream);
 /* metrics: double[4] at heap offset `off` on every rank -> d_total (local) = sum over ranks. */
 int pmd_metric_allreduce(const PmdSym* sym, int slot, unsigned long long off, double* d_total, void* stream);
 

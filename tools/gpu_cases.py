@@ -536,7 +536,8 @@ def _bn_multi():
     class Br(C.Structure):
         _fields_ = [('y', C.c_void_p), ('mean', C.c_void_p), ('invstd', C.c_void_p), ('gamma', C.c_void_p),
                     ('sums', C.c_void_p), ('totals', C.c_void_p), ('dy', C.c_void_p), ('dgamma', C.c_void_p),
-                    ('dbeta', C.c_void_p)]
+                    ('dbeta', C.c_void_p), ('recv_off', C.c_ulonglong), ('totals_scratch', C.c_void_p),
+                    ('slot', C.c_int), ('pad_', C.c_int)]
     lib = _lib.lib()
     Cc, N, H = 128, 8, 8
     rows = N * H * H
@@ -583,5 +584,62 @@ def _bn_multi():
     torch.cuda.synchronize()
     r['mask_from_y_dy'] = _cmp(dyB, dyA, 1e-3)
     r['mask_from_y_sums'] = _cmp(sB, sA, 1e-5)
+    r['ok'] = all(v['ok'] for v in r.values())
+    return r
+
+
+@case('bn_finalize_apply_fused_matches_separate_kernels')
+def _bn_fused_fwd():
+    """One launch (finalize + apply, incl. the projection shortcut's BatchNorm) == stats -> finalize -> apply."""
+    import ctypes as C
+    from pmdist.ops import _lib, nn as nk
+    from pmdist.ops._lib import check, ptr, stream_ptr
+
+    class Fin(C.Structure):
+        _fields_ = [('stats', C.c_void_p), ('gamma', C.c_void_p), ('beta', C.c_void_p), ('running_mean', C.c_void_p),
+                    ('running_var', C.c_void_p), ('num_batches', C.c_void_p), ('scale', C.c_void_p), ('shift', C.c_void_p),
+                    ('mean', C.c_void_p), ('invstd', C.c_void_p), ('totals_scratch', C.c_void_p),
+                    ('recv_off', C.c_ulonglong), ('slot', C.c_int), ('pad_', C.c_int)]
+    lib = _lib.lib()
+    Cc, N, H = 128, 8, 8
+    rows = N * H * H
+    ys = [(_rand_bf16(N, H, H, Cc, seed=40 + i) * 1.3 + 0.2).to(torch.bfloat16) for i in range(2)]
+    gam = [torch.rand(Cc, device='cuda') + 0.5 for _ in range(2)]
+    bet = [torch.randn(Cc, device='cuda') * 0.1 for _ in range(2)]
+    stats = [nk.bn_stats(y) for y in ys]
+    # separate kernels (oracle), with their own running-stat buffers
+    rmA = [torch.zeros(Cc, device='cuda') for _ in range(2)]
+    rvA = [torch.ones(Cc, device='cuda') for _ in range(2)]
+    nbA = [torch.zeros(1, dtype=torch.int64, device='cuda') for _ in range(2)]
+    fin = [nk.bn_finalize([st], float(rows), g, b, rm, rv, nb) for st, g, b, rm, rv, nb in zip(stats, gam, bet, rmA, rvA, nbA)]
+    z_ref = nk.bn_apply(ys[0], fin[0][0], fin[0][1], True, ys[1], fin[1][0], fin[1][1])
+    # fused kernel
+    rmB = [torch.zeros(Cc, device='cuda') for _ in range(2)]
+    rvB = [torch.ones(Cc, device='cuda') for _ in range(2)]
+    nbB = [torch.zeros(1, dtype=torch.int64, device='cuda') for _ in range(2)]
+    outs = [[torch.empty(Cc, device='cuda') for _ in range(4)] for _ in range(2)]
+    fs = []
+    for i in range(2):
+        fs.append(Fin(stats[i].data_ptr(), gam[i].data_ptr(), bet[i].data_ptr(), rmB[i].data_ptr(), rvB[i].data_ptr(),
+                      nbB[i].data_ptr(), outs[i][0].data_ptr(), outs[i][1].data_ptr(), outs[i][2].data_ptr(),
+                      outs[i][3].data_ptr(), 0, 0, 0, 0))
+    z = torch.empty_like(ys[0])
+    check(lib.pmd_bn_finalize_apply(None, C.byref(fs[0]), C.byref(fs[1]), C.c_float(rows), C.c_float(0.1), C.c_float(1e-5),
+                                    ptr(ys[0]), ptr(ys[1]), C.c_int(1), ptr(z), C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
+    z1 = torch.empty_like(ys[0])          # single BatchNorm, plain residual
+    f_single = Fin(stats[0].data_ptr(), gam[0].data_ptr(), bet[0].data_ptr(), 0, 0, 0, outs[0][0].data_ptr(),
+                   outs[0][1].data_ptr(), outs[0][2].data_ptr(), outs[0][3].data_ptr(), 0, 0, 0, 0)
+    check(lib.pmd_bn_finalize_apply(None, C.byref(f_single), None, C.c_float(rows), C.c_float(0.1), C.c_float(1e-5),
+                                    ptr(ys[0]), ptr(ys[1]), C.c_int(1), ptr(z1), C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
+    torch.cuda.synchronize()
+    z1_ref = nk.bn_apply(ys[0], fin[0][0], fin[0][1], True, ys[1])
+    torch.cuda.synchronize()
+    r = {'z': _cmp(z, z_ref, 1e-3), 'z_plain_residual': _cmp(z1, z1_ref, 1e-3)}
+    for i in range(2):
+        r[f'scale{i}'] = _cmp(outs[i][0], fin[i][0], 1e-6)
+        r[f'mean{i}'] = _cmp(outs[i][2], fin[i][2], 1e-6)
+        r[f'invstd{i}'] = _cmp(outs[i][3], fin[i][3], 1e-6)
+        r[f'running_var{i}'] = _cmp(rvB[i], rvA[i], 1e-6)
+        r[f'nbt{i}'] = {'ok': int(nbB[i]) == 1}
     r['ok'] = all(v['ok'] for v in r.values())
     return r
