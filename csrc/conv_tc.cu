@@ -54,7 +54,10 @@ __device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* raw) {
 }
 
 // ============================================================================ fprop / dgrad
-template <int BN, int STAGES>
+// B_MN: the B operand is consumed MN-major -- dgrad reading the SAME KRSC weights as fprop ([k][tap][c]: for
+// one tap a [k rows][c contiguous] matrix, i.e. the output-channel dim of dgrad is the contiguous one), so no
+// transposed RSCK copy of the weights has to be maintained.  The tile is BN/64 boxes of [64 k][64 c].
+template <int BN, int STAGES, bool B_MN = false>
 __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
   constexpr int kStageBytes = kABytes + BN * 128;
   extern __shared__ uint8_t smem_raw[];
@@ -101,16 +104,21 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         uint8_t* sb = sa + kABytes;
         mbar_expect_tx(&bars->full[s], kStageBytes);
         tma_load_4d(&p.a[kb.a_map], &bars->full[s], sa, kb.a_ch, w0 + kb.dw, h0 + kb.dh, n0);
-        if (p.b_tap_last)
+        if (B_MN) {
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j)   // KRSC map (c, tap, k): 64 output channels x 64 reduction rows per box
+            tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb + j * 8192, ntile * BN + j * 64, kb.tap, kb.b_c0);
+        } else if (p.b_tap_last) {
           tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, ntile * BN, kb.tap);
-        else
+        } else {
           tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, kb.tap, ntile * BN);
+        }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, false);
+      constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, B_MN);
       for (int i = 0; i < nkb; ++i) {
         const int s = i % STAGES;
         const uint32_t ph = (i / STAGES) & 1;
@@ -119,9 +127,10 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
         const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {   // 64-channel chunk = 4 x (K = 16)
-          umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 32, 16, 1024),
-                    make_smem_desc_sw128(b_addr + k * 32, 16, 1024), idesc, (i | k) != 0 ? 1u : 0u);
+        for (int k = 0; k < 4; ++k) {   // 64-deep reduction chunk = 4 x (K = 16)
+          const uint64_t bdesc = B_MN ? make_smem_desc_sw128(b_addr + k * 2048, 8192, 1024)
+                                      : make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+          umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 32, 16, 1024), bdesc, idesc, (i | k) != 0 ? 1u : 0u);
         }
         umma_commit(&bars->empty[s]);   // frees the smem slot once these MMAs have read it
       }
@@ -900,7 +909,8 @@ int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc,
 }
 
 int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const PmdConvShape* s2,
-                       const void* dy2, const void* w2_rsck, const void* addend, void* dx, ConvGemmParams* out) {
+                       const void* dy2, const void* w2_rsck, const void* addend, void* dx, ConvGemmParams* out,
+                       bool w_is_krsc) {
   PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
   ConvGemmParams& p = *out;
   memset(&p, 0, sizeof(p));
@@ -936,7 +946,14 @@ int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck
   if (act_map(&p.a[0], dy, s.N, Ho, Wo, s.K, 1, 0, 0, p.w_box, p.h_box, p.n_box)) return -1;
   if (s2 != nullptr && act_map(&p.a[1], dy2, s.N, Ho, Wo, s2->K, 1, 0, 0, p.w_box, p.h_box, p.n_box)) return -1;
   // B operands: RSCK weights as (k inner, c rows, tap)
+  p.b_mn_major = w_is_krsc ? 1 : 0;
   auto wmap = [&](CUtensorMap* m, const void* w, const PmdConvShape& cs) {
+    if (w_is_krsc) {   // (c inner, tap, k): boxes of 64 c x 64 k, consumed MN-major
+      const uint64_t dims[3] = {(uint64_t)cs.C, (uint64_t)(cs.R * cs.R), (uint64_t)cs.K};
+      const uint64_t strides[2] = {(uint64_t)cs.C * 2, (uint64_t)(cs.R * cs.R) * cs.C * 2};
+      const uint32_t box[3] = {64u, 1u, 64u};
+      return encode_map(m, w, 3, dims, strides, box);
+    }
     const uint64_t dims[3] = {(uint64_t)cs.K, (uint64_t)cs.C, (uint64_t)(cs.R * cs.R)};
     const uint64_t strides[2] = {(uint64_t)cs.K * 2, (uint64_t)cs.C * cs.K * 2};
     const uint32_t box[3] = {64u, (uint32_t)p.bn_tile, 1u};
@@ -1128,15 +1145,15 @@ int conv_halo_mode() {
 bool conv_halo_enabled() { return conv_halo_mode() == 1; }
 bool conv_halo_dgrad_enabled() { return conv_halo_mode() >= 1; }
 
-template <int BN, int ST>
+template <int BN, int ST, bool B_MN = false>
 static int launch_conv_gemm_t(const ConvGemmParams& p, const dim3& grid, cudaStream_t stream) {
   constexpr int smem = ST * (kABytes + BN * 128) + sizeof(PipeBars<ST>) + 1024;
   static bool once = false;
   if (!once) {
-    if (set_smem(conv_gemm_kernel<BN, ST>, smem)) return -1;
+    if (set_smem(conv_gemm_kernel<BN, ST, B_MN>, smem)) return -1;
     once = true;
   }
-  conv_gemm_kernel<BN, ST><<<grid, kThreads, smem, stream>>>(p);
+  conv_gemm_kernel<BN, ST, B_MN><<<grid, kThreads, smem, stream>>>(p);
   return 0;
 }
 
@@ -1180,7 +1197,9 @@ int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream) {
   static const int st64 = stages_from_env("PMD_GEMM64_STAGES", 2), st128 = stages_from_env("PMD_GEMM128_STAGES", 3);
   static const bool persistent = getenv("PMD_GEMM_PERSISTENT") != nullptr && atoi(getenv("PMD_GEMM_PERSISTENT")) != 0;
   int rc;
-  if (persistent) {
+  if (p.b_mn_major) {
+    rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true>(p, grid, stream) : launch_conv_gemm_t<128, 3, true>(p, grid, stream);
+  } else if (persistent) {
     if (p.bn_tile == 64)
       rc = st64 == 2 ? launch_conv_gemm_persistent_t<64, 2>(p, stream)
                      : (st64 == 4 ? launch_conv_gemm_persistent_t<64, 4>(p, stream)
@@ -1250,6 +1269,14 @@ extern "C" PMD_API int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, c
   }
   ConvGemmParams p;
   if (build_dgrad_params(*s, d_dy, d_w_rsck, s2, d_dy2, d_w2_rsck, d_addend, d_dx, &p)) return -1;
+  return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" PMD_API int pmd_conv_dgrad_krsc(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc,
+                                           const PmdConvShape* s2, const void* d_dy2, const void* d_w2_krsc,
+                                           const void* d_addend, void* d_dx, void* stream) {
+  ConvGemmParams p;
+  if (build_dgrad_params(*s, d_dy, d_w_krsc, s2, d_dy2, d_w2_krsc, d_addend, d_dx, &p, true)) return -1;
   return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
 }
 

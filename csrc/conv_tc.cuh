@@ -33,6 +33,7 @@ struct ConvGemmParams {
   int w_box, h_box, n_box, tiles_w, tiles_h, tiles_n;
   int n_classes;
   int b_tap_last;            // weight-map coordinate order: 0 = (c, tap, n) [KRSC], 1 = (c, n, tap) [RSCK]
+  int b_mn_major;            // dgrad straight from KRSC weights: B tile = [64 k][64 c] boxes, MN-major descriptors
   int out_channels;          // total channels of the output tensor
   int bn_tile;               // 64 or 128
   float* stats;              // optional [2 * out_channels]
@@ -93,7 +94,8 @@ bool conv_halo_dgrad_enabled();  // column-patch kernel for dgrad (PMD_CONV_HALO
 int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
                        ConvGemmParams* out);
 int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const PmdConvShape* s2,
-                       const void* dy2, const void* w2_rsck, const void* addend, void* dx, ConvGemmParams* out);
+                       const void* dy2, const void* w2_rsck, const void* addend, void* dx, ConvGemmParams* out,
+                       bool w_is_krsc = false);
 int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, float* dw, int split, int sm_count,
                        WgradParams* out, int rsc_override = 0, int c_valid = 64);
 int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream);

@@ -102,7 +102,7 @@ struct PmdEngine {
   double* metrics = nullptr;
   // local buffers
   std::vector<void*> owned;
-  bf16* wt = nullptr;                 // RSCK copies for dgrad (same element offsets as the slab)
+  bf16* wt = nullptr;                 // RSCK copies, only for the opt-in column-patch dgrad (same offsets as the slab)
   PmdRepackEntry* d_repack = nullptr;
   int n_repack = 0;
   long long repack_max = 0;
@@ -284,6 +284,7 @@ int allocate(PmdEngine* e) {
       e->repack_max = el > e->repack_max ? el : e->repack_max;
     }
   }
+  if (!conv_halo_dgrad_enabled()) rep.clear();   // dgrad reads the KRSC weights directly (MN-major B): no RSCK copy
   e->n_repack = static_cast<int>(rep.size());
   if (e->n_repack > 0) {
     E_CHECK(e->dalloc(&e->d_repack, e->n_repack));
@@ -359,8 +360,8 @@ Plan* get_plan(PmdEngine* e, int n) {
       Conv& cv = e->convs[b.main[j]];
       PmdConvShape s = cv.s;
       s.N = n;
-      if (build_dgrad_params(s, cv.dy, e->wt + cv.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_mid[j - 1],
-                             &pl->inner_dgrad[b.main[j]]))
+      if (build_dgrad_params(s, cv.dy, e->wbf16 + cv.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_mid[j - 1],
+                             &pl->inner_dgrad[b.main[j]], true))
         return nullptr;
       if (halo_dgrad && conv_halo_supported(s)) {
         if (build_dgrad_halo_params(s, cv.dy, e->wt + cv.w_off, nullptr, b.dz_mid[j - 1], &pl->inner_dgrad_h[b.main[j]]))
@@ -375,8 +376,8 @@ Plan* get_plan(PmdEngine* e, int n) {
       Conv& cs = e->convs[b.sc];
       PmdConvShape ss = cs.s;
       ss.N = n;
-      if (build_dgrad_params(s0, c0.dy, e->wt + c0.w_off, &ss, cs.dy, e->wt + cs.w_off, nullptr, b.dz_in,
-                             &pl->block_dgrad[bi]))
+      if (build_dgrad_params(s0, c0.dy, e->wbf16 + c0.w_off, &ss, cs.dy, e->wbf16 + cs.w_off, nullptr, b.dz_in,
+                             &pl->block_dgrad[bi], true))
         return nullptr;
     } else if (b.sc >= 0) {
       // Bottleneck stage entry: conv0 is 1x1 stride 1 but the projection is 1x1 stride 2.  The shortcut's
@@ -384,15 +385,15 @@ Plan* get_plan(PmdEngine* e, int n) {
       Conv& cs = e->convs[b.sc];
       PmdConvShape ss = cs.s;
       ss.N = n;
-      if (build_dgrad_params(ss, cs.dy, e->wt + cs.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_in,
-                             &pl->sc_dgrad[bi]))
+      if (build_dgrad_params(ss, cs.dy, e->wbf16 + cs.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_in,
+                             &pl->sc_dgrad[bi], true))
         return nullptr;
-      if (build_dgrad_params(s0, c0.dy, e->wt + c0.w_off, nullptr, nullptr, nullptr, b.dz_in, b.dz_in,
-                             &pl->block_dgrad[bi]))
+      if (build_dgrad_params(s0, c0.dy, e->wbf16 + c0.w_off, nullptr, nullptr, nullptr, b.dz_in, b.dz_in,
+                             &pl->block_dgrad[bi], true))
         return nullptr;
     } else {
-      if (build_dgrad_params(s0, c0.dy, e->wt + c0.w_off, nullptr, nullptr, nullptr, b.g_out, b.dz_in,
-                             &pl->block_dgrad[bi]))
+      if (build_dgrad_params(s0, c0.dy, e->wbf16 + c0.w_off, nullptr, nullptr, nullptr, b.g_out, b.dz_in,
+                             &pl->block_dgrad[bi], true))
         return nullptr;
       if (halo_dgrad && conv_halo_supported(s0)) {
         if (build_dgrad_halo_params(s0, c0.dy, e->wt + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_h[bi])) return nullptr;

@@ -45,6 +45,10 @@ int pmd_conv_fprop(const PmdConvShape* s, const void* d_x, const void* d_w_krsc,
  * d_addend (may be NULL) is an NHWC bf16 tensor shaped like dx (identity-shortcut gradient). */
 int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, const void* d_w_rsck, const PmdConvShape* s2,
                    const void* d_dy2, const void* d_w2_rsck, const void* d_addend, void* d_dx, void* stream);
+/* Same as pmd_conv_dgrad but reads the KRSC weights fprop uses (consumed MN-major by tcgen05): no transposed RSCK
+ * copy of the weights is needed at all. */
+int pmd_conv_dgrad_krsc(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const PmdConvShape* s2,
+                        const void* d_dy2, const void* d_w2_krsc, const void* d_addend, void* d_dx, void* stream);
 /* dw (fp32, KRSC) += x^T * dy, reduction over all N*Ho*Wo pixels split over `split_k` CTAs per
  * output tile (0 = choose); partial tiles are added with red.global.add.f32, so d_dw is an
  * accumulator the caller zeroes (it is a slice of the flat gradient bucket slab). */

@@ -50,23 +50,24 @@ def conv_fprop(x: torch.Tensor, w_krsc: torch.Tensor, stride: int = 1, stats: Op
 
 def conv_dgrad(dy: torch.Tensor, w: torch.Tensor, x_shape: Tuple[int, int, int, int], R: int, stride: int = 1,
                second: Optional[Tuple[torch.Tensor, torch.Tensor, int]] = None,
-               addend: Optional[torch.Tensor] = None, direct: bool = False) -> torch.Tensor:
-    """``w`` is RSCK for the tensor-core path and KRSC for ``direct``.  ``second`` = (dy2, w2_rsck, R2)
-    fuses a second convolution over the same input (projection shortcut)."""
+               addend: Optional[torch.Tensor] = None, direct: bool = False, krsc: bool = False) -> torch.Tensor:
+    """``w`` is RSCK for the tensor-core path (KRSC with ``krsc=True``: MN-major B operand, no transposed copy) and
+    KRSC for ``direct``.  ``second`` = (dy2, w2, R2) fuses a second convolution over the same input (projection
+    shortcut); its weight uses the same layout as ``w``."""
     K = dy.shape[-1]
     dx = torch.empty(x_shape, dtype=torch.bfloat16, device=dy.device)
     s = _shape(x_shape, K, R, stride)
     if direct:
         check(_lib.lib().pmd_conv_dgrad_direct(C.byref(s), ptr(dy), ptr(w), ptr(dx), stream_ptr()))
         return dx
+    fn = _lib.lib().pmd_conv_dgrad_krsc if krsc else _lib.lib().pmd_conv_dgrad
     if second is not None:
         dy2, w2, R2 = second
         s2 = _shape(x_shape, dy2.shape[-1], R2, stride)
-        check(_lib.lib().pmd_conv_dgrad(C.byref(s), ptr(dy), ptr(w), C.byref(s2), ptr(dy2), ptr(w2), ptr(addend),
+        check(fn(C.byref(s), ptr(dy), ptr(w), C.byref(s2), ptr(dy2), ptr(w2), ptr(addend),
                                         ptr(dx), stream_ptr()))
     else:
-        check(_lib.lib().pmd_conv_dgrad(C.byref(s), ptr(dy), ptr(w), None, None, None, ptr(addend), ptr(dx),
-                                        stream_ptr()))
+        check(fn(C.byref(s), ptr(dy), ptr(w), None, None, None, ptr(addend), ptr(dx), stream_ptr()))
     return dx
 
 

@@ -92,7 +92,7 @@ def _dgrad_ref(dy_nhwc, w_kcrs, x_shape_nhwc, stride):
     return dx.permute(0, 2, 3, 1).contiguous()
 
 
-def _dgrad_case(N, H, C, K, R, stride, shortcut_K=0, addend=False, direct=False):
+def _dgrad_case(N, H, C, K, R, stride, shortcut_K=0, addend=False, direct=False, krsc=False):
     from pmdist.ops import conv as cv
     Ho = cv.out_dim(H, R, stride)
     dy = _rand_bf16(N, Ho, Ho, K, seed=3)
@@ -103,13 +103,15 @@ def _dgrad_case(N, H, C, K, R, stride, shortcut_K=0, addend=False, direct=False)
         dy2 = _rand_bf16(N, Ho, Ho, shortcut_K, seed=5)
         w2 = _rand_bf16(shortcut_K, C, 1, 1, scale=1.0 / math.sqrt(shortcut_K), seed=6)
         ref = ref + _dgrad_ref(dy2, w2, (N, H, H, C), stride)
-        second = (dy2, cv.rsck_from_torch(w2), 1)
+        second = (dy2, cv.krsc_from_torch(w2) if krsc else cv.rsck_from_torch(w2), 1)
     add = None
     if addend:
         add = _rand_bf16(N, H, H, C, seed=7)
         ref = ref + add.float()
     if direct:
         dx = cv.conv_dgrad(dy, cv.krsc_from_torch(w), (N, H, H, C), R, stride, direct=True)
+    elif krsc:
+        dx = cv.conv_dgrad(dy, cv.krsc_from_torch(w), (N, H, H, C), R, stride, second=second, addend=add, krsc=True)
     else:
         dx = cv.conv_dgrad(dy, cv.rsck_from_torch(w), (N, H, H, C), R, stride, second=second, addend=add)
     torch.cuda.synchronize()
@@ -128,6 +130,18 @@ for _name, _args in {
 }.items():
     CASES[_name] = (lambda a=_args: _dgrad_case(*a))
 CASES['dgrad_direct_c16_s2'] = lambda: _dgrad_case(2, 8, 16, 24, 3, 2, direct=True)
+# dgrad straight from the KRSC weights (MN-major B operand): the path the engine uses
+for _name, _args in {
+    'dgrad_krsc_3x3_s1_c64_k64_h32': (4, 32, 64, 64, 3, 1),
+    'dgrad_krsc_3x3_s1_c128_k128_h16_addend': (4, 16, 128, 128, 3, 1, 0, True),
+    'dgrad_krsc_3x3_s2_c64_k128_h32_shortcut': (4, 32, 64, 128, 3, 2, 128),
+    'dgrad_krsc_1x1_s2_c64_k128_h32': (4, 32, 64, 128, 1, 2),
+    'dgrad_krsc_1x1_s1_c256_k64_h8_shortcut': (8, 8, 256, 64, 1, 1, 256),
+    'dgrad_krsc_3x3_s1_c512_k512_h4': (16, 4, 512, 512, 3, 1),
+    'dgrad_krsc_3x3_s2_c256_k512_h8_n3_shortcut': (3, 8, 256, 512, 3, 2, 512),
+}.items():
+    CASES[_name] = (lambda a=_args: _dgrad_case(*a[:6], shortcut_K=(a[6] if len(a) > 6 else 0),
+                                                addend=(a[7] if len(a) > 7 else False), krsc=True))
 
 
 # ------------------------------------------------------------------ wgrad
