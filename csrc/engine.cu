@@ -556,7 +556,7 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
   const PmdEngineConfig& c = e->cfg;
   const int n = pl->n;
   E_CHECK(pmd_augment_im2col(e->in_u8, e->in_aug, n, c.image_hw, c.image_hw, 8, e->x0, st));
-  auto conv_fwd = [&](int ci) -> int {
+  auto conv_fwd = [&](int ci, cudaStream_t st) -> int {
     Conv& cv = e->convs[ci];
     if (cv.tc && pl->conv[ci].halo) {
       E_CHECK(launch_conv_halo(train ? pl->conv[ci].fprop_h : pl->conv[ci].fprop_eval_h, st));
@@ -570,20 +570,30 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
     }
     return 0;
   };
-  E_CHECK(conv_fwd(0));
+  E_CHECK(conv_fwd(0, st));
   {
     Conv& cv = e->convs[0];
     E_CHECK(bn_apply_step(e, 0, -1, nullptr, e->z_stem, 1LL * n * cv.Ho * cv.Wo, train, st));
   }
   for (Block& b : e->blocks) {
+    cudaEvent_t sc_done = nullptr;
+    if (b.sc >= 0) {
+      // the projection shortcut only needs the block input: run it on the side stream next to the main path
+      cudaEvent_t ev = e->wg_events[(e->wg_event_next++) % e->wg_events.size()];
+      PMD_CHECK_CUDA(cudaEventRecord(ev, st));
+      PMD_CHECK_CUDA(cudaStreamWaitEvent(e->wg_stream, ev, 0));
+      E_CHECK(conv_fwd(b.sc, e->wg_stream));
+      sc_done = e->wg_events[(e->wg_event_next++) % e->wg_events.size()];
+      PMD_CHECK_CUDA(cudaEventRecord(sc_done, e->wg_stream));
+    }
     for (int j = 0; j < b.n_main; ++j) {
-      E_CHECK(conv_fwd(b.main[j]));
+      E_CHECK(conv_fwd(b.main[j], st));
       if (j < b.n_main - 1) {
         Conv& cv = e->convs[b.main[j]];
         E_CHECK(bn_apply_step(e, b.main[j], -1, nullptr, b.z_mid[j], 1LL * n * cv.Ho * cv.Wo, train, st));
       }
     }
-    if (b.sc >= 0) E_CHECK(conv_fwd(b.sc));
+    if (sc_done != nullptr) PMD_CHECK_CUDA(cudaStreamWaitEvent(st, sc_done, 0));
     Conv& last = e->convs[b.main[b.n_main - 1]];
     E_CHECK(bn_apply_step(e, b.main[b.n_main - 1], b.sc, b.sc >= 0 ? nullptr : b.z_in, b.z_out,
                           1LL * n * last.Ho * last.Wo, train, st));
@@ -752,7 +762,7 @@ extern "C" PMD_API int pmd_engine_create(const PmdEngineConfig* cfg, PmdComm* co
   PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
   PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->main_stream, cudaStreamNonBlocking));
   PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->wg_stream, cudaStreamNonBlocking));
-  e->wg_events.resize(2 * (cfg->n_convs + cfg->n_buckets) + 8);
+  e->wg_events.resize(4 * (cfg->n_convs + cfg->n_buckets) + 16);
   for (auto& ev : e->wg_events) PMD_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   PMD_CHECK_CUDA(cudaEventCreateWithFlags(&e->ev_in, cudaEventDisableTiming));
   PMD_CHECK_CUDA(cudaEventCreateWithFlags(&e->ev_out, cudaEventDisableTiming));
