@@ -32,10 +32,21 @@ class NativeError(RuntimeError):
 
 
 def build(force: bool = False) -> str:
+    """Builds the library in-tree (tools/build_native.py).  Serialised with a file lock: under torchrun all
+    ranks of a fresh checkout arrive here at once and must not run nvcc over each other's objects."""
+    import fcntl
     sys.path.insert(0, os.path.join(REPO_ROOT, 'tools'))
+    os.makedirs(os.path.dirname(LIB_PATH), exist_ok=True)
     try:
         import build_native
-        return build_native.build(force=force)
+        with open(os.path.join(os.path.dirname(LIB_PATH), '.build.lock'), 'w') as lock:
+            fcntl.flock(lock, fcntl.LOCK_EX)
+            try:
+                if os.path.exists(LIB_PATH) and not force:
+                    return build_native.build(force=False)      # up-to-date check only (another rank built it)
+                return build_native.build(force=force)
+            finally:
+                fcntl.flock(lock, fcntl.LOCK_UN)
     finally:
         sys.path.pop(0)
 

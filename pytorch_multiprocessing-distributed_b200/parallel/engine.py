@@ -83,7 +83,7 @@ class NativeEngine:
         infos = params_of(model)
         comm.verify_same('model structure', repr([(i.name, i.numel) for i in infos]).encode())
 
-        first_cap, cap = (4 * MiB, 16 * MiB) if bucket_mb <= 0 else (int(bucket_mb * MiB),) * 2
+        first_cap, cap = (1 * MiB, 4 * MiB) if bucket_mb <= 0 else (int(bucket_mb * MiB),) * 2
         while True:
             buckets, total = plan_buckets(infos, first_cap, cap, align_elems=ALIGN)
             if len(buckets) <= MAX_BUCKETS:
