@@ -661,3 +661,37 @@ extern "C" PMD_API int pmd_comm_host_barrier(PmdComm* c) { return pmd_rdv_barrie
 extern "C" PMD_API int pmd_comm_allgather_host(PmdComm* c, const void* in, int bytes, void* out) {
   return pmd_rdv_allgather(c->rdv, in, bytes, out);
 }
+
+// ------------------------------------------------------------------------------------ topology probe
+// What NCCL discovers internally (NVML / sysfs topology graph) reduced to what this transport needs to know
+// about a single NVSwitch box: for every ordered device pair whether peer access exists, its performance rank,
+// whether native atomics work across the link, and per device whether multicast (NVLS) is offered.
+extern "C" PMD_API int pmd_topology_probe(int max_devices, int* n_devices, int* can_access /*[max*max]*/,
+                                          int* perf_rank /*[max*max]*/, int* native_atomics /*[max*max]*/,
+                                          int* multicast /*[max]*/) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    set_error("cudaGetDeviceCount failed (no CUDA device?)");
+    return -1;
+  }
+  if (n > max_devices) n = max_devices;
+  *n_devices = n;
+  Driver& d = driver();
+  for (int a = 0; a < n; ++a) {
+    int mc = 0;
+    if (d.ok) d.DeviceGetAttribute(&mc, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, a);
+    multicast[a] = mc;
+    for (int b = 0; b < n; ++b) {
+      int acc = a == b, rank = 0, atom = a == b;
+      if (a != b) {
+        cudaDeviceCanAccessPeer(&acc, a, b);
+        cudaDeviceGetP2PAttribute(&rank, cudaDevP2PAttrPerformanceRank, a, b);
+        cudaDeviceGetP2PAttribute(&atom, cudaDevP2PAttrNativeAtomicSupported, a, b);
+      }
+      can_access[a * max_devices + b] = acc;
+      perf_rank[a * max_devices + b] = rank;
+      native_atomics[a * max_devices + b] = atom;
+    }
+  }
+  return 0;
+}

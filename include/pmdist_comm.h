@@ -63,6 +63,11 @@ int pmd_rdv_allgather(PmdRendezvous* r, const void* in, int bytes, void* out);
 int pmd_rdv_barrier(PmdRendezvous* r);
 int pmd_rdv_allgather_fds(PmdRendezvous* r, int fd, int* fds_out);
 
+/* ---- topology probe (no communicator needed): peer reachability, link performance rank, cross-link atomics
+ * for every ordered device pair (row-major [max_devices x max_devices]) and multicast/NVLS support per device. */
+int pmd_topology_probe(int max_devices, int* n_devices, int* can_access, int* perf_rank, int* native_atomics,
+                       int* multicast);
+
 /* ---- communicator */
 int pmd_comm_create(int rank, int world, const char* run_id, int device, unsigned long long heap_bytes, int flags,
                     PmdComm** out);

@@ -24,3 +24,12 @@ def test_native_library_is_loaded_and_counts_launches():
     nk.bn_stats(torch.zeros(8, 8, 8, 64, dtype=torch.bfloat16, device='cuda'))
     assert _lib.launch_count() == before + 1
     assert any('libpmdist.so' in ln for ln in open('/proc/self/maps'))
+
+
+@pytest.mark.gpu
+def test_topology_probe_reports_devices():
+    from pmdist.parallel.topology import describe, probe
+    p = probe()
+    assert p['devices'] >= 1 and len(p['can_access_peer']) == p['devices']
+    assert all(p['can_access_peer'][i][i] == 1 for i in range(p['devices']))
+    assert 'GPU(s)' in describe(p)
