@@ -57,6 +57,26 @@ __device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* raw) {
 // B_MN: the B operand is consumed MN-major -- dgrad reading the SAME KRSC weights as fprop ([k][tap][c]: for
 // one tap a [k rows][c contiguous] matrix, i.e. the output-channel dim of dgrad is the contiguous one), so no
 // transposed RSCK copy of the weights has to be maintained.  The tile is BN/64 boxes of [64 k][64 c].
+__device__ __forceinline__ void trace_mark(const ConvGemmParams& p, int slot) {
+  if (p.trace == nullptr) return;
+  const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  if (cta < p.trace_cap) p.trace[static_cast<long long>(cta) * kTraceSlots + slot] = clock64();
+}
+__device__ __forceinline__ void trace_begin(const ConvGemmParams& p, int tiles) {
+  if (p.trace == nullptr) return;
+  const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  if (cta >= p.trace_cap) return;
+  long long* t = p.trace + static_cast<long long>(cta) * kTraceSlots;
+  unsigned long long ns;
+  unsigned sm;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+  t[kTrEntry] = clock64();
+  t[kTrGlobalNs] = static_cast<long long>(ns);
+  t[kTrSm] = sm;
+  t[kTrTiles] = tiles;
+}
+
 template <int BN, int STAGES, bool B_MN = false>
 __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
   constexpr int kStageBytes = kABytes + BN * 128;
@@ -75,6 +95,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
   const int kb0 = p.kb_begin[cls], nkb = p.kb_count[cls];
 
   if (threadIdx.x == 0) {
+    trace_begin(p, 1);
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&bars->full[s], 1);
@@ -91,6 +112,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
+  if (threadIdx.x == 0) trace_mark(p, kTrSetup);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -113,6 +135,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         } else {
           tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, kb.tap, ntile * BN);
         }
+        if (i == 0) trace_mark(p, kTrFirstLoad);
       }
     }
   } else if (warp == 1) {
@@ -124,6 +147,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         const uint32_t ph = (i / STAGES) & 1;
         mbar_wait(&bars->full[s], ph);
         tc_fence_after();
+        if (i == 0) trace_mark(p, kTrFirstFull);
         const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
         const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
@@ -135,6 +159,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         umma_commit(&bars->empty[s]);   // frees the smem slot once these MMAs have read it
       }
       if (nkb > 0) umma_commit(&bars->tmem_full);
+      trace_mark(p, kTrMmaIssued);
     }
   } else {
     // ------------------------------------------------------------------ epilogue (128 threads)
@@ -153,6 +178,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
       mbar_wait(&bars->tmem_full, 0);
       tc_fence_after();
     }
+    if (threadIdx.x == 64) trace_mark(p, kTrAccReady);
     uint8_t* stage_out = smem;           // pipeline buffers are idle now: reuse them as the store staging
 #pragma unroll
     for (int hf = 0; hf < BN / 64; ++hf) {
@@ -201,6 +227,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
     fence_proxy_async_smem();
     asm volatile("bar.sync 1, 128;" ::: "memory");
     const int et = threadIdx.x - 64;
+    if (et == 0) trace_mark(p, kTrStaged);
     if (et == 0) {
 #pragma unroll
       for (int hf = 0; hf < BN / 64; ++hf)
@@ -227,9 +254,11 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
       }
     }
     if (et == 0) tma_store_wait_read0();
+    if (et == 0) trace_mark(p, kTrEpiDone);
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) trace_mark(p, kTrExit);
   if (warp == 1) tmem_dealloc<BN>(tmem_base);
 }
 
@@ -284,6 +313,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
+    trace_begin(p, (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x));
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&bars->full[s], 1);
@@ -303,6 +333,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
+  if (threadIdx.x == 0) trace_mark(p, kTrSetup);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -323,6 +354,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
             tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, c.ntile * BN, kb.tap);
           else
             tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, kb.tap, c.ntile * BN);
+          if (it == 0) trace_mark(p, kTrFirstLoad);
         }
       }
     }
@@ -343,6 +375,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(&bars->full[s], ph);
           tc_fence_after();
+          if (it == 0) trace_mark(p, kTrFirstFull);
           const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
           const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
@@ -353,6 +386,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
           umma_commit(&bars->empty[s]);
         }
         umma_commit(&bars->tmem_full[acc]);
+        if (jm == 0) trace_mark(p, kTrMmaIssued);
         ++jm;
       }
     }
@@ -380,6 +414,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
         mbar_wait(&bars->tmem_full[acc], use & 1);
         tc_fence_after();
       }
+      if (et == 0 && jm == 0) trace_mark(p, kTrAccReady);
       // the previous tile's TMA store must have finished reading the staging buffer (and every thread must
       // have finished its statistics pass over it) before anybody overwrites it
       if (et == 0 && store_pending) tma_store_wait_read0();
@@ -436,6 +471,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
       }
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (et == 0 && !store_pending) trace_mark(p, kTrStaged);
       if (et == 0) {
 #pragma unroll
         for (int hf = 0; hf < BN / 64; ++hf)
@@ -463,9 +499,11 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
       }
     }
     if (et == 0 && store_pending) tma_store_wait_read0();
+    if (et == 0) trace_mark(p, kTrEpiDone);       // end of the LAST tile's epilogue
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) trace_mark(p, kTrExit);
   if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
 }
 
@@ -663,6 +701,275 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_halo_kernel(const __grid_c
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<BN>(tmem_base);
+}
+
+// ============================================================================ 3x3, C = K = 64: weights resident
+// The 64-channel 3x3 layers (32x32 maps) are the worst case for the per-tap kernel: a 128x64 tile needs only 36
+// MMAs (1152 tensor cycles) but pulls 216 KB of operands through L2 (the activation brick nine times plus the
+// 72 KB of weights once per tile) and pays the whole CTA set-up for it; tools/conv_trace.py shows a CTA lifetime
+// of ~13.7k cycles of which the tensor pipe works ~1.2k.  This kernel removes both costs:
+//   * persistent: one CTA per SM walks tiles t = blockIdx.x, + gridDim.x, ...; barriers, TMEM and tensor maps are
+//     set up once;
+//   * the nine 64x64 weight slices (72 KB) are loaded ONCE per CTA and stay in shared memory;
+//   * activations arrive as column patches (see conv_gemm_halo_kernel): 3 x 18 KB per tile instead of 9 x 16 KB,
+//     through a ring of six patch slots that runs ahead across tile boundaries;
+//   * two accumulators in TMEM and TWO epilogue warpgroups (tiles alternate between them), each with its own
+//     staging buffer, so tcgen05.ld -> bf16 -> smem -> TMA store of tile j overlaps the MMAs of tiles j+1, j+2;
+//   * BatchNorm statistics are accumulated in registers over all tiles of the CTA and leave as 128 red.global
+//     per CTA instead of 256 per tile.
+// L2->SM traffic per tile drops from 216 KB to 54 KB.  B_MN = true is dgrad straight from the KRSC weights (the
+// very same shared-memory image, read MN-major, taps flipped).
+constexpr int kResSlots = 6;
+constexpr int kResThreads = 64 + 256;
+constexpr int kResWBytes = 9 * 8192;
+struct ResBars {
+  uint64_t a_full[kResSlots], a_empty[kResSlots];
+  uint64_t w_full;
+  uint64_t tmem_full[2], tmem_empty[2];
+  uint32_t tmem_base;
+  float stat_part[2][128];      // per epilogue group: [sum 64 | sum of squares 64]
+};
+constexpr int kResSmem = kResWBytes + kResSlots * kColPatchBytes + 2 * kABytes + sizeof(ResBars) + 1024;
+
+template <bool B_MN>
+__global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __grid_constant__ ConvHaloParams p,
+                                                                       int total_tiles) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  uint8_t* smem_w = smem;
+  uint8_t* smem_a = smem + kResWBytes;
+  uint8_t* smem_out = smem_a + kResSlots * kColPatchBytes;
+  ResBars* bars = reinterpret_cast<ResBars*>(smem_out + 2 * kABytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_per_img = p.tiles_w * p.tiles_h;
+
+  const bool tracing = p.trace != nullptr && static_cast<int>(blockIdx.x) < p.trace_cap;
+  long long* trec = tracing ? p.trace + static_cast<long long>(blockIdx.x) * kTraceSlots : nullptr;
+  if (threadIdx.x == 0) {
+    if (tracing) {
+      unsigned long long ns;
+      unsigned sm;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+      trec[kRtEntry] = clock64();
+      trec[kTrGlobalNs] = static_cast<long long>(ns);
+      trec[kTrSm] = sm;
+      trec[kTrTiles] = (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    }
+#pragma unroll
+    for (int s = 0; s < kResSlots; ++s) {
+      mbar_init(&bars->a_full[s], 1);
+      mbar_init(&bars->a_empty[s], 1);
+    }
+    mbar_init(&bars->w_full, 1);
+    mbar_init(&bars->tmem_full[0], 1);
+    mbar_init(&bars->tmem_full[1], 1);
+    mbar_init(&bars->tmem_empty[0], 128);
+    mbar_init(&bars->tmem_empty[1], 128);
+    fence_mbar_init();
+    prefetch_tmap(&p.a);
+    prefetch_tmap(&p.b);
+    prefetch_tmap(&p.out);
+  }
+  if (warp == 1) tmem_alloc<128>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+  if (threadIdx.x == 0 && tracing) trec[kRtSetup] = clock64();
+  long long w0c = 0, w1c = 0, w2c = 0, tt = 0;      // trace accumulators (dead code unless tracing)
+#define RT_WAIT(acc, stmt)          \
+  do {                              \
+    if (tracing) tt = clock64();    \
+    stmt;                           \
+    if (tracing) acc += clock64() - tt; \
+  } while (0)
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      mbar_expect_tx(&bars->w_full, kResWBytes);
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap)      // KRSC map (c, tap, k): box = 64 k-rows x 64 c
+        tma_load_3d(&p.b, &bars->w_full, smem_w + tap * 8192, 0, tap, 0);
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int n0 = t / tiles_per_img, r = t % tiles_per_img;
+        const int h0 = (r / p.tiles_w) * 16, w0 = (r % p.tiles_w) * 8;
+#pragma unroll
+        for (int q = 0; q < 3; ++q, ++it) {
+          const int s = it % kResSlots;
+          RT_WAIT(w0c, mbar_wait(&bars->a_empty[s], ((it / kResSlots) & 1) ^ 1u));
+          mbar_expect_tx(&bars->a_full[s], kColPatchBytes);
+          tma_load_4d(&p.a, &bars->a_full[s], smem_a + s * kColPatchBytes, 0, w0 + q - 1, h0 - 1, n0);
+        }
+      }
+      if (tracing) trec[kRtProdWaitEmpty] = w0c;
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, 64, false, B_MN);
+      const uint32_t w_addr = smem_u32(smem_w);
+      mbar_wait(&bars->w_full, 0);
+      tc_fence_after();
+      uint32_t it = 0, j = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
+        const uint32_t acc = j & 1, use = j >> 1;
+        RT_WAIT(w1c, mbar_wait(&bars->tmem_empty[acc], (use & 1) ^ 1u));
+        tc_fence_after();
+        const uint32_t d_addr = tmem_base + acc * 64;
+#pragma unroll
+        for (int q = 0; q < 3; ++q, ++it) {
+          const int s = it % kResSlots;
+          RT_WAIT(w0c, mbar_wait(&bars->a_full[s], (it / kResSlots) & 1));
+          tc_fence_after();
+          const uint32_t patch = smem_u32(smem_a + s * kColPatchBytes);
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            const int tap = r * 3 + q;
+            const uint32_t b_addr = w_addr + (p.flip_taps ? 8 - tap : tap) * 8192;
+            const uint32_t a_addr = patch + r * 1024;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t bdesc = B_MN ? make_smem_desc_sw128(b_addr + k * 2048, 8192, 1024)
+                                          : make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+              umma_bf16(d_addr, make_smem_desc_sw128(a_addr + k * 32, 16, 1024), bdesc, idesc,
+                        (q | r | k) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit(&bars->a_empty[s]);
+        }
+        umma_commit(&bars->tmem_full[acc]);
+      }
+      if (tracing) {
+        trec[kRtMmaWaitFull] = w0c;
+        trec[kRtMmaWaitAcc] = w1c;
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ two epilogue warpgroups
+    const int g = (warp - 2) >> 2;                 // group 0: warps 2-5, group 1: warps 6-9
+    const int q4 = warp & 3;                       // TMEM lane quarter this warp may read
+    const int row = q4 * 32 + lane;                // accumulator row = h_i * 8 + w_i
+    const int wi = row & 7, hi = row >> 3;
+    const int et = threadIdx.x - 64 - g * 128;     // 0..127 inside the group
+    uint8_t* stage_out = smem_out + g * kABytes;
+    const int bar_id = 1 + g;
+    float s1[8], s2[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s1[i] = s2[i] = 0.f;
+    uint32_t u = 0;
+    bool store_pending = false;
+    for (int t = blockIdx.x + g * gridDim.x; t < total_tiles; t += 2 * gridDim.x, ++u) {
+      const int n0 = t / tiles_per_img, r = t % tiles_per_img;
+      const int h0 = (r / p.tiles_w) * 16, w0 = (r % p.tiles_w) * 8;
+      const __nv_bfloat16* add_row = nullptr;
+      if (p.addend != nullptr) {
+        const long long pix = (static_cast<long long>(n0) * p.GH + (h0 + hi)) * p.GW + (w0 + wi);
+        add_row = p.addend + pix * 64;
+      }
+      RT_WAIT(w0c, mbar_wait(&bars->tmem_full[g], u & 1));
+      tc_fence_after();
+      // the previous store of this group must have finished reading the staging buffer
+      if (et == 0 && store_pending) RT_WAIT(w1c, tma_store_wait_read0());
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+      if (tracing) tt = clock64();
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q4 * 32) << 16) + g * 64 + cc * 32, v);
+        tmem_ld_wait();
+        uint32_t packed[16];
+        if (add_row != nullptr) {
+          const uint4* ap = reinterpret_cast<const uint4*>(add_row + cc * 32);
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const uint4 a4 = ap[jj];
+            const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 af = unpack_bf16x2(aw[e]);
+              packed[jj * 4 + e] = pack_bf16x2(__uint_as_float(v[jj * 8 + e * 2]) + af.x,
+                                               __uint_as_float(v[jj * 8 + e * 2 + 1]) + af.y);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) packed[i] = pack_bf16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+        }
+        uint8_t* rowp = stage_out + row * 128;
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          const int chunk = (cc * 4 + jj) ^ (row & 7);
+          *reinterpret_cast<uint4*>(rowp + chunk * 16) =
+              make_uint4(packed[jj * 4], packed[jj * 4 + 1], packed[jj * 4 + 2], packed[jj * 4 + 3]);
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&bars->tmem_empty[g]);          // this thread's TMEM reads are complete: accumulator g is free
+      fence_proxy_async_smem();
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+      if (et == 0) {
+        tma_store_4d(&p.out, stage_out, 0, w0, h0, n0);
+        tma_store_commit();
+      }
+      store_pending = true;
+      if (p.stats != nullptr) {
+        // thread -> 16-byte channel group (et & 7) of rows (et >> 3) + 16 i: one LDS.128 covers 8 channels
+        const int cg = et & 7;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = (et >> 3) + 16 * i;
+          const uint4 h4 = *reinterpret_cast<const uint4*>(stage_out + rr * 128 + ((cg ^ (rr & 7)) << 4));
+          const uint32_t hw[4] = {h4.x, h4.y, h4.z, h4.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = unpack_bf16x2(hw[e]);
+            s1[2 * e] += f.x;
+            s2[2 * e] += f.x * f.x;
+            s1[2 * e + 1] += f.y;
+            s2[2 * e + 1] += f.y * f.y;
+          }
+        }
+      }
+      if (tracing) w2c += clock64() - tt;
+    }
+    if (tracing && g == 0 && et == 0) {
+      trec[kRtEpiWaitAcc] = w0c;
+      trec[kRtEpiWaitStore] = w1c;
+      trec[kRtEpiBusy] = w2c;
+    }
+    if (et == 0 && store_pending) tma_store_wait_read0();
+    if (p.stats != nullptr) {
+      // lanes with equal (lane & 7) hold the same channel group: fold 4 lanes, then the 4 warps via shared memory
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        s1[i] += __shfl_xor_sync(0xffffffffu, s1[i], 8);
+        s1[i] += __shfl_xor_sync(0xffffffffu, s1[i], 16);
+        s2[i] += __shfl_xor_sync(0xffffffffu, s2[i], 8);
+        s2[i] += __shfl_xor_sync(0xffffffffu, s2[i], 16);
+      }
+      float* part = bars->stat_part[g];
+      if (et < 128) part[et] = 0.f;
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+      if (lane < 8) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          atomicAdd(&part[lane * 8 + i], s1[i]);
+          atomicAdd(&part[64 + lane * 8 + i], s2[i]);
+        }
+      }
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+      red_add_f32(p.stats + (et < 64 ? et : p.out_channels + et - 64), part[et]);
+    }
+  }
+#undef RT_WAIT
+  tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x == 0 && tracing) trec[kRtExit] = clock64();
+  if (warp == 1) tmem_dealloc<128>(tmem_base);
 }
 
 // ============================================================================ wgrad
@@ -1059,6 +1366,9 @@ int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, flo
   return 0;
 }
 
+static long long* g_trace_buf = nullptr;   // pmd_conv_set_trace
+static int g_trace_cap = 0;
+
 template <typename Kernel>
 static int set_smem(Kernel k, int bytes) {
   PMD_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
@@ -1101,16 +1411,37 @@ int build_fprop_halo_params(const PmdConvShape& s, const void* x, const void* w_
   out->b_tap_last = 0;
   out->flip_taps = 0;
   out->stats = stats;
+  out->resident = conv_resident_enabled() && conv_resident_supported(s);
   return 0;
 }
 
-int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const void* addend, void* dx,
-                            ConvHaloParams* out) {
+int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w, const void* addend, void* dx,
+                            ConvHaloParams* out, bool w_is_krsc) {
   // same-size 3x3 stride-1: dx = conv(dy, flipped w), reduction over K, output channels C
-  if (build_halo_common(s, s.K, s.C, dy, w_rsck, true, dx, out)) return -1;
-  out->b_tap_last = 1;
+  PMD_REQUIRE(!w_is_krsc || conv_resident_supported(s), "KRSC weights: only the resident kernel reads them for dgrad");
+  if (build_halo_common(s, s.K, s.C, dy, w, !w_is_krsc, dx, out)) return -1;
+  out->b_tap_last = w_is_krsc ? 0 : 1;
+  out->b_mn = w_is_krsc ? 1 : 0;
+  out->resident = w_is_krsc ? 1 : 0;
   out->flip_taps = 1;
   out->addend = static_cast<const __nv_bfloat16*>(addend);
+  return 0;
+}
+
+template <bool B_MN>
+static int launch_conv_resident_t(const ConvHaloParams& p, cudaStream_t stream) {
+  static bool once = false;
+  static int sms = 0;
+  if (!once) {
+    if (set_smem(conv3x3_resident_kernel<B_MN>, kResSmem)) return -1;
+    int dev = 0;
+    PMD_CHECK_CUDA(cudaGetDevice(&dev));
+    PMD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    once = true;
+  }
+  const int total = p.tiles_w * p.tiles_h * p.N;
+  const int grid = total < sms ? total : sms;
+  conv3x3_resident_kernel<B_MN><<<grid, kResThreads, kResSmem, stream>>>(p, total);
   return 0;
 }
 
@@ -1127,7 +1458,20 @@ static int launch_conv_halo_t(const ConvHaloParams& p, cudaStream_t stream) {
   return 0;
 }
 
-int launch_conv_halo(const ConvHaloParams& p, cudaStream_t stream) {
+int launch_conv_halo(const ConvHaloParams& p_in, cudaStream_t stream) {
+  ConvHaloParams p_traced;
+  if (g_trace_buf != nullptr) {
+    p_traced = p_in;
+    p_traced.trace = g_trace_buf;
+    p_traced.trace_cap = g_trace_cap;
+  }
+  const ConvHaloParams& p = g_trace_buf != nullptr ? p_traced : p_in;
+  if (p.resident) {
+    if ((p.b_mn ? launch_conv_resident_t<true>(p, stream) : launch_conv_resident_t<false>(p, stream)) != 0) return -1;
+    count_launch();
+    PMD_LAUNCH_CHECK();
+    return 0;
+  }
   // one 54 KB patch stage + 32 KB of weight slices = 86 KB -> 2 CTAs per SM (their phases interleave)
   const int rc = p.bn_tile == 64 ? launch_conv_halo_t<64, 1, 4>(p, stream) : launch_conv_halo_t<128, 1, 2>(p, stream);
   if (rc != 0) return -1;
@@ -1142,6 +1486,13 @@ int conv_halo_mode() {
   static const int mode = getenv("PMD_CONV_HALO") == nullptr ? 0 : atoi(getenv("PMD_CONV_HALO"));
   return mode;
 }
+// PMD_CONV_RESIDENT: 1 (default) fprop and dgrad, 0 off, 2 fprop only, 3 dgrad only
+static int conv_resident_mode() {
+  static const int mode = getenv("PMD_CONV_RESIDENT") == nullptr ? 1 : atoi(getenv("PMD_CONV_RESIDENT"));
+  return mode;
+}
+bool conv_resident_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 2; }
+bool conv_resident_dgrad_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 3; }
 bool conv_halo_enabled() { return conv_halo_mode() == 1; }
 bool conv_halo_dgrad_enabled() { return conv_halo_mode() >= 1; }
 
@@ -1190,7 +1541,14 @@ static int launch_conv_gemm_persistent_t(const ConvGemmParams& p, cudaStream_t s
   return 0;
 }
 
-int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream) {
+int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
+  ConvGemmParams p_traced;
+  if (g_trace_buf != nullptr) {                 // tracing is a tool mode: the copy costs nothing when it is off
+    p_traced = p_in;
+    p_traced.trace = g_trace_buf;
+    p_traced.trace_cap = g_trace_cap;
+  }
+  const ConvGemmParams& p = g_trace_buf != nullptr ? p_traced : p_in;
   const dim3 grid(p.tiles_w * p.tiles_h * p.tiles_n, p.out_channels / p.bn_tile, p.n_classes);
   // Measured on B200 (profiles/r1_conv_variants.md): one tile per CTA with 2 resident CTAs per SM beats the
   // persistent double-buffered variant on these shapes, so the latter is opt-in (PMD_GEMM_PERSISTENT=1).
@@ -1249,7 +1607,7 @@ using namespace pmd;
 
 extern "C" PMD_API int pmd_conv_fprop(const PmdConvShape* s, const void* d_x, const void* d_w_krsc, void* d_y, float* d_stats,
                               void* stream) {
-  if (conv_halo_enabled() && conv_halo_supported(*s)) {
+  if ((conv_halo_enabled() && conv_halo_supported(*s)) || (conv_resident_enabled() && conv_resident_supported(*s))) {
     ConvHaloParams hp;
     if (build_fprop_halo_params(*s, d_x, d_w_krsc, d_y, d_stats, &hp)) return -1;
     return launch_conv_halo(hp, static_cast<cudaStream_t>(stream));
@@ -1257,6 +1615,12 @@ extern "C" PMD_API int pmd_conv_fprop(const PmdConvShape* s, const void* d_x, co
   ConvGemmParams p;
   if (build_fprop_params(*s, d_x, d_w_krsc, d_y, d_stats, &p)) return -1;
   return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" PMD_API int pmd_conv_set_trace(void* d_buf, int cap_ctas) {
+  g_trace_buf = static_cast<long long*>(d_buf);
+  g_trace_cap = d_buf != nullptr ? cap_ctas : 0;
+  return 0;
 }
 
 extern "C" PMD_API int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, const void* d_w_rsck, const PmdConvShape* s2,
@@ -1275,6 +1639,11 @@ extern "C" PMD_API int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, c
 extern "C" PMD_API int pmd_conv_dgrad_krsc(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc,
                                            const PmdConvShape* s2, const void* d_dy2, const void* d_w2_krsc,
                                            const void* d_addend, void* d_dx, void* stream) {
+  if (s2 == nullptr && conv_resident_dgrad_enabled() && conv_resident_supported(*s)) {
+    ConvHaloParams hp;
+    if (build_dgrad_halo_params(*s, d_dy, d_w_krsc, d_addend, d_dx, &hp, true)) return -1;
+    return launch_conv_halo(hp, static_cast<cudaStream_t>(stream));
+  }
   ConvGemmParams p;
   if (build_dgrad_params(*s, d_dy, d_w_krsc, s2, d_dy2, d_w2_krsc, d_addend, d_dx, &p, true)) return -1;
   return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));

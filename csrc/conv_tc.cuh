@@ -38,6 +38,26 @@ struct ConvGemmParams {
   int bn_tile;               // 64 or 128
   float* stats;              // optional [2 * out_channels]
   const __nv_bfloat16* addend;  // optional NHWC tensor shaped like the (single-class) output
+  long long* trace;          // optional [trace_cap][kTraceSlots] per-CTA timestamps (pmd_conv_set_trace), else null
+  int trace_cap;
+};
+
+// Per-CTA trace record written by the fprop/dgrad kernels when tracing is on (tools/conv_trace.py decodes it).
+// Slots hold clock64() of the CTA's SM unless noted.
+enum {
+  kTrEntry = 0,      // kernel entry
+  kTrSetup = 1,      // barriers initialised, TMEM allocated, CTA-wide sync passed
+  kTrFirstLoad = 2,  // producer: first stage's TMA issued
+  kTrFirstFull = 3,  // MMA thread: first stage has landed
+  kTrMmaIssued = 4,  // MMA thread: last MMA + commit issued (first tile for the persistent kernel)
+  kTrAccReady = 5,   // epilogue: accumulator complete (tmem_full observed)
+  kTrStaged = 6,     // epilogue: tile converted and staged in smem, store about to be issued
+  kTrEpiDone = 7,    // epilogue: statistics reduced, store has read the staging buffer
+  kTrExit = 8,       // after the final CTA-wide sync
+  kTrGlobalNs = 9,   // %globaltimer at entry (ns, comparable across SMs)
+  kTrSm = 10,        // %smid
+  kTrTiles = 11,     // tiles processed by this CTA
+  kTraceSlots = 12
 };
 
 struct WBox {
@@ -75,17 +95,36 @@ struct ConvHaloParams {
   int tiles_w, tiles_h, N, GW, GH;
   int b_tap_last;      // 0: KRSC (fprop), 1: RSCK (dgrad)
   int flip_taps;       // dgrad: weight tap (2-r, 2-s) pairs with patch offset (r, s)
+  int b_mn;            // dgrad straight from the KRSC weights (MN-major B operand); resident kernel only
+  int resident;        // C = K = 64: persistent kernel with the weights resident in shared memory
   int out_channels, bn_tile;
   float* stats;
   const __nv_bfloat16* addend;
+  long long* trace;    // resident kernel: optional [trace_cap][kTraceSlots] per-CTA record (kRt* slots), else null
+  int trace_cap;
+};
+// Trace record of conv3x3_resident_kernel: total cycles each role spent WAITING over all tiles of the CTA.
+enum {
+  kRtEntry = 0, kRtSetup = 1,
+  kRtProdWaitEmpty = 2,   // producer: waiting for a free patch slot (consumer-bound when large)
+  kRtMmaWaitFull = 3,     // MMA thread: waiting for a patch to land (load-bound when large and the above is small)
+  kRtMmaWaitAcc = 4,      // MMA thread: waiting for the epilogue to release an accumulator
+  kRtEpiWaitAcc = 5,      // epilogue group 0: waiting for an accumulator to complete
+  kRtEpiBusy = 6,         // epilogue group 0: tcgen05.ld .. statistics, excluding the waits
+  kRtEpiWaitStore = 7,    // epilogue group 0: waiting for the previous TMA store to release the staging buffer
+  kRtExit = 8             // then kTrGlobalNs, kTrSm, kTrTiles as in the per-tile kernels
 };
 inline bool conv_halo_supported(const PmdConvShape& s) {
   return conv_tc_supported(s) && s.R == 3 && s.stride == 1 && s.W % 8 == 0 && s.H % 16 == 0;
 }
 int build_fprop_halo_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
                             ConvHaloParams* out);
-int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w_rsck, const void* addend, void* dx,
-                            ConvHaloParams* out);
+// C = K = 64 (the 32x32 stage): conv3x3_resident_kernel.  On by default; PMD_CONV_RESIDENT=0 switches it off.
+inline bool conv_resident_supported(const PmdConvShape& s) { return conv_halo_supported(s) && s.C == 64 && s.K == 64; }
+bool conv_resident_enabled();        // fprop
+bool conv_resident_dgrad_enabled();  // dgrad (PMD_CONV_RESIDENT: 1 both [default], 0 off, 2 fprop only, 3 dgrad only)
+int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w, const void* addend, void* dx,
+                            ConvHaloParams* out, bool w_is_krsc = false);
 int launch_conv_halo(const ConvHaloParams& p, cudaStream_t stream);
 bool conv_halo_enabled();        // column-patch kernel for fprop
 bool conv_halo_dgrad_enabled();  // column-patch kernel for dgrad (PMD_CONV_HALO: 0 never, 1 both, 2 dgrad only)

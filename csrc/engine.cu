@@ -335,6 +335,8 @@ Plan* get_plan(PmdEngine* e, int n) {
   pl->block_halo.assign(e->blocks.size(), 0);
   pl->inner_halo.assign(e->convs.size(), 0);
   const bool halo_on = conv_halo_enabled(), halo_dgrad = conv_halo_dgrad_enabled();
+  // C = K = 64 3x3 layers: weight-resident persistent kernel
+  const bool resident_on = conv_resident_enabled(), resident_dgrad = conv_resident_dgrad_enabled();
   for (size_t i = 0; i < e->convs.size(); ++i) {
     Conv& cv = e->convs[i];
     if (!cv.tc) continue;
@@ -344,7 +346,7 @@ Plan* get_plan(PmdEngine* e, int n) {
     if (build_fprop_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop)) return nullptr;
     pl->conv[i].fprop_eval = pl->conv[i].fprop;
     pl->conv[i].fprop_eval.stats = nullptr;
-    if (halo_on && !cv.stem_col && conv_halo_supported(s)) {
+    if (!cv.stem_col && ((halo_on && conv_halo_supported(s)) || (resident_on && conv_resident_supported(s)))) {
       if (build_fprop_halo_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop_h)) return nullptr;
       pl->conv[i].fprop_eval_h = pl->conv[i].fprop_h;
       pl->conv[i].fprop_eval_h.stats = nullptr;
@@ -363,7 +365,12 @@ Plan* get_plan(PmdEngine* e, int n) {
       if (build_dgrad_params(s, cv.dy, e->wbf16 + cv.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_mid[j - 1],
                              &pl->inner_dgrad[b.main[j]], true))
         return nullptr;
-      if (halo_dgrad && conv_halo_supported(s)) {
+      if (resident_dgrad && conv_resident_supported(s)) {
+        if (build_dgrad_halo_params(s, cv.dy, e->wbf16 + cv.w_off, nullptr, b.dz_mid[j - 1],
+                                    &pl->inner_dgrad_h[b.main[j]], true))
+          return nullptr;
+        pl->inner_halo[b.main[j]] = 1;
+      } else if (halo_dgrad && conv_halo_supported(s)) {
         if (build_dgrad_halo_params(s, cv.dy, e->wt + cv.w_off, nullptr, b.dz_mid[j - 1], &pl->inner_dgrad_h[b.main[j]]))
           return nullptr;
         pl->inner_halo[b.main[j]] = 1;
@@ -395,7 +402,11 @@ Plan* get_plan(PmdEngine* e, int n) {
       if (build_dgrad_params(s0, c0.dy, e->wbf16 + c0.w_off, nullptr, nullptr, nullptr, b.g_out, b.dz_in,
                              &pl->block_dgrad[bi], true))
         return nullptr;
-      if (halo_dgrad && conv_halo_supported(s0)) {
+      if (resident_dgrad && conv_resident_supported(s0)) {
+        if (build_dgrad_halo_params(s0, c0.dy, e->wbf16 + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_h[bi], true))
+          return nullptr;
+        pl->block_halo[bi] = 1;
+      } else if (halo_dgrad && conv_halo_supported(s0)) {
         if (build_dgrad_halo_params(s0, c0.dy, e->wt + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_h[bi])) return nullptr;
         pl->block_halo[bi] = 1;
       }
@@ -635,8 +646,13 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
       s.N = n;
       E_CHECK(pmd_conv_wgrad_direct(&s, cv.x_cstride, cv.x, cv.dy, e->grad + cv.w_off, e->wg_stream));
     }
-    return bt.done(cv.w_bkt);
+    return 0;
   };
+  // A weight bucket may be handed to the fused all-reduce + SGD only once every reader of the CURRENT weights has
+  // been enqueued on the main stream: the update rewrites the bf16 working copy in place, and the dgrad of the same
+  // convolution (launched after its wgrad) still reads it.  done() records the main-stream event, so calling it
+  // after the dgrad launch orders the update behind that kernel.
+  auto w_done = [&](int ci) -> int { return bt.done(e->convs[ci].w_bkt); };
   {   // the wgrad stream joins the step after the gradient slab was cleared
     cudaEvent_t ev = e->wg_events[(e->wg_event_next++) % e->wg_events.size()];
     PMD_CHECK_CUDA(cudaEventRecord(ev, st));
@@ -656,6 +672,7 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
         E_CHECK(launch_conv_halo(pl->inner_dgrad_h[ci], st));
       else
         E_CHECK(launch_conv_gemm(pl->inner_dgrad[ci], st));
+      E_CHECK(w_done(ci));
       Conv& pv = e->convs[prev];
       E_CHECK(bn_backward(e, prev, -1, b.dz_mid[j - 1], nullptr, 1LL * n * pv.Ho * pv.Wo, nullptr, st));
       E_CHECK(bn_done(prev));
@@ -668,12 +685,15 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
       E_CHECK(launch_conv_halo(pl->block_dgrad_h[bi], st));
     else
       E_CHECK(launch_conv_gemm(pl->block_dgrad[bi], st));
+    E_CHECK(w_done(b.main[0]));
+    if (b.sc >= 0) E_CHECK(w_done(b.sc));
   }
   {
     Conv& cv = e->convs[0];
     E_CHECK(bn_backward(e, 0, -1, e->dz_stem, nullptr, 1LL * n * cv.Ho * cv.Wo, nullptr, st));
     E_CHECK(bn_done(0));
     E_CHECK(wgrad(0));
+    E_CHECK(w_done(0));       // the stem has no dgrad
   }
   PMD_REQUIRE(bt.launched == c.n_buckets, "internal: not every gradient bucket was launched");
   PMD_CHECK_CUDA(cudaEventRecord(e->ev_join, e->comm_stream));

@@ -54,6 +54,11 @@ int pmd_conv_dgrad_krsc(const PmdConvShape* s, const void* d_dy, const void* d_w
  * accumulator the caller zeroes (it is a slice of the flat gradient bucket slab). */
 int pmd_conv_wgrad(const PmdConvShape* s, const void* d_x, const void* d_dy, float* d_dw_krsc, int split_k,
                    void* stream);
+/* Tool mode (tools/conv_trace.py): while d_buf is non-NULL every fprop/dgrad tensor-core launch writes, per CTA,
+ * PMD_CONV_TRACE_SLOTS long-long timestamps (clock64 per pipeline milestone, %globaltimer, %smid, tile count; slot
+ * meaning in csrc/conv_tc.cuh) for its first cap_ctas CTAs.  d_buf = NULL switches tracing off.  Not thread-safe. */
+#define PMD_CONV_TRACE_SLOTS 12
+int pmd_conv_set_trace(void* d_buf, int cap_ctas);
 
 /* Direct (SIMT) convolution for shapes the tensor-core path does not take (the C=3 stem) and as
  * an in-library cross-check.  Same layouts; C, K arbitrary.  x may carry `x_cstride` >= C channels

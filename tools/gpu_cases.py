@@ -78,6 +78,9 @@ for _name, _args in {
     'fprop_3x3_s1_c64_k64_h32_n3_tail': (3, 32, 64, 64, 3, 1),
     'fprop_3x3_s2_c256_k512_h8_n3': (3, 8, 256, 512, 3, 2),
     'fprop_3x3_s1_c64_k64_h28_imagenetish': (2, 28, 64, 64, 3, 1),
+    # weight-resident persistent kernel with several tiles per CTA (96 images -> 768 tiles on 148 SMs), 64x64 maps
+    'fprop_3x3_s1_c64_k64_h32_n96_resident': (96, 32, 64, 64, 3, 1),
+    'fprop_3x3_s1_c64_k64_h64_n5_resident': (5, 64, 64, 64, 3, 1),
 }.items():
     CASES[_name] = (lambda a=_args: _fprop_case(*a))
 CASES['fprop_direct_stem_c3'] = lambda: _fprop_case(4, 32, 3, 64, 3, 1, direct=True)
@@ -139,6 +142,8 @@ for _name, _args in {
     'dgrad_krsc_1x1_s1_c256_k64_h8_shortcut': (8, 8, 256, 64, 1, 1, 256),
     'dgrad_krsc_3x3_s1_c512_k512_h4': (16, 4, 512, 512, 3, 1),
     'dgrad_krsc_3x3_s2_c256_k512_h8_n3_shortcut': (3, 8, 256, 512, 3, 2, 512),
+    'dgrad_krsc_3x3_s1_c64_k64_h32_n96_addend_resident': (96, 32, 64, 64, 3, 1, 0, True),
+    'dgrad_krsc_3x3_s1_c64_k64_h16_n7_resident': (7, 16, 64, 64, 3, 1),
 }.items():
     CASES[_name] = (lambda a=_args: _dgrad_case(*a[:6], shortcut_K=(a[6] if len(a) > 6 else 0),
                                                 addend=(a[7] if len(a) > 7 else False), krsc=True))

@@ -16,6 +16,7 @@ ap.add_argument('--c', type=int, default=64)
 ap.add_argument('--k', type=int, default=64)
 ap.add_argument('--r', type=int, default=3)
 ap.add_argument('--iters', type=int, default=4)
+ap.add_argument('--timed', type=int, default=1, help='launches inside the timed region (mean is printed)')
 ap.add_argument('--what', default='fprop', choices=['fprop', 'wgrad', 'dgrad'])
 a = ap.parse_args()
 x = torch.randn(a.n, a.h, a.h, a.c, device='cuda').to(torch.bfloat16)
@@ -24,7 +25,7 @@ stats = torch.zeros(2 * a.k, device='cuda')
 dy = torch.randn(a.n, a.h, a.h, a.k, device='cuda').to(torch.bfloat16)
 wt = w.permute(1, 2, 3, 0).contiguous()
 ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-for i in range(a.iters):
+for i in range(a.iters - 1 + a.timed):
     if i == a.iters - 1:
         ev0.record()
     if a.what == 'fprop':
@@ -35,4 +36,4 @@ for i in range(a.iters):
         cv.conv_wgrad(x, dy, a.r, 1)
 ev1.record()
 torch.cuda.synchronize()
-print(f'{a.what} n={a.n} h={a.h} c={a.c} k={a.k}: {ev0.elapsed_time(ev1) * 1e3:.1f} us')
+print(f'{a.what} n={a.n} h={a.h} c={a.c} k={a.k}: {ev0.elapsed_time(ev1) * 1e3 / a.timed:.1f} us')
