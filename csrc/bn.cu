@@ -14,6 +14,14 @@ namespace pmd {
 namespace {
 
 constexpr int kBlock = 256;
+// The streaming kernels run with a block size that is a multiple of the number of 8-channel groups (C / 8), and
+// their grid stride is a multiple of the block size, so a thread meets the SAME channel group in every iteration:
+// its per-channel coefficients are loaded into registers once, and the loop carries no index arithmetic (the
+// 64-bit `i % groups` and the per-iteration shared-memory loads used to cost more issue slots than the math).
+inline int fixed_block(int C) {
+  const int groups = C / 8;
+  return groups >= kBlock ? groups : (kBlock / groups) * groups;
+}
 
 // Generic per-channel two-value reduction over rows of a [rows, C] bf16 tensor.  A thread owns a
 // group of 8 consecutive channels (one 16-byte load) and walks rows with stride (threads / groups).
@@ -145,18 +153,21 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float
   __syncthreads();
   const int groups = C / 8;
   const long long T = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int c0 = static_cast<int>(threadIdx.x % groups) * 8;      // blockDim.x % groups == 0 (fixed_block)
+  float sc[8], sh[8], rsc[8], rsh[8];
+  lds8(aff + c0, sc);
+  lds8(aff + C + c0, sh);
+  if (RES == 2) {
+    lds8(aff + 2 * C + c0, rsc);
+    lds8(aff + 3 * C + c0, rsh);
+  }
   auto one = [&](long long i, const float (&v)[8], const float (&rv)[8]) {
-    const int c0 = static_cast<int>(i % groups) * 8;
-    float o[8], sc[8], sh[8];
-    lds8(aff + c0, sc);
-    lds8(aff + C + c0, sh);
+    float o[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = fmaf(v[j], sc[j], sh[j]);
     if (RES == 2) {
-      lds8(aff + 2 * C + c0, sc);
-      lds8(aff + 3 * C + c0, sh);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], sc[j], sh[j]);
+      for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], rsc[j], rsh[j]);
     } else if (RES == 1) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] += rv[j];
@@ -250,18 +261,21 @@ __global__ void bn_finalize_apply_kernel(PmdSym sym, BnFinalizeDev f0, BnFinaliz
   }
   const int groups = C / 8;
   const long long T = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int c0 = static_cast<int>(threadIdx.x % groups) * 8;      // blockDim.x % groups == 0 (fixed_block)
+  float sc[8], sh[8], rsc[8], rsh[8];
+  lds8(aff + c0, sc);
+  lds8(aff + C + c0, sh);
+  if (RES == 2) {
+    lds8(aff + 2 * C + c0, rsc);
+    lds8(aff + 3 * C + c0, rsh);
+  }
   auto one = [&](long long i, const float (&v)[8], const float (&rv)[8]) {
-    const int c0 = static_cast<int>(i % groups) * 8;
-    float o[8], sc[8], sh[8];
-    lds8(aff + c0, sc);
-    lds8(aff + C + c0, sh);
+    float o[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = fmaf(v[j], sc[j], sh[j]);
     if (RES == 2) {
-      lds8(aff + 2 * C + c0, sc);
-      lds8(aff + 3 * C + c0, sh);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], sc[j], sh[j]);
+      for (int j = 0; j < 8; ++j) o[j] += fmaf(rv[j], rsc[j], rsh[j]);
     } else if (RES == 1) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] += rv[j];
@@ -340,12 +354,12 @@ bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bflo
   for (int i = 0; i < 8; ++i) sg[i] = sgy0[i] = sgy1[i] = 0.f;
   if (rl < rpi) {
     const long long stride = static_cast<long long>(gridDim.x) * rpi;
+    float ms[8], mh[8];
+    if (MASK == 2) {
+      lds8(msm + c0, ms);
+      lds8(msm + C + c0, mh);
+    }
     auto body = [&](const float (&gin)[8], const float (&y0)[8], const float (&zin)[8], const float (&y1)[8]) {
-      float ms[8], mh[8];
-      if (MASK == 2) {
-        lds8(msm + c0, ms);
-        lds8(msm + C + c0, mh);
-      }
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         float gv = gin[i];
@@ -408,7 +422,7 @@ bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bflo
 }
 
 template <int NB, int MASK, bool SYNC>
-__global__ void bn_bwd_apply_multi_kernel(PmdSym sym, const __nv_bfloat16* __restrict__ dz,
+__global__ void __launch_bounds__(kBlock, NB == 1 ? 3 : 2) bn_bwd_apply_multi_kernel(PmdSym sym, const __nv_bfloat16* __restrict__ dz,
                                           const __nv_bfloat16* __restrict__ z, const float* __restrict__ mscale,
                                           const float* __restrict__ mshift, BnBranchDev b0, BnBranchDev b1,
                                           float count_total, __nv_bfloat16* __restrict__ g_out, long long total8,
@@ -451,31 +465,36 @@ __global__ void bn_bwd_apply_multi_kernel(PmdSym sym, const __nv_bfloat16* __res
   __syncthreads();
   const int groups = C / 8;
   const long long T = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int c0 = static_cast<int>(threadIdx.x % groups) * 8;      // blockDim.x % groups == 0 (fixed_block)
+  float ka[8], k1[8], k0[8], qa[8], q1[8], q0[8], ms[8], mh[8];   // this thread's channel group, for the whole loop
+  lds8(coef + c0, ka);
+  lds8(coef + C + c0, k1);
+  lds8(coef + 2 * C + c0, k0);
+  if (NB == 2) {
+    lds8(coef + 3 * C + c0, qa);
+    lds8(coef + 4 * C + c0, q1);
+    lds8(coef + 5 * C + c0, q0);
+  }
+  if (MASK == 2) {
+    lds8(coef + NB * 3 * C + c0, ms);
+    lds8(coef + NB * 3 * C + C + c0, mh);
+  }
   auto one = [&](long long i, float (&gv)[8], const float (&y0)[8], const float (&zv)[8], const float (&y1)[8]) {
-    const int c0 = static_cast<int>(i % groups) * 8;
-    float o[8], ka[8], k1[8], k0[8];
+    float o[8];
     if (MASK == 1) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) gv[j] = zv[j] > 0.f ? gv[j] : 0.f;
     } else if (MASK == 2) {
-      lds8(coef + NB * 3 * C + c0, ka);
-      lds8(coef + NB * 3 * C + C + c0, k1);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) gv[j] = fmaf(y0[j], ka[j], k1[j]) > 0.f ? gv[j] : 0.f;
+      for (int j = 0; j < 8; ++j) gv[j] = fmaf(y0[j], ms[j], mh[j]) > 0.f ? gv[j] : 0.f;
     }
     if (g_out != nullptr) store8(g_out + i * 8, gv);
-    lds8(coef + c0, ka);
-    lds8(coef + C + c0, k1);
-    lds8(coef + 2 * C + c0, k0);
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = fmaf(ka[j], gv[j], fmaf(k1[j], y0[j], k0[j]));
     store8(b0.dy + i * 8, o);
     if (NB == 2) {
-      lds8(coef + 3 * C + c0, ka);
-      lds8(coef + 4 * C + c0, k1);
-      lds8(coef + 5 * C + c0, k0);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = fmaf(ka[j], gv[j], fmaf(k1[j], y1[j], k0[j]));
+      for (int j = 0; j < 8; ++j) o[j] = fmaf(qa[j], gv[j], fmaf(q1[j], y1[j], q0[j]));
       store8(b1.dy + i * 8, o);
     }
   };
@@ -510,6 +529,19 @@ __global__ void bn_bwd_apply_multi_kernel(PmdSym sym, const __nv_bfloat16* __res
 int grid_for(long long work_items, int per_block) {
   long long b = ceil_div_ll(work_items, per_block);
   const long long cap = 148LL * 8;
+  return static_cast<int>(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+// Grid-stride kernels: at most ONE resident wave (148 SMs x the blocks of this kernel an SM holds), so there is no
+// partial last wave and every block streams for the whole kernel.
+template <typename Kernel>
+int wave_grid(Kernel kernel, int block, int smem, long long work_items, int per_block) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem) != cudaSuccess || per_sm < 1) {
+    cudaGetLastError();
+    per_sm = 1;
+  }
+  const long long b = ceil_div_ll(work_items, per_block), cap = 148LL * per_sm;
   return static_cast<int>(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
@@ -558,17 +590,20 @@ extern "C" PMD_API int pmd_bn_apply(const void* d_y, const float* d_scale, const
                             int C, void* stream) {
   BN_CHECK_C(C);
   const long long total8 = rows * C / 8;
-  const int grid = grid_for(total8, kBlock * 2);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const __nv_bfloat16* y = static_cast<const __nv_bfloat16*>(d_y);
   const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(d_res);
   __nv_bfloat16* z = static_cast<__nv_bfloat16*>(d_z);
+  const int blk = fixed_block(C);
   if (d_res == nullptr)
-    bn_apply_kernel<0><<<grid, kBlock, 2 * C * 4, st>>>(y, d_scale, d_shift, nullptr, nullptr, nullptr, relu, z, total8, C);
+    bn_apply_kernel<0><<<wave_grid(bn_apply_kernel<0>, blk, 2 * C * 4, total8, blk * 2), blk, 2 * C * 4, st>>>(
+        y, d_scale, d_shift, nullptr, nullptr, nullptr, relu, z, total8, C);
   else if (d_res_scale == nullptr)
-    bn_apply_kernel<1><<<grid, kBlock, 2 * C * 4, st>>>(y, d_scale, d_shift, res, nullptr, nullptr, relu, z, total8, C);
+    bn_apply_kernel<1><<<wave_grid(bn_apply_kernel<1>, blk, 2 * C * 4, total8, blk * 2), blk, 2 * C * 4, st>>>(
+        y, d_scale, d_shift, res, nullptr, nullptr, relu, z, total8, C);
   else
-    bn_apply_kernel<2><<<grid, kBlock, 4 * C * 4, st>>>(y, d_scale, d_shift, res, d_res_scale, d_res_shift, relu, z, total8, C);
+    bn_apply_kernel<2><<<wave_grid(bn_apply_kernel<2>, blk, 4 * C * 4, total8, blk * 2), blk, 4 * C * 4, st>>>(
+        y, d_scale, d_shift, res, d_res_scale, d_res_shift, relu, z, total8, C);
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
@@ -594,9 +629,15 @@ static BnBranchDev to_dev(const PmdBnBranch& b) {
 template <int NB>
 static void launch_reduce(int mask, int grid, int smem, cudaStream_t st, const __nv_bfloat16* dz, const __nv_bfloat16* z,
                           const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, long long rows, int C) {
-  if (mask == 0) bn_bwd_reduce_multi_kernel<NB, 0><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
-  if (mask == 1) bn_bwd_reduce_multi_kernel<NB, 1><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
-  if (mask == 2) bn_bwd_reduce_multi_kernel<NB, 2><<<grid, kBlock, smem, st>>>(dz, z, ms, mh, b0, b1, rows, C);
+  const int rpi8 = (kBlock / (C / 8) > 0 ? kBlock / (C / 8) : 1) * 8;
+  (void)grid;
+#define PMD_RED(M)                                                                                         \
+  bn_bwd_reduce_multi_kernel<NB, M><<<wave_grid(bn_bwd_reduce_multi_kernel<NB, M>, kBlock, smem, rows, rpi8), kBlock, \
+                                      smem, st>>>(dz, z, ms, mh, b0, b1, rows, C)
+  if (mask == 0) PMD_RED(0);
+  if (mask == 1) PMD_RED(1);
+  if (mask == 2) PMD_RED(2);
+#undef PMD_RED
 }
 template <int NB, int MASK, bool SYNC>
 static void allow_big_smem() {
@@ -616,12 +657,15 @@ static void launch_apply(const PmdSym& sym, int mask, int grid, int smem, cudaSt
     allow_big_smem<NB, 1, SYNC>();
     allow_big_smem<NB, 2, SYNC>();
   }
-  if (mask == 0)
-    bn_bwd_apply_multi_kernel<NB, 0, SYNC><<<grid, kBlock, smem, st>>>(sym, dz, z, ms, mh, b0, b1, count, g_out, total8, C);
-  if (mask == 1)
-    bn_bwd_apply_multi_kernel<NB, 1, SYNC><<<grid, kBlock, smem, st>>>(sym, dz, z, ms, mh, b0, b1, count, g_out, total8, C);
-  if (mask == 2)
-    bn_bwd_apply_multi_kernel<NB, 2, SYNC><<<grid, kBlock, smem, st>>>(sym, dz, z, ms, mh, b0, b1, count, g_out, total8, C);
+  const int blk = fixed_block(C);
+  (void)grid;
+#define PMD_APP(M)                                                                                                \
+  bn_bwd_apply_multi_kernel<NB, M, SYNC><<<wave_grid(bn_bwd_apply_multi_kernel<NB, M, SYNC>, blk, smem, total8, blk * 2), \
+                                           blk, smem, st>>>(sym, dz, z, ms, mh, b0, b1, count, g_out, total8, C)
+  if (mask == 0) PMD_APP(0);
+  if (mask == 1) PMD_APP(1);
+  if (mask == 2) PMD_APP(2);
+#undef PMD_APP
 }
 
 extern "C" PMD_API int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
@@ -708,7 +752,10 @@ static void launch_finalize_apply(const PmdSym& sym, int grid, int smem, cudaStr
     cudaFuncSetAttribute(bn_finalize_apply_kernel<RES, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     once = true;
   }
-  bn_finalize_apply_kernel<RES, SYNC><<<grid, kBlock, smem, st>>>(sym, f0, f1, count, momentum, eps, y, res, relu, z, total8, C);
+  const int blk = fixed_block(C);
+  (void)grid;
+  bn_finalize_apply_kernel<RES, SYNC><<<wave_grid(bn_finalize_apply_kernel<RES, SYNC>, blk, smem, total8, blk * 2), blk, smem,
+                                        st>>>(sym, f0, f1, count, momentum, eps, y, res, relu, z, total8, C);
 }
 
 static BnFinalizeDev to_dev(const PmdBnFinalize& f) {

@@ -119,10 +119,10 @@ inline bool conv_halo_supported(const PmdConvShape& s) {
 }
 int build_fprop_halo_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
                             ConvHaloParams* out);
-// C = K = 64 (the 32x32 stage): conv3x3_resident_kernel.  On by default; PMD_CONV_RESIDENT=0 switches it off.
+// C = K = 64 (the 32x32 stage): conv3x3_resident_kernel.  Default: fprop only (see conv_resident_mode()).
 inline bool conv_resident_supported(const PmdConvShape& s) { return conv_halo_supported(s) && s.C == 64 && s.K == 64; }
 bool conv_resident_enabled();        // fprop
-bool conv_resident_dgrad_enabled();  // dgrad (PMD_CONV_RESIDENT: 1 both [default], 0 off, 2 fprop only, 3 dgrad only)
+bool conv_resident_dgrad_enabled();  // dgrad (PMD_CONV_RESIDENT: 2 fprop only [default], 1 both, 0 off, 3 dgrad only)
 int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w, const void* addend, void* dx,
                             ConvHaloParams* out, bool w_is_krsc = false);
 int launch_conv_halo(const ConvHaloParams& p, cudaStream_t stream);

@@ -779,9 +779,18 @@ extern "C" PMD_API int pmd_engine_create(const PmdEngineConfig* cfg, PmdComm* co
   e->cfg.conv_w_off = e->cfg.bn_g_off = e->cfg.bn_b_off = nullptr;
   e->cfg.bucket_start = e->cfg.bucket_numel = nullptr;
   e->cfg.bucket_algo = e->cfg.bucket_blocks = nullptr;
-  PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
-  PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->main_stream, cudaStreamNonBlocking));
-  PMD_CHECK_CUDA(cudaStreamCreateWithFlags(&e->wg_stream, cudaStreamNonBlocking));
+  {
+    // The main stream carries the step's critical path (forward, BatchNorm backward, dgrad); the comm stream's
+    // kernels are short and other ranks wait on them; weight gradients are consumed only by the bucket update.
+    // So pending wgrad CTAs yield to the other two streams when SM resources free up (PMD_STREAM_PRIORITY=0: off).
+    int least = 0, greatest = 0;
+    PMD_CHECK_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    const bool prio = getenv("PMD_STREAM_PRIORITY") == nullptr || atoi(getenv("PMD_STREAM_PRIORITY")) != 0;
+    const int hi = prio ? greatest : 0, lo = prio ? least : 0;
+    PMD_CHECK_CUDA(cudaStreamCreateWithPriority(&e->comm_stream, cudaStreamNonBlocking, hi));
+    PMD_CHECK_CUDA(cudaStreamCreateWithPriority(&e->main_stream, cudaStreamNonBlocking, hi));
+    PMD_CHECK_CUDA(cudaStreamCreateWithPriority(&e->wg_stream, cudaStreamNonBlocking, lo));
+  }
   e->wg_events.resize(4 * (cfg->n_convs + cfg->n_buckets) + 16);
   for (auto& ev : e->wg_events) PMD_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   PMD_CHECK_CUDA(cudaEventCreateWithFlags(&e->ev_in, cudaEventDisableTiming));
