@@ -141,6 +141,7 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float
                                 const float* __restrict__ shift, const __nv_bfloat16* __restrict__ res,
                                 const float* __restrict__ rscale, const float* __restrict__ rshift, int relu,
                                 __nv_bfloat16* __restrict__ z, long long total8, int C) {
+  pdl_wait();
   extern __shared__ float aff[];     // [scale | shift | rscale | rshift], C floats each: 2-4 wide shared loads per
   for (int c = threadIdx.x; c < C; c += blockDim.x) {   // 8 elements instead of 16-32 scalar global loads
     aff[c] = scale[c];
@@ -224,6 +225,7 @@ __global__ void bn_finalize_apply_kernel(PmdSym sym, BnFinalizeDev f0, BnFinaliz
                                          float momentum, float eps, const __nv_bfloat16* __restrict__ y,
                                          const __nv_bfloat16* __restrict__ res, int relu, __nv_bfloat16* __restrict__ z,
                                          long long total8, int C) {
+  pdl_wait();
   extern __shared__ float aff[];     // [scale | shift | rscale | rshift] (C each) + totals scratch [2C]
   float* tot = aff + 4 * C;
   const float n = count_per_rank * (SYNC ? sym.world : 1);
@@ -334,6 +336,7 @@ bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bflo
   // Accumulates S_g = sum(g) and S_gy = sum(g*y) per channel; sum(g*xhat) = (S_gy - mean*S_g)*invstd is formed
   // once per block at the end, so the streaming loop carries no per-channel statistics in registers (the
   // register budget decides how many of these DRAM-bound blocks fit on an SM).
+  pdl_wait();
   extern __shared__ float red[];      // [mask consts 2C] + reduction scratch [(1+NB) * rpi * C]
   float* msm = red;
   float* scratch = red + 2 * C;
@@ -430,6 +433,7 @@ __global__ void __launch_bounds__(kBlock, NB == 1 ? 3 : 2) bn_bwd_apply_multi_ke
   // dy = gamma*invstd * (g - mean_g - xhat*mean_gx), xhat = (y - mean)*invstd, folded per channel into
   // dy = a*g + k1*y + k0.  Shared layout: per branch [a | k1 | k0] (C floats each), then [mscale | mshift].
   // SYNC: the cross-GPU sum of [sum_g, sum_gx] is exchanged right here (block 0 pushes/polls, see sym.cuh)
+  pdl_wait();
   extern __shared__ float coef[];
   float* tot = coef + (NB * 3 + 2) * C;      // [NB][2C], SYNC only
   if (SYNC) {
@@ -596,14 +600,14 @@ extern "C" PMD_API int pmd_bn_apply(const void* d_y, const float* d_scale, const
   __nv_bfloat16* z = static_cast<__nv_bfloat16*>(d_z);
   const int blk = fixed_block(C);
   if (d_res == nullptr)
-    bn_apply_kernel<0><<<wave_grid(bn_apply_kernel<0>, blk, 2 * C * 4, total8, blk * 2), blk, 2 * C * 4, st>>>(
-        y, d_scale, d_shift, nullptr, nullptr, nullptr, relu, z, total8, C);
+    PMD_CHECK_CUDA(launch_pdl(bn_apply_kernel<0>, dim3(wave_grid(bn_apply_kernel<0>, blk, 2 * C * 4, total8, blk * 2)), dim3(blk),
+                              2 * C * 4, st, y, d_scale, d_shift, nullptr, nullptr, nullptr, relu, z, total8, C));
   else if (d_res_scale == nullptr)
-    bn_apply_kernel<1><<<wave_grid(bn_apply_kernel<1>, blk, 2 * C * 4, total8, blk * 2), blk, 2 * C * 4, st>>>(
-        y, d_scale, d_shift, res, nullptr, nullptr, relu, z, total8, C);
+    PMD_CHECK_CUDA(launch_pdl(bn_apply_kernel<1>, dim3(wave_grid(bn_apply_kernel<1>, blk, 2 * C * 4, total8, blk * 2)), dim3(blk),
+                              2 * C * 4, st, y, d_scale, d_shift, res, nullptr, nullptr, relu, z, total8, C));
   else
-    bn_apply_kernel<2><<<wave_grid(bn_apply_kernel<2>, blk, 4 * C * 4, total8, blk * 2), blk, 4 * C * 4, st>>>(
-        y, d_scale, d_shift, res, d_res_scale, d_res_shift, relu, z, total8, C);
+    PMD_CHECK_CUDA(launch_pdl(bn_apply_kernel<2>, dim3(wave_grid(bn_apply_kernel<2>, blk, 4 * C * 4, total8, blk * 2)), dim3(blk),
+                              4 * C * 4, st, y, d_scale, d_shift, res, d_res_scale, d_res_shift, relu, z, total8, C));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
@@ -631,9 +635,9 @@ static void launch_reduce(int mask, int grid, int smem, cudaStream_t st, const _
                           const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, long long rows, int C) {
   const int rpi8 = (kBlock / (C / 8) > 0 ? kBlock / (C / 8) : 1) * 8;
   (void)grid;
-#define PMD_RED(M)                                                                                         \
-  bn_bwd_reduce_multi_kernel<NB, M><<<wave_grid(bn_bwd_reduce_multi_kernel<NB, M>, kBlock, smem, rows, rpi8), kBlock, \
-                                      smem, st>>>(dz, z, ms, mh, b0, b1, rows, C)
+#define PMD_RED(M)                                                                                                  \
+  launch_pdl(bn_bwd_reduce_multi_kernel<NB, M>, dim3(wave_grid(bn_bwd_reduce_multi_kernel<NB, M>, kBlock, smem, rows, rpi8)), \
+             dim3(kBlock), smem, st, dz, z, ms, mh, b0, b1, rows, C)
   if (mask == 0) PMD_RED(0);
   if (mask == 1) PMD_RED(1);
   if (mask == 2) PMD_RED(2);
@@ -659,9 +663,10 @@ static void launch_apply(const PmdSym& sym, int mask, int grid, int smem, cudaSt
   }
   const int blk = fixed_block(C);
   (void)grid;
-#define PMD_APP(M)                                                                                                \
-  bn_bwd_apply_multi_kernel<NB, M, SYNC><<<wave_grid(bn_bwd_apply_multi_kernel<NB, M, SYNC>, blk, smem, total8, blk * 2), \
-                                           blk, smem, st>>>(sym, dz, z, ms, mh, b0, b1, count, g_out, total8, C)
+#define PMD_APP(M)                                                                                             \
+  launch_pdl(bn_bwd_apply_multi_kernel<NB, M, SYNC>,                                                           \
+             dim3(wave_grid(bn_bwd_apply_multi_kernel<NB, M, SYNC>, blk, smem, total8, blk * 2)), dim3(blk), smem, st, sym, dz, z, \
+             ms, mh, b0, b1, count, g_out, total8, C)
   if (mask == 0) PMD_APP(0);
   if (mask == 1) PMD_APP(1);
   if (mask == 2) PMD_APP(2);
@@ -754,8 +759,8 @@ static void launch_finalize_apply(const PmdSym& sym, int grid, int smem, cudaStr
   }
   const int blk = fixed_block(C);
   (void)grid;
-  bn_finalize_apply_kernel<RES, SYNC><<<wave_grid(bn_finalize_apply_kernel<RES, SYNC>, blk, smem, total8, blk * 2), blk, smem,
-                                        st>>>(sym, f0, f1, count, momentum, eps, y, res, relu, z, total8, C);
+  launch_pdl(bn_finalize_apply_kernel<RES, SYNC>, dim3(wave_grid(bn_finalize_apply_kernel<RES, SYNC>, blk, smem, total8, blk * 2)),
+             dim3(blk), smem, st, sym, f0, f1, count, momentum, eps, y, res, relu, z, total8, C);
 }
 
 static BnFinalizeDev to_dev(const PmdBnFinalize& f) {

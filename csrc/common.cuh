@@ -8,8 +8,10 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 
 #define PMD_API __attribute__((visibility("default")))
 
@@ -73,6 +75,40 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 __device__ __forceinline__ void red_add_f32(float* addr, float v) {
   asm volatile("red.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
+}
+
+// Programmatic dependent launch.  A kernel launched with launch_pdl() may become resident while its predecessor
+// in the stream is still draining; it runs its private prologue (barrier init, TMEM allocation, tensor-map
+// prefetch) and then blocks in pdl_wait() until the predecessor has completed and its writes are visible.  The
+// trigger sits right behind the wait, so at most one dependent grid is ever staged ahead.  Both instructions are
+// no-ops for a kernel launched the ordinary way.  RULE: every kernel launched through launch_pdl() must execute
+// pdl_wait() before its first access to global memory that another kernel produces or consumes.
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+#endif
+
+#ifdef __CUDACC__
+// PMD_PDL=0 disables programmatic dependent launch (every kernel then waits for its predecessor to drain).
+inline bool pdl_enabled() {
+  static const bool on = getenv("PMD_PDL") == nullptr || atoi(getenv("PMD_PDL")) != 0;
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(std::forward<Args>(args))...);
 }
 #endif
 

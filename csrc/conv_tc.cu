@@ -113,6 +113,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
   if (threadIdx.x == 0) trace_mark(p, kTrSetup);
+  pdl_wait();        // everything above is private to this CTA; operands below come from the previous kernel
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -334,6 +335,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
   if (threadIdx.x == 0) trace_mark(p, kTrSetup);
+  pdl_wait();        // everything above is private to this CTA; operands below come from the previous kernel
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -567,6 +569,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_halo_kernel(const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -778,6 +781,7 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
   if (threadIdx.x == 0 && tracing) trec[kRtSetup] = clock64();
+  pdl_wait();
   long long w0c = 0, w1c = 0, w2c = 0, tt = 0;      // trace accumulators (dead code unless tracing)
 #define RT_WAIT(acc, stmt)          \
   do {                              \
@@ -1007,6 +1011,7 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -1441,7 +1446,7 @@ static int launch_conv_resident_t(const ConvHaloParams& p, cudaStream_t stream) 
   }
   const int total = p.tiles_w * p.tiles_h * p.N;
   const int grid = total < sms ? total : sms;
-  conv3x3_resident_kernel<B_MN><<<grid, kResThreads, kResSmem, stream>>>(p, total);
+  PMD_CHECK_CUDA(launch_pdl(conv3x3_resident_kernel<B_MN>, dim3(grid), dim3(kResThreads), kResSmem, stream, p, total));
   return 0;
 }
 
@@ -1454,7 +1459,7 @@ static int launch_conv_halo_t(const ConvHaloParams& p, cudaStream_t stream) {
     once = true;
   }
   const dim3 grid(p.tiles_w * p.tiles_h * p.N, p.out_channels / BN, 1);
-  conv_gemm_halo_kernel<BN, AS, BS><<<grid, kThreads, smem, stream>>>(p);
+  PMD_CHECK_CUDA(launch_pdl(conv_gemm_halo_kernel<BN, AS, BS>, grid, dim3(kThreads), smem, stream, p));
   return 0;
 }
 
@@ -1506,7 +1511,7 @@ static int launch_conv_gemm_t(const ConvGemmParams& p, const dim3& grid, cudaStr
     if (set_smem(conv_gemm_kernel<BN, ST, B_MN>, smem)) return -1;
     once = true;
   }
-  conv_gemm_kernel<BN, ST, B_MN><<<grid, kThreads, smem, stream>>>(p);
+  PMD_CHECK_CUDA(launch_pdl(conv_gemm_kernel<BN, ST, B_MN>, grid, dim3(kThreads), smem, stream, p));
   return 0;
 }
 
@@ -1539,7 +1544,7 @@ static int launch_conv_gemm_persistent_t(const ConvGemmParams& p, cudaStream_t s
   }
   const int total = p.tiles_w * p.tiles_h * p.tiles_n * (p.out_channels / BN) * p.n_classes;
   const int grid = total < ctas_per_sm * sms ? total : ctas_per_sm * sms;
-  conv_gemm_persistent_kernel<BN, ST><<<grid, kThreads, smem, stream>>>(p, total);
+  PMD_CHECK_CUDA(launch_pdl(conv_gemm_persistent_kernel<BN, ST>, dim3(grid), dim3(kThreads), smem, stream, p, total));
   return 0;
 }
 
@@ -1590,7 +1595,7 @@ static int launch_wgrad_t(const WgradParams& p, cudaStream_t stream) {
     once = true;
   }
   const dim3 grid(ceil_div(p.n_boxes, 2), p.K / BNW, p.split);
-  conv_wgrad_kernel<BNW, ST><<<grid, kThreads, smem, stream>>>(p);
+  PMD_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BNW, ST>, grid, dim3(kThreads), smem, stream, p));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

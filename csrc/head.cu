@@ -14,6 +14,7 @@ constexpr int kFcSplit = 16;
 __global__ void pool_fc_fwd_kernel(const __nv_bfloat16* __restrict__ z, int HW, int C, const float* __restrict__ w,
                                    const float* __restrict__ b, int classes, float* __restrict__ feat,
                                    float* __restrict__ logits) {
+  pdl_wait();
   extern __shared__ float fs[];   // [C]
   const int n = blockIdx.x;
   const __nv_bfloat16* zn = z + static_cast<long long>(n) * HW * C;
@@ -44,6 +45,7 @@ __global__ void pool_fc_fwd_kernel(const __nv_bfloat16* __restrict__ z, int HW, 
 __global__ void ce_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
                           const unsigned char* __restrict__ valid, int N, int classes, float grad_scale,
                           float* __restrict__ dlogits, double* metrics) {
+  pdl_wait();
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   __shared__ float acc_s[4];
@@ -86,6 +88,7 @@ __global__ void ce_kernel(const float* __restrict__ logits, const long long* __r
 __global__ void pool_fc_bwd_kernel(const float* __restrict__ dlogits, const float* __restrict__ feat,
                                    const float* __restrict__ w, int N, int HW, int C, int classes, float* dw,
                                    float* db, __nv_bfloat16* __restrict__ dz) {
+  pdl_wait();
   if (static_cast<int>(blockIdx.x) < N) {
     // d(feature) -> broadcast over the pooled window
     extern __shared__ float dls[];   // [classes]
@@ -132,8 +135,8 @@ using namespace pmd;
 extern "C" PMD_API int pmd_pool_fc_fwd(const void* d_z, int N, int HW, int C, const float* d_w, const float* d_b, int classes,
                                float* d_feat, float* d_logits, void* stream) {
   PMD_REQUIRE(C % 2 == 0, "feature width must be even");
-  pool_fc_fwd_kernel<<<N, 256, C * 4, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(d_z), HW, C, d_w, d_b, classes, d_feat, d_logits);
+  PMD_CHECK_CUDA(launch_pdl(pool_fc_fwd_kernel, dim3(N), dim3(256), C * 4, static_cast<cudaStream_t>(stream),
+                            static_cast<const __nv_bfloat16*>(d_z), HW, C, d_w, d_b, classes, d_feat, d_logits));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
@@ -141,9 +144,8 @@ extern "C" PMD_API int pmd_pool_fc_fwd(const void* d_z, int N, int HW, int C, co
 
 extern "C" PMD_API int pmd_ce_fwd_bwd(const float* d_logits, const long long* d_labels, const unsigned char* d_valid, int N,
                               int classes, float grad_scale, float* d_dlogits, double* d_metrics, void* stream) {
-  ce_kernel<<<ceil_div(N * 32, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_logits, d_labels, d_valid, N,
-                                                                                  classes, grad_scale, d_dlogits,
-                                                                                  d_metrics);
+  PMD_CHECK_CUDA(launch_pdl(ce_kernel, dim3(ceil_div(N * 32, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), d_logits,
+                            d_labels, d_valid, N, classes, grad_scale, d_dlogits, d_metrics));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
@@ -153,8 +155,8 @@ extern "C" PMD_API int pmd_pool_fc_bwd(const float* d_dlogits, const float* d_fe
                                int classes, float* d_dw, float* d_db, void* d_dz, void* stream) {
   PMD_REQUIRE(C % 2 == 0, "feature width must be even");
   const int extra = ceil_div(classes * C, 256) * kFcSplit;
-  pool_fc_bwd_kernel<<<N + extra, 256, classes * 4, static_cast<cudaStream_t>(stream)>>>(
-      d_dlogits, d_feat, d_w, N, HW, C, classes, d_dw, d_db, static_cast<__nv_bfloat16*>(d_dz));
+  PMD_CHECK_CUDA(launch_pdl(pool_fc_bwd_kernel, dim3(N + extra), dim3(256), classes * 4, static_cast<cudaStream_t>(stream),
+                            d_dlogits, d_feat, d_w, N, HW, C, classes, d_dw, d_db, static_cast<__nv_bfloat16*>(d_dz)));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
