@@ -1155,6 +1155,18 @@ void choose_brick(int P, int GW, int GH, int* w_box, int* h_box, int* n_box) {
 
 }  // namespace
 
+// Output-channel tile of the fprop/dgrad GEMM.  256-wide tiles halve the A traffic and take an N=256 MMA under the
+// shared-memory operand limit (96 B/clk instead of 128), but leave half as many CTAs; PMD_GEMM_BN256: 0 never,
+// 1 whenever the channel count allows, 2 (default) only when at least `148` CTAs remain.
+static int pick_bn_tile(int out_channels, int pixel_tiles, int classes) {
+  static const int mode = getenv("PMD_GEMM_BN256") == nullptr ? 2 : atoi(getenv("PMD_GEMM_BN256"));
+  if (out_channels % 256 == 0 && mode != 0) {
+    const int ctas = pixel_tiles * (out_channels / 256) * classes;
+    if (mode == 1 || ctas >= 148) return 256;
+  }
+  return out_channels % 128 == 0 ? 128 : 64;
+}
+
 int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
                        ConvGemmParams* out) {
   PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
@@ -1172,7 +1184,7 @@ int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc,
   p.GH[0] = Ho;
   p.b_tap_last = 0;
   p.out_channels = s.K;
-  p.bn_tile = (s.K % 128 == 0) ? 128 : 64;
+  p.bn_tile = pick_bn_tile(s.K, p.tiles_w * p.tiles_h * p.tiles_n, 1);
   p.stats = stats;
   p.addend = nullptr;
   if (s.stride == 1) {
@@ -1251,7 +1263,7 @@ int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck
   p.N = s.N;
   p.b_tap_last = 1;
   p.out_channels = s.C;
-  p.bn_tile = (s.C % 128 == 0) ? 128 : 64;
+  p.bn_tile = pick_bn_tile(s.C, p.tiles_w * p.tiles_h * p.tiles_n, st * st);
   p.stats = nullptr;
   p.addend = static_cast<const __nv_bfloat16*>(addend);
   // A operands: the output-gradient tensors on the (Ho, Wo) grid
@@ -1563,7 +1575,11 @@ int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
   static const bool persistent = getenv("PMD_GEMM_PERSISTENT") != nullptr && atoi(getenv("PMD_GEMM_PERSISTENT")) != 0;
   int rc;
   if (p.b_mn_major) {
-    rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true>(p, grid, stream) : launch_conv_gemm_t<128, 3, true>(p, grid, stream);
+    rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true>(p, grid, stream)
+                         : (p.bn_tile == 128 ? launch_conv_gemm_t<128, 3, true>(p, grid, stream)
+                                             : launch_conv_gemm_t<256, 2, true>(p, grid, stream));
+  } else if (p.bn_tile == 256) {
+    rc = launch_conv_gemm_t<256, 2>(p, grid, stream);
   } else if (persistent) {
     if (p.bn_tile == 64)
       rc = st64 == 2 ? launch_conv_gemm_persistent_t<64, 2>(p, stream)

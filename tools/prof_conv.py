@@ -31,7 +31,7 @@ for i in range(a.iters - 1 + a.timed):
     if a.what == 'fprop':
         cv.conv_fprop(x, w, 1, stats)
     elif a.what == 'dgrad':
-        cv.conv_dgrad(dy, wt, tuple(x.shape), a.r, 1)
+        cv.conv_dgrad(dy, w, tuple(x.shape), a.r, 1, krsc=True)   # the engine's path: KRSC weights, MN-major B
     else:
         cv.conv_wgrad(x, dy, a.r, 1)
 ev1.record()
