@@ -77,12 +77,21 @@ __device__ __forceinline__ void trace_begin(const ConvGemmParams& p, int tiles) 
   t[kTrTiles] = tiles;
 }
 
-template <int BN, int STAGES, bool B_MN = false>
+template <int BN>
+struct RedExtra {          // extra shared state of the RED (dgrad + BatchNorm-backward reduction) instantiations
+  uint64_t y_full;
+  uint64_t pad_;           // keeps sc/sh 16-byte aligned (read as float4)
+  float sc[BN], sh[BN];
+};
+
+template <int BN, int STAGES, bool B_MN = false, bool RED = false>
 __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
   constexpr int kStageBytes = kABytes + BN * 128;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
   PipeBars<STAGES>* bars = reinterpret_cast<PipeBars<STAGES>*>(smem + STAGES * kStageBytes);
+  RedExtra<BN>* rx = reinterpret_cast<RedExtra<BN>*>(reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBars<STAGES>) + 15) & ~15));
+  static_assert(!RED || STAGES * kStageBytes >= 2 * (BN / 64) * kABytes, "y tile does not fit beside the output staging");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cls = blockIdx.z, ntile = blockIdx.y;
@@ -102,6 +111,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
       mbar_init(&bars->empty[s], 1);
     }
     mbar_init(&bars->tmem_full, 1);
+    if (RED) mbar_init(&rx->y_full, 1);
     fence_mbar_init();
     prefetch_tmap(&p.a[0]);
     prefetch_tmap(&p.b[0]);
@@ -114,6 +124,13 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
   const uint32_t tmem_base = bars->tmem_base;
   if (threadIdx.x == 0) trace_mark(p, kTrSetup);
   pdl_wait();        // everything above is private to this CTA; operands below come from the previous kernel
+  if (RED) {
+    for (int c = threadIdx.x; c < BN; c += kThreads) {
+      rx->sc[c] = p.red_scale[ntile * BN + c];
+      rx->sh[c] = p.red_shift[ntile * BN + c];
+    }
+    __syncthreads();
+  }
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -181,6 +198,16 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
     }
     if (threadIdx.x == 64) trace_mark(p, kTrAccReady);
     uint8_t* stage_out = smem;           // pipeline buffers are idle now: reuse them as the store staging
+    uint8_t* stage_y = smem + (BN / 64) * kABytes;
+    if (RED) {
+      if (threadIdx.x == 64) {           // every MMA has completed (tmem_full): the ring can take the y tile
+        mbar_expect_tx(&rx->y_full, (BN / 64) * kABytes);
+#pragma unroll
+        for (int hf = 0; hf < BN / 64; ++hf)
+          tma_load_4d(&p.ymap, &rx->y_full, stage_y + hf * kABytes, ntile * BN + hf * 64, w0, h0, n0);
+      }
+      mbar_wait(&rx->y_full, 0);
+    }
 #pragma unroll
     for (int hf = 0; hf < BN / 64; ++hf) {
 #pragma unroll
@@ -211,6 +238,29 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
 #pragma unroll
           for (int j = 0; j < 16; ++j)
             packed[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+        }
+        if (RED) {
+          // ReLU mask of the layer below, recomputed from its pre-activation y: g = (scale*y + shift > 0) ? dz : 0
+          const uint8_t* yrow = stage_y + hf * kABytes + row * 128;
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const uint4 y4 = *reinterpret_cast<const uint4*>(yrow + (((cc * 4 + jj) ^ (row & 7)) << 4));
+            const uint32_t yw[4] = {y4.x, y4.y, y4.z, y4.w};
+            const float4 sa = *reinterpret_cast<const float4*>(&rx->sc[hf * 64 + cc * 32 + jj * 8]);
+            const float4 sb = *reinterpret_cast<const float4*>(&rx->sc[hf * 64 + cc * 32 + jj * 8 + 4]);
+            const float4 ha = *reinterpret_cast<const float4*>(&rx->sh[hf * 64 + cc * 32 + jj * 8]);
+            const float4 hb = *reinterpret_cast<const float4*>(&rx->sh[hf * 64 + cc * 32 + jj * 8 + 4]);
+            const float scv[8] = {sa.x, sa.y, sa.z, sa.w, sb.x, sb.y, sb.z, sb.w};
+            const float shv[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 yf = unpack_bf16x2(yw[e]);
+              float2 gf = unpack_bf16x2(packed[jj * 4 + e]);
+              if (!(fmaf(yf.x, scv[2 * e], shv[2 * e]) > 0.f)) gf.x = 0.f;
+              if (!(fmaf(yf.y, scv[2 * e + 1], shv[2 * e + 1]) > 0.f)) gf.y = 0.f;
+              packed[jj * 4 + e] = pack_bf16x2(gf.x, gf.y);
+            }
+          }
         }
         if (!valid) {
 #pragma unroll
@@ -252,6 +302,27 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         }
         red_add_f32(p.stats + ntile * BN + hf * 64 + c, s1);
         red_add_f32(p.stats + p.out_channels + ntile * BN + hf * 64 + c, s2);
+      }
+    }
+    if (RED) {
+      // per channel: S_g = sum(g), S_gy = sum(g*y) over this tile; sum(g*xhat) = (S_gy - mean*S_g)*invstd is linear in them
+      const int c = et & 63, rh = et >> 6;
+#pragma unroll
+      for (int hf = 0; hf < BN / 64; ++hf) {
+        float s1 = 0.f, s2 = 0.f;
+        const uint8_t* gb = stage_out + hf * kABytes;
+        const uint8_t* yb = stage_y + hf * kABytes;
+#pragma unroll 8
+        for (int r = rh * 64; r < rh * 64 + 64; ++r) {
+          const int off = r * 128 + (((c >> 3) ^ (r & 7)) << 4) + (c & 7) * 2;
+          const float g = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gb + off));
+          const float yv = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(yb + off));
+          s1 += g;
+          s2 = fmaf(g, yv, s2);
+        }
+        const int ch = ntile * BN + hf * 64 + c;
+        red_add_f32(p.red_sums + ch, s1);
+        red_add_f32(p.red_sums + p.out_channels + ch, (s2 - p.red_mean[ch] * s1) * p.red_invstd[ch]);
       }
     }
     if (et == 0) tma_store_wait_read0();
@@ -977,17 +1048,20 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
 }
 
 // ============================================================================ wgrad
-template <int BNW, int STAGES>
+// MB = number of 128-row accumulators (pairs of x boxes) per CTA.  With MB = 2 the dy tile of a stage feeds twice as
+// many MMAs: (32 + 32) KB per 1024 tensor cycles for BNW = 256 instead of (16 + 32) KB per 512, i.e. a third less
+// operand traffic out of L2, which is what bounds this kernel.
+template <int BNW, int STAGES, int MB = 1>
 __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_constant__ WgradParams p) {
   constexpr int kBoxBytes = 8192;                       // 64 pixels x 128 B
-  constexpr int kStageBytes = 2 * kBoxBytes + (BNW / 64) * kBoxBytes;
+  constexpr int kABox = 2 * MB;                         // x boxes per stage
+  constexpr int kStageBytes = kABox * kBoxBytes + (BNW / 64) * kBoxBytes;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
   PipeBars<STAGES>* bars = reinterpret_cast<PipeBars<STAGES>*>(smem + STAGES * kStageBytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int box0 = 2 * blockIdx.x;
-  const int box1 = min(box0 + 1, p.n_boxes - 1);
+  const int box0 = kABox * blockIdx.x;
   const int k0 = blockIdx.y * BNW;
   const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_n;
   const int per = (tiles_total + gridDim.z - 1) / gridDim.z;
@@ -1006,7 +1080,7 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
     prefetch_tmap(&p.dy);
     prefetch_tmap(&p.x[0]);
   }
-  if (warp == 1) tmem_alloc<BNW>(&bars->tmem_base);
+  if (warp == 1) tmem_alloc<MB * BNW>(&bars->tmem_base);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -1015,7 +1089,9 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
 
   if (warp == 0) {
     if (lane == 0) {
-      const WBox b0 = p.box[box0], b1 = p.box[box1];
+      WBox bx[kABox];
+#pragma unroll
+      for (int j = 0; j < kABox; ++j) bx[j] = p.box[min(box0 + j, p.n_boxes - 1)];
       for (int i = 0; i < niter; ++i) {
         const int s = i % STAGES;
         const uint32_t ph = (i / STAGES) & 1;
@@ -1026,10 +1102,11 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
         const int n0 = (t / p.tiles_h) * p.n_box;
         mbar_wait(&bars->empty[s], ph ^ 1u);
         uint8_t* sa = smem + s * kStageBytes;
-        uint8_t* sb = sa + 2 * kBoxBytes;
+        uint8_t* sb = sa + kABox * kBoxBytes;
         mbar_expect_tx(&bars->full[s], kStageBytes);
-        tma_load_4d(&p.x[b0.a_map], &bars->full[s], sa, b0.a_ch, w0 + b0.dw, h0 + b0.dh, n0);
-        tma_load_4d(&p.x[b1.a_map], &bars->full[s], sa + kBoxBytes, b1.a_ch, w0 + b1.dw, h0 + b1.dh, n0);
+#pragma unroll
+        for (int j = 0; j < kABox; ++j)
+          tma_load_4d(&p.x[bx[j].a_map], &bars->full[s], sa + j * kBoxBytes, bx[j].a_ch, w0 + bx[j].dw, h0 + bx[j].dh, n0);
 #pragma unroll
         for (int j = 0; j < BNW / 64; ++j)
           tma_load_4d(&p.dy, &bars->full[s], sb + j * kBoxBytes, k0 + j * 64, w0, h0, n0);
@@ -1044,11 +1121,14 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
         mbar_wait(&bars->full[s], ph);
         tc_fence_after();
         const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
-        const uint32_t b_addr = a_addr + 2 * kBoxBytes;
+        const uint32_t b_addr = a_addr + kABox * kBoxBytes;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {   // 64 pixels = 4 x (K = 16 rows of 128 B)
-          umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 2048, kBoxBytes, 1024),
-                    make_smem_desc_sw128(b_addr + k * 2048, kBoxBytes, 1024), idesc, (i | k) != 0 ? 1u : 0u);
+        for (int m = 0; m < MB; ++m) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {   // 64 pixels = 4 x (K = 16 rows of 128 B)
+            umma_bf16(tmem_base + m * BNW, make_smem_desc_sw128(a_addr + m * 2 * kBoxBytes + k * 2048, kBoxBytes, 1024),
+                      make_smem_desc_sw128(b_addr + k * 2048, kBoxBytes, 1024), idesc, (i | k) != 0 ? 1u : 0u);
+          }
         }
         umma_commit(&bars->empty[s]);
       }
@@ -1057,18 +1137,21 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
   } else {
     const int q = warp & 3;
     const int row = q * 32 + lane;
-    const int bx = row >> 6, c = row & 63;
-    const bool live = (niter > 0) && (box0 + bx < p.n_boxes) && (c < p.c_valid);
+    const int c = row & 63;
     if (niter > 0) {
       mbar_wait(&bars->tmem_full, 0);
       tc_fence_after();
     }
-    const int out_col = p.box[min(box0 + bx, p.n_boxes - 1)].out_col + c;
-    if (niter > 0) {
+#pragma unroll 1
+    for (int m = 0; m < MB; ++m) {
+      const int bx = 2 * m + (row >> 6);
+      const bool live = (niter > 0) && (box0 + bx < p.n_boxes) && (c < p.c_valid);
+      const int out_col = p.box[min(box0 + bx, p.n_boxes - 1)].out_col + c;
+      if (niter <= 0) break;
 #pragma unroll 1
       for (int cc = 0; cc < BNW / 32; ++cc) {
         uint32_t v[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cc * 32, v);
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + m * BNW + cc * 32, v);
         tmem_ld_wait();
         if (live) {
           float* dst = p.dw + static_cast<long long>(k0 + cc * 32) * p.RSC + out_col;
@@ -1080,7 +1163,7 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<BNW>(tmem_base);
+  if (warp == 1) tmem_dealloc<MB * BNW>(tmem_base);
 }
 
 // ============================================================================ host side
@@ -1371,9 +1454,20 @@ int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, flo
     }
   p.n_boxes = n;
   const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_n;
+  // PMD_WGRAD_MB: 0 (default) two accumulators per CTA when at least 16 boxes keep the padding waste <= 10 %, 1, 2
+  static const int mb_mode = getenv("PMD_WGRAD_MB") == nullptr ? 0 : atoi(getenv("PMD_WGRAD_MB"));
+  p.mb = mb_mode == 0 ? (n >= 16 ? 2 : 1) : (mb_mode == 2 ? 2 : 1);
   if (split <= 0) {
-    const int ctas = ceil_div(n, 2) * (s.K / p.bn_tile);
-    split = ceil_div(3 * (sm_count > 0 ? sm_count : 148), ctas);
+    const int sms = sm_count > 0 ? sm_count : 148;
+    const int ctas = ceil_div(n, 2 * p.mb) * (s.K / p.bn_tile);
+    if (p.mb == 2) {
+      split = sms / ctas;                                // one CTA per SM fits (>= 144 KB of stages): exactly one wave
+      if (split < 1) split = 1;
+    } else {
+      static const int target = getenv("PMD_WGRAD_TARGET") == nullptr ? 3 : atoi(getenv("PMD_WGRAD_TARGET"));
+      split = target > 0 ? ceil_div(target * sms, ctas) : (2 * sms) / ctas;   // 0: exactly one wave of 2 CTAs per SM
+      if (split < 1) split = 1;
+    }
     const int max_split = ceil_div(tiles_total, 8);     // keep >= 8 pipeline iterations per CTA
     if (split > max_split) split = max_split;
   }
@@ -1515,15 +1609,15 @@ bool conv_resident_dgrad_enabled() { return conv_resident_mode() == 1 || conv_re
 bool conv_halo_enabled() { return conv_halo_mode() == 1; }
 bool conv_halo_dgrad_enabled() { return conv_halo_mode() >= 1; }
 
-template <int BN, int ST, bool B_MN = false>
+template <int BN, int ST, bool B_MN = false, bool RED = false>
 static int launch_conv_gemm_t(const ConvGemmParams& p, const dim3& grid, cudaStream_t stream) {
-  constexpr int smem = ST * (kABytes + BN * 128) + sizeof(PipeBars<ST>) + 1024;
+  constexpr int smem = ST * (kABytes + BN * 128) + sizeof(PipeBars<ST>) + 16 + (RED ? sizeof(RedExtra<BN>) : 0) + 1024;
   static bool once = false;
   if (!once) {
-    if (set_smem(conv_gemm_kernel<BN, ST, B_MN>, smem)) return -1;
+    if (set_smem(conv_gemm_kernel<BN, ST, B_MN, RED>, smem)) return -1;
     once = true;
   }
-  PMD_CHECK_CUDA(launch_pdl(conv_gemm_kernel<BN, ST, B_MN>, grid, dim3(kThreads), smem, stream, p));
+  PMD_CHECK_CUDA(launch_pdl(conv_gemm_kernel<BN, ST, B_MN, RED>, grid, dim3(kThreads), smem, stream, p));
   return 0;
 }
 
@@ -1560,6 +1654,28 @@ static int launch_conv_gemm_persistent_t(const ConvGemmParams& p, cudaStream_t s
   return 0;
 }
 
+// PMD_DGRAD_BN_REDUCE=0 keeps the stand-alone reduction kernels.
+int attach_bn_reduce(ConvGemmParams* p, const PmdConvShape& s, const void* y, const float* scale, const float* shift,
+                     const float* mean, const float* invstd, float* sums) {
+  static const bool on = getenv("PMD_DGRAD_BN_REDUCE") == nullptr || atoi(getenv("PMD_DGRAD_BN_REDUCE")) != 0;
+  if (!on || !p->b_mn_major || p->n_classes != 1 || p->addend != nullptr || s.stride != 1) return 0;
+  if (p->out_channels % 256 == 0 && p->bn_tile == 256) {
+    // the y tile does not fit beside a 256-wide output staging area: fall back to 128-wide tiles for this dgrad
+    p->bn_tile = 128;
+  }
+  if (p->bn_tile != 64 && p->bn_tile != 128) return 0;
+  for (int i = 0; i < p->kb_count[0]; ++i)
+    if (p->kb[p->kb_begin[0] + i].a_map != 0) return 0;    // fused shortcut branch: two A tensors, not handled
+  if (act_map(&p->ymap, y, s.N, s.H, s.W, s.C, 1, 0, 0, p->w_box, p->h_box, p->n_box)) return -1;
+  p->red_scale = scale;
+  p->red_shift = shift;
+  p->red_mean = mean;
+  p->red_invstd = invstd;
+  p->red_sums = sums;
+  p->bn_reduce = 1;
+  return 1;
+}
+
 int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
   ConvGemmParams p_traced;
   if (g_trace_buf != nullptr) {                 // tracing is a tool mode: the copy costs nothing when it is off
@@ -1574,7 +1690,10 @@ int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
   static const int st64 = stages_from_env("PMD_GEMM64_STAGES", 2), st128 = stages_from_env("PMD_GEMM128_STAGES", 3);
   static const bool persistent = getenv("PMD_GEMM_PERSISTENT") != nullptr && atoi(getenv("PMD_GEMM_PERSISTENT")) != 0;
   int rc;
-  if (p.b_mn_major) {
+  if (p.b_mn_major && p.bn_reduce) {
+    rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true, true>(p, grid, stream)
+                         : launch_conv_gemm_t<128, 3, true, true>(p, grid, stream);
+  } else if (p.b_mn_major) {
     rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true>(p, grid, stream)
                          : (p.bn_tile == 128 ? launch_conv_gemm_t<128, 3, true>(p, grid, stream)
                                              : launch_conv_gemm_t<256, 2, true>(p, grid, stream));
@@ -1602,22 +1721,28 @@ int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
   return 0;
 }
 
-template <int BNW, int ST>
+template <int BNW, int ST, int MB = 1>
 static int launch_wgrad_t(const WgradParams& p, cudaStream_t stream) {
-  constexpr int smem = ST * (2 * 8192 + (BNW / 64) * 8192) + sizeof(PipeBars<ST>) + 1024;
+  constexpr int smem = ST * (2 * MB * 8192 + (BNW / 64) * 8192) + sizeof(PipeBars<ST>) + 1024;
+  static_assert(smem <= 227 * 1024, "wgrad pipeline does not fit in shared memory");
   static bool once = false;
   if (!once) {
-    if (set_smem(conv_wgrad_kernel<BNW, ST>, smem)) return -1;
+    if (set_smem(conv_wgrad_kernel<BNW, ST, MB>, smem)) return -1;
     once = true;
   }
-  const dim3 grid(ceil_div(p.n_boxes, 2), p.K / BNW, p.split);
-  PMD_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BNW, ST>, grid, dim3(kThreads), smem, stream, p));
+  const dim3 grid(ceil_div(p.n_boxes, 2 * MB), p.K / BNW, p.split);
+  PMD_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BNW, ST, MB>, grid, dim3(kThreads), smem, stream, p));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
 }
 
 int launch_wgrad(const WgradParams& p, cudaStream_t stream) {
+  if (p.mb == 2) {
+    if (p.bn_tile == 256) return launch_wgrad_t<256, 3, 2>(p, stream);
+    if (p.bn_tile == 128) return launch_wgrad_t<128, 4, 2>(p, stream);
+    return launch_wgrad_t<64, 4, 2>(p, stream);
+  }
   if (p.bn_tile == 256) return launch_wgrad_t<256, 4>(p, stream);
   if (p.bn_tile == 128) return launch_wgrad_t<128, 4>(p, stream);
   return launch_wgrad_t<64, 4>(p, stream);
@@ -1669,6 +1794,17 @@ extern "C" PMD_API int pmd_conv_dgrad_krsc(const PmdConvShape* s, const void* d_
   }
   ConvGemmParams p;
   if (build_dgrad_params(*s, d_dy, d_w_krsc, s2, d_dy2, d_w2_krsc, d_addend, d_dx, &p, true)) return -1;
+  return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" PMD_API int pmd_conv_dgrad_bn_reduce(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const void* d_y_prev,
+                                                const float* d_scale, const float* d_shift, const float* d_mean,
+                                                const float* d_invstd, float* d_sums, void* d_dz, void* stream) {
+  ConvGemmParams p;
+  if (build_dgrad_params(*s, d_dy, d_w_krsc, nullptr, nullptr, nullptr, nullptr, d_dz, &p, true)) return -1;
+  const int rc = attach_bn_reduce(&p, *s, d_y_prev, d_scale, d_shift, d_mean, d_invstd, d_sums);
+  if (rc < 0) return -1;
+  PMD_REQUIRE(rc == 1, "this dgrad cannot carry the BatchNorm reduction (needs stride 1, C % 64 == 0, and the fusion enabled)");
   return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
 }
 

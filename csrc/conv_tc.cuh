@@ -40,6 +40,15 @@ struct ConvGemmParams {
   const __nv_bfloat16* addend;  // optional NHWC tensor shaped like the (single-class) output
   long long* trace;          // optional [trace_cap][kTraceSlots] per-CTA timestamps (pmd_conv_set_trace), else null
   int trace_cap;
+  // dgrad + BatchNorm-backward reduction in one kernel (attach_bn_reduce): the output dz = dL/dz of the previous
+  // layer's activation z = relu(BN(y)).  The epilogue loads the y tile, applies the ReLU mask to dz before storing
+  // it and accumulates per channel  sum(g), sum(g * xhat)  into red_sums -- exactly what the stand-alone
+  // bn_bwd_reduce kernel would compute from a second pass over dz and y.
+  int bn_reduce;
+  CUtensorMap ymap;                      // y of that BatchNorm, same shape and box as the output
+  const float *red_scale, *red_shift;    // forward affine (mask = scale*y + shift > 0)
+  const float *red_mean, *red_invstd;
+  float* red_sums;                       // [2 * out_channels], accumulated with red.global.add
 };
 
 // Per-CTA trace record written by the fprop/dgrad kernels when tracing is on (tools/conv_trace.py decodes it).
@@ -77,6 +86,7 @@ struct WgradParams {
   int bn_tile;               // 64, 128 or 256 output-channel columns per CTA
   int split;
   int c_valid;                 // rows (channels within a box) >= c_valid are not written (stem: 27 of 64)
+  int mb;                      // 128-row accumulators per CTA: 1 (two x boxes) or 2 (four)
   float* dw;
 };
 
@@ -137,6 +147,10 @@ int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck
                        bool w_is_krsc = false);
 int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, float* dw, int split, int sm_count,
                        WgradParams* out, int rsc_override = 0, int c_valid = 64);
+// Fuses the BatchNorm-backward reduction of the layer below into a stride-1, single-branch dgrad (see ConvGemmParams).
+// Returns 1 if attached, 0 if this dgrad cannot take it (the caller then runs the stand-alone reduce), -1 on error.
+int attach_bn_reduce(ConvGemmParams* p, const PmdConvShape& s, const void* y, const float* scale, const float* shift,
+                     const float* mean, const float* invstd, float* sums);
 int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream);
 int launch_wgrad(const WgradParams& p, cudaStream_t stream);
 

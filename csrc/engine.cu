@@ -76,6 +76,7 @@ struct Plan {
   std::vector<ConvGemmParams> inner_dgrad;   // per conv index (main[j], j >= 1)
   std::vector<ConvHaloParams> block_dgrad_h, inner_dgrad_h;
   std::vector<char> block_halo, inner_halo;
+  std::vector<char> inner_reduced;          // inner dgrad also does the BatchNorm-backward reduction of the layer below
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_launches = 0, eval_launches = 0;
   bool train_warm = false, eval_warm = false;
@@ -334,6 +335,7 @@ Plan* get_plan(PmdEngine* e, int n) {
   pl->inner_dgrad_h.resize(e->convs.size());
   pl->block_halo.assign(e->blocks.size(), 0);
   pl->inner_halo.assign(e->convs.size(), 0);
+  pl->inner_reduced.assign(e->convs.size(), 0);
   const bool halo_on = conv_halo_enabled(), halo_dgrad = conv_halo_dgrad_enabled();
   // C = K = 64 3x3 layers: weight-resident persistent kernel
   const bool resident_on = conv_resident_enabled(), resident_dgrad = conv_resident_dgrad_enabled();
@@ -365,6 +367,14 @@ Plan* get_plan(PmdEngine* e, int n) {
       if (build_dgrad_params(s, cv.dy, e->wbf16 + cv.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_mid[j - 1],
                              &pl->inner_dgrad[b.main[j]], true))
         return nullptr;
+      const bool halo_dgrad_here = (resident_dgrad && conv_resident_supported(s)) || (halo_dgrad && conv_halo_supported(s));
+      if (!halo_dgrad_here) {
+        // dz_mid[j-1] is consumed only by the BatchNorm backward of conv j-1: let the dgrad epilogue do its reduction
+        Conv& pv = e->convs[b.main[j - 1]];
+        const int rc = attach_bn_reduce(&pl->inner_dgrad[b.main[j]], s, pv.y, pv.scale, pv.shift, pv.mean, pv.invstd, pv.sums);
+        if (rc < 0) return nullptr;
+        pl->inner_reduced[b.main[j]] = static_cast<char>(rc);
+      }
       if (resident_dgrad && conv_resident_supported(s)) {
         if (build_dgrad_halo_params(s, cv.dy, e->wbf16 + cv.w_off, nullptr, b.dz_mid[j - 1],
                                     &pl->inner_dgrad_h[b.main[j]], true))
@@ -526,7 +536,7 @@ int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long
 // in the same two passes).  dz = gradient wrt the activation that followed; the ReLU mask comes from z
 // (block outputs, where a residual was added before the ReLU) or is recomputed from y (z == nullptr).
 int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, long long rows, bf16* g_out,
-                cudaStream_t st) {
+                cudaStream_t st, bool already_reduced = false) {
   const bool sync = e->sym.world > 1 && e->cfg.sync_bn;
   const int nb = cj >= 0 ? 2 : 1;
   PmdBnBranch br[2];
@@ -548,7 +558,8 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
   }
   Conv& c0 = e->convs[ci];
   const int mask = z != nullptr ? 1 : 2;
-  E_CHECK(pmd_bn_bwd_reduce_multi(dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
+  // already_reduced: the dgrad that produced dz accumulated the sums (and masked dz) in its epilogue
+  if (!already_reduced) E_CHECK(pmd_bn_bwd_reduce_multi(dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
   if (sync && !fused_sync_exchange()) {
     for (int b = 0; b < nb; ++b) {
       Conv& cv = e->convs[idx[b]];
@@ -634,11 +645,19 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
   };
   // Weight gradients are off the critical path (nothing in backward consumes them), so they run on a
   // side stream: the L2-bound wgrad GEMMs overlap the DRAM-bound BatchNorm passes of the layer below.
+  // dy_ready() marks the point on the main stream where a convolution's dy exists; wgrad(ci, ev) runs behind that
+  // mark on the side stream.  The dgrad of the same layer is enqueued BETWEEN the two calls: it is on the critical
+  // path, so its CTAs should reach the SMs first (PMD_DGRAD_FIRST=0 restores wgrad-first submission).
+  static const bool dgrad_first = getenv("PMD_DGRAD_FIRST") == nullptr || atoi(getenv("PMD_DGRAD_FIRST")) != 0;
+  cudaEvent_t ev_dy = nullptr;
+  auto dy_ready = [&]() -> int {
+    ev_dy = e->wg_events[(e->wg_event_next++) % e->wg_events.size()];
+    PMD_CHECK_CUDA(cudaEventRecord(ev_dy, st));
+    return 0;
+  };
   auto wgrad = [&](int ci) -> int {
     Conv& cv = e->convs[ci];
-    cudaEvent_t ev = e->wg_events[(e->wg_event_next++) % e->wg_events.size()];
-    PMD_CHECK_CUDA(cudaEventRecord(ev, st));                       // dy of this conv is ready
-    PMD_CHECK_CUDA(cudaStreamWaitEvent(e->wg_stream, ev, 0));
+    PMD_CHECK_CUDA(cudaStreamWaitEvent(e->wg_stream, ev_dy, 0));
     if (cv.tc) {
       E_CHECK(launch_wgrad(pl->conv[ci].wgrad, e->wg_stream));
     } else {
@@ -667,24 +686,34 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     if (b.sc >= 0) E_CHECK(bn_done(b.sc));
     for (int j = b.n_main - 1; j >= 1; --j) {
       const int ci = b.main[j], prev = b.main[j - 1];
-      E_CHECK(wgrad(ci));
+      E_CHECK(dy_ready());
+      if (!dgrad_first) E_CHECK(wgrad(ci));
       if (pl->inner_halo[ci])
         E_CHECK(launch_conv_halo(pl->inner_dgrad_h[ci], st));
       else
         E_CHECK(launch_conv_gemm(pl->inner_dgrad[ci], st));
+      if (dgrad_first) E_CHECK(wgrad(ci));
       E_CHECK(w_done(ci));
       Conv& pv = e->convs[prev];
-      E_CHECK(bn_backward(e, prev, -1, b.dz_mid[j - 1], nullptr, 1LL * n * pv.Ho * pv.Wo, nullptr, st));
+      E_CHECK(bn_backward(e, prev, -1, b.dz_mid[j - 1], nullptr, 1LL * n * pv.Ho * pv.Wo, nullptr, st,
+                          pl->inner_reduced[ci] != 0));
       E_CHECK(bn_done(prev));
     }
-    E_CHECK(wgrad(b.main[0]));
-    if (b.sc >= 0) E_CHECK(wgrad(b.sc));
+    E_CHECK(dy_ready());
+    if (!dgrad_first) {
+      E_CHECK(wgrad(b.main[0]));
+      if (b.sc >= 0) E_CHECK(wgrad(b.sc));
+    }
     if (b.sc >= 0 && e->convs[b.sc].s.stride != e->convs[b.main[0]].s.stride)
       E_CHECK(launch_conv_gemm(pl->sc_dgrad[bi], st));
     if (pl->block_halo[bi])
       E_CHECK(launch_conv_halo(pl->block_dgrad_h[bi], st));
     else
       E_CHECK(launch_conv_gemm(pl->block_dgrad[bi], st));
+    if (dgrad_first) {
+      E_CHECK(wgrad(b.main[0]));
+      if (b.sc >= 0) E_CHECK(wgrad(b.sc));
+    }
     E_CHECK(w_done(b.main[0]));
     if (b.sc >= 0) E_CHECK(w_done(b.sc));
   }
@@ -692,6 +721,7 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     Conv& cv = e->convs[0];
     E_CHECK(bn_backward(e, 0, -1, e->dz_stem, nullptr, 1LL * n * cv.Ho * cv.Wo, nullptr, st));
     E_CHECK(bn_done(0));
+    E_CHECK(dy_ready());
     E_CHECK(wgrad(0));
     E_CHECK(w_done(0));       // the stem has no dgrad
   }

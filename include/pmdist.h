@@ -49,6 +49,13 @@ int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, const void* d_w_rsck
  * copy of the weights is needed at all. */
 int pmd_conv_dgrad_krsc(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const PmdConvShape* s2,
                         const void* d_dy2, const void* d_w2_krsc, const void* d_addend, void* d_dx, void* stream);
+/* dgrad (stride 1, KRSC weights) fused with the BatchNorm-backward reduction of the layer below, whose output
+ * z = relu(scale*y_prev + shift) was this convolution's input: writes d_dz = mask(z > 0) * conv_transpose(dy, w) and
+ * accumulates d_sums[0..C) += sum(dz), d_sums[C..2C) += sum(dz * (y_prev - mean) * invstd) over all pixels (d_sums is
+ * an accumulator the caller zeroes).  Replaces pmd_conv_dgrad_krsc + pmd_bn_bwd_reduce_multi(mask_mode 2). */
+int pmd_conv_dgrad_bn_reduce(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const void* d_y_prev,
+                             const float* d_scale, const float* d_shift, const float* d_mean, const float* d_invstd,
+                             float* d_sums, void* d_dz, void* stream);
 /* dw (fp32, KRSC) += x^T * dy, reduction over all N*Ho*Wo pixels split over `split_k` CTAs per
  * output tile (0 = choose); partial tiles are added with red.global.add.f32, so d_dw is an
  * accumulator the caller zeroes (it is a slice of the flat gradient bucket slab). */

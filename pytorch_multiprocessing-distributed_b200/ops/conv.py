@@ -71,6 +71,19 @@ def conv_dgrad(dy: torch.Tensor, w: torch.Tensor, x_shape: Tuple[int, int, int, 
     return dx
 
 
+def conv_dgrad_bn_reduce(dy: torch.Tensor, w_krsc: torch.Tensor, y_prev: torch.Tensor, scale: torch.Tensor,
+                         shift: torch.Tensor, mean: torch.Tensor, invstd: torch.Tensor,
+                         sums: torch.Tensor) -> torch.Tensor:
+    """Stride-1 dgrad whose epilogue applies the ReLU mask of the layer below and accumulates that layer's
+    BatchNorm-backward sums (``pmd_conv_dgrad_bn_reduce``).  ``y_prev`` is that layer's pre-BN output [N,H,W,C]."""
+    K, R = w_krsc.shape[0], w_krsc.shape[1]
+    dz = torch.empty_like(y_prev)
+    s = _shape(tuple(y_prev.shape), K, R, 1)
+    check(_lib.lib().pmd_conv_dgrad_bn_reduce(C.byref(s), ptr(dy), ptr(w_krsc), ptr(y_prev), ptr(scale), ptr(shift), ptr(mean),
+                                              ptr(invstd), ptr(sums), ptr(dz), stream_ptr()))
+    return dz
+
+
 def conv_wgrad(x: torch.Tensor, dy: torch.Tensor, R: int, stride: int = 1, split_k: int = 0,
                out: Optional[torch.Tensor] = None, direct: bool = False,
                x_channels: Optional[int] = None) -> torch.Tensor:

@@ -149,6 +149,44 @@ for _name, _args in {
                                                 addend=(a[7] if len(a) > 7 else False), krsc=True))
 
 
+def _dgrad_bn_reduce_case(N, H, C, K, R):
+    """dgrad + BatchNorm-backward reduction in one kernel vs plain PyTorch fp32: masked dz and both channel sums."""
+    from pmdist.ops import conv as cv
+    dy = _rand_bf16(N, H, H, K, seed=11)
+    w = _rand_bf16(K, C, R, R, scale=1.0 / math.sqrt(K * R * R), seed=12)
+    y_prev = _rand_bf16(N, H, H, C, seed=13)
+    g = torch.Generator(device='cuda').manual_seed(14)
+    scale = torch.rand(C, device='cuda', generator=g) + 0.5
+    shift = torch.randn(C, device='cuda', generator=g) * 0.3
+    mean = torch.randn(C, device='cuda', generator=g) * 0.1
+    invstd = torch.rand(C, device='cuda', generator=g) + 0.5
+    sums = torch.zeros(2 * C, device='cuda')
+    dz = cv.conv_dgrad_bn_reduce(dy, cv.krsc_from_torch(w), y_prev, scale, shift, mean, invstd, sums)
+    torch.cuda.synchronize()
+    ref = _dgrad_ref(dy, w, (N, H, H, C), 1)
+    yf = y_prev.float()
+    mask = (yf * scale + shift) > 0
+    ref = torch.where(mask, ref, torch.zeros_like(ref))
+    res = _cmp(dz, ref, 2e-2)
+    dzf = dz.float()                      # the sums are defined over the bf16 tensor that was written
+    s1 = dzf.sum((0, 1, 2))
+    s2 = (dzf * (yf - mean) * invstd).sum((0, 1, 2))
+    r1, r2 = _cmp(sums[:C], s1, 2e-3), _cmp(sums[C:], s2, 2e-3)
+    res['sum_g_rel'], res['sum_gx_rel'] = r1['rel_to_max'], r2['rel_to_max']
+    res['ok'] = res['ok'] and r1['ok'] and r2['ok']
+    return res
+
+
+for _name, _args in {
+    'dgrad_bn_reduce_3x3_c64_k64_h32': (4, 32, 64, 64, 3),
+    'dgrad_bn_reduce_3x3_c128_k128_h16_n3': (3, 16, 128, 128, 3),
+    'dgrad_bn_reduce_3x3_c256_k256_h8': (8, 8, 256, 256, 3),
+    'dgrad_bn_reduce_1x1_c64_k256_h8': (8, 8, 64, 256, 1),
+    'dgrad_bn_reduce_3x3_c512_k512_h4': (16, 4, 512, 512, 3),
+}.items():
+    CASES[_name] = (lambda a=_args: _dgrad_bn_reduce_case(*a))
+
+
 # ------------------------------------------------------------------ wgrad
 def _wgrad_case(N, H, C, K, R, stride, split=0, direct=False):
     from pmdist.ops import conv as cv
