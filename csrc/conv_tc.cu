@@ -1166,6 +1166,126 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
   if (warp == 1) tmem_dealloc<MB * BNW>(tmem_base);
 }
 
+// ============================================================================ wgrad, all nine taps per CTA
+// For 3x3 stride-1 layers with few output channels the kernel above is bound by x traffic: every 64-pixel tile of x is
+// fetched once per tap (9 x 8 KB) and the small dy tile (8 KB) cannot amortise it (layer1: 786 MB through L2 = the
+// whole 78 us).  Here a CTA owns one 64-channel chunk of C, one 64-channel chunk of K and ALL nine taps: per 8x8-pixel
+// tile it loads three column patches of x (8 w x 10 h pixels, one per horizontal tap offset, as in
+// conv_gemm_halo_kernel) and one dy tile -- 38 KB instead of 96 KB -- and issues five M=128 MMAs per 16 pixels, each
+// covering two taps: the A descriptor is MN-major, so its two 64-row halves may sit anywhere in shared memory (LBO =
+// distance between the two tap views; a vertical tap offset is a whole 1024-byte swizzle atom, so every view starts
+// atom-aligned).  Five accumulators of 64 columns live in TMEM; tap order inside the accumulators is (s, r).
+constexpr int kWPatchBytes = 8 * 10 * 128;                 // 10240
+constexpr int kWPatchStage = 3 * kWPatchBytes + 8192;      // 38912 = 38 atoms
+__device__ __forceinline__ uint32_t wpatch_view(int u) {   // byte offset of tap view u = s*3 + r inside a stage
+  return static_cast<uint32_t>((u / 3) * kWPatchBytes + (u % 3) * 1024);
+}
+
+template <int STAGES>
+__global__ void __launch_bounds__(kThreads) conv_wgrad_patch_kernel(const __grid_constant__ WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  PipeBars<STAGES>* bars = reinterpret_cast<PipeBars<STAGES>*>(smem + STAGES * kWPatchStage);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c0 = blockIdx.x * 64, k0 = blockIdx.y * 64;
+  const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_n;
+  const int per = (tiles_total + gridDim.z - 1) / gridDim.z;
+  const int pt_begin = blockIdx.z * per;
+  const int pt_end = min(pt_begin + per, tiles_total);
+  const int niter = max(pt_end - pt_begin, 0);
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&bars->full[s], 1);
+      mbar_init(&bars->empty[s], 1);
+    }
+    mbar_init(&bars->tmem_full, 1);
+    fence_mbar_init();
+    prefetch_tmap(&p.dy);
+    prefetch_tmap(&p.x[0]);
+  }
+  if (warp == 1) tmem_alloc<512>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+  pdl_wait();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int i = 0; i < niter; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        int t = pt_begin + i;
+        const int w0 = (t % p.tiles_w) * 8;
+        t /= p.tiles_w;
+        const int h0 = (t % p.tiles_h) * 8;
+        const int n0 = t / p.tiles_h;
+        mbar_wait(&bars->empty[s], ph ^ 1u);
+        uint8_t* sa = smem + s * kWPatchStage;
+        mbar_expect_tx(&bars->full[s], kWPatchStage);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          tma_load_4d(&p.x[0], &bars->full[s], sa + q * kWPatchBytes, c0, w0 + q - 1, h0 - 1, n0);
+        tma_load_4d(&p.dy, &bars->full[s], sa + 3 * kWPatchBytes, k0, w0, h0, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, 64, true, true);
+      for (int i = 0; i < niter; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&bars->full[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + s * kWPatchStage);
+        const uint32_t b_addr = a_addr + 3 * kWPatchBytes;
+#pragma unroll
+        for (int pr = 0; pr < 5; ++pr) {
+          const uint32_t v0 = wpatch_view(2 * pr);
+          const uint32_t lbo = pr < 4 ? wpatch_view(2 * pr + 1) - v0 : 1024u;   // pair 4: second half is padding
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {   // 64 pixels = 4 x (K = 16 pixel rows of 128 B)
+            umma_bf16(tmem_base + pr * 64, make_smem_desc_sw128(a_addr + v0 + k * 2048, lbo, 1024),
+                      make_smem_desc_sw128(b_addr + k * 2048, 8192, 1024), idesc, (i | k) != 0 ? 1u : 0u);
+          }
+        }
+        umma_commit(&bars->empty[s]);
+      }
+      if (niter > 0) umma_commit(&bars->tmem_full);
+    }
+  } else if (niter > 0) {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int c = row & 63;
+    mbar_wait(&bars->tmem_full, 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int pr = 0; pr < 5; ++pr) {
+      const int u = 2 * pr + (row >> 6);              // tap view (s, r) of this accumulator row
+      const bool live = u < 9;
+      const int tap = (u % 3) * 3 + (u / 3);          // weight tap index r*3 + s
+      const int out_col = tap * p.C + c0 + c;
+#pragma unroll 1
+      for (int cc = 0; cc < 2; ++cc) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + pr * 64 + cc * 32, v);
+        tmem_ld_wait();
+        if (live) {
+          float* dst = p.dw + static_cast<long long>(k0 + cc * 32) * p.RSC + out_col;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) red_add_f32(dst + static_cast<long long>(j) * p.RSC, __uint_as_float(v[j]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
 // ============================================================================ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -1411,6 +1531,38 @@ int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, flo
   memset(&p, 0, sizeof(p));
   const int pad = s.R / 2, RS = s.R * s.R;
   const int Ho = conv_out_dim(s.H, s.R, s.stride), Wo = conv_out_dim(s.W, s.R, s.stride);
+  {
+    // PMD_WGRAD_PATCH: 1 (default) all-taps-per-CTA kernel for 3x3 stride-1 layers with K == 64, 2 for every K, 0 never
+    static const int patch_mode = getenv("PMD_WGRAD_PATCH") == nullptr ? 1 : atoi(getenv("PMD_WGRAD_PATCH"));
+    const bool shape_ok = s.R == 3 && s.stride == 1 && s.W % 8 == 0 && s.H % 8 == 0 && rsc_override == 0 && c_valid == 64;
+    if (shape_ok && (patch_mode == 2 || (patch_mode == 1 && s.K == 64))) {
+      p.patch = 1;
+      p.C = s.C;
+      p.K = s.K;
+      p.RSC = RS * s.C;
+      p.c_valid = 64;
+      p.dw = dw;
+      p.w_box = 8;
+      p.h_box = 8;
+      p.n_box = 1;
+      p.tiles_w = s.W / 8;
+      p.tiles_h = s.H / 8;
+      p.tiles_n = s.N;
+      if (act_map(&p.x[0], x, s.N, s.H, s.W, s.C, 1, 0, 0, 8, 10, 1)) return -1;
+      if (act_map(&p.dy, dy, s.N, s.H, s.W, s.K, 1, 0, 0, 8, 8, 1)) return -1;
+      const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_n;
+      const int ctas = (s.C / 64) * (s.K / 64);
+      if (split <= 0) {
+        split = (sm_count > 0 ? sm_count : 148) / ctas;     // one CTA per SM (152 KB of stages, all of TMEM): one wave
+        const int max_split = ceil_div(tiles_total, 8);
+        if (split > max_split) split = max_split;
+      }
+      if (split > tiles_total) split = tiles_total;
+      if (split < 1) split = 1;
+      p.split = split;
+      return 0;
+    }
+  }
   choose_brick(64, Wo, Ho, &p.w_box, &p.h_box, &p.n_box);
   p.tiles_w = ceil_div(Wo, p.w_box);
   p.tiles_h = ceil_div(Ho, p.h_box);
@@ -1738,7 +1890,23 @@ static int launch_wgrad_t(const WgradParams& p, cudaStream_t stream) {
   return 0;
 }
 
+static int launch_wgrad_patch(const WgradParams& p, cudaStream_t stream) {
+  constexpr int ST = 4;
+  constexpr int smem = ST * kWPatchStage + sizeof(PipeBars<ST>) + 1024;
+  static bool once = false;
+  if (!once) {
+    if (set_smem(conv_wgrad_patch_kernel<ST>, smem)) return -1;
+    once = true;
+  }
+  const dim3 grid(p.C / 64, p.K / 64, p.split);
+  PMD_CHECK_CUDA(launch_pdl(conv_wgrad_patch_kernel<ST>, grid, dim3(kThreads), smem, stream, p));
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
 int launch_wgrad(const WgradParams& p, cudaStream_t stream) {
+  if (p.patch) return launch_wgrad_patch(p, stream);
   if (p.mb == 2) {
     if (p.bn_tile == 256) return launch_wgrad_t<256, 3, 2>(p, stream);
     if (p.bn_tile == 128) return launch_wgrad_t<128, 4, 2>(p, stream);

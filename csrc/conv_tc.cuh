@@ -87,6 +87,8 @@ struct WgradParams {
   int split;
   int c_valid;                 // rows (channels within a box) >= c_valid are not written (stem: 27 of 64)
   int mb;                      // 128-row accumulators per CTA: 1 (two x boxes) or 2 (four)
+  int patch;                   // 3x3 stride-1, 64 output channels per CTA: conv_wgrad_patch_kernel (all nine taps per CTA)
+  int C;
   float* dw;
 };
 
