@@ -1842,8 +1842,17 @@ int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
   // persistent double-buffered variant on these shapes, so the latter is opt-in (PMD_GEMM_PERSISTENT=1).
   static const int st64 = stages_from_env("PMD_GEMM64_STAGES", 2), st128 = stages_from_env("PMD_GEMM128_STAGES", 3);
   static const bool persistent = getenv("PMD_GEMM_PERSISTENT") != nullptr && atoi(getenv("PMD_GEMM_PERSISTENT")) != 0;
+  // Layers whose tiles need only one or two k-blocks (the im2col'ed stem, 1x1 convolutions on 64-128 channels) are
+  // all set-up and epilogue in the one-tile-per-CTA kernel; PMD_GEMM_PERSISTENT_SMALL=1 sends them to the persistent
+  // kernel, whose TMA ring and TMEM double buffer run across tile boundaries.
+  static const bool persistent_small =
+      getenv("PMD_GEMM_PERSISTENT_SMALL") != nullptr && atoi(getenv("PMD_GEMM_PERSISTENT_SMALL")) != 0;
+  bool small = persistent_small && !p.b_mn_major && p.bn_tile != 256;
+  for (int c = 0; c < p.n_classes && small; ++c) small = p.kb_count[c] <= 2;
   int rc;
-  if (p.b_mn_major && p.bn_reduce) {
+  if (small) {
+    rc = p.bn_tile == 64 ? launch_conv_gemm_persistent_t<64, 4>(p, stream) : launch_conv_gemm_persistent_t<128, 3>(p, stream);
+  } else if (p.b_mn_major && p.bn_reduce) {
     rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true, true>(p, grid, stream)
                          : launch_conv_gemm_t<128, 3, true, true>(p, grid, stream);
   } else if (p.b_mn_major) {
