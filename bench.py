@@ -155,12 +155,25 @@ def run_native(a) -> None:
     # before that read, so it overlaps the running step.  (Also tried: H2D one step ahead on a copy stream into a
     # second set of device buffers + device-to-device copy -- the extra stream operations cost more host time than
     # the 63 us PCIe transfer they hide: 1.81 vs 1.69 ms/step.)
+    # With PMD_BENCH_ASYNC_METRICS=1 the read of step i's metrics is enqueued right behind step i but consumed on
+    # the host after step i+1 has been launched (NativeEngine.read_metrics_async), so the launch leaves the critical path.
+    async_metrics = os.environ.get('PMD_BENCH_ASYNC_METRICS', '0') != '0'
     nxt = next(it)
+    fut = None
     t0 = time.perf_counter()
     for _ in range(a.steps):
         eng.train_step(nxt, lr)                  # H2D of this step's batch from pinned memory + one graph launch
-        nxt = next(it)
-        m = eng.read_metrics()                   # device -> host read of the step's loss / accuracy
+        if async_metrics:
+            f2 = eng.read_metrics_async()        # D2H of this step's metrics, enqueued behind the step
+            nxt = next(it)
+            if fut is not None:
+                m = fut.result()                 # the previous step's loss / accuracy, on the host by now
+            fut = f2
+        else:
+            nxt = next(it)
+            m = eng.read_metrics()               # device -> host read of the step's loss / accuracy
+    if fut is not None:
+        m = fut.result()
     torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - t0) * 1e3
     comm.barrier()

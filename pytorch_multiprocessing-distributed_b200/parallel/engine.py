@@ -62,6 +62,26 @@ def _arr(ctype, values):
     return (ctype * len(values))(*values)
 
 
+def alias_tensor_f64(addr: int, device) -> torch.Tensor:
+    """double[4] view of the engine's metric accumulators."""
+    from .peer import alias_tensor
+    return alias_tensor(addr, 32, device).view(torch.float64)
+
+
+class MetricsFuture:
+    """Result of :meth:`NativeEngine.read_metrics_async`: ``[loss_sum, top1, top5, count]`` once the copy has landed."""
+
+    def __init__(self, slot: torch.Tensor, event: 'torch.cuda.Event') -> None:
+        self._slot, self._event = slot, event
+
+    def done(self) -> bool:
+        return self._event.query()
+
+    def result(self) -> List[float]:
+        self._event.synchronize()
+        return [float(x) for x in self._slot.tolist()]
+
+
 class NativeEngine:
     kind = 'native'
 
@@ -187,6 +207,9 @@ class NativeEngine:
             p.requires_grad_(False)
         self.step_count = 0
         self._pending_events: List[torch.cuda.Event] = []
+        self._metric_slots = None                  # read_metrics_async(): pinned host slots + alias of the device accumulators
+        self._metric_dev = None
+        self._metric_next = 0
         self.sync_params(broadcast=True)
 
     # ------------------------------------------------------------------ plumbing
@@ -232,6 +255,27 @@ class NativeEngine:
         check(self.lib.pmd_engine_read_metrics(self._h, C.c_int(int(reduce)), C.c_int(int(reset)), out,
                                                _lib.stream_ptr()))
         return [float(x) for x in out]
+
+    def read_metrics_async(self, reset: bool = True) -> 'MetricsFuture':
+        """Like :meth:`read_metrics` (this rank only) but without stalling the host: the device->host copy of the
+        accumulators into a pinned slot (and the reset) are enqueued behind the steps issued so far, and the
+        returned future's ``result()`` waits for just that copy.  A loop that calls ``result()`` one step late keeps
+        the next step's launch off the critical path::
+
+            eng.train_step(b0, lr); f = eng.read_metrics_async()
+            eng.train_step(b1, lr); g = eng.read_metrics_async(); loss0 = f.result()[0]
+        """
+        if self._metric_slots is None:
+            self._metric_dev = alias_tensor_f64(self.bufs.metrics, self.device)
+            self._metric_slots = [torch.empty(4, dtype=torch.float64).pin_memory() for _ in range(4)]
+        slot = self._metric_slots[self._metric_next % len(self._metric_slots)]
+        self._metric_next += 1
+        slot.copy_(self._metric_dev, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        if reset:
+            self._metric_dev.zero_()
+        return MetricsFuture(slot, ev)
 
     def launches_per_step(self, n: Optional[int] = None) -> int:
         return int(self.lib.pmd_engine_launches_per_step(self._h, C.c_int(n or self.max_batch)))
