@@ -133,19 +133,37 @@ def run_native(a) -> None:
     eng.read_metrics()
     torch.cuda.synchronize()
 
-    # ---- device-timed region: inputs resident in device memory
-    comm.barrier()
-    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # ---- device-timed region: inputs resident in device memory.  The ranks are aligned ON THE DEVICE (a barrier
+    # kernel in the stream right before the start event), so the window holds K steps and no host-side entry skew.
+    def timed_steps(k: int) -> float:
+        comm.barrier()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if world > 1:
+            comm.device_barrier()
+        marks = []
+        t0.record()
+        for _ in range(k):
+            eng.train_step_staged(B, lr)
+            if trace_steps:                      # diagnostic only (PMD_BENCH_STEP_EVENTS=1): one event per step
+                marks.append(torch.cuda.Event(enable_timing=True))
+                marks[-1].record()
+        t1.record()
+        torch.cuda.synchronize()
+        comm.barrier()
+        if marks:
+            prev, per = t0, []
+            for m_ in marks:
+                per.append(round(prev.elapsed_time(m_), 4))
+                prev = m_
+            step_traces.append(per)
+        return t0.elapsed_time(t1)
+
+    trace_steps = os.environ.get('PMD_BENCH_STEP_EVENTS', '0') != '0'
+    step_traces = []
     launches0 = _lib.launch_count()
     with ClockSampler(local) as clk:
-        start.record()
-        for _ in range(a.steps):
-            eng.train_step_staged(B, lr)
-        stop.record()
-        torch.cuda.synchronize()
+        dev_ms = timed_steps(a.steps)
     launches = _lib.launch_count() - launches0
-    comm.barrier()
-    dev_ms = start.elapsed_time(stop)
     loss_dev = eng.read_metrics()
 
     # ---- end-to-end region: public API, H2D of every batch from pinned memory, D2H of the metrics
@@ -178,10 +196,29 @@ def run_native(a) -> None:
     e2e_ms = (time.perf_counter() - t0) * 1e3
     comm.barrier()
 
+    # ---- exposed communication: the same K steps with the collectives stubbed out (BatchNorm statistics and
+    # gradient buckets stay rank-local: the kernels of a 1-GPU run on every GPU at once).  Last, because the
+    # ranks' weights diverge under the stub.
+    lps = eng.launches_per_step(B)
+    stub_ms = {}
+    if world > 1 and not a.no_exposed_comm:
+        for name, mask in (('no_comm', 3), ('no_bn_exchange', 1), ('no_grad_allreduce', 2)):
+            eng.set_comm_stub(mask)
+            for _ in range(3):
+                eng.train_step_staged(B, lr)       # eager, capture, first replay
+            torch.cuda.synchronize()
+            stub_ms[name] = timed_steps(a.steps)
+        eng.set_comm_stub(0)
     import struct
-    gathered = comm.all_gather_bytes(struct.pack('dd', dev_ms, e2e_ms))
-    dev_max = max(struct.unpack('dd', g)[0] for g in gathered)
-    e2e_max = max(struct.unpack('dd', g)[1] for g in gathered)
+    names = sorted(stub_ms)
+    gathered = comm.all_gather_bytes(struct.pack('%dd' % (2 + len(names)), dev_ms, e2e_ms, *[stub_ms[k] for k in names]))
+    cols = list(zip(*[struct.unpack('%dd' % (2 + len(names)), g) for g in gathered]))
+    dev_max, e2e_max = max(cols[0]), max(cols[1])
+    stub_max = {k: max(cols[2 + i]) for i, k in enumerate(names)}
+    if step_traces:
+        os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
+        with open(os.path.join(ROOT, 'gpurun_out', f'step_ms_n{world}_rank{rank}.json'), 'w') as f:
+            json.dump(step_traces, f)
     if rank == 0:
         gb = B * world
         value = gb * a.steps / (dev_max / 1e3)
@@ -201,7 +238,13 @@ def run_native(a) -> None:
                     'ms_per_step': round(e2e_max / a.steps, 4),
                     'h2d_bytes_per_step': eng.h2d_bytes(B), 'd2h_bytes_per_step': 32,
                     'path': 'BatchLoader(pinned) -> NativeEngine.train_step -> read_metrics'},
-            'gpu_launches': int(launches), 'launches_per_step': eng.launches_per_step(B),
+            'exposed_comm_ms': (round((dev_max - stub_max['no_comm']) / a.steps, 4) if stub_max else
+                                (0.0 if world == 1 else None)),
+            'exposed_comm': ({'ms_per_step_full': round(dev_max / a.steps, 4),
+                              **{f'ms_per_step_{k}': round(v / a.steps, 4) for k, v in stub_max.items()},
+                              'how': 'same build, same K steps, collectives stubbed by NativeEngine.set_comm_stub '
+                                     '(exchanges read local data only); exposed = full - no_comm'} if stub_max else None),
+            'gpu_launches': int(launches), 'launches_per_step': lps,
             'loss_after_bench': (m[0] / m[3]) if m[3] else None,
             'achieved_tflops_per_gpu': round(spec.train_flops_per_image(a.image_size) * B * a.steps / (dev_max / 1e3) / 1e12, 2),
         }
@@ -292,6 +335,7 @@ def main() -> None:
     ap.add_argument('--algo', default='auto')
     ap.add_argument('--bucket-mb', type=float, default=0.0)
     ap.add_argument('--no-graph', action='store_true')
+    ap.add_argument('--no-exposed-comm', action='store_true', help='skip the collectives-stubbed timing runs')
     a = ap.parse_args()
     if a.impl == 'reference':
         run_reference(a)

@@ -7,7 +7,7 @@
 // tables so that one code path serves 1..8 ranks and rank-order-fixed summation keeps every rank
 // bitwise identical.
 #include "common.cuh"
-#include "sym.cuh"
+#include "sync_tail.cuh"
 #include "../include/pmdist.h"
 
 namespace pmd {
@@ -204,9 +204,9 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float
 // (a single tiny block between two large kernels, i.e. pure dependency latency) can go: every block of the
 // apply kernel derives scale/shift from the [sum, sumsq] vector itself (2C loads, C rsqrt -- noise next to the
 // activation traffic), and block 0 also stores what backward and the checkpoint need (mean, invstd, scale, shift,
-// running statistics, num_batches_tracked).  Under SyncBatchNorm the cross-GPU exchange happens in the same
-// prologue (ll_exchange_sum_grid: block 0 pushes and polls over NVLink, the other blocks pick the totals up from
-// local memory).  With RES == 2 the projection shortcut's BatchNorm is finalised here too.
+// running statistics, num_batches_tracked).  With RES == 2 the projection shortcut's BatchNorm is finalised here
+// too.  Single-rank statistics only: under multi-rank SyncBatchNorm the producer's last CTA has already exchanged
+// and finalised them (sync_tail.cuh) and the plain bn_apply_kernel runs instead.
 struct BnFinalizeDev {
   const float* stats;
   const float* gamma;
@@ -215,29 +215,22 @@ struct BnFinalizeDev {
   float* running_var;
   long long* nbt;
   float *scale, *shift, *mean, *invstd;
-  float* totals;                // local scratch [2C] (multi-rank only)
-  unsigned long long recv_off;  // push-exchange receive area (multi-rank only)
-  int slot;
 };
 
-template <int RES, bool SYNC>
-__global__ void bn_finalize_apply_kernel(PmdSym sym, BnFinalizeDev f0, BnFinalizeDev f1, float count_per_rank,
+template <int RES>
+__global__ void bn_finalize_apply_kernel(BnFinalizeDev f0, BnFinalizeDev f1, float count_per_rank,
                                          float momentum, float eps, const __nv_bfloat16* __restrict__ y,
                                          const __nv_bfloat16* __restrict__ res, int relu, __nv_bfloat16* __restrict__ z,
                                          long long total8, int C) {
   pdl_wait();
   extern __shared__ float aff[];     // [scale | shift | rscale | rshift] (C each) + totals scratch [2C]
   float* tot = aff + 4 * C;
-  const float n = count_per_rank * (SYNC ? sym.world : 1);
+  const float n = count_per_rank;
 #pragma unroll
   for (int b = 0; b < (RES == 2 ? 2 : 1); ++b) {
     const BnFinalizeDev& f = b == 0 ? f0 : f1;
-    if (SYNC) {
-      ll_exchange_sum_grid(sym, f.slot, f.stats, 2 * C, f.recv_off, f.totals, tot);
-    } else {
-      for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) tot[c] = f.stats[c];
-      __syncthreads();
-    }
+    for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) tot[c] = f.stats[c];
+    __syncthreads();
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
       const float mean = tot[c] / n;
       const float var = fmaxf(tot[C + c] / n - mean * mean, 0.f);
@@ -314,9 +307,6 @@ __global__ void bn_finalize_apply_kernel(PmdSym sym, BnFinalizeDev f0, BnFinaliz
 // source once instead of twice.  MASK: 0 none, 1 z > 0, 2 recomputed from branch 0's own forward
 // affine (scale*y + shift > 0; valid when that BatchNorm had no residual), which skips reading z at all.
 struct BnBranchDev {
-  unsigned long long recv_off;  // push-exchange receive area (multi-rank fused exchange only)
-  float* totals_scratch;        // local [2C] where block 0 publishes the exchanged totals
-  int slot;
   const __nv_bfloat16* y;
   const float* mean;
   const float* invstd;
@@ -328,11 +318,15 @@ struct BnBranchDev {
   float* dbeta;
 };
 
+struct BnReduceTails {    // multi-rank SyncBatchNorm: the exchange(s) the last block of the reduction completes
+  SyncTail t[2];
+};
+
 template <int NB, int MASK>
 __global__ void __launch_bounds__(kBlock, 4)
 bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
                            const float* __restrict__ mscale, const float* __restrict__ mshift, BnBranchDev b0,
-                           BnBranchDev b1, long long rows, int C) {
+                           BnBranchDev b1, long long rows, int C, const __grid_constant__ BnReduceTails tails) {
   // Accumulates S_g = sum(g) and S_gy = sum(g*y) per channel; sum(g*xhat) = (S_gy - mean*S_g)*invstd is formed
   // once per block at the end, so the streaming loop carries no per-channel statistics in registers (the
   // register budget decides how many of these DRAM-bound blocks fit on an SM).
@@ -422,27 +416,23 @@ bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bflo
       red_add_f32(b1.sums + C + c, (t1 - b1.mean[c] * tg) * b1.invstd[c]);
     }
   }
+  if (tails.t[0].mode != 0) {
+    __syncthreads();       // the block-reduction scratch is free again: (1 + NB) * rpi * C >= NB * 2C floats
+    sync_tail_run(tails.t[0], b0.sums, NB == 2 ? &tails.t[1] : nullptr, b1.sums, scratch, gridDim.x);
+  }
 }
 
-template <int NB, int MASK, bool SYNC>
-__global__ void __launch_bounds__(kBlock, NB == 1 ? 3 : 2) bn_bwd_apply_multi_kernel(PmdSym sym, const __nv_bfloat16* __restrict__ dz,
+template <int NB, int MASK>
+__global__ void __launch_bounds__(kBlock, NB == 1 ? 3 : 2) bn_bwd_apply_multi_kernel(const __nv_bfloat16* __restrict__ dz,
                                           const __nv_bfloat16* __restrict__ z, const float* __restrict__ mscale,
                                           const float* __restrict__ mshift, BnBranchDev b0, BnBranchDev b1,
                                           float count_total, __nv_bfloat16* __restrict__ g_out, long long total8,
                                           int C) {
   // dy = gamma*invstd * (g - mean_g - xhat*mean_gx), xhat = (y - mean)*invstd, folded per channel into
   // dy = a*g + k1*y + k0.  Shared layout: per branch [a | k1 | k0] (C floats each), then [mscale | mshift].
-  // SYNC: the cross-GPU sum of [sum_g, sum_gx] is exchanged right here (block 0 pushes/polls, see sym.cuh)
+  // br.totals = [sum_g, sum_gx] over ALL ranks (left there by the producer's exchange under SyncBatchNorm).
   pdl_wait();
   extern __shared__ float coef[];
-  float* tot = coef + (NB * 3 + 2) * C;      // [NB][2C], SYNC only
-  if (SYNC) {
-#pragma unroll
-    for (int b = 0; b < NB; ++b) {
-      const BnBranchDev& br = b == 0 ? b0 : b1;
-      ll_exchange_sum_grid(sym, br.slot, br.sums, 2 * C, br.recv_off, br.totals_scratch, tot + b * 2 * C);
-    }
-  }
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
@@ -450,8 +440,8 @@ __global__ void __launch_bounds__(kBlock, NB == 1 ? 3 : 2) bn_bwd_apply_multi_ke
       float* cf = coef + b * 3 * C;
       const float is = br.invstd[c], mu = br.mean[c];
       const float a = br.gamma[c] * is;
-      const float tg = SYNC ? tot[b * 2 * C + c] : br.totals[c];
-      const float tgx = SYNC ? tot[b * 2 * C + C + c] : br.totals[C + c];
+      const float tg = br.totals[c];
+      const float tgx = br.totals[C + c];
       const float mg = tg / count_total, mgx = tgx / count_total;
       cf[c] = a;
       cf[C + c] = -a * mgx * is;
@@ -615,9 +605,6 @@ extern "C" PMD_API int pmd_bn_apply(const void* d_y, const float* d_scale, const
 
 static BnBranchDev to_dev(const PmdBnBranch& b) {
   BnBranchDev d;
-  d.recv_off = b.recv_off;
-  d.totals_scratch = b.totals_scratch;
-  d.slot = b.slot;
   d.y = static_cast<const __nv_bfloat16*>(b.y);
   d.mean = b.mean;
   d.invstd = b.invstd;
@@ -631,136 +618,133 @@ static BnBranchDev to_dev(const PmdBnBranch& b) {
 }
 
 template <int NB>
-static void launch_reduce(int mask, int grid, int smem, cudaStream_t st, const __nv_bfloat16* dz, const __nv_bfloat16* z,
-                          const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, long long rows, int C) {
+static cudaError_t launch_reduce(int mask, int smem, cudaStream_t st, const __nv_bfloat16* dz, const __nv_bfloat16* z,
+                                 const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, long long rows, int C,
+                                 const BnReduceTails& tails) {
   const int rpi8 = (kBlock / (C / 8) > 0 ? kBlock / (C / 8) : 1) * 8;
-  (void)grid;
 #define PMD_RED(M)                                                                                                  \
-  launch_pdl(bn_bwd_reduce_multi_kernel<NB, M>, dim3(wave_grid(bn_bwd_reduce_multi_kernel<NB, M>, kBlock, smem, rows, rpi8)), \
-             dim3(kBlock), smem, st, dz, z, ms, mh, b0, b1, rows, C)
+  return launch_pdl(bn_bwd_reduce_multi_kernel<NB, M>,                                                              \
+                    dim3(wave_grid(bn_bwd_reduce_multi_kernel<NB, M>, kBlock, smem, rows, rpi8)), dim3(kBlock), smem, \
+                    st, dz, z, ms, mh, b0, b1, rows, C, tails)
   if (mask == 0) PMD_RED(0);
   if (mask == 1) PMD_RED(1);
-  if (mask == 2) PMD_RED(2);
+  PMD_RED(2);
 #undef PMD_RED
 }
-template <int NB, int MASK, bool SYNC>
-static void allow_big_smem() {
-  static bool once = false;
-  if (!once) {
-    cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, MASK, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
-    once = true;
-  }
-}
 
-template <int NB, bool SYNC>
-static void launch_apply(const PmdSym& sym, int mask, int grid, int smem, cudaStream_t st, const __nv_bfloat16* dz,
-                         const __nv_bfloat16* z, const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1,
-                         float count, __nv_bfloat16* g_out, long long total8, int C) {
-  if (smem > 48 * 1024) {
-    allow_big_smem<NB, 0, SYNC>();
-    allow_big_smem<NB, 1, SYNC>();
-    allow_big_smem<NB, 2, SYNC>();
+static int bn_bwd_reduce_impl(const PmdSym* sym, const void* d_dz, const void* d_z, const float* d_mask_scale,
+                              const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb, long long rows,
+                              int C, void* stream) {
+  BN_CHECK_C(C);
+  PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
+  PMD_REQUIRE(mask_mode >= 0 && mask_mode <= 2, "mask mode must be 0, 1 or 2");
+  PMD_REQUIRE(mask_mode != 1 || d_z != nullptr, "mask mode 1 needs z");
+  PMD_REQUIRE(mask_mode != 2 || (d_mask_scale != nullptr && d_mask_shift != nullptr), "mask mode 2 needs the forward affine");
+  const int groups = C / 8, rpi = kBlock / groups > 0 ? kBlock / groups : 1;
+  PMD_REQUIRE(groups <= kBlock, "C too large for bn_bwd_reduce");
+  BnReduceTails tails{};
+  int scratch_floats = (1 + nb) * rpi * C;
+  if (sym != nullptr && sym->world > 1) {
+    for (int i = 0; i < nb; ++i) {
+      PMD_REQUIRE(br[i].totals_out != nullptr, "the exchanging reduction needs totals_out for every branch");
+      SyncTail& t = tails.t[i];
+      t.mode = 2;
+      t.slot = br[i].slot;
+      t.sym = *sym;
+      t.recv_off = br[i].recv_off;
+      t.C = C;
+      t.totals = br[i].totals_out;
+    }
+    if (scratch_floats < nb * 2 * C) scratch_floats = nb * 2 * C;
   }
-  const int blk = fixed_block(C);
-  (void)grid;
-#define PMD_APP(M)                                                                                             \
-  launch_pdl(bn_bwd_apply_multi_kernel<NB, M, SYNC>,                                                           \
-             dim3(wave_grid(bn_bwd_apply_multi_kernel<NB, M, SYNC>, blk, smem, total8, blk * 2)), dim3(blk), smem, st, sym, dz, z, \
-             ms, mh, b0, b1, count, g_out, total8, C)
-  if (mask == 0) PMD_APP(0);
-  if (mask == 1) PMD_APP(1);
-  if (mask == 2) PMD_APP(2);
-#undef PMD_APP
+  const int smem = (2 * C + scratch_floats) * 4;
+  const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
+  const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);
+  if (nb == 1)
+    PMD_CHECK_CUDA(launch_reduce<1>(mask_mode, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C, tails));
+  else
+    PMD_CHECK_CUDA(launch_reduce<2>(mask_mode, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C, tails));
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
 }
 
 extern "C" PMD_API int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
                                                const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
                                                long long rows, int C, void* stream) {
-  BN_CHECK_C(C);
-  PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
-  PMD_REQUIRE(mask_mode != 1 || d_z != nullptr, "mask mode 1 needs z");
-  PMD_REQUIRE(mask_mode != 2 || (d_mask_scale != nullptr && d_mask_shift != nullptr), "mask mode 2 needs the forward affine");
-  const int groups = C / 8, rpi = kBlock / groups > 0 ? kBlock / groups : 1;
-  PMD_REQUIRE(groups <= kBlock, "C too large for bn_bwd_reduce");
-  const int smem = (2 * C + (1 + nb) * rpi * C) * 4;
-  const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
-  const int grid = grid_for(rows, rpi * 8);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
-  const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);
-  if (nb == 1)
-    launch_reduce<1>(mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C);
-  else
-    launch_reduce<2>(mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C);
-  count_launch();
-  PMD_LAUNCH_CHECK();
-  return 0;
+  return bn_bwd_reduce_impl(nullptr, d_dz, d_z, d_mask_scale, d_mask_shift, mask_mode, br, nb, rows, C, stream);
 }
 
-static int bn_bwd_apply_impl(const PmdSym* sym, const void* d_dz, const void* d_z, const float* d_mask_scale,
-                             const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb, float count_total,
-                             void* d_g_out, long long rows, int C, void* stream) {
-  BN_CHECK_C(C);
-  PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
-  const bool sync = sym != nullptr && sym->world > 1;
-  const long long total8 = rows * C / 8;
-  const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
-  const int grid = grid_for(total8, kBlock * 2);
-  const int smem = (nb * 3 + 2 + (sync ? nb * 2 : 0)) * C * 4;
-  PMD_REQUIRE(smem <= 128 * 1024, "too many channels for the fused BatchNorm backward");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
-  const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);
-  __nv_bfloat16* g = static_cast<__nv_bfloat16*>(d_g_out);
-  PmdSym none{};
-  none.world = 1;
-  if (!sync) {
-    if (nb == 1)
-      launch_apply<1, false>(none, mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
-    else
-      launch_apply<2, false>(none, mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
-  } else {
-    if (nb == 1)
-      launch_apply<1, true>(*sym, mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
-    else
-      launch_apply<2, true>(*sym, mask_mode, grid, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C);
+extern "C" PMD_API int pmd_bn_bwd_reduce_multi_sync(const PmdSym* sym, const void* d_dz, const void* d_z,
+                                                    const float* d_mask_scale, const float* d_mask_shift, int mask_mode,
+                                                    const PmdBnBranch* br, int nb, long long rows, int C, void* stream) {
+  return bn_bwd_reduce_impl(sym, d_dz, d_z, d_mask_scale, d_mask_shift, mask_mode, br, nb, rows, C, stream);
+}
+
+template <int NB>
+static cudaError_t launch_apply(int mask, int smem, cudaStream_t st, const __nv_bfloat16* dz, const __nv_bfloat16* z,
+                                const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, float count,
+                                __nv_bfloat16* g_out, long long total8, int C) {
+  static PerDevice<bool> ready;       // > 48 KB of dynamic shared memory must be allowed per kernel, per device
+  bool* once = ready.get();
+  if (once == nullptr) return cudaErrorInvalidDevice;
+  if (!*once) {
+    cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+    cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+    cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+    *once = true;
   }
-  count_launch();
-  PMD_LAUNCH_CHECK();
-  return 0;
+  const int blk = fixed_block(C);
+#define PMD_APP(M)                                                                                                     \
+  return launch_pdl(bn_bwd_apply_multi_kernel<NB, M>,                                                                  \
+                    dim3(wave_grid(bn_bwd_apply_multi_kernel<NB, M>, blk, smem, total8, blk * 2)), dim3(blk), smem, st, \
+                    dz, z, ms, mh, b0, b1, count, g_out, total8, C)
+  if (mask == 0) PMD_APP(0);
+  if (mask == 1) PMD_APP(1);
+  PMD_APP(2);
+#undef PMD_APP
 }
 
 extern "C" PMD_API int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
                                               const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
                                               float count_total, void* d_g_out, long long rows, int C, void* stream) {
-  return bn_bwd_apply_impl(nullptr, d_dz, d_z, d_mask_scale, d_mask_shift, mask_mode, br, nb, count_total, d_g_out, rows, C,
-                           stream);
+  BN_CHECK_C(C);
+  PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
+  PMD_REQUIRE(mask_mode >= 0 && mask_mode <= 2, "mask mode must be 0, 1 or 2");
+  const long long total8 = rows * C / 8;
+  const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
+  const int smem = (nb * 3 + 2) * C * 4;
+  PMD_REQUIRE(smem <= 128 * 1024, "too many channels for the fused BatchNorm backward");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
+  const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);
+  __nv_bfloat16* g = static_cast<__nv_bfloat16*>(d_g_out);
+  if (nb == 1)
+    PMD_CHECK_CUDA(launch_apply<1>(mask_mode, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C));
+  else
+    PMD_CHECK_CUDA(launch_apply<2>(mask_mode, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, count_total, g, total8, C));
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
 }
 
-// Multi-rank form: the [sum_g, sum_gx] vectors of all ranks are exchanged inside the kernel's prologue
-// (br[i].slot / recv_off / totals_scratch must be set; br[i].totals is ignored).
-extern "C" PMD_API int pmd_bn_bwd_apply_multi_sync(const PmdSym* sym, const void* d_dz, const void* d_z,
-                                                   const float* d_mask_scale, const float* d_mask_shift, int mask_mode,
-                                                   const PmdBnBranch* br, int nb, float count_total, void* d_g_out,
-                                                   long long rows, int C, void* stream) {
-  return bn_bwd_apply_impl(sym, d_dz, d_z, d_mask_scale, d_mask_shift, mask_mode, br, nb, count_total, d_g_out, rows, C,
-                           stream);
-}
-
-// Forward: finalize (+ SyncBatchNorm exchange) + apply in one launch.
-template <int RES, bool SYNC>
-static void launch_finalize_apply(const PmdSym& sym, int grid, int smem, cudaStream_t st, const BnFinalizeDev& f0,
-                                  const BnFinalizeDev& f1, float count, float momentum, float eps, const __nv_bfloat16* y,
-                                  const __nv_bfloat16* res, int relu, __nv_bfloat16* z, long long total8, int C) {
-  static bool once = false;
-  if (!once && smem > 48 * 1024) {
-    cudaFuncSetAttribute(bn_finalize_apply_kernel<RES, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-    once = true;
+// Forward: finalize + apply in one launch (single-rank statistics).
+template <int RES>
+static cudaError_t launch_finalize_apply(int smem, cudaStream_t st, const BnFinalizeDev& f0, const BnFinalizeDev& f1,
+                                         float count, float momentum, float eps, const __nv_bfloat16* y,
+                                         const __nv_bfloat16* res, int relu, __nv_bfloat16* z, long long total8, int C) {
+  static PerDevice<bool> ready;
+  bool* once = ready.get();
+  if (once == nullptr) return cudaErrorInvalidDevice;
+  if (!*once) {
+    cudaFuncSetAttribute(bn_finalize_apply_kernel<RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    *once = true;
   }
   const int blk = fixed_block(C);
-  (void)grid;
-  launch_pdl(bn_finalize_apply_kernel<RES, SYNC>, dim3(wave_grid(bn_finalize_apply_kernel<RES, SYNC>, blk, smem, total8, blk * 2)),
-             dim3(blk), smem, st, sym, f0, f1, count, momentum, eps, y, res, relu, z, total8, C);
+  return launch_pdl(bn_finalize_apply_kernel<RES>, dim3(wave_grid(bn_finalize_apply_kernel<RES>, blk, smem, total8, blk * 2)),
+                    dim3(blk), smem, st, f0, f1, count, momentum, eps, y, res, relu, z, total8, C);
 }
 
 static BnFinalizeDev to_dev(const PmdBnFinalize& f) {
@@ -775,41 +759,29 @@ static BnFinalizeDev to_dev(const PmdBnFinalize& f) {
   d.shift = f.shift;
   d.mean = f.mean;
   d.invstd = f.invstd;
-  d.totals = f.totals_scratch;
-  d.recv_off = f.recv_off;
-  d.slot = f.slot;
   return d;
 }
 
-extern "C" PMD_API int pmd_bn_finalize_apply(const PmdSym* sym, const PmdBnFinalize* f, const PmdBnFinalize* f_res,
-                                             float count_per_rank, float momentum, float eps, const void* d_y,
-                                             const void* d_res, int relu, void* d_z, long long rows, int C, void* stream) {
+extern "C" PMD_API int pmd_bn_finalize_apply(const PmdBnFinalize* f, const PmdBnFinalize* f_res, float count,
+                                             float momentum, float eps, const void* d_y, const void* d_res, int relu,
+                                             void* d_z, long long rows, int C, void* stream) {
   BN_CHECK_C(C);
   PMD_REQUIRE(f != nullptr, "missing BatchNorm description");
   PMD_REQUIRE(f_res == nullptr || d_res != nullptr, "a residual BatchNorm needs the residual tensor");
-  const bool sync = sym != nullptr && sym->world > 1;
   const long long total8 = rows * C / 8;
-  const int grid = grid_for(total8, kBlock * 2);
   const int smem = 6 * C * 4;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const __nv_bfloat16* y = static_cast<const __nv_bfloat16*>(d_y);
   const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(d_res);
   __nv_bfloat16* z = static_cast<__nv_bfloat16*>(d_z);
   const BnFinalizeDev f0 = to_dev(*f), f1 = to_dev(f_res != nullptr ? *f_res : *f);
-  PmdSym none{};
-  none.world = 1;
   const int resmode = f_res != nullptr ? 2 : (d_res != nullptr ? 1 : 0);
-#define PMD_FA(RES, SYNC, S) launch_finalize_apply<RES, SYNC>(S, grid, smem, st, f0, f1, count_per_rank, momentum, eps, y, res, relu, z, total8, C)
-  if (!sync) {
-    if (resmode == 0) PMD_FA(0, false, none);
-    if (resmode == 1) PMD_FA(1, false, none);
-    if (resmode == 2) PMD_FA(2, false, none);
-  } else {
-    if (resmode == 0) PMD_FA(0, true, *sym);
-    if (resmode == 1) PMD_FA(1, true, *sym);
-    if (resmode == 2) PMD_FA(2, true, *sym);
-  }
-#undef PMD_FA
+  if (resmode == 0)
+    PMD_CHECK_CUDA(launch_finalize_apply<0>(smem, st, f0, f1, count, momentum, eps, y, res, relu, z, total8, C));
+  else if (resmode == 1)
+    PMD_CHECK_CUDA(launch_finalize_apply<1>(smem, st, f0, f1, count, momentum, eps, y, res, relu, z, total8, C));
+  else
+    PMD_CHECK_CUDA(launch_finalize_apply<2>(smem, st, f0, f1, count, momentum, eps, y, res, relu, z, total8, C));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
@@ -840,14 +812,31 @@ __global__ void sum_tables_kernel(const float* const* tabs, int world, int n, fl
 }  // namespace
 }  // namespace pmd
 
+namespace {
+struct BwdApplyScratch {
+  pmd::PerDevice<float*> slots;
+  ~BwdApplyScratch() {
+    int cur = 0;
+    if (cudaGetDevice(&cur) != cudaSuccess) return;     // runtime already torn down at process exit: nothing to free
+    for (int d = 0; d < 64; ++d)
+      if (slots.slot[d] != nullptr && cudaSetDevice(d) == cudaSuccess) cudaFree(slots.slot[d]);
+    cudaSetDevice(cur);
+  }
+} g_bwd_apply_scratch;
+}  // namespace
+
 extern "C" PMD_API int pmd_bn_bwd_apply(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean,
                                         const float* d_invstd, const float* d_gamma, const float* const* d_sums_ranks,
                                         int world, const float* d_local_sums, float count_total, int relu, void* d_dy,
                                         float* d_dgamma, float* d_dbeta, void* d_g_out, long long rows, int C,
                                         void* stream) {
   BN_CHECK_C(C);
-  static float* totals = nullptr;      // [2 * 2048] scratch for the table sum
-  if (totals == nullptr) PMD_CHECK_CUDA(cudaMalloc(&totals, 2 * 2048 * sizeof(float)));
+  // [2 * 2048] scratch for the table sum: one buffer per device, allocated on that device's first call and
+  // released when the library is unloaded
+  float** slot = g_bwd_apply_scratch.slots.get();
+  if (slot == nullptr) return -1;
+  if (*slot == nullptr) PMD_CHECK_CUDA(cudaMalloc(slot, 2 * 2048 * sizeof(float)));
+  float* totals = *slot;
   sum_tables_kernel<<<ceil_div(2 * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_sums_ranks, world, 2 * C, totals);
   count_launch();
   PmdBnBranch b{};

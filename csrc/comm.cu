@@ -10,7 +10,7 @@
 // always in rank order 0..W-1, so all ranks compute bitwise-identical results.
 #include "common.cuh"
 #include "sgd_math.cuh"
-#include "sym.cuh"
+#include "sync_tail.cuh"
 
 namespace pmd {
 namespace {
@@ -154,77 +154,27 @@ __global__ void __launch_bounds__(512) broadcast_kernel(PmdSym s, unsigned long 
 }
 
 // ------------------------------------------------------------------ tiny exchanges
-__global__ void bn_finalize_sync_kernel(PmdSym s, int slot, unsigned long long stats_off, float count_per_rank, int C,
-                                        const float* __restrict__ gamma, const float* __restrict__ beta,
-                                        float* running_mean, float* running_var, long long* num_batches,
-                                        float momentum, float eps, float* scale, float* shift, float* save_mean,
-                                        float* save_invstd) {
-  rank_barrier(s, slot, false);
-  if (threadIdx.x == 0 && num_batches != nullptr) *num_batches += 1;
-  const float n = count_per_rank * s.world;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    float s1 = 0.f, s2 = 0.f;
-    for (int w = 0; w < s.world; ++w) {
-      const float* st = heap_ptr<const float>(s, w, stats_off);
-      s1 += ld_peer_f(st + c);
-      s2 += ld_peer_f(st + C + c);
-    }
-    const float mean = s1 / n;
-    const float var = fmaxf(s2 / n - mean * mean, 0.f);
-    const float invstd = rsqrtf(var + eps);
-    const float a = gamma[c] * invstd;
-    scale[c] = a;
-    shift[c] = beta[c] - mean * a;
-    save_mean[c] = mean;
-    save_invstd[c] = invstd;
-    if (running_mean != nullptr) {
-      const float unbiased = var * (n / fmaxf(n - 1.f, 1.f));
-      running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-      running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
-    }
-  }
-}
-
 __global__ void bn_finalize_push_kernel(PmdSym s, int slot, const float* __restrict__ stats, unsigned long long recv_off,
                                         float count_per_rank, int C, const float* __restrict__ gamma,
                                         const float* __restrict__ beta, float* running_mean, float* running_var,
                                         long long* num_batches, float momentum, float eps, float* scale, float* shift,
                                         float* save_mean, float* save_invstd) {
   extern __shared__ float tot[];     // [2C]
+  pdl_wait();
   ll_exchange_sum(s, slot, stats, 2 * C, recv_off, tot);
   if (threadIdx.x == 0 && num_batches != nullptr) *num_batches += 1;
   const float n = count_per_rank * s.world;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float mean = tot[c] / n;
-    const float var = fmaxf(tot[C + c] / n - mean * mean, 0.f);
-    const float invstd = rsqrtf(var + eps);
-    const float a = gamma[c] * invstd;
-    scale[c] = a;
-    shift[c] = beta[c] - mean * a;
-    save_mean[c] = mean;
-    save_invstd[c] = invstd;
-    if (running_mean != nullptr) {
-      const float unbiased = var * (n / fmaxf(n - 1.f, 1.f));
-      running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-      running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
-    }
-  }
+  for (int c = threadIdx.x; c < C; c += blockDim.x)
+    bn_finalize_channel(c, tot[c], tot[C + c], n, gamma, beta, running_mean, running_var, momentum, eps, scale, shift,
+                        save_mean, save_invstd);
 }
 
 __global__ void small_allreduce_push_kernel(PmdSym s, int slot, const float* __restrict__ local, int n,
                                             unsigned long long recv_off, float* total) {
   extern __shared__ float tot[];
+  pdl_wait();
   ll_exchange_sum(s, slot, local, n, recv_off, tot);
   for (int i = threadIdx.x; i < n; i += blockDim.x) total[i] = tot[i];
-}
-
-__global__ void small_allreduce_sync_kernel(PmdSym s, int slot, unsigned long long off, int n, float* total) {
-  rank_barrier(s, slot, false);
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    float acc = 0.f;
-    for (int w = 0; w < s.world; ++w) acc += ld_peer_f(heap_ptr<const float>(s, w, off) + i);
-    total[i] = acc;
-  }
 }
 
 __global__ void metric_allreduce_kernel(PmdSym s, int slot, unsigned long long off, double* total) {
@@ -321,29 +271,6 @@ extern "C" PMD_API int pmd_broadcast(const PmdSym* sym, unsigned long long off, 
   return 0;
 }
 
-extern "C" PMD_API int pmd_bn_finalize_sync(const PmdSym* sym, int slot, unsigned long long stats_off,
-                                            float count_per_rank, int C, const float* d_gamma, const float* d_beta,
-                                            float* d_running_mean, float* d_running_var, long long* d_num_batches,
-                                            float momentum, float eps, float* d_scale, float* d_shift, float* d_mean,
-                                            float* d_invstd, void* stream) {
-  SYM_CHECK(sym);
-  bn_finalize_sync_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      *sym, slot, stats_off, count_per_rank, C, d_gamma, d_beta, d_running_mean, d_running_var, d_num_batches, momentum,
-      eps, d_scale, d_shift, d_mean, d_invstd);
-  count_launch();
-  PMD_LAUNCH_CHECK();
-  return 0;
-}
-
-extern "C" PMD_API int pmd_small_allreduce_sync(const PmdSym* sym, int slot, unsigned long long off, int n,
-                                                float* d_total, void* stream) {
-  SYM_CHECK(sym);
-  small_allreduce_sync_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(*sym, slot, off, n, d_total);
-  count_launch();
-  PMD_LAUNCH_CHECK();
-  return 0;
-}
-
 extern "C" PMD_API int pmd_metric_allreduce(const PmdSym* sym, int slot, unsigned long long off, double* d_total,
                                             void* stream) {
   SYM_CHECK(sym);
@@ -360,9 +287,9 @@ extern "C" PMD_API int pmd_bn_finalize_push(const PmdSym* sym, int slot, const f
                                             float* d_invstd, void* stream) {
   SYM_CHECK(sym);
   PMD_REQUIRE(2 * C * 4 <= 48 * 1024, "too many channels for the push exchange");
-  bn_finalize_push_kernel<<<1, 512, 2 * C * 4, static_cast<cudaStream_t>(stream)>>>(
-      *sym, slot, d_stats, recv_off, count_per_rank, C, d_gamma, d_beta, d_running_mean, d_running_var, d_num_batches,
-      momentum, eps, d_scale, d_shift, d_mean, d_invstd);
+  PMD_CHECK_CUDA(launch_pdl(bn_finalize_push_kernel, dim3(1), dim3(512), 2 * C * 4, static_cast<cudaStream_t>(stream), *sym,
+                            slot, d_stats, recv_off, count_per_rank, C, d_gamma, d_beta, d_running_mean, d_running_var,
+                            d_num_batches, momentum, eps, d_scale, d_shift, d_mean, d_invstd));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
@@ -372,8 +299,8 @@ extern "C" PMD_API int pmd_small_allreduce_push(const PmdSym* sym, int slot, con
                                                 unsigned long long recv_off, float* d_total, void* stream) {
   SYM_CHECK(sym);
   PMD_REQUIRE(n * 4 <= 48 * 1024, "vector too long for the push exchange");
-  small_allreduce_push_kernel<<<1, 512, n * 4, static_cast<cudaStream_t>(stream)>>>(*sym, slot, d_local, n, recv_off,
-                                                                                  d_total);
+  PMD_CHECK_CUDA(launch_pdl(small_allreduce_push_kernel, dim3(1), dim3(512), n * 4, static_cast<cudaStream_t>(stream), *sym,
+                            slot, d_local, n, recv_off, d_total));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

@@ -54,6 +54,22 @@ const char* last_error_cstr();
 extern unsigned long long g_launch_count;
 inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
 
+// Host-side per-device state (function attributes already set, cached scratch pointers, SM counts): the C ABI may be
+// driven on several GPUs from one process, so "did this once" has to be keyed by the current device.
+// get() returns the zero-initialised slot of the current device (nullptr if the device cannot be determined).
+template <typename T, int kMaxDevices = 64>
+struct PerDevice {
+  T slot[kMaxDevices] = {};
+  T* get() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+      set_error("cannot determine the current CUDA device (or ordinal >= 64)");
+      return nullptr;
+    }
+    return &slot[dev];
+  }
+};
+
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }
 

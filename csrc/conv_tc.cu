@@ -332,450 +332,14 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
   __syncthreads();
   if (threadIdx.x == 0) trace_mark(p, kTrExit);
   if (warp == 1) tmem_dealloc<BN>(tmem_base);
+  // multi-rank SyncBatchNorm: the last CTA of the grid exchanges the finished vector with the peers (sync_tail.cuh);
+  // the pipeline buffers are idle by now (every TMA store has been read), so they serve as scratch
+  if (p.tail.mode != 0)
+    sync_tail_run(p.tail, RED ? p.red_sums : p.stats, nullptr, nullptr, reinterpret_cast<float*>(smem),
+                  gridDim.x * gridDim.y * gridDim.z);
 }
 
-// ============================================================================ fprop / dgrad, persistent
-// Same math as conv_gemm_kernel, restructured so that the fixed per-CTA costs (barrier init, TMEM
-// allocation, first-load latency, epilogue) are paid once per SM instead of once per tile: each CTA loops
-// over tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...; the TMA ring runs continuously across tile
-// boundaries; the accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile j
-// (tcgen05.ld -> bf16 -> smem -> TMA store + BN statistics) overlaps the MMAs of tile j+1.
-template <int STAGES>
-struct PersistBars {
-  uint64_t full[STAGES];
-  uint64_t empty[STAGES];
-  uint64_t tmem_full[2];
-  uint64_t tmem_empty[2];
-  uint32_t tmem_base;
-};
-
-struct TileCoord {
-  int cls, ntile, w0, h0, n0, kb0, nkb;
-};
-
-__device__ __forceinline__ TileCoord decode_tile(const ConvGemmParams& p, int t, int bn) {
-  TileCoord c;
-  const int ntiles_n = p.out_channels / bn;
-  const int pix_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
-  c.ntile = t % ntiles_n;          // channel tiles of one pixel brick are adjacent: they share the A loads in L2
-  int r = t / ntiles_n;
-  const int pt = r % pix_tiles;
-  c.cls = r / pix_tiles;
-  const int tw = pt % p.tiles_w;
-  const int th = (pt / p.tiles_w) % p.tiles_h;
-  const int tn = pt / (p.tiles_w * p.tiles_h);
-  c.w0 = tw * p.w_box;
-  c.h0 = th * p.h_box;
-  c.n0 = tn * p.n_box;
-  c.kb0 = p.kb_begin[c.cls];
-  c.nkb = p.kb_count[c.cls];
-  return c;
-}
-
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(kThreads) conv_gemm_persistent_kernel(const __grid_constant__ ConvGemmParams p,
-                                                                       int total_tiles) {
-  constexpr int kStageBytes = kABytes + BN * 128;
-  constexpr int kStagingBytes = (BN / 64) * kABytes;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = align_smem_1024(smem_raw);
-  uint8_t* stage_out = smem + STAGES * kStageBytes;
-  PersistBars<STAGES>* bars = reinterpret_cast<PersistBars<STAGES>*>(stage_out + kStagingBytes);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-  if (threadIdx.x == 0) {
-    trace_begin(p, (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x));
-#pragma unroll
-    for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&bars->full[s], 1);
-      mbar_init(&bars->empty[s], 1);
-    }
-    mbar_init(&bars->tmem_full[0], 1);
-    mbar_init(&bars->tmem_full[1], 1);
-    mbar_init(&bars->tmem_empty[0], 128);
-    mbar_init(&bars->tmem_empty[1], 128);
-    fence_mbar_init();
-    prefetch_tmap(&p.a[0]);
-    prefetch_tmap(&p.b[0]);
-    prefetch_tmap(&p.out[0]);
-  }
-  if (warp == 1) tmem_alloc<2 * BN>(&bars->tmem_base);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = bars->tmem_base;
-  if (threadIdx.x == 0) trace_mark(p, kTrSetup);
-  pdl_wait();        // everything above is private to this CTA; operands below come from the previous kernel
-
-  if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const TileCoord c = decode_tile(p, t, BN);
-        for (int i = 0; i < c.nkb; ++i, ++it) {
-          const int s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
-          mbar_wait(&bars->empty[s], ph ^ 1u);
-          const KBlock kb = p.kb[c.kb0 + i];
-          uint8_t* sa = smem + s * kStageBytes;
-          uint8_t* sb = sa + kABytes;
-          mbar_expect_tx(&bars->full[s], kStageBytes);
-          tma_load_4d(&p.a[kb.a_map], &bars->full[s], sa, kb.a_ch, c.w0 + kb.dw, c.h0 + kb.dh, c.n0);
-          if (p.b_tap_last)
-            tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, c.ntile * BN, kb.tap);
-          else
-            tma_load_3d(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, kb.tap, c.ntile * BN);
-          if (it == 0) trace_mark(p, kTrFirstLoad);
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, false);
-      uint32_t it = 0, jm = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const TileCoord c = decode_tile(p, t, BN);
-        if (c.nkb == 0) continue;
-        const uint32_t acc = jm & 1, use = jm >> 1;
-        mbar_wait(&bars->tmem_empty[acc], (use & 1) ^ 1u);     // epilogue has drained this accumulator
-        tc_fence_after();
-        const uint32_t d_addr = tmem_base + acc * BN;
-        for (int i = 0; i < c.nkb; ++i, ++it) {
-          const int s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
-          mbar_wait(&bars->full[s], ph);
-          tc_fence_after();
-          if (it == 0) trace_mark(p, kTrFirstFull);
-          const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
-          const uint32_t b_addr = a_addr + kABytes;
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            umma_bf16(d_addr, make_smem_desc_sw128(a_addr + k * 32, 16, 1024),
-                      make_smem_desc_sw128(b_addr + k * 32, 16, 1024), idesc, (i | k) != 0 ? 1u : 0u);
-          }
-          umma_commit(&bars->empty[s]);
-        }
-        umma_commit(&bars->tmem_full[acc]);
-        if (jm == 0) trace_mark(p, kTrMmaIssued);
-        ++jm;
-      }
-    }
-  } else {
-    // ------------------------------------------------------------------ epilogue (128 threads)
-    const int q = warp & 3;
-    const int row = q * 32 + lane;
-    const int wi = row % p.w_box;
-    const int hi = (row / p.w_box) % p.h_box;
-    const int ni = row / (p.w_box * p.h_box);
-    const int et = threadIdx.x - 64;
-    uint32_t jm = 0;
-    bool store_pending = false;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const TileCoord c = decode_tile(p, t, BN);
-      const bool valid = (c.w0 + wi < p.GW[c.cls]) && (c.h0 + hi < p.GH[c.cls]) && (c.n0 + ni < p.N);
-      const __nv_bfloat16* add_row = nullptr;
-      if (p.addend != nullptr && valid) {
-        const long long pix =
-            (static_cast<long long>(c.n0 + ni) * p.GH[c.cls] + (c.h0 + hi)) * p.GW[c.cls] + (c.w0 + wi);
-        add_row = p.addend + pix * p.out_channels + c.ntile * BN;
-      }
-      const uint32_t acc = jm & 1, use = jm >> 1;
-      if (c.nkb > 0) {
-        mbar_wait(&bars->tmem_full[acc], use & 1);
-        tc_fence_after();
-      }
-      if (et == 0 && jm == 0) trace_mark(p, kTrAccReady);
-      // the previous tile's TMA store must have finished reading the staging buffer (and every thread must
-      // have finished its statistics pass over it) before anybody overwrites it
-      if (et == 0 && store_pending) tma_store_wait_read0();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-#pragma unroll
-      for (int hf = 0; hf < BN / 64; ++hf) {
-#pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          uint32_t v[32];
-          if (c.nkb > 0) {
-            tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + hf * 64 + cc * 32, v);
-            tmem_ld_wait();
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = 0u;
-          }
-          uint32_t packed[16];
-          if (add_row != nullptr) {
-            const uint4* ap = reinterpret_cast<const uint4*>(add_row + hf * 64 + cc * 32);
-#pragma unroll
-            for (int jj = 0; jj < 4; ++jj) {
-              const uint4 a4 = ap[jj];
-              const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float2 af = unpack_bf16x2(aw[e]);
-                packed[jj * 4 + e] = pack_bf16x2(__uint_as_float(v[jj * 8 + e * 2]) + af.x,
-                                                 __uint_as_float(v[jj * 8 + e * 2 + 1]) + af.y);
-              }
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              packed[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-          }
-          if (!valid) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) packed[j] = 0u;
-          }
-          uint8_t* rowp = stage_out + hf * kABytes + row * 128;
-#pragma unroll
-          for (int jj = 0; jj < 4; ++jj) {
-            const int chunk = (cc * 4 + jj) ^ (row & 7);
-            *reinterpret_cast<uint4*>(rowp + chunk * 16) =
-                make_uint4(packed[jj * 4], packed[jj * 4 + 1], packed[jj * 4 + 2], packed[jj * 4 + 3]);
-          }
-        }
-      }
-      if (c.nkb > 0) {
-        // all of this thread's TMEM reads have completed (tcgen05.wait::ld above): release the accumulator
-        tc_fence_before();
-        mbar_arrive(&bars->tmem_empty[acc]);
-        ++jm;
-      }
-      fence_proxy_async_smem();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (et == 0 && !store_pending) trace_mark(p, kTrStaged);
-      if (et == 0) {
-#pragma unroll
-        for (int hf = 0; hf < BN / 64; ++hf)
-          tma_store_4d(&p.out[c.cls], stage_out + hf * kABytes, c.ntile * BN + hf * 64, c.w0, c.h0, c.n0);
-        tma_store_commit();
-      }
-      store_pending = true;
-      if (p.stats != nullptr) {
-        const int ch = et & 63, rh = et >> 6;
-#pragma unroll
-        for (int hf = 0; hf < BN / 64; ++hf) {
-          float s1 = 0.f, s2 = 0.f;
-          const uint8_t* base = stage_out + hf * kABytes;
-#pragma unroll 8
-          for (int r = rh * 64; r < rh * 64 + 64; ++r) {
-            const __nv_bfloat16 hv =
-                *reinterpret_cast<const __nv_bfloat16*>(base + r * 128 + (((ch >> 3) ^ (r & 7)) << 4) + (ch & 7) * 2);
-            const float f = __bfloat162float(hv);
-            s1 += f;
-            s2 += f * f;
-          }
-          red_add_f32(p.stats + c.ntile * BN + hf * 64 + ch, s1);
-          red_add_f32(p.stats + p.out_channels + c.ntile * BN + hf * 64 + ch, s2);
-        }
-      }
-    }
-    if (et == 0 && store_pending) tma_store_wait_read0();
-    if (et == 0) trace_mark(p, kTrEpiDone);       // end of the LAST tile's epilogue
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (threadIdx.x == 0) trace_mark(p, kTrExit);
-  if (warp == 1) tmem_dealloc<2 * BN>(tmem_base);
-}
-
-// ============================================================================ fprop / dgrad with column patches
-// For a 3x3 stride-1 convolution the nine per-tap A bricks of a tile overlap almost entirely: fetching each of
-// them separately reads the activations nine times from L2, and ncu shows these kernels sitting at the L2->SM
-// read-bandwidth limit.  Here the CTA's output tile is 8 (w) x 16 (h) pixels and, per 64-channel chunk, THREE TMA
-// boxes of 8 x 18 pixels are loaded -- one per horizontal tap offset s (columns w0+s-1 .. w0+s+6, rows h0-1 ..
-// h0+16).  In such a patch a pixel row is exactly one 8-row swizzle atom (1024 B), so the A operand of tap (r, s)
-// is the ordinary K-major SW128 tile that starts r atoms into patch s: start = patch_s + r * 1024, SBO = 1024.
-// Every start stays 1024-byte aligned (an earlier single-patch variant with 128-byte-shifted starts gave wrong
-// results, see profiles/r1_conv_variants.md).  Activation traffic drops from 9 x 16 KB to 3 x 18 KB per chunk.
-// Weights stream through their own ring, one (chunk, tap) slice per stage.
-template <int A_STAGES, int B_STAGES>
-struct HaloBars {
-  uint64_t a_full[A_STAGES], a_empty[A_STAGES];
-  uint64_t b_full[B_STAGES], b_empty[B_STAGES];
-  uint64_t tmem_full;
-  uint32_t tmem_base;
-};
-constexpr int kColPatchBytes = 8 * 18 * 128;      // 18432: one horizontal offset
-constexpr int kHaloPatchBytes = 3 * kColPatchBytes;  // 55296: all three
-
-template <int BN, int A_STAGES, int B_STAGES>
-__global__ void __launch_bounds__(kThreads) conv_gemm_halo_kernel(const __grid_constant__ ConvHaloParams p) {
-  constexpr int kBBytes = BN * 128;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = align_smem_1024(smem_raw);
-  uint8_t* smem_b = smem + A_STAGES * kHaloPatchBytes;
-  HaloBars<A_STAGES, B_STAGES>* bars =
-      reinterpret_cast<HaloBars<A_STAGES, B_STAGES>*>(smem_b + B_STAGES * kBBytes);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ntile = blockIdx.y;
-  int t = blockIdx.x;
-  const int tw = t % p.tiles_w;
-  t /= p.tiles_w;
-  const int th = t % p.tiles_h;
-  const int n0 = t / p.tiles_h;
-  const int w0 = tw * 8, h0 = th * 16;
-
-  if (threadIdx.x == 0) {
-#pragma unroll
-    for (int s = 0; s < A_STAGES; ++s) {
-      mbar_init(&bars->a_full[s], 1);
-      mbar_init(&bars->a_empty[s], 1);
-    }
-#pragma unroll
-    for (int s = 0; s < B_STAGES; ++s) {
-      mbar_init(&bars->b_full[s], 1);
-      mbar_init(&bars->b_empty[s], 1);
-    }
-    mbar_init(&bars->tmem_full, 1);
-    fence_mbar_init();
-    prefetch_tmap(&p.a);
-    prefetch_tmap(&p.b);
-    prefetch_tmap(&p.out);
-  }
-  if (warp == 1) tmem_alloc<BN>(&bars->tmem_base);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = bars->tmem_base;
-  pdl_wait();
-
-  if (warp == 0) {
-    if (lane == 0) {
-      uint32_t ib = 0;
-      for (int c = 0; c < p.n_chunks; ++c) {
-        const int sa = c % A_STAGES;
-        mbar_wait(&bars->a_empty[sa], ((c / A_STAGES) & 1) ^ 1u);
-        mbar_expect_tx(&bars->a_full[sa], kHaloPatchBytes);
-#pragma unroll
-        for (int q = 0; q < 3; ++q)
-          tma_load_4d(&p.a, &bars->a_full[sa], smem + sa * kHaloPatchBytes + q * kColPatchBytes, c * 64, w0 + q - 1,
-                      h0 - 1, n0);
-        for (int tap = 0; tap < 9; ++tap, ++ib) {
-          const int sb = ib % B_STAGES;
-          mbar_wait(&bars->b_empty[sb], ((ib / B_STAGES) & 1) ^ 1u);
-          const int wtap = p.flip_taps ? 8 - tap : tap;
-          mbar_expect_tx(&bars->b_full[sb], kBBytes);
-          if (p.b_tap_last)
-            tma_load_3d(&p.b, &bars->b_full[sb], smem_b + sb * kBBytes, c * 64, ntile * BN, wtap);
-          else
-            tma_load_3d(&p.b, &bars->b_full[sb], smem_b + sb * kBBytes, c * 64, wtap, ntile * BN);
-        }
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, false);
-      uint32_t ib = 0;
-      for (int c = 0; c < p.n_chunks; ++c) {
-        const int sa = c % A_STAGES;
-        mbar_wait(&bars->a_full[sa], (c / A_STAGES) & 1);
-        tc_fence_after();
-        const uint32_t patch = smem_u32(smem + sa * kHaloPatchBytes);
-        for (int tap = 0; tap < 9; ++tap, ++ib) {
-          const int sb = ib % B_STAGES;
-          mbar_wait(&bars->b_full[sb], (ib / B_STAGES) & 1);
-          tc_fence_after();
-          const int r = tap / 3, q = tap % 3;
-          const uint32_t a_addr = patch + q * kColPatchBytes + r * 1024;
-          const uint32_t b_addr = smem_u32(smem_b + sb * kBBytes);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 32, 16, 1024),
-                      make_smem_desc_sw128(b_addr + k * 32, 16, 1024), idesc, (c | tap | k) != 0 ? 1u : 0u);
-          }
-          umma_commit(&bars->b_empty[sb]);
-        }
-        umma_commit(&bars->a_empty[sa]);
-      }
-      umma_commit(&bars->tmem_full);
-    }
-  } else {
-    const int q = warp & 3;
-    const int row = q * 32 + lane;          // = h_i * 8 + w_i
-    const int wi = row & 7, hi = row >> 3;
-    const bool valid = (w0 + wi < p.GW) && (h0 + hi < p.GH) && (n0 < p.N);
-    const __nv_bfloat16* add_row = nullptr;
-    if (p.addend != nullptr && valid) {
-      const long long pix = (static_cast<long long>(n0) * p.GH + (h0 + hi)) * p.GW + (w0 + wi);
-      add_row = p.addend + pix * p.out_channels + ntile * BN;
-    }
-    mbar_wait(&bars->tmem_full, 0);
-    tc_fence_after();
-    uint8_t* stage_out = smem;            // the patch ring is idle once every MMA has completed
-#pragma unroll
-    for (int hf = 0; hf < BN / 64; ++hf) {
-#pragma unroll
-      for (int cc = 0; cc < 2; ++cc) {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + hf * 64 + cc * 32, v);
-        tmem_ld_wait();
-        uint32_t packed[16];
-        if (add_row != nullptr) {
-          const uint4* ap = reinterpret_cast<const uint4*>(add_row + hf * 64 + cc * 32);
-#pragma unroll
-          for (int jj = 0; jj < 4; ++jj) {
-            const uint4 a4 = ap[jj];
-            const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float2 af = unpack_bf16x2(aw[e]);
-              packed[jj * 4 + e] = pack_bf16x2(__uint_as_float(v[jj * 8 + e * 2]) + af.x,
-                                               __uint_as_float(v[jj * 8 + e * 2 + 1]) + af.y);
-            }
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-        }
-        if (!valid) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) packed[j] = 0u;
-        }
-        uint8_t* rowp = stage_out + hf * kABytes + row * 128;
-#pragma unroll
-        for (int jj = 0; jj < 4; ++jj) {
-          const int chunk = (cc * 4 + jj) ^ (row & 7);
-          *reinterpret_cast<uint4*>(rowp + chunk * 16) =
-              make_uint4(packed[jj * 4], packed[jj * 4 + 1], packed[jj * 4 + 2], packed[jj * 4 + 3]);
-        }
-      }
-    }
-    fence_proxy_async_smem();
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    const int et = threadIdx.x - 64;
-    if (et == 0) {
-#pragma unroll
-      for (int hf = 0; hf < BN / 64; ++hf)
-        tma_store_4d(&p.out, stage_out + hf * kABytes, ntile * BN + hf * 64, w0, h0, n0);
-      tma_store_commit();
-    }
-    if (p.stats != nullptr) {
-      const int ch = et & 63, rh = et >> 6;
-#pragma unroll
-      for (int hf = 0; hf < BN / 64; ++hf) {
-        float s1 = 0.f, s2 = 0.f;
-        const uint8_t* base = stage_out + hf * kABytes;
-#pragma unroll 8
-        for (int r = rh * 64; r < rh * 64 + 64; ++r) {
-          const __nv_bfloat16 hv =
-              *reinterpret_cast<const __nv_bfloat16*>(base + r * 128 + (((ch >> 3) ^ (r & 7)) << 4) + (ch & 7) * 2);
-          const float f = __bfloat162float(hv);
-          s1 += f;
-          s2 += f * f;
-        }
-        red_add_f32(p.stats + ntile * BN + hf * 64 + ch, s1);
-        red_add_f32(p.stats + p.out_channels + ntile * BN + hf * 64 + ch, s2);
-      }
-    }
-    if (et == 0) tma_store_wait_read0();
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc<BN>(tmem_base);
-}
+constexpr int kColPatchBytes = 8 * 18 * 128;      // 18432: one 8 x 18-pixel column patch (64 channels)
 
 // ============================================================================ 3x3, C = K = 64: weights resident
 // The 64-channel 3x3 layers (32x32 maps) are the worst case for the per-tap kernel: a 128x64 tile needs only 36
@@ -785,8 +349,11 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_halo_kernel(const __grid_c
 //   * persistent: one CTA per SM walks tiles t = blockIdx.x, + gridDim.x, ...; barriers, TMEM and tensor maps are
 //     set up once;
 //   * the nine 64x64 weight slices (72 KB) are loaded ONCE per CTA and stay in shared memory;
-//   * activations arrive as column patches (see conv_gemm_halo_kernel): 3 x 18 KB per tile instead of 9 x 16 KB,
-//     through a ring of six patch slots that runs ahead across tile boundaries;
+//   * activations arrive as column patches: the CTA's output tile is 8 (w) x 16 (h) pixels and THREE TMA boxes of
+//     8 x 18 pixels are loaded, one per horizontal tap offset s (columns w0+s-1 .. w0+s+6, rows h0-1 .. h0+16).  In
+//     such a patch a pixel row is exactly one 8-row swizzle atom (1024 B), so the A operand of tap (r, s) is the
+//     ordinary K-major SW128 tile that starts r atoms into patch s (every start stays 1024-byte aligned).  3 x 18 KB
+//     per tile instead of 9 x 16 KB, through a ring of six patch slots that runs ahead across tile boundaries;
 //   * two accumulators in TMEM and TWO epilogue warpgroups (tiles alternate between them), each with its own
 //     staging buffer, so tcgen05.ld -> bf16 -> smem -> TMA store of tile j overlaps the MMAs of tiles j+1, j+2;
 //   * BatchNorm statistics are accumulated in registers over all tiles of the CTA and leave as 128 red.global
@@ -806,7 +373,7 @@ struct ResBars {
 constexpr int kResSmem = kResWBytes + kResSlots * kColPatchBytes + 2 * kABytes + sizeof(ResBars) + 1024;
 
 template <bool B_MN>
-__global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __grid_constant__ ConvHaloParams p,
+__global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __grid_constant__ ConvResidentParams p,
                                                                        int total_tiles) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
@@ -1045,6 +612,8 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
   __syncthreads();
   if (threadIdx.x == 0 && tracing) trec[kRtExit] = clock64();
   if (warp == 1) tmem_dealloc<128>(tmem_base);
+  if (p.tail.mode != 0)
+    sync_tail_run(p.tail, p.stats, nullptr, nullptr, reinterpret_cast<float*>(smem_out), gridDim.x);
 }
 
 // ============================================================================ wgrad
@@ -1171,7 +740,7 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
 // fetched once per tap (9 x 8 KB) and the small dy tile (8 KB) cannot amortise it (layer1: 786 MB through L2 = the
 // whole 78 us).  Here a CTA owns one 64-channel chunk of C, one 64-channel chunk of K and ALL nine taps: per 8x8-pixel
 // tile it loads three column patches of x (8 w x 10 h pixels, one per horizontal tap offset, as in
-// conv_gemm_halo_kernel) and one dy tile -- 38 KB instead of 96 KB -- and issues five M=128 MMAs per 16 pixels, each
+// conv3x3_resident_kernel) and one dy tile -- 38 KB instead of 96 KB -- and issues five M=128 MMAs per 16 pixels, each
 // covering two taps: the A descriptor is MN-major, so its two 64-row halves may sit anywhere in shared memory (LBO =
 // distance between the two tap views; a vertical tap offset is a whole 1024-byte swizzle atom, so every view starts
 // atom-aligned).  Five accumulators of 64 columns live in TMEM; tap order inside the accumulators is (s, r).
@@ -1639,117 +1208,74 @@ static int set_smem(Kernel k, int bytes) {
   return 0;
 }
 
-// ---------------------------------------------------------------------------- halo variant, host side
-static int build_halo_common(const PmdConvShape& s, int red_channels, int out_channels, const void* in, const void* w,
-                             bool w_rsck, void* outp, ConvHaloParams* o) {
-  PMD_REQUIRE(conv_halo_supported(s), "shape not eligible for the halo kernel");
-  ConvHaloParams& p = *o;
+// ---------------------------------------------------------------------------- weight-resident 3x3 kernel, host side
+static int build_resident_common(const PmdConvShape& s, const void* in, const void* w_krsc, void* outp,
+                                 ConvResidentParams* o) {
+  PMD_REQUIRE(conv_resident_supported(s), "shape not eligible for the weight-resident 3x3 kernel");
+  ConvResidentParams& p = *o;
   memset(&p, 0, sizeof(p));
-  p.n_chunks = red_channels / 64;
   p.tiles_w = s.W / 8;
   p.tiles_h = s.H / 16;
   p.N = s.N;
   p.GW = s.W;
   p.GH = s.H;
-  p.out_channels = out_channels;
-  p.bn_tile = (out_channels % 128 == 0) ? 128 : 64;
-  if (act_map(&p.a, in, s.N, s.H, s.W, red_channels, 1, 0, 0, 8, 18, 1)) return -1;
-  if (act_map(&p.out, outp, s.N, s.H, s.W, out_channels, 1, 0, 0, 8, 16, 1)) return -1;
-  if (!w_rsck) {   // KRSC: (c inner, tap, k)
-    const uint64_t dims[3] = {(uint64_t)s.C, 9ull, (uint64_t)s.K};
-    const uint64_t strides[2] = {(uint64_t)s.C * 2, 9ull * s.C * 2};
-    const uint32_t box[3] = {64u, 1u, (uint32_t)p.bn_tile};
-    if (encode_map(&p.b, w, 3, dims, strides, box)) return -1;
-  } else {         // RSCK: (k inner, c rows, tap)
-    const uint64_t dims[3] = {(uint64_t)s.K, (uint64_t)s.C, 9ull};
-    const uint64_t strides[2] = {(uint64_t)s.K * 2, (uint64_t)s.C * s.K * 2};
-    const uint32_t box[3] = {64u, (uint32_t)p.bn_tile, 1u};
-    if (encode_map(&p.b, w, 3, dims, strides, box)) return -1;
-  }
-  return 0;
+  p.out_channels = 64;
+  if (act_map(&p.a, in, s.N, s.H, s.W, 64, 1, 0, 0, 8, 18, 1)) return -1;
+  if (act_map(&p.out, outp, s.N, s.H, s.W, 64, 1, 0, 0, 8, 16, 1)) return -1;
+  const uint64_t dims[3] = {64ull, 9ull, 64ull};   // KRSC: (c inner, tap, k)
+  const uint64_t strides[2] = {64ull * 2, 9ull * 64 * 2};
+  const uint32_t box[3] = {64u, 1u, 64u};
+  return encode_map(&p.b, w_krsc, 3, dims, strides, box);
 }
 
-int build_fprop_halo_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
-                            ConvHaloParams* out) {
-  if (build_halo_common(s, s.C, s.K, x, w_krsc, false, y, out)) return -1;
-  out->b_tap_last = 0;
-  out->flip_taps = 0;
+int build_fprop_resident_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
+                                ConvResidentParams* out) {
+  if (build_resident_common(s, x, w_krsc, y, out)) return -1;
   out->stats = stats;
-  out->resident = conv_resident_enabled() && conv_resident_supported(s);
   return 0;
 }
 
-int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w, const void* addend, void* dx,
-                            ConvHaloParams* out, bool w_is_krsc) {
-  // same-size 3x3 stride-1: dx = conv(dy, flipped w), reduction over K, output channels C
-  PMD_REQUIRE(!w_is_krsc || conv_resident_supported(s), "KRSC weights: only the resident kernel reads them for dgrad");
-  if (build_halo_common(s, s.K, s.C, dy, w, !w_is_krsc, dx, out)) return -1;
-  out->b_tap_last = w_is_krsc ? 0 : 1;
-  out->b_mn = w_is_krsc ? 1 : 0;
-  out->resident = w_is_krsc ? 1 : 0;
+int build_dgrad_resident_params(const PmdConvShape& s, const void* dy, const void* w_krsc, const void* addend, void* dx,
+                                ConvResidentParams* out) {
+  // same-size 3x3 stride-1: dx = conv(dy, flipped w); the KRSC weights are consumed MN-major
+  if (build_resident_common(s, dy, w_krsc, dx, out)) return -1;
+  out->b_mn = 1;
   out->flip_taps = 1;
   out->addend = static_cast<const __nv_bfloat16*>(addend);
   return 0;
 }
 
 template <bool B_MN>
-static int launch_conv_resident_t(const ConvHaloParams& p, cudaStream_t stream) {
-  static bool once = false;
-  static int sms = 0;
-  if (!once) {
+static int launch_conv_resident_t(const ConvResidentParams& p, cudaStream_t stream) {
+  static PerDevice<int> sms_of;      // also marks "shared-memory attribute set on this device"
+  int* sms = sms_of.get();
+  if (sms == nullptr) return -1;
+  if (*sms == 0) {
     if (set_smem(conv3x3_resident_kernel<B_MN>, kResSmem)) return -1;
     int dev = 0;
     PMD_CHECK_CUDA(cudaGetDevice(&dev));
-    PMD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    once = true;
+    PMD_CHECK_CUDA(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, dev));
   }
   const int total = p.tiles_w * p.tiles_h * p.N;
-  const int grid = total < sms ? total : sms;
+  const int grid = total < *sms ? total : *sms;
   PMD_CHECK_CUDA(launch_pdl(conv3x3_resident_kernel<B_MN>, dim3(grid), dim3(kResThreads), kResSmem, stream, p, total));
   return 0;
 }
 
-template <int BN, int AS, int BS>
-static int launch_conv_halo_t(const ConvHaloParams& p, cudaStream_t stream) {
-  constexpr int smem = AS * kHaloPatchBytes + BS * BN * 128 + sizeof(HaloBars<AS, BS>) + 1024;
-  static bool once = false;
-  if (!once) {
-    if (set_smem(conv_gemm_halo_kernel<BN, AS, BS>, smem)) return -1;
-    once = true;
-  }
-  const dim3 grid(p.tiles_w * p.tiles_h * p.N, p.out_channels / BN, 1);
-  PMD_CHECK_CUDA(launch_pdl(conv_gemm_halo_kernel<BN, AS, BS>, grid, dim3(kThreads), smem, stream, p));
-  return 0;
-}
-
-int launch_conv_halo(const ConvHaloParams& p_in, cudaStream_t stream) {
-  ConvHaloParams p_traced;
+int launch_conv_resident(const ConvResidentParams& p_in, cudaStream_t stream) {
+  ConvResidentParams p_traced;
   if (g_trace_buf != nullptr) {
     p_traced = p_in;
     p_traced.trace = g_trace_buf;
     p_traced.trace_cap = g_trace_cap;
   }
-  const ConvHaloParams& p = g_trace_buf != nullptr ? p_traced : p_in;
-  if (p.resident) {
-    if ((p.b_mn ? launch_conv_resident_t<true>(p, stream) : launch_conv_resident_t<false>(p, stream)) != 0) return -1;
-    count_launch();
-    PMD_LAUNCH_CHECK();
-    return 0;
-  }
-  // one 54 KB patch stage + 32 KB of weight slices = 86 KB -> 2 CTAs per SM (their phases interleave)
-  const int rc = p.bn_tile == 64 ? launch_conv_halo_t<64, 1, 4>(p, stream) : launch_conv_halo_t<128, 1, 2>(p, stream);
-  if (rc != 0) return -1;
+  const ConvResidentParams& p = g_trace_buf != nullptr ? p_traced : p_in;
+  if ((p.b_mn ? launch_conv_resident_t<true>(p, stream) : launch_conv_resident_t<false>(p, stream)) != 0) return -1;
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
 }
 
-// PMD_CONV_HALO: 0 = never (default), 1 = fprop and dgrad, 2 = dgrad only.  The variant is correct but, measured
-// inside the training step, slower than per-tap loads (profiles/r1_conv_variants.md), so it is opt-in.
-int conv_halo_mode() {
-  static const int mode = getenv("PMD_CONV_HALO") == nullptr ? 0 : atoi(getenv("PMD_CONV_HALO"));
-  return mode;
-}
 // PMD_CONV_RESIDENT: 2 (default) fprop only, 1 fprop and dgrad, 0 off, 3 dgrad only.  In the training step the
 // dgrad runs beside the wgrad of the same layer (side stream); a CTA that owns a whole SM's shared memory cannot
 // share SMs with those, and the lost overlap costs more than the faster kernel gains (1.941 vs 1.918 ms/step).
@@ -1759,16 +1285,16 @@ static int conv_resident_mode() {
 }
 bool conv_resident_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 2; }
 bool conv_resident_dgrad_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 3; }
-bool conv_halo_enabled() { return conv_halo_mode() == 1; }
-bool conv_halo_dgrad_enabled() { return conv_halo_mode() >= 1; }
 
 template <int BN, int ST, bool B_MN = false, bool RED = false>
 static int launch_conv_gemm_t(const ConvGemmParams& p, const dim3& grid, cudaStream_t stream) {
   constexpr int smem = ST * (kABytes + BN * 128) + sizeof(PipeBars<ST>) + 16 + (RED ? sizeof(RedExtra<BN>) : 0) + 1024;
-  static bool once = false;
-  if (!once) {
+  static PerDevice<bool> ready;
+  bool* once = ready.get();
+  if (once == nullptr) return -1;
+  if (!*once) {
     if (set_smem(conv_gemm_kernel<BN, ST, B_MN, RED>, smem)) return -1;
-    once = true;
+    *once = true;
   }
   PMD_CHECK_CUDA(launch_pdl(conv_gemm_kernel<BN, ST, B_MN, RED>, grid, dim3(kThreads), smem, stream, p));
   return 0;
@@ -1781,30 +1307,6 @@ static int stages_from_env(const char* name, int dflt) {
   if (v == nullptr) return dflt;
   const int s = atoi(v);
   return (s >= 2 && s <= 4) ? s : dflt;
-}
-
-template <int BN, int ST>
-static int launch_conv_gemm_persistent_t(const ConvGemmParams& p, cudaStream_t stream) {
-  constexpr int smem = ST * (kABytes + BN * 128) + (BN / 64) * kABytes + sizeof(PersistBars<ST>) + 1024;
-  static int ctas_per_sm = 0, sms = 0;
-  if (ctas_per_sm == 0) {
-    if (set_smem(conv_gemm_persistent_kernel<BN, ST>, smem)) return -1;
-    int dev = 0;
-    PMD_CHECK_CUDA(cudaGetDevice(&dev));
-    PMD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    // (cudaOccupancyMaxActiveBlocksPerMultiprocessor answered 1 here -- it assumes the default carve-out -- which
-    // left two thirds of every SM idle in the first measurements; compute the residency directly.)
-    PMD_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_persistent_kernel<BN, ST>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                        cudaSharedmemCarveoutMaxShared));
-    const int by_smem = (227 * 1024) / (smem + 1024);
-    const int by_tmem = 512 / (2 * BN);          // each CTA owns 2*BN TMEM columns of the SM's 512
-    ctas_per_sm = by_smem < by_tmem ? by_smem : by_tmem;
-    if (ctas_per_sm < 1) ctas_per_sm = 1;
-  }
-  const int total = p.tiles_w * p.tiles_h * p.tiles_n * (p.out_channels / BN) * p.n_classes;
-  const int grid = total < ctas_per_sm * sms ? total : ctas_per_sm * sms;
-  PMD_CHECK_CUDA(launch_pdl(conv_gemm_persistent_kernel<BN, ST>, dim3(grid), dim3(kThreads), smem, stream, p, total));
-  return 0;
 }
 
 // PMD_DGRAD_BN_REDUCE=0 keeps the stand-alone reduction kernels.
@@ -1838,21 +1340,11 @@ int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
   }
   const ConvGemmParams& p = g_trace_buf != nullptr ? p_traced : p_in;
   const dim3 grid(p.tiles_w * p.tiles_h * p.tiles_n, p.out_channels / p.bn_tile, p.n_classes);
-  // Measured on B200 (profiles/r1_conv_variants.md): one tile per CTA with 2 resident CTAs per SM beats the
-  // persistent double-buffered variant on these shapes, so the latter is opt-in (PMD_GEMM_PERSISTENT=1).
+  // One tile per CTA with 2-4 resident CTAs per SM (a persistent double-buffered variant measured slower on these
+  // shapes, profiles/r1_conv_variants.md, and was removed).  PMD_GEMM64_STAGES / PMD_GEMM128_STAGES in {2,3,4}.
   static const int st64 = stages_from_env("PMD_GEMM64_STAGES", 2), st128 = stages_from_env("PMD_GEMM128_STAGES", 3);
-  static const bool persistent = getenv("PMD_GEMM_PERSISTENT") != nullptr && atoi(getenv("PMD_GEMM_PERSISTENT")) != 0;
-  // Layers whose tiles need only one or two k-blocks (the im2col'ed stem, 1x1 convolutions on 64-128 channels) are
-  // all set-up and epilogue in the one-tile-per-CTA kernel; PMD_GEMM_PERSISTENT_SMALL=1 sends them to the persistent
-  // kernel, whose TMA ring and TMEM double buffer run across tile boundaries.
-  static const bool persistent_small =
-      getenv("PMD_GEMM_PERSISTENT_SMALL") != nullptr && atoi(getenv("PMD_GEMM_PERSISTENT_SMALL")) != 0;
-  bool small = persistent_small && !p.b_mn_major && p.bn_tile != 256;
-  for (int c = 0; c < p.n_classes && small; ++c) small = p.kb_count[c] <= 2;
   int rc;
-  if (small) {
-    rc = p.bn_tile == 64 ? launch_conv_gemm_persistent_t<64, 4>(p, stream) : launch_conv_gemm_persistent_t<128, 3>(p, stream);
-  } else if (p.b_mn_major && p.bn_reduce) {
+  if (p.b_mn_major && p.bn_reduce) {
     rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true, true>(p, grid, stream)
                          : launch_conv_gemm_t<128, 3, true, true>(p, grid, stream);
   } else if (p.b_mn_major) {
@@ -1861,15 +1353,6 @@ int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
                                              : launch_conv_gemm_t<256, 2, true>(p, grid, stream));
   } else if (p.bn_tile == 256) {
     rc = launch_conv_gemm_t<256, 2>(p, grid, stream);
-  } else if (persistent) {
-    if (p.bn_tile == 64)
-      rc = st64 == 2 ? launch_conv_gemm_persistent_t<64, 2>(p, stream)
-                     : (st64 == 4 ? launch_conv_gemm_persistent_t<64, 4>(p, stream)
-                                  : launch_conv_gemm_persistent_t<64, 3>(p, stream));
-    else
-      rc = st128 == 4 ? launch_conv_gemm_persistent_t<128, 4>(p, stream)
-                      : (st128 == 3 ? launch_conv_gemm_persistent_t<128, 3>(p, stream)
-                                    : launch_conv_gemm_persistent_t<128, 2>(p, stream));
   } else if (p.bn_tile == 64) {
     rc = st64 == 2 ? launch_conv_gemm_t<64, 2>(p, grid, stream)
                    : (st64 == 3 ? launch_conv_gemm_t<64, 3>(p, grid, stream) : launch_conv_gemm_t<64, 4>(p, grid, stream));
@@ -1887,10 +1370,12 @@ template <int BNW, int ST, int MB = 1>
 static int launch_wgrad_t(const WgradParams& p, cudaStream_t stream) {
   constexpr int smem = ST * (2 * MB * 8192 + (BNW / 64) * 8192) + sizeof(PipeBars<ST>) + 1024;
   static_assert(smem <= 227 * 1024, "wgrad pipeline does not fit in shared memory");
-  static bool once = false;
-  if (!once) {
+  static PerDevice<bool> ready;
+  bool* once = ready.get();
+  if (once == nullptr) return -1;
+  if (!*once) {
     if (set_smem(conv_wgrad_kernel<BNW, ST, MB>, smem)) return -1;
-    once = true;
+    *once = true;
   }
   const dim3 grid(ceil_div(p.n_boxes, 2 * MB), p.K / BNW, p.split);
   PMD_CHECK_CUDA(launch_pdl(conv_wgrad_kernel<BNW, ST, MB>, grid, dim3(kThreads), smem, stream, p));
@@ -1902,10 +1387,12 @@ static int launch_wgrad_t(const WgradParams& p, cudaStream_t stream) {
 static int launch_wgrad_patch(const WgradParams& p, cudaStream_t stream) {
   constexpr int ST = 4;
   constexpr int smem = ST * kWPatchStage + sizeof(PipeBars<ST>) + 1024;
-  static bool once = false;
-  if (!once) {
+  static PerDevice<bool> ready;
+  bool* once = ready.get();
+  if (once == nullptr) return -1;
+  if (!*once) {
     if (set_smem(conv_wgrad_patch_kernel<ST>, smem)) return -1;
-    once = true;
+    *once = true;
   }
   const dim3 grid(p.C / 64, p.K / 64, p.split);
   PMD_CHECK_CUDA(launch_pdl(conv_wgrad_patch_kernel<ST>, grid, dim3(kThreads), smem, stream, p));
@@ -1933,10 +1420,10 @@ using namespace pmd;
 
 extern "C" PMD_API int pmd_conv_fprop(const PmdConvShape* s, const void* d_x, const void* d_w_krsc, void* d_y, float* d_stats,
                               void* stream) {
-  if ((conv_halo_enabled() && conv_halo_supported(*s)) || (conv_resident_enabled() && conv_resident_supported(*s))) {
-    ConvHaloParams hp;
-    if (build_fprop_halo_params(*s, d_x, d_w_krsc, d_y, d_stats, &hp)) return -1;
-    return launch_conv_halo(hp, static_cast<cudaStream_t>(stream));
+  if (conv_resident_enabled() && conv_resident_supported(*s)) {
+    ConvResidentParams hp;
+    if (build_fprop_resident_params(*s, d_x, d_w_krsc, d_y, d_stats, &hp)) return -1;
+    return launch_conv_resident(hp, static_cast<cudaStream_t>(stream));
   }
   ConvGemmParams p;
   if (build_fprop_params(*s, d_x, d_w_krsc, d_y, d_stats, &p)) return -1;
@@ -1952,11 +1439,6 @@ extern "C" PMD_API int pmd_conv_set_trace(void* d_buf, int cap_ctas) {
 extern "C" PMD_API int pmd_conv_dgrad(const PmdConvShape* s, const void* d_dy, const void* d_w_rsck, const PmdConvShape* s2,
                               const void* d_dy2, const void* d_w2_rsck, const void* d_addend, void* d_dx,
                               void* stream) {
-  if (conv_halo_dgrad_enabled() && conv_halo_supported(*s) && s2 == nullptr) {
-    ConvHaloParams hp;
-    if (build_dgrad_halo_params(*s, d_dy, d_w_rsck, d_addend, d_dx, &hp)) return -1;
-    return launch_conv_halo(hp, static_cast<cudaStream_t>(stream));
-  }
   ConvGemmParams p;
   if (build_dgrad_params(*s, d_dy, d_w_rsck, s2, d_dy2, d_w2_rsck, d_addend, d_dx, &p)) return -1;
   return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
@@ -1966,9 +1448,9 @@ extern "C" PMD_API int pmd_conv_dgrad_krsc(const PmdConvShape* s, const void* d_
                                            const PmdConvShape* s2, const void* d_dy2, const void* d_w2_krsc,
                                            const void* d_addend, void* d_dx, void* stream) {
   if (s2 == nullptr && conv_resident_dgrad_enabled() && conv_resident_supported(*s)) {
-    ConvHaloParams hp;
-    if (build_dgrad_halo_params(*s, d_dy, d_w_krsc, d_addend, d_dx, &hp, true)) return -1;
-    return launch_conv_halo(hp, static_cast<cudaStream_t>(stream));
+    ConvResidentParams hp;
+    if (build_dgrad_resident_params(*s, d_dy, d_w_krsc, d_addend, d_dx, &hp)) return -1;
+    return launch_conv_resident(hp, static_cast<cudaStream_t>(stream));
   }
   ConvGemmParams p;
   if (build_dgrad_params(*s, d_dy, d_w_krsc, s2, d_dy2, d_w2_krsc, d_addend, d_dx, &p, true)) return -1;

@@ -3,6 +3,7 @@
 #pragma once
 
 #include "common.cuh"
+#include "sync_tail.cuh"
 #include "../include/pmdist.h"
 
 namespace pmd {
@@ -49,6 +50,9 @@ struct ConvGemmParams {
   const float *red_scale, *red_shift;    // forward affine (mask = scale*y + shift > 0)
   const float *red_mean, *red_invstd;
   float* red_sums;                       // [2 * out_channels], accumulated with red.global.add
+  // multi-rank SyncBatchNorm: the grid's last CTA (by arrival) completes the cross-GPU exchange of the vector this
+  // kernel accumulated (`stats` in fprop, `red_sums` in a RED dgrad) -- see sym.cuh.  tail.mode == 0: nothing.
+  SyncTail tail;
 };
 
 // Per-CTA trace record written by the fprop/dgrad kernels when tracing is on (tools/conv_trace.py decodes it).
@@ -97,23 +101,22 @@ inline bool conv_tc_supported(const PmdConvShape& s) {
   return s.C % 64 == 0 && s.K % 64 == 0 && (s.R == 1 || s.R == 3) && (s.stride == 1 || s.stride == 2);
 }
 
-// 3x3 stride-1 convolutions on maps with W % 8 == 0 and H % 16 == 0: the A operand of all nine taps comes from
-// three column patches per 64-channel chunk (see conv_gemm_halo_kernel), cutting L2->SM activation traffic 2.7x.
-struct ConvHaloParams {
+// 3x3 stride-1 convolutions with C = K = 64 on maps with W % 8 == 0 and H % 16 == 0 (the 32x32 stage):
+// conv3x3_resident_kernel -- persistent, weights resident in shared memory, activations as three column patches
+// per tile (L2->SM activation traffic 2.7x lower than per-tap boxes).
+struct ConvResidentParams {
   CUtensorMap a;       // input, box (64 ch, 8, 18, 1): one column patch
-  CUtensorMap b;       // weights (3-D, as in ConvGemmParams)
+  CUtensorMap b;       // KRSC weights (c, tap, k), box 64 x 1 x 64
   CUtensorMap out;     // output, box (64 ch, 8, 16, 1)
-  int n_chunks;        // reduction channels / 64
   int tiles_w, tiles_h, N, GW, GH;
-  int b_tap_last;      // 0: KRSC (fprop), 1: RSCK (dgrad)
   int flip_taps;       // dgrad: weight tap (2-r, 2-s) pairs with patch offset (r, s)
-  int b_mn;            // dgrad straight from the KRSC weights (MN-major B operand); resident kernel only
-  int resident;        // C = K = 64: persistent kernel with the weights resident in shared memory
-  int out_channels, bn_tile;
+  int b_mn;            // dgrad straight from the KRSC weights (MN-major B operand)
+  int out_channels;    // 64
   float* stats;
   const __nv_bfloat16* addend;
-  long long* trace;    // resident kernel: optional [trace_cap][kTraceSlots] per-CTA record (kRt* slots), else null
+  long long* trace;    // optional [trace_cap][kTraceSlots] per-CTA record (kRt* slots), else null
   int trace_cap;
+  SyncTail tail;       // optional: the grid's last CTA completes the SyncBatchNorm exchange of `stats`
 };
 // Trace record of conv3x3_resident_kernel: total cycles each role spent WAITING over all tiles of the CTA.
 enum {
@@ -126,20 +129,16 @@ enum {
   kRtEpiWaitStore = 7,    // epilogue group 0: waiting for the previous TMA store to release the staging buffer
   kRtExit = 8             // then kTrGlobalNs, kTrSm, kTrTiles as in the per-tile kernels
 };
-inline bool conv_halo_supported(const PmdConvShape& s) {
-  return conv_tc_supported(s) && s.R == 3 && s.stride == 1 && s.W % 8 == 0 && s.H % 16 == 0;
+inline bool conv_resident_supported(const PmdConvShape& s) {
+  return conv_tc_supported(s) && s.R == 3 && s.stride == 1 && s.W % 8 == 0 && s.H % 16 == 0 && s.C == 64 && s.K == 64;
 }
-int build_fprop_halo_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
-                            ConvHaloParams* out);
-// C = K = 64 (the 32x32 stage): conv3x3_resident_kernel.  Default: fprop only (see conv_resident_mode()).
-inline bool conv_resident_supported(const PmdConvShape& s) { return conv_halo_supported(s) && s.C == 64 && s.K == 64; }
 bool conv_resident_enabled();        // fprop
 bool conv_resident_dgrad_enabled();  // dgrad (PMD_CONV_RESIDENT: 2 fprop only [default], 1 both, 0 off, 3 dgrad only)
-int build_dgrad_halo_params(const PmdConvShape& s, const void* dy, const void* w, const void* addend, void* dx,
-                            ConvHaloParams* out, bool w_is_krsc = false);
-int launch_conv_halo(const ConvHaloParams& p, cudaStream_t stream);
-bool conv_halo_enabled();        // column-patch kernel for fprop
-bool conv_halo_dgrad_enabled();  // column-patch kernel for dgrad (PMD_CONV_HALO: 0 never, 1 both, 2 dgrad only)
+int build_fprop_resident_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
+                                ConvResidentParams* out);
+int build_dgrad_resident_params(const PmdConvShape& s, const void* dy, const void* w_krsc, const void* addend, void* dx,
+                                ConvResidentParams* out);
+int launch_conv_resident(const ConvResidentParams& p, cudaStream_t stream);
 
 // Builders return 0 / -1 (error text via pmd_last_error()).
 int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,

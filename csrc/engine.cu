@@ -63,8 +63,9 @@ struct Block {
 
 struct ConvPlan {
   ConvGemmParams fprop, fprop_eval;
-  ConvHaloParams fprop_h, fprop_eval_h;     // used instead when halo == true (3x3 stride-1, large maps)
-  bool halo = false;
+  ConvResidentParams fprop_r, fprop_eval_r;   // used instead when resident == true (3x3 stride-1, C = K = 64)
+  bool resident = false;
+  bool fwd_tail = false;                      // the fprop kernel's last CTA completes the SyncBatchNorm exchange
   WgradParams wgrad;
 };
 
@@ -74,9 +75,10 @@ struct Plan {
   std::vector<ConvGemmParams> block_dgrad;   // one per block (conv0 + fused shortcut / addend)
   std::vector<ConvGemmParams> sc_dgrad;      // per block: shortcut alone, when it cannot share conv0's tile grid
   std::vector<ConvGemmParams> inner_dgrad;   // per conv index (main[j], j >= 1)
-  std::vector<ConvHaloParams> block_dgrad_h, inner_dgrad_h;
-  std::vector<char> block_halo, inner_halo;
+  std::vector<ConvResidentParams> block_dgrad_r, inner_dgrad_r;
+  std::vector<char> block_resident, inner_resident;
   std::vector<char> inner_reduced;          // inner dgrad also does the BatchNorm-backward reduction of the layer below
+  std::vector<char> inner_tail;             // ... and its last CTA completes that reduction's cross-GPU exchange
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_launches = 0, eval_launches = 0;
   bool train_warm = false, eval_warm = false;
@@ -103,10 +105,11 @@ struct PmdEngine {
   double* metrics = nullptr;
   // local buffers
   std::vector<void*> owned;
-  bf16* wt = nullptr;                 // RSCK copies, only for the opt-in column-patch dgrad (same offsets as the slab)
-  PmdRepackEntry* d_repack = nullptr;
-  int n_repack = 0;
-  long long repack_max = 0;
+  // PMD_COMM_STUB-style measurement switch (pmd_engine_set_comm_stub): bit 0 = SyncBatchNorm statistics stay local,
+  // bit 1 = gradient buckets are "reduced" over this rank alone.  The kernels are the ones a 1-GPU run uses.
+  int comm_stub = 0;
+  PmdSym sym_local{};                 // this rank seen as a world of one (d_bases -> d_local_base)
+  unsigned long long* d_local_base = nullptr;
   bf16* x0 = nullptr;
   bf16* stem_w_pad = nullptr;         // [64][64] zero-padded stem weight
   unsigned char *in_u8 = nullptr, *in_valid = nullptr;
@@ -229,7 +232,12 @@ int allocate(PmdEngine* e) {
   PMD_CHECK_CUDA(cudaMemset(e->metrics, 0, 64));
   PMD_CHECK_CUDA(cudaMemset(e->hptr<char>(e->bnpart_off), 0, part));
 
-  E_CHECK(e->dalloc(&e->wt, S));
+  E_CHECK(e->dalloc(&e->d_local_base, 1));
+  PMD_CHECK_CUDA(cudaMemcpy(e->d_local_base, &e->info.local_base, sizeof(unsigned long long), cudaMemcpyHostToDevice));
+  e->sym_local.rank = 0;
+  e->sym_local.world = 1;
+  e->sym_local.d_bases = e->d_local_base;
+  e->sym_local.mc_base = 0;
   E_CHECK(e->dalloc(&e->x0, 1LL * B * c.image_hw * c.image_hw * 64));
   E_CHECK(e->dalloc(&e->stem_w_pad, 64 * 64));
   E_CHECK(e->dalloc(&e->in_u8, 1LL * B * c.image_hw * c.image_hw * 3));
@@ -243,7 +251,6 @@ int allocate(PmdEngine* e) {
   E_CHECK(e->dalloc(&e->metrics_total, 4));
 
   unsigned long long poff = e->bnpart_off;
-  std::vector<PmdRepackEntry> rep;
   for (size_t i = 0; i < e->convs.size(); ++i) {
     Conv& cv = e->convs[i];
     const long long out_elems = 1LL * B * cv.Ho * cv.Wo * cv.s.K;
@@ -278,18 +285,6 @@ int allocate(PmdEngine* e) {
     cv.rm = c.d_bn_float + c.bn_rm_off[i];
     cv.rv = c.d_bn_float + c.bn_rv_off[i];
     cv.nb = c.d_bn_nbt + i;
-    if (cv.tc && i > 0) {
-      PmdRepackEntry r{cv.w_off, cv.w_off, cv.s.K, cv.s.R * cv.s.R, cv.s.C, 0};
-      rep.push_back(r);
-      const long long el = 1LL * cv.s.K * cv.s.R * cv.s.R * cv.s.C;
-      e->repack_max = el > e->repack_max ? el : e->repack_max;
-    }
-  }
-  if (!conv_halo_dgrad_enabled()) rep.clear();   // dgrad reads the KRSC weights directly (MN-major B): no RSCK copy
-  e->n_repack = static_cast<int>(rep.size());
-  if (e->n_repack > 0) {
-    E_CHECK(e->dalloc(&e->d_repack, e->n_repack));
-    PMD_CHECK_CUDA(cudaMemcpy(e->d_repack, rep.data(), rep.size() * sizeof(PmdRepackEntry), cudaMemcpyHostToDevice));
   }
   // activations between convs
   Conv& st = e->convs[0];
@@ -322,6 +317,63 @@ int allocate(PmdEngine* e) {
   return 0;
 }
 
+// Multi-rank SyncBatchNorm is in effect (and not stubbed out for a communication-free timing run).
+bool sync_bn_active(const PmdEngine* e) { return e->sym.world > 1 && e->cfg.sync_bn && (e->comm_stub & 1) == 0; }
+
+// Who completes a SyncBatchNorm exchange (PMD_SYNC_TAIL): the producer's last CTA (sync_tail.cuh) or a stand-alone
+// single-block kernel between producer and consumer.  The tail costs every CTA of the producer a __threadfence +
+// ticket at its very end (~0.7 us during which its shared memory stays occupied), so it pays for grids of about one
+// wave (persistent kernels, the BatchNorm reductions, the convolutions of the small maps) and loses on the 1024-4096
+// CTA grids of the large maps.  2 (default): tail when the producer's grid has at most `kTailMaxCtas` CTAs;
+// 1: always; 0: never (round-1 behaviour).
+constexpr int kTailMaxCtas = 2 * 148;
+int sync_tail_mode() {
+  static const int mode = getenv("PMD_SYNC_TAIL") == nullptr ? 0 : atoi(getenv("PMD_SYNC_TAIL"));
+  return mode;
+}
+bool sync_tail_enabled() { return sync_tail_mode() != 0; }
+bool sync_tail_for_grid(long long ctas) { return sync_tail_mode() == 1 || (sync_tail_mode() == 2 && ctas <= kTailMaxCtas); }
+long long gemm_ctas(const ConvGemmParams& p) {
+  return 1LL * p.tiles_w * p.tiles_h * p.tiles_n * (p.out_channels / p.bn_tile) * p.n_classes;
+}
+
+// Forward exchange of conv `ci`'s [sum, sumsq] + BatchNorm finalize, as done by the fprop kernel's last CTA.
+SyncTail forward_tail(PmdEngine* e, int ci, long long rows) {
+  Conv& cv = e->convs[ci];
+  SyncTail t{};
+  t.mode = 1;
+  t.slot = ci;
+  t.sym = e->sym;
+  t.recv_off = cv.recv_fwd_off;
+  t.C = cv.s.K;
+  t.count_per_rank = static_cast<float>(rows);
+  t.momentum = e->cfg.bn_momentum;
+  t.eps = e->cfg.bn_eps;
+  t.gamma = e->param + cv.g_off;
+  t.beta = e->param + cv.b_off;
+  t.running_mean = cv.rm;
+  t.running_var = cv.rv;
+  t.nbt = cv.nb;
+  t.scale = cv.scale;
+  t.shift = cv.shift;
+  t.mean = cv.mean;
+  t.invstd = cv.invstd;
+  return t;
+}
+
+// Backward exchange of conv `ci`'s [sum_g, sum_g*xhat] into sums_total.
+SyncTail backward_tail(PmdEngine* e, int ci) {
+  Conv& cv = e->convs[ci];
+  SyncTail t{};
+  t.mode = 2;
+  t.slot = static_cast<int>(e->convs.size()) + ci;
+  t.sym = e->sym;
+  t.recv_off = cv.recv_bwd_off;
+  t.C = cv.s.K;
+  t.totals = cv.sums_total;
+  return t;
+}
+
 Plan* get_plan(PmdEngine* e, int n) {
   auto it = e->plans.find(n);
   if (it != e->plans.end()) return it->second.get();
@@ -331,14 +383,15 @@ Plan* get_plan(PmdEngine* e, int n) {
   pl->inner_dgrad.resize(e->convs.size());
   pl->block_dgrad.resize(e->blocks.size());
   pl->sc_dgrad.resize(e->blocks.size());
-  pl->block_dgrad_h.resize(e->blocks.size());
-  pl->inner_dgrad_h.resize(e->convs.size());
-  pl->block_halo.assign(e->blocks.size(), 0);
-  pl->inner_halo.assign(e->convs.size(), 0);
+  pl->block_dgrad_r.resize(e->blocks.size());
+  pl->inner_dgrad_r.resize(e->convs.size());
+  pl->block_resident.assign(e->blocks.size(), 0);
+  pl->inner_resident.assign(e->convs.size(), 0);
   pl->inner_reduced.assign(e->convs.size(), 0);
-  const bool halo_on = conv_halo_enabled(), halo_dgrad = conv_halo_dgrad_enabled();
+  pl->inner_tail.assign(e->convs.size(), 0);
   // C = K = 64 3x3 layers: weight-resident persistent kernel
   const bool resident_on = conv_resident_enabled(), resident_dgrad = conv_resident_dgrad_enabled();
+  const bool tails = sync_bn_active(e) && sync_tail_enabled();
   for (size_t i = 0; i < e->convs.size(); ++i) {
     Conv& cv = e->convs[i];
     if (!cv.tc) continue;
@@ -348,11 +401,19 @@ Plan* get_plan(PmdEngine* e, int n) {
     if (build_fprop_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop)) return nullptr;
     pl->conv[i].fprop_eval = pl->conv[i].fprop;
     pl->conv[i].fprop_eval.stats = nullptr;
-    if (!cv.stem_col && ((halo_on && conv_halo_supported(s)) || (resident_on && conv_resident_supported(s)))) {
-      if (build_fprop_halo_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop_h)) return nullptr;
-      pl->conv[i].fprop_eval_h = pl->conv[i].fprop_h;
-      pl->conv[i].fprop_eval_h.stats = nullptr;
-      pl->conv[i].halo = true;
+    const long long rows = 1LL * n * cv.Ho * cv.Wo;
+    bool tail_here = tails && sync_tail_for_grid(gemm_ctas(pl->conv[i].fprop));
+    if (!cv.stem_col && resident_on && conv_resident_supported(s)) {
+      if (build_fprop_resident_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop_r)) return nullptr;
+      pl->conv[i].fprop_eval_r = pl->conv[i].fprop_r;
+      pl->conv[i].fprop_eval_r.stats = nullptr;
+      tail_here = tails;       // persistent: one CTA per SM
+      if (tail_here) pl->conv[i].fprop_r.tail = forward_tail(e, static_cast<int>(i), rows);
+      pl->conv[i].resident = true;
+    }
+    if (tail_here) {
+      pl->conv[i].fprop.tail = forward_tail(e, static_cast<int>(i), rows);
+      pl->conv[i].fwd_tail = true;
     }
     if (build_wgrad_params(s, cv.x, cv.dy, e->grad + cv.w_off, 0, e->sm_count, &pl->conv[i].wgrad,
                            cv.stem_col ? cv.real_rsc : 0, cv.stem_col ? cv.real_rsc : 64))
@@ -367,23 +428,23 @@ Plan* get_plan(PmdEngine* e, int n) {
       if (build_dgrad_params(s, cv.dy, e->wbf16 + cv.w_off, nullptr, nullptr, nullptr, nullptr, b.dz_mid[j - 1],
                              &pl->inner_dgrad[b.main[j]], true))
         return nullptr;
-      const bool halo_dgrad_here = (resident_dgrad && conv_resident_supported(s)) || (halo_dgrad && conv_halo_supported(s));
-      if (!halo_dgrad_here) {
+      if (resident_dgrad && conv_resident_supported(s)) {
+        if (build_dgrad_resident_params(s, cv.dy, e->wbf16 + cv.w_off, nullptr, b.dz_mid[j - 1],
+                                        &pl->inner_dgrad_r[b.main[j]]))
+          return nullptr;
+        pl->inner_resident[b.main[j]] = 1;
+      } else {
         // dz_mid[j-1] is consumed only by the BatchNorm backward of conv j-1: let the dgrad epilogue do its reduction
-        Conv& pv = e->convs[b.main[j - 1]];
+        // (and, under multi-rank SyncBatchNorm, let its last CTA exchange the sums with the peers)
+        const int prev = b.main[j - 1];
+        Conv& pv = e->convs[prev];
         const int rc = attach_bn_reduce(&pl->inner_dgrad[b.main[j]], s, pv.y, pv.scale, pv.shift, pv.mean, pv.invstd, pv.sums);
         if (rc < 0) return nullptr;
         pl->inner_reduced[b.main[j]] = static_cast<char>(rc);
-      }
-      if (resident_dgrad && conv_resident_supported(s)) {
-        if (build_dgrad_halo_params(s, cv.dy, e->wbf16 + cv.w_off, nullptr, b.dz_mid[j - 1],
-                                    &pl->inner_dgrad_h[b.main[j]], true))
-          return nullptr;
-        pl->inner_halo[b.main[j]] = 1;
-      } else if (halo_dgrad && conv_halo_supported(s)) {
-        if (build_dgrad_halo_params(s, cv.dy, e->wt + cv.w_off, nullptr, b.dz_mid[j - 1], &pl->inner_dgrad_h[b.main[j]]))
-          return nullptr;
-        pl->inner_halo[b.main[j]] = 1;
+        if (rc == 1 && tails && sync_tail_for_grid(gemm_ctas(pl->inner_dgrad[b.main[j]]))) {
+          pl->inner_dgrad[b.main[j]].tail = backward_tail(e, prev);
+          pl->inner_tail[b.main[j]] = 1;
+        }
       }
     }
     Conv& c0 = e->convs[b.main[0]];
@@ -413,12 +474,9 @@ Plan* get_plan(PmdEngine* e, int n) {
                              &pl->block_dgrad[bi], true))
         return nullptr;
       if (resident_dgrad && conv_resident_supported(s0)) {
-        if (build_dgrad_halo_params(s0, c0.dy, e->wbf16 + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_h[bi], true))
+        if (build_dgrad_resident_params(s0, c0.dy, e->wbf16 + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_r[bi]))
           return nullptr;
-        pl->block_halo[bi] = 1;
-      } else if (halo_dgrad && conv_halo_supported(s0)) {
-        if (build_dgrad_halo_params(s0, c0.dy, e->wt + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_h[bi])) return nullptr;
-        pl->block_halo[bi] = 1;
+        pl->block_resident[bi] = 1;
       }
     }
   }
@@ -456,21 +514,15 @@ struct BucketTracker {
     a.weight_decay = e->cfg.weight_decay;
     a.nesterov = e->cfg.nesterov;
     a.algo = e->bucket_algo[bkt];
-    a.blocks = e->sym.world == 1 ? 4 * e->sm_count : e->bucket_blocks[bkt];
+    const bool local = e->sym.world == 1 || (e->comm_stub & 2) != 0;
+    a.blocks = local ? 4 * e->sm_count : e->bucket_blocks[bkt];
     a.d_lr = e->d_lr;
     const int slot = 2 * static_cast<int>(e->convs.size()) + 8 + bkt * 128;
-    E_CHECK(pmd_allreduce_sgd(&e->sym, &a, slot, e->comm_stream));
+    E_CHECK(pmd_allreduce_sgd(local ? &e->sym_local : &e->sym, &a, slot, e->comm_stream));
     ++launched;
     return 0;
   }
 };
-
-// PMD_BN_FUSED_SYNC=1: do the SyncBatchNorm exchange inside the BatchNorm kernels instead of in stand-alone
-// single-block kernels (correct, but measured slower; kept for experiments).
-bool fused_sync_exchange() {
-  static const bool on = getenv("PMD_BN_FUSED_SYNC") != nullptr && atoi(getenv("PMD_BN_FUSED_SYNC")) != 0;
-  return on;
-}
 
 // Describes conv `ci`'s BatchNorm for the fused finalize+apply kernel.
 PmdBnFinalize bn_desc(PmdEngine* e, int ci) {
@@ -486,24 +538,21 @@ PmdBnFinalize bn_desc(PmdEngine* e, int ci) {
   f.shift = cv.shift;
   f.mean = cv.mean;
   f.invstd = cv.invstd;
-  f.totals_scratch = cv.stats_total;
-  f.recv_off = cv.recv_fwd_off;
-  f.slot = ci;
   return f;
 }
 
-// z = relu(BN_ci(y_ci) [+ res | + BN_cres(y_cres)]): training mode finalises the statistics (and exchanges them
-// with the peers under SyncBatchNorm) inside the same kernel; evaluation mode uses the running statistics.
-int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long long rows, bool train, cudaStream_t st) {
+// z = relu(BN_ci(y_ci) [+ res | + BN_cres(y_cres)]).  Training, one rank: the statistics are finalised inside the
+// apply kernel.  Training, multi-rank SyncBatchNorm: the convolution's last CTA has already exchanged and finalised
+// them (Plan::fwd_tail), so only the plain apply remains; a producer without that tail (non-tensor-core conv,
+// PMD_SYNC_TAIL=0) is followed by the stand-alone push-exchange kernel.  Evaluation uses the running statistics.
+int bn_apply_step(PmdEngine* e, Plan* pl, int ci, int cres, const bf16* res, bf16* z, long long rows, bool train,
+                  cudaStream_t st) {
   Conv& cv = e->convs[ci];
   const PmdEngineConfig& c = e->cfg;
-  if (train && e->sym.world > 1 && c.sync_bn && !fused_sync_exchange()) {
-    // multi-rank default: stand-alone push exchange + finalize kernel per BatchNorm, then the plain apply
-    // (measured at 2 GPUs: 2.173 ms/step vs 2.215 ms with the exchange inside the apply kernel, where the whole
-    // grid idles on block 0's NVLink round trip)
+  if (train && sync_bn_active(e)) {
     const int todo[2] = {ci, cres};
     for (int k = 0; k < 2; ++k) {
-      if (todo[k] < 0) continue;
+      if (todo[k] < 0 || pl->conv[todo[k]].fwd_tail) continue;
       Conv& b = e->convs[todo[k]];
       E_CHECK(pmd_bn_finalize_push(&e->sym, todo[k], b.stats, b.recv_fwd_off, static_cast<float>(rows), b.s.K,
                                    e->param + b.g_off, e->param + b.b_off, b.rm, b.rv, b.nb, c.bn_momentum, c.bn_eps,
@@ -516,12 +565,11 @@ int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long
     return pmd_bn_apply(cv.y, cv.scale, cv.shift, res, nullptr, nullptr, 1, z, rows, cv.s.K, st);
   }
   if (train) {
-    const bool sync = e->sym.world > 1 && c.sync_bn;
     const PmdBnFinalize f = bn_desc(e, ci);
     PmdBnFinalize fr{};
     if (cres >= 0) fr = bn_desc(e, cres);
-    return pmd_bn_finalize_apply(sync ? &e->sym : nullptr, &f, cres >= 0 ? &fr : nullptr, static_cast<float>(rows),
-                                 c.bn_momentum, c.bn_eps, cv.y, cres >= 0 ? e->convs[cres].y : res, 1, z, rows, cv.s.K, st);
+    return pmd_bn_finalize_apply(&f, cres >= 0 ? &fr : nullptr, static_cast<float>(rows), c.bn_momentum, c.bn_eps, cv.y,
+                                 cres >= 0 ? e->convs[cres].y : res, 1, z, rows, cv.s.K, st);
   }
   E_CHECK(pmd_bn_eval_affine(cv.s.K, e->param + cv.g_off, e->param + cv.b_off, cv.rm, cv.rv, c.bn_eps, cv.scale, cv.shift, st));
   if (cres >= 0) {
@@ -535,14 +583,17 @@ int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long
 // BatchNorm backward of conv `ci` (and, for a projection block's output, of the shortcut conv `cj`
 // in the same two passes).  dz = gradient wrt the activation that followed; the ReLU mask comes from z
 // (block outputs, where a residual was added before the ReLU) or is recomputed from y (z == nullptr).
+// reduced: 0 = run the reduction here; 1 = the dgrad that produced dz accumulated the sums (and masked dz) in its
+// epilogue; 2 = ... and its last CTA also exchanged them across ranks.
 int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, long long rows, bf16* g_out,
-                cudaStream_t st, bool already_reduced = false) {
-  const bool sync = e->sym.world > 1 && e->cfg.sync_bn;
+                cudaStream_t st, int reduced = 0) {
+  const bool sync = sync_bn_active(e);
   const int nb = cj >= 0 ? 2 : 1;
   PmdBnBranch br[2];
   const int idx[2] = {ci, cj};
   for (int b = 0; b < nb; ++b) {
     Conv& cv = e->convs[idx[b]];
+    br[b] = PmdBnBranch{};
     br[b].y = cv.y;
     br[b].mean = cv.mean;
     br[b].invstd = cv.invstd;
@@ -553,25 +604,26 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
     br[b].dgamma = e->grad + cv.g_off;
     br[b].dbeta = e->grad + cv.b_off;
     br[b].recv_off = cv.recv_bwd_off;
-    br[b].totals_scratch = cv.sums_total;
+    br[b].totals_out = cv.sums_total;
     br[b].slot = static_cast<int>(e->convs.size()) + idx[b];
   }
   Conv& c0 = e->convs[ci];
   const int mask = z != nullptr ? 1 : 2;
-  // already_reduced: the dgrad that produced dz accumulated the sums (and masked dz) in its epilogue
-  if (!already_reduced) E_CHECK(pmd_bn_bwd_reduce_multi(dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
-  if (sync && !fused_sync_exchange()) {
+  const bool tail = sync && sync_tail_enabled();
+  if (reduced == 0) {
+    if (tail)   // the reduction's last block exchanges the sums (both branches of a projection block in one trip)
+      E_CHECK(pmd_bn_bwd_reduce_multi_sync(&e->sym, dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
+    else
+      E_CHECK(pmd_bn_bwd_reduce_multi(dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
+  }
+  if (sync && !(tail && reduced != 1)) {
     for (int b = 0; b < nb; ++b) {
       Conv& cv = e->convs[idx[b]];
       E_CHECK(pmd_small_allreduce_push(&e->sym, br[b].slot, cv.sums, 2 * cv.s.K, cv.recv_bwd_off, cv.sums_total, st));
     }
-    return pmd_bn_bwd_apply_multi(dz, z, c0.scale, c0.shift, mask, br, nb, static_cast<float>(rows) * e->sym.world, g_out,
-                                  rows, c0.s.K, st);
   }
-  if (sync)
-    return pmd_bn_bwd_apply_multi_sync(&e->sym, dz, z, c0.scale, c0.shift, mask, br, nb,
-                                       static_cast<float>(rows) * e->sym.world, g_out, rows, c0.s.K, st);
-  return pmd_bn_bwd_apply_multi(dz, z, c0.scale, c0.shift, mask, br, nb, static_cast<float>(rows), g_out, rows, c0.s.K, st);
+  const float count = static_cast<float>(rows) * (sync ? e->sym.world : 1);
+  return pmd_bn_bwd_apply_multi(dz, z, c0.scale, c0.shift, mask, br, nb, count, g_out, rows, c0.s.K, st);
 }
 
 int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
@@ -580,8 +632,8 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
   E_CHECK(pmd_augment_im2col(e->in_u8, e->in_aug, n, c.image_hw, c.image_hw, 8, e->x0, st));
   auto conv_fwd = [&](int ci, cudaStream_t st) -> int {
     Conv& cv = e->convs[ci];
-    if (cv.tc && pl->conv[ci].halo) {
-      E_CHECK(launch_conv_halo(train ? pl->conv[ci].fprop_h : pl->conv[ci].fprop_eval_h, st));
+    if (cv.tc && pl->conv[ci].resident) {
+      E_CHECK(launch_conv_resident(train ? pl->conv[ci].fprop_r : pl->conv[ci].fprop_eval_r, st));
     } else if (cv.tc) {
       E_CHECK(launch_conv_gemm(train ? pl->conv[ci].fprop : pl->conv[ci].fprop_eval, st));
     } else {
@@ -595,7 +647,7 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
   E_CHECK(conv_fwd(0, st));
   {
     Conv& cv = e->convs[0];
-    E_CHECK(bn_apply_step(e, 0, -1, nullptr, e->z_stem, 1LL * n * cv.Ho * cv.Wo, train, st));
+    E_CHECK(bn_apply_step(e, pl, 0, -1, nullptr, e->z_stem, 1LL * n * cv.Ho * cv.Wo, train, st));
   }
   for (Block& b : e->blocks) {
     cudaEvent_t sc_done = nullptr;
@@ -612,12 +664,12 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
       E_CHECK(conv_fwd(b.main[j], st));
       if (j < b.n_main - 1) {
         Conv& cv = e->convs[b.main[j]];
-        E_CHECK(bn_apply_step(e, b.main[j], -1, nullptr, b.z_mid[j], 1LL * n * cv.Ho * cv.Wo, train, st));
+        E_CHECK(bn_apply_step(e, pl, b.main[j], -1, nullptr, b.z_mid[j], 1LL * n * cv.Ho * cv.Wo, train, st));
       }
     }
     if (sc_done != nullptr) PMD_CHECK_CUDA(cudaStreamWaitEvent(st, sc_done, 0));
     Conv& last = e->convs[b.main[b.n_main - 1]];
-    E_CHECK(bn_apply_step(e, b.main[b.n_main - 1], b.sc, b.sc >= 0 ? nullptr : b.z_in, b.z_out,
+    E_CHECK(bn_apply_step(e, pl, b.main[b.n_main - 1], b.sc, b.sc >= 0 ? nullptr : b.z_in, b.z_out,
                           1LL * n * last.Ho * last.Wo, train, st));
   }
   Block& lb = e->blocks.back();
@@ -688,15 +740,15 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
       const int ci = b.main[j], prev = b.main[j - 1];
       E_CHECK(dy_ready());
       if (!dgrad_first) E_CHECK(wgrad(ci));
-      if (pl->inner_halo[ci])
-        E_CHECK(launch_conv_halo(pl->inner_dgrad_h[ci], st));
+      if (pl->inner_resident[ci])
+        E_CHECK(launch_conv_resident(pl->inner_dgrad_r[ci], st));
       else
         E_CHECK(launch_conv_gemm(pl->inner_dgrad[ci], st));
       if (dgrad_first) E_CHECK(wgrad(ci));
       E_CHECK(w_done(ci));
       Conv& pv = e->convs[prev];
       E_CHECK(bn_backward(e, prev, -1, b.dz_mid[j - 1], nullptr, 1LL * n * pv.Ho * pv.Wo, nullptr, st,
-                          pl->inner_reduced[ci] != 0));
+                          pl->inner_reduced[ci] != 0 ? (pl->inner_tail[ci] ? 2 : 1) : 0));
       E_CHECK(bn_done(prev));
     }
     E_CHECK(dy_ready());
@@ -706,8 +758,8 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     }
     if (b.sc >= 0 && e->convs[b.sc].s.stride != e->convs[b.main[0]].s.stride)
       E_CHECK(launch_conv_gemm(pl->sc_dgrad[bi], st));
-    if (pl->block_halo[bi])
-      E_CHECK(launch_conv_halo(pl->block_dgrad_h[bi], st));
+    if (pl->block_resident[bi])
+      E_CHECK(launch_conv_resident(pl->block_dgrad_r[bi], st));
     else
       E_CHECK(launch_conv_gemm(pl->block_dgrad[bi], st));
     if (dgrad_first) {
@@ -733,7 +785,6 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     PMD_CHECK_CUDA(cudaEventRecord(ev, e->wg_stream));
     PMD_CHECK_CUDA(cudaStreamWaitEvent(st, ev, 0));
   }
-  if (e->n_repack > 0) E_CHECK(pmd_repack_dgrad_weights(e->wbf16, e->wt, e->d_repack, e->n_repack, e->repack_max, st));
   E_CHECK(pmd_pad_stem_weight(e->wbf16 + e->convs[0].w_off, e->stem_w_pad, 64, e->convs[0].real_rsc, st));
   return 0;
 }
@@ -767,6 +818,7 @@ int run_or_replay(PmdEngine* e, cudaGraphExec_t* graph, bool* warm, int* launche
     PMD_CHECK_CUDA(ce);
     PMD_CHECK_CUDA(cudaGraphInstantiate(graph, g, 0));
     cudaGraphDestroy(g);
+    PMD_CHECK_CUDA(cudaGraphUpload(*graph, st));   // device-side set-up of the graph now, not inside its first launch
   }
   PMD_CHECK_CUDA(cudaGraphLaunch(*graph, st));
   count_launch(*launches);
@@ -879,7 +931,6 @@ extern "C" PMD_API int pmd_engine_sync_params(PmdEngine* e, int broadcast_from_r
                           PMD_MAX_SLOTS - 128, st));
   }
   E_CHECK(pmd_cast_f32_to_bf16(e->param, e->wbf16, e->cfg.slab_elems, st));
-  if (e->n_repack > 0) E_CHECK(pmd_repack_dgrad_weights(e->wbf16, e->wt, e->d_repack, e->n_repack, e->repack_max, st));
   E_CHECK(pmd_pad_stem_weight(e->wbf16 + e->convs[0].w_off, e->stem_w_pad, 64, e->convs[0].real_rsc, st));
   PMD_CHECK_CUDA(cudaStreamSynchronize(st));
   return 0;
@@ -936,6 +987,19 @@ extern "C" PMD_API int pmd_engine_read_metrics(PmdEngine* e, int reduce_over_ran
   PMD_CHECK_CUDA(cudaMemcpyAsync(out4, src, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
   if (reset) PMD_CHECK_CUDA(cudaMemsetAsync(e->metrics, 0, 4 * sizeof(double), st));
   PMD_CHECK_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" PMD_API int pmd_engine_set_comm_stub(PmdEngine* e, int mask) {
+  PMD_REQUIRE(mask >= 0 && mask <= 3, "comm stub mask: bit 0 = BatchNorm statistics local, bit 1 = gradients local");
+  if (mask == e->comm_stub) return 0;
+  PMD_CHECK_CUDA(cudaDeviceSynchronize());
+  for (auto& kv : e->plans) {       // plans (tensor maps, exchange descriptors, captured graphs) depend on the setting
+    if (kv.second->train_graph) cudaGraphExecDestroy(kv.second->train_graph);
+    if (kv.second->eval_graph) cudaGraphExecDestroy(kv.second->eval_graph);
+  }
+  e->plans.clear();
+  e->comm_stub = mask;
   return 0;
 }
 

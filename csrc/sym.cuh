@@ -58,12 +58,9 @@ __device__ __forceinline__ uint32_t* flag_ptr(const PmdSym& s, int heap_rank, in
 __device__ __forceinline__ uint32_t* epoch_ptr(const PmdSym& s, int slot) {
   return reinterpret_cast<uint32_t*>(s.d_bases[s.rank] + PMD_FLAGS_BYTES) + slot;
 }
-// grid-wide exchanges: arrival tickets and "totals are published" markers, both local to the rank
+// arrival tickets of the kernels whose LAST CTA completes an exchange (sync_tail.cuh); local to the rank
 __device__ __forceinline__ uint32_t* ticket_ptr(const PmdSym& s, int slot) {
   return reinterpret_cast<uint32_t*>(s.d_bases[s.rank] + PMD_FLAGS_BYTES) + PMD_MAX_SLOTS + slot;
-}
-__device__ __forceinline__ uint32_t* done_ptr(const PmdSym& s, int slot) {
-  return reinterpret_cast<uint32_t*>(s.d_bases[s.rank] + PMD_FLAGS_BYTES) + 2 * PMD_MAX_SLOTS + slot;
 }
 
 template <typename T>
@@ -81,113 +78,77 @@ __device__ __forceinline__ T* heap_ptr(const PmdSym& s, int w, unsigned long lon
 __device__ __forceinline__ void st_ll(uint2* p, float v, uint32_t epoch) {
   asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
 }
-__device__ __forceinline__ float poll_ll(const uint2* p, uint32_t epoch, int rank, int src, int slot) {
-  uint32_t v, f;
+// Polls the words of element i from every peer's row of the local receive area, all peers in flight at once (a
+// dependent load-compare loop per peer would serialise W L2 round trips), and returns the rank-ordered sum.
+__device__ __forceinline__ float ll_poll_sum_one(const PmdSym& s, const uint2* mine, int n, int i, float own,
+                                                 uint32_t epoch, int slot) {
+  uint32_t v[PMD_MAX_RANKS], f[PMD_MAX_RANKS];
+  uint32_t pending = ((1u << s.world) - 1u) & ~(1u << s.rank);
   const unsigned long long t0 = globaltimer_ns();
   uint32_t spins = 0;
-  for (;;) {
-    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(f) : "l"(p) : "memory");
-    if (f == epoch) break;
-    if (((++spins) & 0xfff) == 0 && globaltimer_ns() - t0 > 30000000000ULL) {
-      printf("pmdist: rank %d timed out waiting for rank %d's data (slot %d, epoch %u, saw %u)\n", rank, src, slot, epoch,
-             f);
+  while (pending != 0u) {
+#pragma unroll
+    for (int w = 0; w < PMD_MAX_RANKS; ++w)
+      if ((pending >> w) & 1u)
+        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];"
+                     : "=r"(v[w]), "=r"(f[w])
+                     : "l"(mine + static_cast<long long>(w) * n + i)
+                     : "memory");
+#pragma unroll
+    for (int w = 0; w < PMD_MAX_RANKS; ++w)
+      if (((pending >> w) & 1u) && f[w] == epoch) pending &= ~(1u << w);
+    if (pending != 0u && ((++spins) & 0xfff) == 0 && globaltimer_ns() - t0 > 30000000000ULL) {
+      printf("pmdist: rank %d timed out waiting for pushed data (slot %d, epoch %u, missing ranks mask 0x%x)\n", s.rank,
+             slot, epoch, pending);
       __trap();
     }
   }
-  return __uint_as_float(v);
+  float acc = 0.f;
+#pragma unroll
+  for (int w = 0; w < PMD_MAX_RANKS; ++w)      // rank order: identical bits on every rank
+    if (w < s.world) acc += (w == s.rank) ? own : __uint_as_float(v[w]);
+  return acc;
+}
+
+// The three phases of a push exchange, for ONE block (all its threads call each phase):
+//   ll_next_epoch  advances the exchange's device-resident epoch counter and returns the new value to every thread;
+//   ll_push        stores this rank's vector into every peer's receive area as {value, epoch} words;
+//   ll_poll_sum    waits for every peer's words in the LOCAL receive area and leaves the rank-ordered totals in sum_s.
+// `local` is read with ld.cg: it may have been accumulated by red.global.add from other SMs just before.
+__device__ __forceinline__ uint32_t ll_next_epoch(const PmdSym& s, int slot, uint32_t* bcast_s) {
+  if (threadIdx.x == 0) {
+    volatile uint32_t* ep = epoch_ptr(s, slot);
+    const uint32_t e = *ep + 1;
+    *ep = e;
+    *bcast_s = e;
+  }
+  __syncthreads();
+  return *bcast_s;
+}
+__device__ __forceinline__ void ll_push(const PmdSym& s, const float* local, int n, unsigned long long recv_off,
+                                        uint32_t epoch) {
+  const int parity = epoch & 1;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float v = __ldcg(local + i);
+    for (int w = 0; w < s.world; ++w) {
+      if (w == s.rank) continue;
+      st_ll(heap_ptr<uint2>(s, w, recv_off) + (static_cast<long long>(parity) * s.world + s.rank) * n + i, v, epoch);
+    }
+  }
+}
+__device__ __forceinline__ void ll_poll_sum(const PmdSym& s, int slot, const float* local, int n,
+                                            unsigned long long recv_off, uint32_t epoch, float* sum_s) {
+  const uint2* mine = heap_ptr<const uint2>(s, s.rank, recv_off) + static_cast<long long>(epoch & 1) * s.world * n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) sum_s[i] = ll_poll_sum_one(s, mine, n, i, __ldcg(local + i), epoch, slot);
 }
 
 // Every thread of the (single) block calls this; returns with sum_s[0..n) = rank-ordered total in shared memory.
-__device__ void ll_exchange_sum(const PmdSym& s, int slot, const float* local, int n, unsigned long long recv_off,
-                                float* sum_s) {
+__device__ __forceinline__ void ll_exchange_sum(const PmdSym& s, int slot, const float* local, int n,
+                                                unsigned long long recv_off, float* sum_s) {
   __shared__ uint32_t epoch_s;
-  if (threadIdx.x == 0) {
-    uint32_t* ep = epoch_ptr(s, slot);
-    const uint32_t e = *ep + 1;
-    *ep = e;
-    epoch_s = e;
-  }
-  __syncthreads();
-  const uint32_t epoch = epoch_s;
-  const int parity = epoch & 1;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    const float v = local[i];
-    for (int w = 0; w < s.world; ++w) {
-      if (w == s.rank) continue;
-      uint2* dst = heap_ptr<uint2>(s, w, recv_off) + (static_cast<long long>(parity) * s.world + s.rank) * n + i;
-      st_ll(dst, v, epoch);
-    }
-  }
-  const uint2* mine = heap_ptr<const uint2>(s, s.rank, recv_off) + static_cast<long long>(parity) * s.world * n;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    float acc = 0.f;
-    for (int w = 0; w < s.world; ++w)      // rank order: identical bits on every rank
-      acc += (w == s.rank) ? local[i] : poll_ll(mine + static_cast<long long>(w) * n + i, epoch, s.rank, w, slot);
-    sum_s[i] = acc;
-  }
-  __syncthreads();
-}
-
-
-// Grid-wide form for kernels with many blocks (the fused BatchNorm kernels): every block needs the totals, but
-// only block 0 talks to the peers.  All blocks agree on the epoch through an arrival ticket (each block reads the
-// epoch BEFORE taking its ticket; the last arrival advances it, so a launch never sees its own increment);
-// block 0 pushes, polls, writes the totals to `totals_gmem` and publishes done[slot] = epoch; the other blocks
-// wait for that marker and read the totals from local memory.  Returns with sum_s[0..n) filled on every block.
-__device__ void ll_exchange_sum_grid(const PmdSym& s, int slot, const float* local, int n, unsigned long long recv_off,
-                                     float* totals_gmem, float* sum_s) {
-  __shared__ uint32_t epoch_g;
-  if (threadIdx.x == 0) {
-    volatile uint32_t* ep = epoch_ptr(s, slot);
-    const uint32_t e0 = *ep;
-    uint32_t* tk = ticket_ptr(s, slot);
-    const uint32_t t = atomicAdd(tk, 1u);
-    if (t == gridDim.x - 1) {
-      *tk = 0;
-      __threadfence();
-      *ep = e0 + 1;
-    }
-    epoch_g = e0 + 1;
-  }
-  __syncthreads();
-  const uint32_t epoch = epoch_g;
-  if (blockIdx.x == 0) {
-    const int parity = epoch & 1;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const float v = local[i];
-      for (int w = 0; w < s.world; ++w) {
-        if (w == s.rank) continue;
-        st_ll(heap_ptr<uint2>(s, w, recv_off) + (static_cast<long long>(parity) * s.world + s.rank) * n + i, v, epoch);
-      }
-    }
-    const uint2* mine = heap_ptr<const uint2>(s, s.rank, recv_off) + static_cast<long long>(parity) * s.world * n;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      float acc = 0.f;
-      for (int w = 0; w < s.world; ++w)
-        acc += (w == s.rank) ? local[i] : poll_ll(mine + static_cast<long long>(w) * n + i, epoch, s.rank, w, slot);
-      sum_s[i] = acc;
-      totals_gmem[i] = acc;
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(done_ptr(s, slot)), "r"(epoch) : "memory");
-  } else {
-    if (threadIdx.x == 0) {
-      const uint32_t* dp = done_ptr(s, slot);
-      const unsigned long long t0 = globaltimer_ns();
-      uint32_t v, spins = 0;
-      for (;;) {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(dp) : "memory");
-        if (v == epoch) break;
-        if (((++spins) & 0xfff) == 0 && globaltimer_ns() - t0 > 30000000000ULL) {
-          printf("pmdist: rank %d block %d timed out waiting for the exchanged totals (slot %d)\n", s.rank, blockIdx.x, slot);
-          __trap();
-        }
-      }
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < n; i += blockDim.x) sum_s[i] = __ldcg(totals_gmem + i);
-  }
+  const uint32_t epoch = ll_next_epoch(s, slot, &epoch_s);
+  ll_push(s, local, n, recv_off, epoch);
+  ll_poll_sum(s, slot, local, n, recv_off, epoch, sum_s);
   __syncthreads();
 }
 

@@ -135,10 +135,10 @@ typedef struct {
   void* dy;             /* apply only */
   float* dgamma;        /* apply only, may be NULL; += */
   float* dbeta;
-  /* pmd_bn_bwd_apply_multi_sync only: where this BatchNorm's cross-GPU exchange lives */
+  /* pmd_bn_bwd_reduce_multi_sync only: the cross-GPU exchange that the reduction's last thread block completes */
   unsigned long long recv_off; /* heap offset of a PMD_LL_RECV_BYTES(world, 2C) receive area */
-  float* totals_scratch;       /* local [2C] */
-  int slot;
+  float* totals_out;           /* local [2C]: receives the rank-ordered sum of every rank's `sums` */
+  int slot;                    /* signal-pad slot (epoch counter + arrival ticket) of this exchange */
   int pad_;
 } PmdBnBranch;
 int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale, const float* d_mask_shift,
@@ -150,9 +150,9 @@ int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z, const float* d_mas
 /* Forward finalize + apply in ONE launch (no separate pmd_bn_finalize between the convolution and the apply):
  * z = act(BN(y) [+ res | + BN_res(res)]) with the batch statistics taken from `stats` ([sum, sumsq], as left by
  * pmd_conv_fprop); writes scale/shift/mean/invstd and updates the running statistics exactly like
- * pmd_bn_finalize.  With sym != NULL and world > 1 the statistics are exchanged across ranks inside the kernel
- * (SyncBatchNorm; slot / recv_off / totals_scratch required).  f_res describes the projection shortcut's
- * BatchNorm when the residual needs its own affine (then d_res is that branch's conv output). */
+ * pmd_bn_finalize.  f_res describes the projection shortcut's BatchNorm when the residual needs its own affine
+ * (then d_res is that branch's conv output).  Single-rank statistics: under multi-rank SyncBatchNorm the kernel
+ * that produced `stats` finishes the exchange itself (csrc/sync_tail.cuh) and pmd_bn_apply follows. */
 typedef struct {
   const float* stats;           /* [2C] local sums */
   const float* gamma;
@@ -161,12 +161,9 @@ typedef struct {
   float* running_var;
   long long* num_batches;       /* may be NULL */
   float *scale, *shift, *mean, *invstd; /* [C] outputs */
-  float* totals_scratch;        /* [2C] local scratch (multi-rank only) */
-  unsigned long long recv_off;  /* push-exchange receive area (multi-rank only) */
-  int slot;
-  int pad_;
 } PmdBnFinalize;
-/* (pmd_bn_finalize_apply and pmd_bn_bwd_apply_multi_sync take a PmdSym and are declared in pmdist_comm.h) */
+int pmd_bn_finalize_apply(const PmdBnFinalize* f, const PmdBnFinalize* f_res, float count, float momentum, float eps,
+                          const void* d_y, const void* d_res, int relu, void* d_z, long long rows, int C, void* stream);
 
 /* ------------------------------------------------------------------ head + loss (head.cu)
  * Global average pool + Linear, cross-entropy with top-1/top-5 counters (ref:model/resnet.py:102-104,

@@ -114,19 +114,15 @@ int pmd_allreduce_f32(const PmdSym* sym, unsigned long long in_off, unsigned lon
 int pmd_broadcast(const PmdSym* sym, unsigned long long off, unsigned long long bytes, int src, int blocks, int slot,
                   void* stream);
 
-/* SyncBatchNorm exchanges.  stats_off / sums_off: [2C] fp32 at the same heap offset on every rank.
- * Forward: wait for all ranks' partial sums, then do what pmd_bn_finalize does over them.
- * Backward: wait, then write the rank-order total of all ranks' [2C] sums to d_total (local). */
-int pmd_bn_finalize_sync(const PmdSym* sym, int slot, unsigned long long stats_off, float count_per_rank, int C,
-                         const float* d_gamma, const float* d_beta, float* d_running_mean, float* d_running_var,
-                         long long* d_num_batches, float momentum, float eps, float* d_scale, float* d_shift,
-                         float* d_mean, float* d_invstd, void* stream);
-int pmd_small_allreduce_sync(const PmdSym* sym, int slot, unsigned long long off, int n, float* d_total,
-                             void* stream);
-/* Push ("LL") forms of the two exchanges above: one one-way NVLink trip instead of two round trips.  Every rank
- * stores its vector into every peer's receive area as {value, epoch} words and polls only its own memory.
- * recv_off: heap offset (same on every rank) of a zero-initialised area of PMD_LL_RECV_BYTES(world, n) bytes
- * that belongs to this exchange alone; d_stats / d_local may be any device pointer of this rank. */
+/* SyncBatchNorm exchanges.  Push ("LL") protocol: every rank stores its [2C] vector into every
+ * peer's receive area as 8-byte {value, epoch} words and polls only its own memory -- one one-way NVLink trip.
+ * recv_off: heap offset (same on every rank) of a zero-initialised area of PMD_LL_RECV_BYTES(world, n) bytes that
+ * belongs to this exchange alone.
+ *
+ * In the training step no kernel is launched for these exchanges: the LAST thread block of the kernel that
+ * accumulated the vector performs them (csrc/sync_tail.cuh; conv epilogues forward, BatchNorm-backward reduction
+ * or the dgrad that carries it backward).  The two stand-alone single-block kernels below do the same work for a
+ * vector that some other producer left in memory (tests, PMD_SYNC_TAIL=0 A/B runs). */
 #define PMD_LL_RECV_BYTES(world, n) (2ull * (world) * (n) * 8ull)
 int pmd_bn_finalize_push(const PmdSym* sym, int slot, const float* d_stats, unsigned long long recv_off,
                          float count_per_rank, int C, const float* d_gamma, const float* d_beta, float* d_running_mean,
@@ -134,15 +130,11 @@ int pmd_bn_finalize_push(const PmdSym* sym, int slot, const float* d_stats, unsi
                          float* d_shift, float* d_mean, float* d_invstd, void* stream);
 int pmd_small_allreduce_push(const PmdSym* sym, int slot, const float* d_local, int n, unsigned long long recv_off,
                              float* d_total, void* stream);
-/* BatchNorm kernels with the SyncBatchNorm exchange INSIDE (bn.cu; structs in pmdist.h): no stand-alone exchange
- * launch sits between the producer of the partial sums and their consumer any more.  sym may be NULL (or describe
- * one rank): then these are the plain single-GPU fused kernels. */
-int pmd_bn_finalize_apply(const PmdSym* sym, const PmdBnFinalize* f, const PmdBnFinalize* f_res, float count_per_rank,
-                          float momentum, float eps, const void* d_y, const void* d_res, int relu, void* d_z,
-                          long long rows, int C, void* stream);
-int pmd_bn_bwd_apply_multi_sync(const PmdSym* sym, const void* d_dz, const void* d_z, const float* d_mask_scale,
-                                const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
-                                float count_total, void* d_g_out, long long rows, int C, void* stream);
+/* pmd_bn_bwd_reduce_multi whose last thread block also completes the exchange of every branch's `sums`
+ * (br[i].recv_off / slot / totals_out; a projection block's two vectors leave in one trip). */
+int pmd_bn_bwd_reduce_multi_sync(const PmdSym* sym, const void* d_dz, const void* d_z, const float* d_mask_scale,
+                                 const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb, long long rows,
+                                 int C, void* stream);
 /* metrics: double[4] at heap offset `off` on every rank -> d_total (local) = sum over ranks. */
 int pmd_metric_allreduce(const PmdSym* sym, int slot, unsigned long long off, double* d_total, void* stream);
 

@@ -80,6 +80,12 @@ int pmd_engine_train_step(PmdEngine* e, int n, float lr, void* stream);
 int pmd_engine_eval_step(PmdEngine* e, int n, void* stream);
 /* Copies the (optionally cross-rank reduced) metric accumulators to the host and optionally clears them. */
 int pmd_engine_read_metrics(PmdEngine* e, int reduce_over_ranks, int reset, double* out4, void* stream);
+/* Measurement switch for "exposed communication" (BASELINE.json metric): with bit 0 set the
+ * SyncBatchNorm statistics stay rank-local, with bit 1 set every gradient bucket is reduced over this rank alone --
+ * i.e. the step runs the kernels of a 1-GPU run while the other ranks do the same next to it.  step time with
+ * mask 0 minus step time with mask 3 = communication (and rank skew) the step could not hide.  Ranks diverge while a
+ * stub is active: use it at the end of a benchmark only.  Drops the cached plans / graphs (next step re-captures). */
+int pmd_engine_set_comm_stub(PmdEngine* e, int mask);
 /* kernels launched by one train step of batch n (graph nodes count the same as direct launches) */
 int pmd_engine_launches_per_step(PmdEngine* e, int n);
 

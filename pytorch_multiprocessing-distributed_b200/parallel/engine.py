@@ -277,6 +277,13 @@ class NativeEngine:
             self._metric_dev.zero_()
         return MetricsFuture(slot, ev)
 
+    def set_comm_stub(self, mask: int) -> None:
+        """Measurement switch (collective: every rank must make the same call): bit 0 keeps the SyncBatchNorm
+        statistics rank-local, bit 1 reduces gradient buckets over this rank alone -- the step then runs the kernels
+        of a 1-GPU run.  ``step_ms(mask 0) - step_ms(mask 3)`` is the communication the step could not hide
+        ("exposed comm ms/step", BASELINE.json).  Ranks diverge while a stub is active."""
+        check(self.lib.pmd_engine_set_comm_stub(self._h, C.c_int(int(mask))))
+
     def launches_per_step(self, n: Optional[int] = None) -> int:
         return int(self.lib.pmd_engine_launches_per_step(self._h, C.c_int(n or self.max_batch)))
 

@@ -593,7 +593,7 @@ def _bn_multi():
     class Br(C.Structure):
         _fields_ = [('y', C.c_void_p), ('mean', C.c_void_p), ('invstd', C.c_void_p), ('gamma', C.c_void_p),
                     ('sums', C.c_void_p), ('totals', C.c_void_p), ('dy', C.c_void_p), ('dgamma', C.c_void_p),
-                    ('dbeta', C.c_void_p), ('recv_off', C.c_ulonglong), ('totals_scratch', C.c_void_p),
+                    ('dbeta', C.c_void_p), ('recv_off', C.c_ulonglong), ('totals_out', C.c_void_p),
                     ('slot', C.c_int), ('pad_', C.c_int)]
     lib = _lib.lib()
     Cc, N, H = 128, 8, 8
@@ -655,8 +655,7 @@ def _bn_fused_fwd():
     class Fin(C.Structure):
         _fields_ = [('stats', C.c_void_p), ('gamma', C.c_void_p), ('beta', C.c_void_p), ('running_mean', C.c_void_p),
                     ('running_var', C.c_void_p), ('num_batches', C.c_void_p), ('scale', C.c_void_p), ('shift', C.c_void_p),
-                    ('mean', C.c_void_p), ('invstd', C.c_void_p), ('totals_scratch', C.c_void_p),
-                    ('recv_off', C.c_ulonglong), ('slot', C.c_int), ('pad_', C.c_int)]
+                    ('mean', C.c_void_p), ('invstd', C.c_void_p)]
     lib = _lib.lib()
     Cc, N, H = 128, 8, 8
     rows = N * H * H
@@ -679,14 +678,14 @@ def _bn_fused_fwd():
     for i in range(2):
         fs.append(Fin(stats[i].data_ptr(), gam[i].data_ptr(), bet[i].data_ptr(), rmB[i].data_ptr(), rvB[i].data_ptr(),
                       nbB[i].data_ptr(), outs[i][0].data_ptr(), outs[i][1].data_ptr(), outs[i][2].data_ptr(),
-                      outs[i][3].data_ptr(), 0, 0, 0, 0))
+                      outs[i][3].data_ptr()))
     z = torch.empty_like(ys[0])
-    check(lib.pmd_bn_finalize_apply(None, C.byref(fs[0]), C.byref(fs[1]), C.c_float(rows), C.c_float(0.1), C.c_float(1e-5),
+    check(lib.pmd_bn_finalize_apply(C.byref(fs[0]), C.byref(fs[1]), C.c_float(rows), C.c_float(0.1), C.c_float(1e-5),
                                     ptr(ys[0]), ptr(ys[1]), C.c_int(1), ptr(z), C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
     z1 = torch.empty_like(ys[0])          # single BatchNorm, plain residual
     f_single = Fin(stats[0].data_ptr(), gam[0].data_ptr(), bet[0].data_ptr(), 0, 0, 0, outs[0][0].data_ptr(),
-                   outs[0][1].data_ptr(), outs[0][2].data_ptr(), outs[0][3].data_ptr(), 0, 0, 0, 0)
-    check(lib.pmd_bn_finalize_apply(None, C.byref(f_single), None, C.c_float(rows), C.c_float(0.1), C.c_float(1e-5),
+                   outs[0][1].data_ptr(), outs[0][2].data_ptr(), outs[0][3].data_ptr())
+    check(lib.pmd_bn_finalize_apply(C.byref(f_single), None, C.c_float(rows), C.c_float(0.1), C.c_float(1e-5),
                                     ptr(ys[0]), ptr(ys[1]), C.c_int(1), ptr(z1), C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
     torch.cuda.synchronize()
     z1_ref = nk.bn_apply(ys[0], fin[0][0], fin[0][1], True, ys[1])
