@@ -89,7 +89,7 @@ class ClockSampler:
 # ----------------------------------------------------------------------------- own arm
 def run_native(a) -> None:
     import torch
-    from pmdist.data.loader import BatchLoader
+    from pmdist.data.loader import BatchLoader, DeviceBatchLoader
     from pmdist.data.sampler import ShardSampler
     from pmdist.data.sources import synthetic_source
     from pmdist.models.resnet import MODEL_ALIASES, build_resnet, resnet_spec
@@ -114,7 +114,13 @@ def run_native(a) -> None:
     eng = NativeEngine(model, comm, SGDConfig(), device, B, a.image_size, sync_bn=True, use_graph=not a.no_graph,
                        bucket_mb=a.bucket_mb, algo=a.algo)
     src = synthetic_source(B * 8, a.image_size, seed=rank).pin()
-    loader = BatchLoader(src, ShardSampler(len(src), 1, 0, True, rank), B, True, seed=rank, pin=True)
+    if a.host_dataset:
+        loader = BatchLoader(src, ShardSampler(len(src), 1, 0, True, rank), B, True, seed=rank, pin=True)
+    else:
+        # the framework's default data path: the dataset is uploaded to GPU memory once; per step the host copies
+        # the batch's header + index vector from pinned memory, gather + crop/flip (Philox) + normalise run in-kernel
+        loader = DeviceBatchLoader(src, ShardSampler(len(src), 1, 0, True, rank), B, True, seed=rank)
+        eng.attach_dataset(src)
     lr = 0.1
 
     def batches():
@@ -175,7 +181,7 @@ def run_native(a) -> None:
     # the 63 us PCIe transfer they hide: 1.81 vs 1.69 ms/step.)
     # With PMD_BENCH_ASYNC_METRICS=1 the read of step i's metrics is enqueued right behind step i but consumed on
     # the host after step i+1 has been launched (NativeEngine.read_metrics_async), so the launch leaves the critical path.
-    async_metrics = os.environ.get('PMD_BENCH_ASYNC_METRICS', '0') != '0'
+    async_metrics = os.environ.get('PMD_BENCH_ASYNC_METRICS', '1') != '0'
     nxt = next(it)
     fut = None
     t0 = time.perf_counter()
@@ -236,8 +242,12 @@ def run_native(a) -> None:
             'clocks': clk.summary(),
             'e2e': {'value': round(gb * a.steps / (e2e_max / 1e3), 1), 'unit': 'images/s',
                     'ms_per_step': round(e2e_max / a.steps, 4),
-                    'h2d_bytes_per_step': eng.h2d_bytes(B), 'd2h_bytes_per_step': 32,
-                    'path': 'BatchLoader(pinned) -> NativeEngine.train_step -> read_metrics'},
+                    'h2d_bytes_per_step': eng.h2d_bytes(B, resident=not a.host_dataset), 'd2h_bytes_per_step': 32,
+                    'path': ('BatchLoader(pinned uint8 batch) -> NativeEngine.train_step -> read_metrics' if a.host_dataset else
+                             'DeviceBatchLoader(pinned header + index vector; dataset resident in HBM, in-kernel gather + '
+                             'Philox crop/flip) -> NativeEngine.train_step -> read_metrics') +
+                            (' (every step\'s metrics copied D2H into a pinned slot behind the step, consumed on the host one step '
+                             'later: read_metrics_async)' if async_metrics else '')},
             'exposed_comm_ms': (round((dev_max - stub_max['no_comm']) / a.steps, 4) if stub_max else
                                 (0.0 if world == 1 else None)),
             'exposed_comm': ({'ms_per_step_full': round(dev_max / a.steps, 4),
@@ -335,6 +345,7 @@ def main() -> None:
     ap.add_argument('--algo', default='auto')
     ap.add_argument('--bucket-mb', type=float, default=0.0)
     ap.add_argument('--no-graph', action='store_true')
+    ap.add_argument('--host-dataset', action='store_true', help='e2e: copy every uint8 batch from pinned host memory')
     ap.add_argument('--no-exposed-comm', action='store_true', help='skip the collectives-stubbed timing runs')
     a = ap.parse_args()
     if a.impl == 'reference':

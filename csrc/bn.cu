@@ -7,7 +7,7 @@
 // tables so that one code path serves 1..8 ranks and rank-order-fixed summation keeps every rank
 // bitwise identical.
 #include "common.cuh"
-#include "sync_tail.cuh"
+#include "bn_math.cuh"
 #include "../include/pmdist.h"
 
 namespace pmd {
@@ -205,8 +205,8 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float
 // apply kernel derives scale/shift from the [sum, sumsq] vector itself (2C loads, C rsqrt -- noise next to the
 // activation traffic), and block 0 also stores what backward and the checkpoint need (mean, invstd, scale, shift,
 // running statistics, num_batches_tracked).  With RES == 2 the projection shortcut's BatchNorm is finalised here
-// too.  Single-rank statistics only: under multi-rank SyncBatchNorm the producer's last CTA has already exchanged
-// and finalised them (sync_tail.cuh) and the plain bn_apply_kernel runs instead.
+// too.  Single-rank statistics only: under multi-rank SyncBatchNorm the push-exchange kernel (comm.cu) finalises them
+// and the plain bn_apply_kernel runs instead.
 struct BnFinalizeDev {
   const float* stats;
   const float* gamma;
@@ -318,15 +318,11 @@ struct BnBranchDev {
   float* dbeta;
 };
 
-struct BnReduceTails {    // multi-rank SyncBatchNorm: the exchange(s) the last block of the reduction completes
-  SyncTail t[2];
-};
-
 template <int NB, int MASK>
 __global__ void __launch_bounds__(kBlock, 4)
 bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ z,
                            const float* __restrict__ mscale, const float* __restrict__ mshift, BnBranchDev b0,
-                           BnBranchDev b1, long long rows, int C, const __grid_constant__ BnReduceTails tails) {
+                           BnBranchDev b1, long long rows, int C) {
   // Accumulates S_g = sum(g) and S_gy = sum(g*y) per channel; sum(g*xhat) = (S_gy - mean*S_g)*invstd is formed
   // once per block at the end, so the streaming loop carries no per-channel statistics in registers (the
   // register budget decides how many of these DRAM-bound blocks fit on an SM).
@@ -415,10 +411,6 @@ bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bflo
       red_add_f32(b1.sums + c, tg);
       red_add_f32(b1.sums + C + c, (t1 - b1.mean[c] * tg) * b1.invstd[c]);
     }
-  }
-  if (tails.t[0].mode != 0) {
-    __syncthreads();       // the block-reduction scratch is free again: (1 + NB) * rpi * C >= NB * 2C floats
-    sync_tail_run(tails.t[0], b0.sums, NB == 2 ? &tails.t[1] : nullptr, b1.sums, scratch, gridDim.x);
   }
 }
 
@@ -619,22 +611,21 @@ static BnBranchDev to_dev(const PmdBnBranch& b) {
 
 template <int NB>
 static cudaError_t launch_reduce(int mask, int smem, cudaStream_t st, const __nv_bfloat16* dz, const __nv_bfloat16* z,
-                                 const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, long long rows, int C,
-                                 const BnReduceTails& tails) {
+                                 const float* ms, const float* mh, BnBranchDev b0, BnBranchDev b1, long long rows, int C) {
   const int rpi8 = (kBlock / (C / 8) > 0 ? kBlock / (C / 8) : 1) * 8;
 #define PMD_RED(M)                                                                                                  \
   return launch_pdl(bn_bwd_reduce_multi_kernel<NB, M>,                                                              \
                     dim3(wave_grid(bn_bwd_reduce_multi_kernel<NB, M>, kBlock, smem, rows, rpi8)), dim3(kBlock), smem, \
-                    st, dz, z, ms, mh, b0, b1, rows, C, tails)
+                    st, dz, z, ms, mh, b0, b1, rows, C)
   if (mask == 0) PMD_RED(0);
   if (mask == 1) PMD_RED(1);
   PMD_RED(2);
 #undef PMD_RED
 }
 
-static int bn_bwd_reduce_impl(const PmdSym* sym, const void* d_dz, const void* d_z, const float* d_mask_scale,
-                              const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb, long long rows,
-                              int C, void* stream) {
+extern "C" PMD_API int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
+                                               const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
+                                               long long rows, int C, void* stream) {
   BN_CHECK_C(C);
   PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
   PMD_REQUIRE(mask_mode >= 0 && mask_mode <= 2, "mask mode must be 0, 1 or 2");
@@ -642,45 +633,18 @@ static int bn_bwd_reduce_impl(const PmdSym* sym, const void* d_dz, const void* d
   PMD_REQUIRE(mask_mode != 2 || (d_mask_scale != nullptr && d_mask_shift != nullptr), "mask mode 2 needs the forward affine");
   const int groups = C / 8, rpi = kBlock / groups > 0 ? kBlock / groups : 1;
   PMD_REQUIRE(groups <= kBlock, "C too large for bn_bwd_reduce");
-  BnReduceTails tails{};
-  int scratch_floats = (1 + nb) * rpi * C;
-  if (sym != nullptr && sym->world > 1) {
-    for (int i = 0; i < nb; ++i) {
-      PMD_REQUIRE(br[i].totals_out != nullptr, "the exchanging reduction needs totals_out for every branch");
-      SyncTail& t = tails.t[i];
-      t.mode = 2;
-      t.slot = br[i].slot;
-      t.sym = *sym;
-      t.recv_off = br[i].recv_off;
-      t.C = C;
-      t.totals = br[i].totals_out;
-    }
-    if (scratch_floats < nb * 2 * C) scratch_floats = nb * 2 * C;
-  }
-  const int smem = (2 * C + scratch_floats) * 4;
+  const int smem = (2 * C + (1 + nb) * rpi * C) * 4;
   const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const __nv_bfloat16* dz = static_cast<const __nv_bfloat16*>(d_dz);
   const __nv_bfloat16* z = static_cast<const __nv_bfloat16*>(d_z);
   if (nb == 1)
-    PMD_CHECK_CUDA(launch_reduce<1>(mask_mode, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C, tails));
+    PMD_CHECK_CUDA(launch_reduce<1>(mask_mode, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C));
   else
-    PMD_CHECK_CUDA(launch_reduce<2>(mask_mode, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C, tails));
+    PMD_CHECK_CUDA(launch_reduce<2>(mask_mode, smem, st, dz, z, d_mask_scale, d_mask_shift, b0, b1, rows, C));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
-}
-
-extern "C" PMD_API int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale,
-                                               const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb,
-                                               long long rows, int C, void* stream) {
-  return bn_bwd_reduce_impl(nullptr, d_dz, d_z, d_mask_scale, d_mask_shift, mask_mode, br, nb, rows, C, stream);
-}
-
-extern "C" PMD_API int pmd_bn_bwd_reduce_multi_sync(const PmdSym* sym, const void* d_dz, const void* d_z,
-                                                    const float* d_mask_scale, const float* d_mask_shift, int mask_mode,
-                                                    const PmdBnBranch* br, int nb, long long rows, int C, void* stream) {
-  return bn_bwd_reduce_impl(sym, d_dz, d_z, d_mask_scale, d_mask_shift, mask_mode, br, nb, rows, C, stream);
 }
 
 template <int NB>

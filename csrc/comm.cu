@@ -10,7 +10,8 @@
 // always in rank order 0..W-1, so all ranks compute bitwise-identical results.
 #include "common.cuh"
 #include "sgd_math.cuh"
-#include "sync_tail.cuh"
+#include "bn_math.cuh"
+#include "sym.cuh"
 
 namespace pmd {
 namespace {
@@ -169,12 +170,28 @@ __global__ void bn_finalize_push_kernel(PmdSym s, int slot, const float* __restr
                         save_mean, save_invstd);
 }
 
-__global__ void small_allreduce_push_kernel(PmdSym s, int slot, const float* __restrict__ local, int n,
-                                            unsigned long long recv_off, float* total) {
-  extern __shared__ float tot[];
+// One or two vectors exchanged by ONE block: both are pushed before either is awaited, so a projection block's pair
+// of BatchNorm-backward sums costs one NVLink trip.
+struct SmallExchangeDev {
+  const float* local;
+  float* total;
+  unsigned long long recv_off;
+  int n, slot;
+};
+__global__ void small_allreduce_push_kernel(PmdSym s, SmallExchangeDev x0, SmallExchangeDev x1, int nvec) {
+  extern __shared__ float tot[];     // [x0.n + x1.n]
+  __shared__ uint32_t ep_s[2];
   pdl_wait();
-  ll_exchange_sum(s, slot, local, n, recv_off, tot);
-  for (int i = threadIdx.x; i < n; i += blockDim.x) total[i] = tot[i];
+  const uint32_t e0 = ll_next_epoch(s, x0.slot, &ep_s[0]);
+  const uint32_t e1 = nvec > 1 ? ll_next_epoch(s, x1.slot, &ep_s[1]) : 0u;
+  ll_push(s, x0.local, x0.n, x0.recv_off, e0);
+  if (nvec > 1) ll_push(s, x1.local, x1.n, x1.recv_off, e1);
+  ll_poll_sum(s, x0.slot, x0.local, x0.n, x0.recv_off, e0, tot);
+  if (nvec > 1) ll_poll_sum(s, x1.slot, x1.local, x1.n, x1.recv_off, e1, tot + x0.n);
+  __syncthreads();
+  for (int i = threadIdx.x; i < x0.n; i += blockDim.x) x0.total[i] = tot[i];
+  if (nvec > 1)
+    for (int i = threadIdx.x; i < x1.n; i += blockDim.x) x1.total[i] = tot[x0.n + i];
 }
 
 __global__ void metric_allreduce_kernel(PmdSym s, int slot, unsigned long long off, double* total) {
@@ -295,12 +312,22 @@ extern "C" PMD_API int pmd_bn_finalize_push(const PmdSym* sym, int slot, const f
   return 0;
 }
 
-extern "C" PMD_API int pmd_small_allreduce_push(const PmdSym* sym, int slot, const float* d_local, int n,
-                                                unsigned long long recv_off, float* d_total, void* stream) {
+extern "C" PMD_API int pmd_small_allreduce_push(const PmdSym* sym, const PmdSmallExchange* x, int nvec, void* stream) {
   SYM_CHECK(sym);
-  PMD_REQUIRE(n * 4 <= 48 * 1024, "vector too long for the push exchange");
-  PMD_CHECK_CUDA(launch_pdl(small_allreduce_push_kernel, dim3(1), dim3(512), n * 4, static_cast<cudaStream_t>(stream), *sym,
-                            slot, d_local, n, recv_off, d_total));
+  PMD_REQUIRE(nvec == 1 || nvec == 2, "one or two vectors per exchange kernel");
+  SmallExchangeDev d[2] = {};
+  int total = 0;
+  for (int i = 0; i < nvec; ++i) {
+    d[i].local = x[i].local;
+    d[i].total = x[i].total;
+    d[i].recv_off = x[i].recv_off;
+    d[i].n = x[i].n;
+    d[i].slot = x[i].slot;
+    total += x[i].n;
+  }
+  PMD_REQUIRE(total * 4 <= 48 * 1024, "vectors too long for the push exchange");
+  PMD_CHECK_CUDA(launch_pdl(small_allreduce_push_kernel, dim3(1), dim3(512), total * 4, static_cast<cudaStream_t>(stream), *sym,
+                            d[0], d[1], nvec));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

@@ -332,11 +332,6 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
   __syncthreads();
   if (threadIdx.x == 0) trace_mark(p, kTrExit);
   if (warp == 1) tmem_dealloc<BN>(tmem_base);
-  // multi-rank SyncBatchNorm: the last CTA of the grid exchanges the finished vector with the peers (sync_tail.cuh);
-  // the pipeline buffers are idle by now (every TMA store has been read), so they serve as scratch
-  if (p.tail.mode != 0)
-    sync_tail_run(p.tail, RED ? p.red_sums : p.stats, nullptr, nullptr, reinterpret_cast<float*>(smem),
-                  gridDim.x * gridDim.y * gridDim.z);
 }
 
 constexpr int kColPatchBytes = 8 * 18 * 128;      // 18432: one 8 x 18-pixel column patch (64 channels)
@@ -612,8 +607,6 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
   __syncthreads();
   if (threadIdx.x == 0 && tracing) trec[kRtExit] = clock64();
   if (warp == 1) tmem_dealloc<128>(tmem_base);
-  if (p.tail.mode != 0)
-    sync_tail_run(p.tail, p.stats, nullptr, nullptr, reinterpret_cast<float*>(smem_out), gridDim.x);
 }
 
 // ============================================================================ wgrad

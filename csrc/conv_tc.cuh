@@ -3,7 +3,6 @@
 #pragma once
 
 #include "common.cuh"
-#include "sync_tail.cuh"
 #include "../include/pmdist.h"
 
 namespace pmd {
@@ -50,9 +49,6 @@ struct ConvGemmParams {
   const float *red_scale, *red_shift;    // forward affine (mask = scale*y + shift > 0)
   const float *red_mean, *red_invstd;
   float* red_sums;                       // [2 * out_channels], accumulated with red.global.add
-  // multi-rank SyncBatchNorm: the grid's last CTA (by arrival) completes the cross-GPU exchange of the vector this
-  // kernel accumulated (`stats` in fprop, `red_sums` in a RED dgrad) -- see sym.cuh.  tail.mode == 0: nothing.
-  SyncTail tail;
 };
 
 // Per-CTA trace record written by the fprop/dgrad kernels when tracing is on (tools/conv_trace.py decodes it).
@@ -116,7 +112,6 @@ struct ConvResidentParams {
   const __nv_bfloat16* addend;
   long long* trace;    // optional [trace_cap][kTraceSlots] per-CTA record (kRt* slots), else null
   int trace_cap;
-  SyncTail tail;       // optional: the grid's last CTA completes the SyncBatchNorm exchange of `stats`
 };
 // Trace record of conv3x3_resident_kernel: total cycles each role spent WAITING over all tiles of the CTA.
 enum {

@@ -1,13 +1,58 @@
 // Input pipeline on the GPU: zero-pad random crop + horizontal flip + ToTensor + Normalize(0.5, 0.5),
 // uint8 NHWC RGB -> NHWC bf16 with the channel dim padded to `c_out`.  Replaces the PIL/torchvision
 // transforms that run in 8 DataLoader worker processes per rank in the reference
-// (ref:data.py:11-19, 41-53).  Crop/flip parameters are drawn on the host
-// (pmdist/data/loader.py) so this kernel is bit-comparable with the CPU path.
+// (ref:data.py:11-19, 41-53).  Two sources of a batch: (a) uint8 images + crop/flip parameters staged
+// from the host (pmdist/data/loader.py), (b) a dataset that lives in device memory, gathered by an index vector
+// with crop/flip drawn in the kernel from Philox(seed, epoch, dataset index).  The host can reproduce (b)'s draws
+// (pmdist/data/philox.py), so both forms are bit-comparable with the CPU path.
 #include "common.cuh"
 #include "../include/pmdist.h"
 
 namespace pmd {
 namespace {
+
+// Philox4x32-10 (Salmon et al., SC'11): counter-based, so the crop/flip of a sample is a pure function of
+// (seed, epoch, dataset index) -- no generator state, identical on the device and in the host oracle
+// (pmdist/data/philox.py), and independent of the rank that happens to own the sample this epoch.
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+
+// Device-resident dataset: which stored image, and which crop / flip, sample n of the batch uses.
+// hdr = {seed, stream, epoch, train}; idx[n] = dataset index, or ~index for a sampler wrap-around duplicate that
+// must not count in the evaluation metrics.
+struct GatherSrc {
+  const int* hdr;
+  const int* idx;
+  const unsigned long long* ds;   // device-resident descriptor {images address, labels address}: read at run time, so
+                                  // switching between resident datasets (train / test) needs no new CUDA graph
+  long long* labels_out;       // [N] labels of this batch (read by the loss kernel)
+  unsigned char* valid_out;    // [N]
+};
+__device__ __forceinline__ void gather_params(const GatherSrc& g, int n, int pad, int* src, int* ox, int* oy, int* fl) {
+  const int raw = g.idx[n];
+  const int id = raw < 0 ? ~raw : raw;
+  *src = id;
+  if (g.hdr[3] != 0) {
+    const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(id), static_cast<uint32_t>(g.hdr[2]), 0u, 0u),
+                                  make_uint2(static_cast<uint32_t>(g.hdr[0]), static_cast<uint32_t>(g.hdr[1])));
+    *ox = static_cast<int>(r.x % static_cast<uint32_t>(2 * pad + 1));
+    *oy = static_cast<int>(r.y % static_cast<uint32_t>(2 * pad + 1));
+    *fl = static_cast<int>(r.z & 1u);
+  } else {
+    *ox = pad;
+    *oy = pad;
+    *fl = 0;
+  }
+}
 
 __global__ void augment_kernel(const unsigned char* __restrict__ u8, const int* __restrict__ aug, int N, int H, int W,
                                int pad, int c_out, __nv_bfloat16* __restrict__ out) {
@@ -40,16 +85,29 @@ __global__ void augment_kernel(const unsigned char* __restrict__ u8, const int* 
 // a 64-wide 1x1 convolution the tcgen05 path handles, and so is its weight gradient.  Positions outside
 // the image are the convolution's zero padding (0), positions inside the image but outside the crop are
 // torchvision's pre-normalisation zero pad (-1 after Normalize).
-__global__ void augment_im2col_kernel(const unsigned char* __restrict__ u8, const int* __restrict__ aug, int N, int H,
-                                      int W, int pad, __nv_bfloat16* __restrict__ out) {
+template <bool GATHER>
+__global__ void augment_im2col_kernel(const unsigned char* __restrict__ u8, const int* __restrict__ aug, GatherSrc g, int N,
+                                      int H, int W, int pad, __nv_bfloat16* __restrict__ out) {
   const long long total = static_cast<long long>(N) * H * W;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int x = static_cast<int>(i % W);
     const int y = static_cast<int>((i / W) % H);
     const int n = static_cast<int>(i / (static_cast<long long>(W) * H));
-    const int ox = aug[n * 3], oy = aug[n * 3 + 1], fl = aug[n * 3 + 2];
-    const unsigned char* img = u8 + static_cast<long long>(n) * H * W * 3;
+    int ox, oy, fl, src = n;
+    if (GATHER) {
+      gather_params(g, n, pad, &src, &ox, &oy, &fl);
+      if (x == 0 && y == 0) {            // one thread per sample also hands label and validity to the loss kernel
+        g.labels_out[n] = reinterpret_cast<const long long*>(g.ds[1])[src];
+        g.valid_out[n] = g.idx[n] < 0 ? 0 : 1;
+      }
+    } else {
+      ox = aug[n * 3];
+      oy = aug[n * 3 + 1];
+      fl = aug[n * 3 + 2];
+    }
+    const unsigned char* img =
+        (GATHER ? reinterpret_cast<const unsigned char*>(g.ds[0]) : u8) + static_cast<long long>(src) * H * W * 3;
     float v[28];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
@@ -108,8 +166,24 @@ extern "C" PMD_API int pmd_augment_im2col(const unsigned char* d_u8, const int* 
   const long long total = static_cast<long long>(N) * H * W;
   long long blocks = ceil_div_ll(total, 128);
   if (blocks > 148 * 32) blocks = 148 * 32;
-  augment_im2col_kernel<<<static_cast<int>(blocks), 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      d_u8, d_aug, N, H, W, pad, static_cast<__nv_bfloat16*>(d_out));
+  augment_im2col_kernel<false><<<static_cast<int>(blocks), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      d_u8, d_aug, GatherSrc{}, N, H, W, pad, static_cast<__nv_bfloat16*>(d_out));
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_augment_im2col_gather(const unsigned long long* d_dataset_desc, const int* d_hdr,
+                                                 const int* d_idx, int N, int H, int W, int pad, void* d_out,
+                                                 long long* d_labels_out, unsigned char* d_valid_out, void* stream) {
+  PMD_REQUIRE(d_dataset_desc != nullptr && d_hdr != nullptr && d_idx != nullptr,
+              "dataset descriptor, header and index vector are required");
+  const long long total = static_cast<long long>(N) * H * W;
+  long long blocks = ceil_div_ll(total, 128);
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  const GatherSrc g{d_hdr, d_idx, d_dataset_desc, d_labels_out, d_valid_out};
+  augment_im2col_kernel<true><<<static_cast<int>(blocks), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      nullptr, nullptr, g, N, H, W, pad, static_cast<__nv_bfloat16*>(d_out));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

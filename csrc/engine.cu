@@ -65,7 +65,6 @@ struct ConvPlan {
   ConvGemmParams fprop, fprop_eval;
   ConvResidentParams fprop_r, fprop_eval_r;   // used instead when resident == true (3x3 stride-1, C = K = 64)
   bool resident = false;
-  bool fwd_tail = false;                      // the fprop kernel's last CTA completes the SyncBatchNorm exchange
   WgradParams wgrad;
 };
 
@@ -78,7 +77,6 @@ struct Plan {
   std::vector<ConvResidentParams> block_dgrad_r, inner_dgrad_r;
   std::vector<char> block_resident, inner_resident;
   std::vector<char> inner_reduced;          // inner dgrad also does the BatchNorm-backward reduction of the layer below
-  std::vector<char> inner_tail;             // ... and its last CTA completes that reduction's cross-GPU exchange
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_launches = 0, eval_launches = 0;
   bool train_warm = false, eval_warm = false;
@@ -114,6 +112,10 @@ struct PmdEngine {
   bf16* stem_w_pad = nullptr;         // [64][64] zero-padded stem weight
   unsigned char *in_u8 = nullptr, *in_valid = nullptr;
   int* in_aug = nullptr;
+  int* in_index = nullptr;            // [4 + max_batch]: Philox header + dataset indices (resident-dataset mode)
+  unsigned long long* d_ds = nullptr; // device {images address, labels address} of the active resident dataset
+  bool ds_on = false;
+  long long ds_count = 0;
   long long* in_labels = nullptr;
   float *feat = nullptr, *logits = nullptr, *dlogits = nullptr, *d_lr = nullptr;
   double* metrics_total = nullptr;
@@ -242,6 +244,8 @@ int allocate(PmdEngine* e) {
   E_CHECK(e->dalloc(&e->stem_w_pad, 64 * 64));
   E_CHECK(e->dalloc(&e->in_u8, 1LL * B * c.image_hw * c.image_hw * 3));
   E_CHECK(e->dalloc(&e->in_aug, 3LL * B));
+  E_CHECK(e->dalloc(&e->in_index, 4LL + B));
+  E_CHECK(e->dalloc(&e->d_ds, 2));
   E_CHECK(e->dalloc(&e->in_labels, B));
   E_CHECK(e->dalloc(&e->in_valid, B));
   E_CHECK(e->dalloc(&e->feat, 1LL * B * 512 * (c.bottleneck ? 4 : 1)));
@@ -320,60 +324,6 @@ int allocate(PmdEngine* e) {
 // Multi-rank SyncBatchNorm is in effect (and not stubbed out for a communication-free timing run).
 bool sync_bn_active(const PmdEngine* e) { return e->sym.world > 1 && e->cfg.sync_bn && (e->comm_stub & 1) == 0; }
 
-// Who completes a SyncBatchNorm exchange (PMD_SYNC_TAIL): the producer's last CTA (sync_tail.cuh) or a stand-alone
-// single-block kernel between producer and consumer.  The tail costs every CTA of the producer a __threadfence +
-// ticket at its very end (~0.7 us during which its shared memory stays occupied), so it pays for grids of about one
-// wave (persistent kernels, the BatchNorm reductions, the convolutions of the small maps) and loses on the 1024-4096
-// CTA grids of the large maps.  2 (default): tail when the producer's grid has at most `kTailMaxCtas` CTAs;
-// 1: always; 0: never (round-1 behaviour).
-constexpr int kTailMaxCtas = 2 * 148;
-int sync_tail_mode() {
-  static const int mode = getenv("PMD_SYNC_TAIL") == nullptr ? 0 : atoi(getenv("PMD_SYNC_TAIL"));
-  return mode;
-}
-bool sync_tail_enabled() { return sync_tail_mode() != 0; }
-bool sync_tail_for_grid(long long ctas) { return sync_tail_mode() == 1 || (sync_tail_mode() == 2 && ctas <= kTailMaxCtas); }
-long long gemm_ctas(const ConvGemmParams& p) {
-  return 1LL * p.tiles_w * p.tiles_h * p.tiles_n * (p.out_channels / p.bn_tile) * p.n_classes;
-}
-
-// Forward exchange of conv `ci`'s [sum, sumsq] + BatchNorm finalize, as done by the fprop kernel's last CTA.
-SyncTail forward_tail(PmdEngine* e, int ci, long long rows) {
-  Conv& cv = e->convs[ci];
-  SyncTail t{};
-  t.mode = 1;
-  t.slot = ci;
-  t.sym = e->sym;
-  t.recv_off = cv.recv_fwd_off;
-  t.C = cv.s.K;
-  t.count_per_rank = static_cast<float>(rows);
-  t.momentum = e->cfg.bn_momentum;
-  t.eps = e->cfg.bn_eps;
-  t.gamma = e->param + cv.g_off;
-  t.beta = e->param + cv.b_off;
-  t.running_mean = cv.rm;
-  t.running_var = cv.rv;
-  t.nbt = cv.nb;
-  t.scale = cv.scale;
-  t.shift = cv.shift;
-  t.mean = cv.mean;
-  t.invstd = cv.invstd;
-  return t;
-}
-
-// Backward exchange of conv `ci`'s [sum_g, sum_g*xhat] into sums_total.
-SyncTail backward_tail(PmdEngine* e, int ci) {
-  Conv& cv = e->convs[ci];
-  SyncTail t{};
-  t.mode = 2;
-  t.slot = static_cast<int>(e->convs.size()) + ci;
-  t.sym = e->sym;
-  t.recv_off = cv.recv_bwd_off;
-  t.C = cv.s.K;
-  t.totals = cv.sums_total;
-  return t;
-}
-
 Plan* get_plan(PmdEngine* e, int n) {
   auto it = e->plans.find(n);
   if (it != e->plans.end()) return it->second.get();
@@ -388,10 +338,8 @@ Plan* get_plan(PmdEngine* e, int n) {
   pl->block_resident.assign(e->blocks.size(), 0);
   pl->inner_resident.assign(e->convs.size(), 0);
   pl->inner_reduced.assign(e->convs.size(), 0);
-  pl->inner_tail.assign(e->convs.size(), 0);
   // C = K = 64 3x3 layers: weight-resident persistent kernel
   const bool resident_on = conv_resident_enabled(), resident_dgrad = conv_resident_dgrad_enabled();
-  const bool tails = sync_bn_active(e) && sync_tail_enabled();
   for (size_t i = 0; i < e->convs.size(); ++i) {
     Conv& cv = e->convs[i];
     if (!cv.tc) continue;
@@ -401,19 +349,11 @@ Plan* get_plan(PmdEngine* e, int n) {
     if (build_fprop_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop)) return nullptr;
     pl->conv[i].fprop_eval = pl->conv[i].fprop;
     pl->conv[i].fprop_eval.stats = nullptr;
-    const long long rows = 1LL * n * cv.Ho * cv.Wo;
-    bool tail_here = tails && sync_tail_for_grid(gemm_ctas(pl->conv[i].fprop));
     if (!cv.stem_col && resident_on && conv_resident_supported(s)) {
       if (build_fprop_resident_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop_r)) return nullptr;
       pl->conv[i].fprop_eval_r = pl->conv[i].fprop_r;
       pl->conv[i].fprop_eval_r.stats = nullptr;
-      tail_here = tails;       // persistent: one CTA per SM
-      if (tail_here) pl->conv[i].fprop_r.tail = forward_tail(e, static_cast<int>(i), rows);
       pl->conv[i].resident = true;
-    }
-    if (tail_here) {
-      pl->conv[i].fprop.tail = forward_tail(e, static_cast<int>(i), rows);
-      pl->conv[i].fwd_tail = true;
     }
     if (build_wgrad_params(s, cv.x, cv.dy, e->grad + cv.w_off, 0, e->sm_count, &pl->conv[i].wgrad,
                            cv.stem_col ? cv.real_rsc : 0, cv.stem_col ? cv.real_rsc : 64))
@@ -435,16 +375,11 @@ Plan* get_plan(PmdEngine* e, int n) {
         pl->inner_resident[b.main[j]] = 1;
       } else {
         // dz_mid[j-1] is consumed only by the BatchNorm backward of conv j-1: let the dgrad epilogue do its reduction
-        // (and, under multi-rank SyncBatchNorm, let its last CTA exchange the sums with the peers)
         const int prev = b.main[j - 1];
         Conv& pv = e->convs[prev];
         const int rc = attach_bn_reduce(&pl->inner_dgrad[b.main[j]], s, pv.y, pv.scale, pv.shift, pv.mean, pv.invstd, pv.sums);
         if (rc < 0) return nullptr;
         pl->inner_reduced[b.main[j]] = static_cast<char>(rc);
-        if (rc == 1 && tails && sync_tail_for_grid(gemm_ctas(pl->inner_dgrad[b.main[j]]))) {
-          pl->inner_dgrad[b.main[j]].tail = backward_tail(e, prev);
-          pl->inner_tail[b.main[j]] = 1;
-        }
       }
     }
     Conv& c0 = e->convs[b.main[0]];
@@ -541,40 +476,39 @@ PmdBnFinalize bn_desc(PmdEngine* e, int ci) {
   return f;
 }
 
+// Multi-rank SyncBatchNorm, forward: exchange conv `ci`'s [sum, sumsq] with the peers and finalise the statistics
+// (one single-block push-exchange kernel, launched right behind the convolution ON ITS STREAM -- a projection
+// shortcut's exchange therefore runs on the side stream, next to the main path's second convolution).
+int exchange_forward(PmdEngine* e, int ci, long long rows, cudaStream_t st) {
+  Conv& b = e->convs[ci];
+  const PmdEngineConfig& c = e->cfg;
+  return pmd_bn_finalize_push(&e->sym, ci, b.stats, b.recv_fwd_off, static_cast<float>(rows), b.s.K, e->param + b.g_off,
+                              e->param + b.b_off, b.rm, b.rv, b.nb, c.bn_momentum, c.bn_eps, b.scale, b.shift, b.mean,
+                              b.invstd, st);
+}
+
 // z = relu(BN_ci(y_ci) [+ res | + BN_cres(y_cres)]).  Training, one rank: the statistics are finalised inside the
-// apply kernel.  Training, multi-rank SyncBatchNorm: the convolution's last CTA has already exchanged and finalised
-// them (Plan::fwd_tail), so only the plain apply remains; a producer without that tail (non-tensor-core conv,
-// PMD_SYNC_TAIL=0) is followed by the stand-alone push-exchange kernel.  Evaluation uses the running statistics.
-int bn_apply_step(PmdEngine* e, Plan* pl, int ci, int cres, const bf16* res, bf16* z, long long rows, bool train,
-                  cudaStream_t st) {
+// apply kernel.  Training, multi-rank SyncBatchNorm: exchange_forward() has finalised them, only the plain apply
+// remains.  Evaluation uses the running statistics.
+int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long long rows, bool train, cudaStream_t st) {
   Conv& cv = e->convs[ci];
   const PmdEngineConfig& c = e->cfg;
-  if (train && sync_bn_active(e)) {
-    const int todo[2] = {ci, cres};
-    for (int k = 0; k < 2; ++k) {
-      if (todo[k] < 0 || pl->conv[todo[k]].fwd_tail) continue;
-      Conv& b = e->convs[todo[k]];
-      E_CHECK(pmd_bn_finalize_push(&e->sym, todo[k], b.stats, b.recv_fwd_off, static_cast<float>(rows), b.s.K,
-                                   e->param + b.g_off, e->param + b.b_off, b.rm, b.rv, b.nb, c.bn_momentum, c.bn_eps,
-                                   b.scale, b.shift, b.mean, b.invstd, st));
-    }
-    if (cres >= 0) {
-      Conv& cr = e->convs[cres];
-      return pmd_bn_apply(cv.y, cv.scale, cv.shift, cr.y, cr.scale, cr.shift, 1, z, rows, cv.s.K, st);
-    }
-    return pmd_bn_apply(cv.y, cv.scale, cv.shift, res, nullptr, nullptr, 1, z, rows, cv.s.K, st);
-  }
-  if (train) {
+  if (train && !sync_bn_active(e)) {
     const PmdBnFinalize f = bn_desc(e, ci);
     PmdBnFinalize fr{};
     if (cres >= 0) fr = bn_desc(e, cres);
     return pmd_bn_finalize_apply(&f, cres >= 0 ? &fr : nullptr, static_cast<float>(rows), c.bn_momentum, c.bn_eps, cv.y,
                                  cres >= 0 ? e->convs[cres].y : res, 1, z, rows, cv.s.K, st);
   }
-  E_CHECK(pmd_bn_eval_affine(cv.s.K, e->param + cv.g_off, e->param + cv.b_off, cv.rm, cv.rv, c.bn_eps, cv.scale, cv.shift, st));
+  if (!train) {
+    E_CHECK(pmd_bn_eval_affine(cv.s.K, e->param + cv.g_off, e->param + cv.b_off, cv.rm, cv.rv, c.bn_eps, cv.scale, cv.shift, st));
+    if (cres >= 0) {
+      Conv& cr = e->convs[cres];
+      E_CHECK(pmd_bn_eval_affine(cr.s.K, e->param + cr.g_off, e->param + cr.b_off, cr.rm, cr.rv, c.bn_eps, cr.scale, cr.shift, st));
+    }
+  }
   if (cres >= 0) {
     Conv& cr = e->convs[cres];
-    E_CHECK(pmd_bn_eval_affine(cr.s.K, e->param + cr.g_off, e->param + cr.b_off, cr.rm, cr.rv, c.bn_eps, cr.scale, cr.shift, st));
     return pmd_bn_apply(cv.y, cv.scale, cv.shift, cr.y, cr.scale, cr.shift, 1, z, rows, cv.s.K, st);
   }
   return pmd_bn_apply(cv.y, cv.scale, cv.shift, res, nullptr, nullptr, 1, z, rows, cv.s.K, st);
@@ -583,10 +517,9 @@ int bn_apply_step(PmdEngine* e, Plan* pl, int ci, int cres, const bf16* res, bf1
 // BatchNorm backward of conv `ci` (and, for a projection block's output, of the shortcut conv `cj`
 // in the same two passes).  dz = gradient wrt the activation that followed; the ReLU mask comes from z
 // (block outputs, where a residual was added before the ReLU) or is recomputed from y (z == nullptr).
-// reduced: 0 = run the reduction here; 1 = the dgrad that produced dz accumulated the sums (and masked dz) in its
-// epilogue; 2 = ... and its last CTA also exchanged them across ranks.
+// already_reduced: the dgrad that produced dz accumulated the sums (and masked dz) in its epilogue.
 int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, long long rows, bf16* g_out,
-                cudaStream_t st, int reduced = 0) {
+                cudaStream_t st, bool already_reduced = false) {
   const bool sync = sync_bn_active(e);
   const int nb = cj >= 0 ? 2 : 1;
   PmdBnBranch br[2];
@@ -603,24 +536,22 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
     br[b].dy = cv.dy;
     br[b].dgamma = e->grad + cv.g_off;
     br[b].dbeta = e->grad + cv.b_off;
-    br[b].recv_off = cv.recv_bwd_off;
-    br[b].totals_out = cv.sums_total;
-    br[b].slot = static_cast<int>(e->convs.size()) + idx[b];
   }
   Conv& c0 = e->convs[ci];
   const int mask = z != nullptr ? 1 : 2;
-  const bool tail = sync && sync_tail_enabled();
-  if (reduced == 0) {
-    if (tail)   // the reduction's last block exchanges the sums (both branches of a projection block in one trip)
-      E_CHECK(pmd_bn_bwd_reduce_multi_sync(&e->sym, dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
-    else
-      E_CHECK(pmd_bn_bwd_reduce_multi(dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
-  }
-  if (sync && !(tail && reduced != 1)) {
+  if (!already_reduced) E_CHECK(pmd_bn_bwd_reduce_multi(dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
+  if (sync) {
+    // one push-exchange kernel; a projection block's two [2C] vectors leave in the same NVLink trip
+    PmdSmallExchange x[2];
     for (int b = 0; b < nb; ++b) {
       Conv& cv = e->convs[idx[b]];
-      E_CHECK(pmd_small_allreduce_push(&e->sym, br[b].slot, cv.sums, 2 * cv.s.K, cv.recv_bwd_off, cv.sums_total, st));
+      x[b].local = cv.sums;
+      x[b].n = 2 * cv.s.K;
+      x[b].recv_off = cv.recv_bwd_off;
+      x[b].total = cv.sums_total;
+      x[b].slot = static_cast<int>(e->convs.size()) + idx[b];
     }
+    E_CHECK(pmd_small_allreduce_push(&e->sym, x, nb, st));
   }
   const float count = static_cast<float>(rows) * (sync ? e->sym.world : 1);
   return pmd_bn_bwd_apply_multi(dz, z, c0.scale, c0.shift, mask, br, nb, count, g_out, rows, c0.s.K, st);
@@ -629,7 +560,11 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
 int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
   const PmdEngineConfig& c = e->cfg;
   const int n = pl->n;
-  E_CHECK(pmd_augment_im2col(e->in_u8, e->in_aug, n, c.image_hw, c.image_hw, 8, e->x0, st));
+  if (e->ds_on)
+    E_CHECK(pmd_augment_im2col_gather(e->d_ds, e->in_index, e->in_index + 4, n, c.image_hw, c.image_hw, 8, e->x0,
+                                      e->in_labels, e->in_valid, st));
+  else
+    E_CHECK(pmd_augment_im2col(e->in_u8, e->in_aug, n, c.image_hw, c.image_hw, 8, e->x0, st));
   auto conv_fwd = [&](int ci, cudaStream_t st) -> int {
     Conv& cv = e->convs[ci];
     if (cv.tc && pl->conv[ci].resident) {
@@ -642,12 +577,13 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
       E_CHECK(pmd_conv_fprop_direct(&s, cv.x_cstride, cv.x, e->wbf16 + cv.w_off, cv.y, st));
       if (train) E_CHECK(pmd_bn_stats(cv.y, 1LL * n * cv.Ho * cv.Wo, cv.s.K, cv.stats, st));
     }
+    if (train && sync_bn_active(e)) E_CHECK(exchange_forward(e, ci, 1LL * n * cv.Ho * cv.Wo, st));
     return 0;
   };
   E_CHECK(conv_fwd(0, st));
   {
     Conv& cv = e->convs[0];
-    E_CHECK(bn_apply_step(e, pl, 0, -1, nullptr, e->z_stem, 1LL * n * cv.Ho * cv.Wo, train, st));
+    E_CHECK(bn_apply_step(e, 0, -1, nullptr, e->z_stem, 1LL * n * cv.Ho * cv.Wo, train, st));
   }
   for (Block& b : e->blocks) {
     cudaEvent_t sc_done = nullptr;
@@ -664,12 +600,12 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
       E_CHECK(conv_fwd(b.main[j], st));
       if (j < b.n_main - 1) {
         Conv& cv = e->convs[b.main[j]];
-        E_CHECK(bn_apply_step(e, pl, b.main[j], -1, nullptr, b.z_mid[j], 1LL * n * cv.Ho * cv.Wo, train, st));
+        E_CHECK(bn_apply_step(e, b.main[j], -1, nullptr, b.z_mid[j], 1LL * n * cv.Ho * cv.Wo, train, st));
       }
     }
     if (sc_done != nullptr) PMD_CHECK_CUDA(cudaStreamWaitEvent(st, sc_done, 0));
     Conv& last = e->convs[b.main[b.n_main - 1]];
-    E_CHECK(bn_apply_step(e, pl, b.main[b.n_main - 1], b.sc, b.sc >= 0 ? nullptr : b.z_in, b.z_out,
+    E_CHECK(bn_apply_step(e, b.main[b.n_main - 1], b.sc, b.sc >= 0 ? nullptr : b.z_in, b.z_out,
                           1LL * n * last.Ho * last.Wo, train, st));
   }
   Block& lb = e->blocks.back();
@@ -748,7 +684,7 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
       E_CHECK(w_done(ci));
       Conv& pv = e->convs[prev];
       E_CHECK(bn_backward(e, prev, -1, b.dz_mid[j - 1], nullptr, 1LL * n * pv.Ho * pv.Wo, nullptr, st,
-                          pl->inner_reduced[ci] != 0 ? (pl->inner_tail[ci] ? 2 : 1) : 0));
+                          pl->inner_reduced[ci] != 0));
       E_CHECK(bn_done(prev));
     }
     E_CHECK(dy_ready());
@@ -914,6 +850,7 @@ extern "C" PMD_API int pmd_engine_buffers(PmdEngine* e, PmdEngineBuffers* o) {
   o->in_aug = reinterpret_cast<unsigned long long>(e->in_aug);
   o->in_labels = reinterpret_cast<unsigned long long>(e->in_labels);
   o->in_valid = reinterpret_cast<unsigned long long>(e->in_valid);
+  o->in_index = reinterpret_cast<unsigned long long>(e->in_index);
   o->logits = reinterpret_cast<unsigned long long>(e->logits);
   o->metrics = reinterpret_cast<unsigned long long>(e->metrics);
   o->slab_elems = e->cfg.slab_elems;
@@ -990,15 +927,37 @@ extern "C" PMD_API int pmd_engine_read_metrics(PmdEngine* e, int reduce_over_ran
   return 0;
 }
 
-extern "C" PMD_API int pmd_engine_set_comm_stub(PmdEngine* e, int mask) {
-  PMD_REQUIRE(mask >= 0 && mask <= 3, "comm stub mask: bit 0 = BatchNorm statistics local, bit 1 = gradients local");
-  if (mask == e->comm_stub) return 0;
+static int drop_plans(PmdEngine* e) {
   PMD_CHECK_CUDA(cudaDeviceSynchronize());
-  for (auto& kv : e->plans) {       // plans (tensor maps, exchange descriptors, captured graphs) depend on the setting
+  for (auto& kv : e->plans) {       // plans (tensor maps, captured graphs) bake in the pointers and switches
     if (kv.second->train_graph) cudaGraphExecDestroy(kv.second->train_graph);
     if (kv.second->eval_graph) cudaGraphExecDestroy(kv.second->eval_graph);
   }
   e->plans.clear();
+  return 0;
+}
+
+extern "C" PMD_API int pmd_engine_set_dataset(PmdEngine* e, const void* d_images_u8, const long long* d_labels,
+                                              long long count) {
+  PMD_REQUIRE(d_images_u8 == nullptr || (d_labels != nullptr && count > 0 && count < (1LL << 31)),
+              "a resident dataset needs labels and 0 < count < 2^31");
+  const bool on = d_images_u8 != nullptr;
+  if (on != e->ds_on) E_CHECK(drop_plans(e));    // the step's first kernel differs; WHICH dataset is read at run time
+  if (on) {
+    const unsigned long long desc[2] = {reinterpret_cast<unsigned long long>(d_images_u8),
+                                        reinterpret_cast<unsigned long long>(d_labels)};
+    // ordered behind the steps already enqueued on the engine's stream (pageable source: copied before returning)
+    PMD_CHECK_CUDA(cudaMemcpyAsync(e->d_ds, desc, sizeof(desc), cudaMemcpyHostToDevice, e->main_stream));
+  }
+  e->ds_on = on;
+  e->ds_count = on ? count : 0;
+  return 0;
+}
+
+extern "C" PMD_API int pmd_engine_set_comm_stub(PmdEngine* e, int mask) {
+  PMD_REQUIRE(mask >= 0 && mask <= 3, "comm stub mask: bit 0 = BatchNorm statistics local, bit 1 = gradients local");
+  if (mask == e->comm_stub) return 0;
+  E_CHECK(drop_plans(e));
   e->comm_stub = mask;
   return 0;
 }

@@ -58,11 +58,6 @@ __device__ __forceinline__ uint32_t* flag_ptr(const PmdSym& s, int heap_rank, in
 __device__ __forceinline__ uint32_t* epoch_ptr(const PmdSym& s, int slot) {
   return reinterpret_cast<uint32_t*>(s.d_bases[s.rank] + PMD_FLAGS_BYTES) + slot;
 }
-// arrival tickets of the kernels whose LAST CTA completes an exchange (sync_tail.cuh); local to the rank
-__device__ __forceinline__ uint32_t* ticket_ptr(const PmdSym& s, int slot) {
-  return reinterpret_cast<uint32_t*>(s.d_bases[s.rank] + PMD_FLAGS_BYTES) + PMD_MAX_SLOTS + slot;
-}
-
 template <typename T>
 __device__ __forceinline__ T* heap_ptr(const PmdSym& s, int w, unsigned long long off) {
   return reinterpret_cast<T*>(s.d_bases[w] + off);

@@ -135,11 +135,6 @@ typedef struct {
   void* dy;             /* apply only */
   float* dgamma;        /* apply only, may be NULL; += */
   float* dbeta;
-  /* pmd_bn_bwd_reduce_multi_sync only: the cross-GPU exchange that the reduction's last thread block completes */
-  unsigned long long recv_off; /* heap offset of a PMD_LL_RECV_BYTES(world, 2C) receive area */
-  float* totals_out;           /* local [2C]: receives the rank-ordered sum of every rank's `sums` */
-  int slot;                    /* signal-pad slot (epoch counter + arrival ticket) of this exchange */
-  int pad_;
 } PmdBnBranch;
 int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale, const float* d_mask_shift,
                             int mask_mode, const PmdBnBranch* br, int nb, long long rows, int C, void* stream);
@@ -151,8 +146,8 @@ int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z, const float* d_mas
  * z = act(BN(y) [+ res | + BN_res(res)]) with the batch statistics taken from `stats` ([sum, sumsq], as left by
  * pmd_conv_fprop); writes scale/shift/mean/invstd and updates the running statistics exactly like
  * pmd_bn_finalize.  f_res describes the projection shortcut's BatchNorm when the residual needs its own affine
- * (then d_res is that branch's conv output).  Single-rank statistics: under multi-rank SyncBatchNorm the kernel
- * that produced `stats` finishes the exchange itself (csrc/sync_tail.cuh) and pmd_bn_apply follows. */
+ * (then d_res is that branch's conv output).  Single-rank statistics: under multi-rank SyncBatchNorm
+ * pmd_bn_finalize_push (pmdist_comm.h) exchanges and finalises them and pmd_bn_apply follows. */
 typedef struct {
   const float* stats;           /* [2C] local sums */
   const float* gamma;
@@ -205,6 +200,17 @@ int pmd_augment(const unsigned char* d_u8, const int* d_aug, int N, int H, int W
  * convolutions on the tensor-core path; pmd_pad_stem_weight makes the matching [K][64] weight. */
 int pmd_augment_im2col(const unsigned char* d_u8, const int* d_aug, int N, int H, int W, int pad, void* d_out,
                        void* stream);
+/* The same kernel fed from a dataset that is RESIDENT in device memory (replaces the DataLoader workers, the pinned
+ * staging and the per-step image H2D of ref:data.py:41-53 / ref:main.py:101): sample n of the
+ * batch is stored image d_idx[n] of the dataset named by d_dataset_desc = device uint64 [2] {address of the uint8
+ * [M,H,W,3] images, address of the int64 [M] labels} (read when the kernel runs) (a negative entry ~i means "image i, but do not count it": the evaluation
+ * sampler's wrap-around duplicates), its label and validity are written to d_labels_out / d_valid_out for the
+ * loss kernel, and crop offsets / flip are drawn inside the kernel from Philox4x32-10 with key (hdr[0], hdr[1]) and
+ * counter (dataset index, hdr[2] = epoch, 0, 0): x = r0 % (2 pad + 1), y = r1 % (2 pad + 1), flip = r2 & 1
+ * (hdr[3] == 0: evaluation, centre crop, no flip).  pmdist/data/philox.py reproduces the draws on the host. */
+int pmd_augment_im2col_gather(const unsigned long long* d_dataset_desc, const int* d_hdr, const int* d_idx, int N, int H,
+                              int W, int pad, void* d_out, long long* d_labels_out, unsigned char* d_valid_out,
+                              void* stream);
 int pmd_pad_stem_weight(const void* d_w_k_rsc, void* d_w_padded_k64, int K, int rsc, void* stream);
 
 #ifdef __cplusplus

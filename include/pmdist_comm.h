@@ -114,27 +114,28 @@ int pmd_allreduce_f32(const PmdSym* sym, unsigned long long in_off, unsigned lon
 int pmd_broadcast(const PmdSym* sym, unsigned long long off, unsigned long long bytes, int src, int blocks, int slot,
                   void* stream);
 
-/* SyncBatchNorm exchanges.  Push ("LL") protocol: every rank stores its [2C] vector into every
+/* SyncBatchNorm exchanges (replace the all_gather / all_reduce of torch's SyncBatchNorm,
+ * torch/nn/modules/_functions.py:65-79, 155-165).  Push ("LL") protocol: every rank stores its vector into every
  * peer's receive area as 8-byte {value, epoch} words and polls only its own memory -- one one-way NVLink trip.
  * recv_off: heap offset (same on every rank) of a zero-initialised area of PMD_LL_RECV_BYTES(world, n) bytes that
- * belongs to this exchange alone.
- *
- * In the training step no kernel is launched for these exchanges: the LAST thread block of the kernel that
- * accumulated the vector performs them (csrc/sync_tail.cuh; conv epilogues forward, BatchNorm-backward reduction
- * or the dgrad that carries it backward).  The two stand-alone single-block kernels below do the same work for a
- * vector that some other producer left in memory (tests, PMD_SYNC_TAIL=0 A/B runs). */
+ * belongs to this exchange alone; `slot` names the exchange's device-resident epoch counter.  Single-block kernels,
+ * launched with programmatic stream serialization directly behind the kernel that accumulated the vector.
+ * (Letting that producer's last CTA do the exchange instead was built and measured slower:
+ * profiles/r2_syncbn_exchange_placement.md.) */
 #define PMD_LL_RECV_BYTES(world, n) (2ull * (world) * (n) * 8ull)
+/* forward: exchange [sum, sumsq], then finalize like pmd_bn_finalize over the rank-ordered totals */
 int pmd_bn_finalize_push(const PmdSym* sym, int slot, const float* d_stats, unsigned long long recv_off,
                          float count_per_rank, int C, const float* d_gamma, const float* d_beta, float* d_running_mean,
                          float* d_running_var, long long* d_num_batches, float momentum, float eps, float* d_scale,
                          float* d_shift, float* d_mean, float* d_invstd, void* stream);
-int pmd_small_allreduce_push(const PmdSym* sym, int slot, const float* d_local, int n, unsigned long long recv_off,
-                             float* d_total, void* stream);
-/* pmd_bn_bwd_reduce_multi whose last thread block also completes the exchange of every branch's `sums`
- * (br[i].recv_off / slot / totals_out; a projection block's two vectors leave in one trip). */
-int pmd_bn_bwd_reduce_multi_sync(const PmdSym* sym, const void* d_dz, const void* d_z, const float* d_mask_scale,
-                                 const float* d_mask_shift, int mask_mode, const PmdBnBranch* br, int nb, long long rows,
-                                 int C, void* stream);
+/* backward / generic: total[i] = sum over ranks (in rank order) of local[i]; one or two vectors per launch */
+typedef struct {
+  const float* local;          /* this rank's vector (any device pointer) */
+  float* total;                /* local output */
+  unsigned long long recv_off;
+  int n, slot;
+} PmdSmallExchange;
+int pmd_small_allreduce_push(const PmdSym* sym, const PmdSmallExchange* x, int nvec, void* stream);
 /* metrics: double[4] at heap offset `off` on every rank -> d_total (local) = sum over ranks. */
 int pmd_metric_allreduce(const PmdSym* sym, int slot, unsigned long long off, double* d_total, void* stream);
 

@@ -61,6 +61,7 @@ typedef struct {
 typedef struct {
   unsigned long long param, grad, mom, bf16; /* device addresses of the flat slabs (in the symmetric heap) */
   unsigned long long in_u8, in_aug, in_labels, in_valid; /* device staging of one step's inputs */
+  unsigned long long in_index; /* int32 [4 + max_batch]: {seed, stream, epoch, train} + dataset indices (resident mode) */
   unsigned long long logits;                 /* fp32 [max_batch, classes] of the last step */
   unsigned long long metrics;                /* double[4] running {loss sum, top1, top5, count} */
   long long slab_elems;
@@ -74,6 +75,13 @@ int pmd_engine_buffers(PmdEngine* e, PmdEngineBuffers* out);
 /* After the fp32 parameter slab was written from the host side (init, load_state_dict): optionally
  * broadcast rank 0's slab + BN buffers to all ranks (C2), then rebuild the bf16 / dgrad copies. */
 int pmd_engine_sync_params(PmdEngine* e, int broadcast_from_rank0, void* stream);
+/* Device-resident dataset: images uint8 [count, hw, hw, 3] and labels int64 [count] in device
+ * memory owned by the caller (must outlive the engine or a later call with NULL).  While attached, a step takes its
+ * batch from `in_index` (header + dataset indices, ~2 KB of H2D per step) instead of in_u8 / in_aug / in_labels:
+ * gather, crop/flip (in-kernel Philox), normalise and stem im2col run in one kernel (pmd_augment_im2col_gather).
+ * Passing d_images == NULL detaches.  Switching between resident datasets (train / test) is a 16-byte descriptor
+ * update on the engine's stream; only attaching / detaching re-captures the CUDA graphs. */
+int pmd_engine_set_dataset(PmdEngine* e, const void* d_images_u8, const long long* d_labels, long long count);
 /* One training step on the n <= max_batch samples currently in the staging buffers. */
 int pmd_engine_train_step(PmdEngine* e, int n, float lr, void* stream);
 /* Forward + loss/metrics only, BatchNorm in evaluation mode. */

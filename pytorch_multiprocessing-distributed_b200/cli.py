@@ -52,6 +52,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--device', default='auto', choices=['auto', 'cuda', 'cpu'])
     p.add_argument('--no-sync-bn', action='store_true', help='per-rank BatchNorm statistics')
     p.add_argument('--no-graph', action='store_true', help='native engine: do not capture CUDA graphs')
+    p.add_argument('--host-dataset', action='store_true',
+                   help='native engine: keep the dataset in pinned host memory and copy every batch (default: the '
+                        'dataset is uploaded once and lives in GPU memory; a step copies only its indices)')
     p.add_argument('--bucket-mb', default=0.0, type=float,
                    help='gradient bucket cap in MiB (0 = engine default; 25 reproduces torch DDP)')
     p.add_argument('--algo', default='auto', choices=['auto', 'oneshot', 'twoshot', 'nvls', 'nccl'],

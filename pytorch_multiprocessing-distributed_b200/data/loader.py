@@ -70,6 +70,75 @@ def augment_cpu(u8: torch.Tensor, aug: torch.Tensor, pad: int = CROP_PAD) -> tor
     return out.permute(0, 3, 1, 2).contiguous()
 
 
+@dataclass
+class IndexBatch:
+    """A batch of a DEVICE-RESIDENT dataset: only the indices travel (``packed`` = int32 [4 + B] in pinned memory:
+    {seed, stream, epoch, train} + dataset indices, ~i for an uncounted wrap-around duplicate).  Images and labels
+    are gathered, cropped / flipped (in-kernel Philox) and normalised on the GPU (csrc/data_aug.cu)."""
+    packed: torch.Tensor
+    n: int
+    train: bool
+    seed: int
+    epoch: int
+
+    @property
+    def indices(self) -> torch.Tensor:
+        raw = self.packed[4:4 + self.n]
+        return torch.where(raw < 0, ~raw, raw).long()
+
+    @property
+    def valid(self) -> torch.Tensor:
+        return self.packed[4:4 + self.n] >= 0
+
+    def to_host_batch(self, source: ImageSource) -> 'Batch':
+        """The same batch in host form with the crop/flip the kernel will draw (oracle / CPU path)."""
+        from .philox import aug_params
+        idx = self.indices
+        return Batch(source.images.index_select(0, idx), source.labels.index_select(0, idx), self.valid.clone(),
+                     aug_params(idx.numpy(), self.seed, self.epoch, self.train), self.train)
+
+
+class DeviceBatchLoader:
+    """Index-only iterator over a dataset that lives in GPU memory (``NativeEngine.attach_dataset``): replaces the
+    reference's worker processes + pin thread + blocking ``.cuda()`` (ref:data.py:41-53, ref:main.py:101).  Per
+    step the host writes B+4 int32 into a pinned slot; the sampler's shard for the epoch is the only host work."""
+
+    SLOTS = 4      # pinned slots in rotation: a slot is rewritten SLOTS steps after its H2D copy was enqueued
+
+    def __init__(self, source: ImageSource, sampler: ShardSampler, batch_size: int, train: bool, seed: int = 0) -> None:
+        if batch_size <= 0:
+            raise ValueError('per-rank batch size must be positive (global batch smaller than world size?)')
+        self.source, self.sampler, self.batch_size, self.train, self.seed = source, sampler, batch_size, train, seed
+        self.epoch = 0
+        slots = torch.empty((self.SLOTS, 4 + batch_size), dtype=torch.int32)
+        self._slots = slots.pin_memory() if torch.cuda.is_available() else slots
+        self._next = 0
+
+    def set_epoch(self, epoch: int) -> None:
+        self.epoch = int(epoch)
+        self.sampler.set_epoch(epoch)
+
+    def __len__(self) -> int:
+        return (len(self.sampler) + self.batch_size - 1) // self.batch_size
+
+    @property
+    def dataset_len(self) -> int:
+        return len(self.source)
+
+    def __iter__(self) -> Iterator[IndexBatch]:
+        from .philox import AUG_STREAM
+        idx, valid = self.sampler.indices_and_mask()
+        enc = torch.where(valid, idx, ~idx).to(torch.int32)
+        hdr = torch.tensor([self.seed & 0x7FFFFFFF, AUG_STREAM, self.epoch, int(self.train)], dtype=torch.int32)
+        for s in range(0, enc.numel(), self.batch_size):
+            n = min(self.batch_size, enc.numel() - s)
+            slot = self._slots[self._next % self.SLOTS]
+            self._next += 1
+            slot[:4] = hdr
+            slot[4:4 + n] = enc[s:s + n]
+            yield IndexBatch(slot, n, self.train, self.seed & 0x7FFFFFFF, self.epoch)
+
+
 class BatchLoader:
     def __init__(self, source: ImageSource, sampler: ShardSampler, batch_size: int, train: bool,
                  seed: int = 0, pin: bool = False) -> None:
@@ -129,4 +198,15 @@ def make_loaders(train_src: ImageSource, test_src: ImageSource, global_batch: in
     tr = BatchLoader(train_src, ShardSampler(len(train_src), world_size, rank, True, seed), bs, True, seed, pin)
     te = BatchLoader(test_src, ShardSampler(len(test_src), world_size, rank, compat_eval_shuffle, seed),
                      bs, False, seed, pin)
+    return tr, te
+
+
+def make_device_loaders(train_src: ImageSource, test_src: ImageSource, global_batch: int, world_size: int,
+                        rank: int, seed: int = 0, compat_eval_shuffle: bool = False):
+    """Index-only loaders for datasets resident in GPU memory (same sharding as make_loaders)."""
+    from .sampler import per_rank_batch
+    bs = per_rank_batch(global_batch, world_size)
+    tr = DeviceBatchLoader(train_src, ShardSampler(len(train_src), world_size, rank, True, seed), bs, True, seed)
+    te = DeviceBatchLoader(test_src, ShardSampler(len(test_src), world_size, rank, compat_eval_shuffle, seed),
+                           bs, False, seed)
     return tr, te

@@ -14,7 +14,7 @@ from typing import Dict, List, Optional
 import torch
 import torch.nn as nn
 
-from ..data.loader import Batch
+from ..data.loader import Batch, IndexBatch
 from ..models.resnet import ResNet
 from ..ops import _lib
 from ..ops._lib import check
@@ -49,7 +49,8 @@ class PmdEngineConfig(C.Structure):
 class PmdEngineBuffers(C.Structure):
     _fields_ = [('param', C.c_ulonglong), ('grad', C.c_ulonglong), ('mom', C.c_ulonglong), ('bf16', C.c_ulonglong),
                 ('in_u8', C.c_ulonglong), ('in_aug', C.c_ulonglong), ('in_labels', C.c_ulonglong),
-                ('in_valid', C.c_ulonglong), ('logits', C.c_ulonglong), ('metrics', C.c_ulonglong),
+                ('in_valid', C.c_ulonglong), ('in_index', C.c_ulonglong), ('logits', C.c_ulonglong),
+                ('metrics', C.c_ulonglong),
                 ('slab_elems', C.c_longlong), ('activation_bytes', C.c_longlong), ('heap_bytes_used', C.c_longlong)]
 
 
@@ -191,6 +192,9 @@ class NativeEngine:
         self.in_aug = alias_tensor(bufs.in_aug, per_rank_batch * 12, device).view(torch.int32).view(per_rank_batch, 3)
         self.in_labels = alias_tensor(bufs.in_labels, per_rank_batch * 8, device).view(torch.int64)
         self.in_valid = alias_tensor(bufs.in_valid, per_rank_batch, device)
+        self.in_index = alias_tensor(bufs.in_index, (4 + per_rank_batch) * 4, device).view(torch.int32)
+        self._datasets: Dict[int, tuple] = {}      # id(source) -> (images, labels) resident in device memory
+        self._attached: Optional[int] = None
         self.logits = alias_tensor(bufs.logits, per_rank_batch * spec.num_classes * 4, device).view(torch.float32).view(
             per_rank_batch, spec.num_classes)
         # parameters become views of the slab; 4-D conv weights are stored KRSC (channels-last)
@@ -217,6 +221,8 @@ class NativeEngine:
         check(self.lib.pmd_engine_sync_params(self._h, C.c_int(int(broadcast)), _lib.stream_ptr()))
 
     def _stage(self, batch: Batch, with_valid: bool) -> int:
+        if self._attached is not None:
+            self.detach_dataset()                  # host-staged batch: back to the staging-buffer input kernel
         n = batch.n
         if n > self.max_batch:
             raise ValueError(f'batch of {n} exceeds the engine capacity {self.max_batch}')
@@ -232,12 +238,49 @@ class NativeEngine:
             self._pending_events.pop(0).synchronize()
         return n
 
-    def h2d_bytes(self, n: int) -> int:
+    def h2d_bytes(self, n: int, resident: bool = False) -> int:
+        """Bytes copied host -> device per step of n samples (device-resident dataset: header + indices only)."""
+        if resident:
+            return (4 + n) * 4
         hw = self.in_u8.shape[1]
         return n * (hw * hw * 3 + 12 + 8)
 
-    def train_step(self, batch: Batch, lr: float) -> None:
-        n = self._stage(batch, False)
+    # ------------------------------------------------------------------ device-resident dataset
+    def attach_dataset(self, source) -> None:
+        """Uploads ``source`` (uint8 [M,H,W,3] + int64 labels) to device memory once (CIFAR-10: 150 MB of 180 GB) and
+        makes it the engine's batch source: steps then take an :class:`IndexBatch`.  Several sources (train / test)
+        may be uploaded; the one named here is the active one."""
+        key = id(source)
+        if key not in self._datasets:
+            self._datasets[key] = (source.images.to(self.device, non_blocking=True).contiguous(),
+                                   source.labels.to(self.device, non_blocking=True).contiguous())
+        if self._attached != key:
+            img, lab = self._datasets[key]
+            check(self.lib.pmd_engine_set_dataset(self._h, C.c_void_p(img.data_ptr()), C.c_void_p(lab.data_ptr()),
+                                                  C.c_longlong(img.shape[0])))
+            self._attached = key
+
+    def detach_dataset(self) -> None:
+        if self._attached is not None:
+            check(self.lib.pmd_engine_set_dataset(self._h, C.c_void_p(0), C.c_void_p(0), C.c_longlong(0)))
+            self._attached = None
+
+    def _stage_index(self, batch: IndexBatch) -> int:
+        if self._attached is None:
+            raise RuntimeError('IndexBatch needs a device-resident dataset: call attach_dataset(source) first')
+        n = batch.n
+        if n > self.max_batch:
+            raise ValueError(f'batch of {n} exceeds the engine capacity {self.max_batch}')
+        self.in_index[:4 + n].copy_(batch.packed[:4 + n], non_blocking=True)     # the step's only H2D copy
+        ev = torch.cuda.Event()
+        ev.record()
+        self._pending_events.append(ev)
+        if len(self._pending_events) > 2:          # the loader rotates 4 pinned slots: never run more than 2 copies ahead
+            self._pending_events.pop(0).synchronize()
+        return n
+
+    def train_step(self, batch, lr: float) -> None:
+        n = self._stage_index(batch) if isinstance(batch, IndexBatch) else self._stage(batch, False)
         check(self.lib.pmd_engine_train_step(self._h, C.c_int(n), C.c_float(lr), _lib.stream_ptr()))
         self.step_count += 1
 
@@ -246,8 +289,8 @@ class NativeEngine:
         check(self.lib.pmd_engine_train_step(self._h, C.c_int(n), C.c_float(lr), _lib.stream_ptr()))
         self.step_count += 1
 
-    def eval_step(self, batch: Batch) -> None:
-        n = self._stage(batch, True)
+    def eval_step(self, batch) -> None:
+        n = self._stage_index(batch) if isinstance(batch, IndexBatch) else self._stage(batch, True)
         check(self.lib.pmd_engine_eval_step(self._h, C.c_int(n), _lib.stream_ptr()))
 
     def read_metrics(self, reset: bool = True, reduce: bool = False) -> List[float]:

@@ -25,7 +25,7 @@ from typing import Optional
 import torch
 
 from .cli import parse_args
-from .data.loader import make_loaders
+from .data.loader import DeviceBatchLoader, make_device_loaders, make_loaders
 from .data.sources import make_sources
 from .models.resnet import model_from_name
 from .parallel import launch
@@ -83,6 +83,8 @@ def train_epoch(engine, loader, epoch: int, lr: float, args, rank: int, logger: 
     end = time.time()
     pending_n = 0
     nb = len(loader)
+    if isinstance(loader, DeviceBatchLoader):
+        engine.attach_dataset(loader.source)
     for i, batch in enumerate(loader):
         if args.max_steps and i >= args.max_steps:
             break
@@ -123,6 +125,8 @@ def validate(engine, loader, epoch: int, args, rank: int, logger: Optional[Logge
     tot = [0.0, 0.0, 0.0, 0.0]
     end = time.time()
     nb = len(loader)
+    if isinstance(loader, DeviceBatchLoader):
+        engine.attach_dataset(loader.source)
     for i, batch in enumerate(loader):
         if args.max_steps and i >= args.max_steps:
             break
@@ -175,11 +179,6 @@ def worker(rank: int, world_size: int, args) -> None:
         if int(args.batch_size / world_size) * world_size != args.batch_size and rank == 0:
             print(f'warning: batch_size {args.batch_size} is not divisible by world_size {world_size}; '
                   f'per-rank batch is int({args.batch_size}/{world_size}) as in the reference', flush=True)
-        pin = device.type == 'cuda'
-        if pin:
-            train_src.pin(); test_src.pin()
-        train_loader, test_loader = make_loaders(train_src, test_src, args.batch_size, world_size, rank,
-                                                 args.seed, pin, compat_eval_shuffle=args.compat_metrics)
         if rank == 0:
             print("-------------------Make loader-------------------")
             print('Train Dataset :', len(train_src), '   Test Dataset :', len(test_src), flush=True)
@@ -196,6 +195,16 @@ def worker(rank: int, world_size: int, args) -> None:
             if spth:
                 resume_state = torch.load(spth, map_location='cpu', weights_only=False)
         engine = build_engine(args, model, comm, device, sgd)
+        if engine.kind == 'native' and not args.host_dataset:
+            # both datasets live in GPU memory (CIFAR-10: 180 MB of 180 GB); a step's input is its index vector
+            train_loader, test_loader = make_device_loaders(train_src, test_src, args.batch_size, world_size, rank,
+                                                            args.seed, compat_eval_shuffle=args.compat_metrics)
+        else:
+            pin = device.type == 'cuda'
+            if pin:
+                train_src.pin(); test_src.pin()
+            train_loader, test_loader = make_loaders(train_src, test_src, args.batch_size, world_size, rank,
+                                                     args.seed, pin, compat_eval_shuffle=args.compat_metrics)
         if resume_state is not None:
             engine.load_optimizer_state(resume_state['optimizer'])
 

@@ -13,6 +13,11 @@ import gpu_cases  # noqa: E402
 @pytest.mark.parametrize('name', sorted(gpu_cases.CASES))
 def test_kernel_matches_torch_reference(name):
     res = gpu_cases.CASES[name]()
+    log = os.environ.get('PMD_PROBE_LOG')          # PMD_PROBE_LOG=file: keep every case's error statistics (profiles/)
+    if log:
+        import json
+        with open(log, 'a') as f:
+            f.write(json.dumps({'case': name, **res}, default=str) + '\n')
     assert res['ok'], res
 
 

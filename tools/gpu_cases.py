@@ -5,6 +5,7 @@ on bf16-rounded inputs and returns a dict with error statistics and a pass flag.
 """
 from __future__ import annotations
 
+import json
 import math
 from typing import Callable, Dict
 
@@ -12,6 +13,9 @@ import torch
 import torch.nn.functional as F
 
 CASES: Dict[str, Callable[[], dict]] = {}
+# the oracles are plain fp32 PyTorch: keep cuDNN / cuBLAS from silently computing them in TF32
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
 
 
 def case(name):
@@ -212,6 +216,32 @@ for _name, _args in {
     CASES[_name] = (lambda a=_args: _wgrad_case(*a))
 CASES['wgrad_direct_stem_c3'] = lambda: _wgrad_case(4, 32, 3, 64, 3, 1, direct=True)
 CASES['wgrad_direct_generic_c16'] = lambda: _wgrad_case(2, 8, 16, 24, 3, 2, direct=True)
+
+
+# ------------------------------------------------------------------ the shapes bench.py actually runs
+# ResNet18-ref at 512 images per GPU (BASELINE.json config 3): every convolution layer x {fprop (+BN statistics),
+# the dgrad form the engine uses for it, wgrad}.  Only at this size do the 256-wide output tiles (>= 148 CTAs), the
+# 29- / 49- / 256-way split-K wgrads and the 148-CTA patch wgrad get selected.
+_BENCH_LAYERS = {          # name: (H_in, C, K, R, stride)
+    'stem_as_1x1': (32, 64, 64, 1, 1),
+    'layer1_conv1': (32, 64, 64, 3, 1), 'layer1_conv2': (32, 64, 64, 3, 1),
+    'layer2_conv1': (32, 64, 128, 3, 2), 'layer2_conv2': (16, 128, 128, 3, 1), 'layer2_shortcut': (32, 64, 128, 1, 2),
+    'layer3_conv1': (16, 128, 256, 3, 2), 'layer3_conv2': (8, 256, 256, 3, 1), 'layer3_shortcut': (16, 128, 256, 1, 2),
+    'layer4_conv1': (8, 256, 512, 3, 2), 'layer4_conv2': (4, 512, 512, 3, 1), 'layer4_shortcut': (8, 256, 512, 1, 2),
+}
+for _ln, (_h, _c, _k, _r, _s) in _BENCH_LAYERS.items():
+    CASES[f'bench512_fprop_{_ln}'] = (lambda a=(512, _h, _c, _k, _r, _s): _fprop_case(*a))
+    CASES[f'bench512_wgrad_{_ln}'] = (lambda a=(512, _h, _c, _k, _r, _s): _wgrad_case(*a))
+# block dgrads: layer1 conv1 carries the identity shortcut as an addend, layers 2-4 fuse the projection's dgrad
+CASES['bench512_dgrad_layer1_conv1_addend'] = lambda: _dgrad_case(512, 32, 64, 64, 3, 1, 0, True, krsc=True)
+CASES['bench512_dgrad_layer2_conv1_shortcut'] = lambda: _dgrad_case(512, 32, 64, 128, 3, 2, 128, krsc=True)
+CASES['bench512_dgrad_layer3_conv1_shortcut'] = lambda: _dgrad_case(512, 16, 128, 256, 3, 2, 256, krsc=True)
+CASES['bench512_dgrad_layer4_conv1_shortcut'] = lambda: _dgrad_case(512, 8, 256, 512, 3, 2, 512, krsc=True)
+# inner dgrads (conv2 of every block) also do the BatchNorm-backward reduction of bn1
+CASES['bench512_dgrad_bn_reduce_layer1_conv2'] = lambda: _dgrad_bn_reduce_case(512, 32, 64, 64, 3)
+CASES['bench512_dgrad_bn_reduce_layer2_conv2'] = lambda: _dgrad_bn_reduce_case(512, 16, 128, 128, 3)
+CASES['bench512_dgrad_bn_reduce_layer3_conv2'] = lambda: _dgrad_bn_reduce_case(512, 8, 256, 256, 3)
+CASES['bench512_dgrad_bn_reduce_layer4_conv2'] = lambda: _dgrad_bn_reduce_case(512, 4, 512, 512, 3)
 
 
 # ------------------------------------------------------------------ BatchNorm
@@ -433,14 +463,59 @@ def _engine_forward_case(depth):
     return r
 
 
+@case('engine_resident_dataset_matches_host_staged_batches')
+def _engine_resident_dataset():
+    """Device-resident dataset + in-kernel Philox crop/flip + index gather == the same samples staged from the host
+    with the host-side Philox parameters.  Forward-only (evaluation of the training-mode augmentation is not possible,
+    so the train batches are checked through the first step's loss): evaluation logits must be BIT-identical (same
+    pixels, same labels, same validity mask); training losses agree to the run-to-run noise of the fp32 atomics."""
+    from pmdist.data.loader import DeviceBatchLoader
+    from pmdist.data.sampler import ShardSampler
+    from pmdist.data.sources import synthetic_source
+    src = synthetic_source(200, 32, seed=9)
+    r = {}
+    outs = []
+    for resident in (True, False):
+        model, eng = _mk_engine(18, 32, seed=3)
+        if resident:
+            eng.attach_dataset(src)
+        ev = DeviceBatchLoader(src, ShardSampler(len(src), 3, 2, False, 5), 32, False, seed=5)  # rank 2: wrap-around pad
+        evm = []
+        for ib in ev:
+            eng.eval_step(ib if resident else ib.to_host_batch(src))
+            eng.synchronize()
+            evm.append((eng.logits[:ib.n].clone(), eng.read_metrics()))
+        dl = DeviceBatchLoader(src, ShardSampler(len(src), 3, 1, True, 5), 32, True, seed=5)   # 67 samples on this rank
+        dl.set_epoch(2)
+        if resident:
+            eng.attach_dataset(src)
+        losses = []
+        for ib in dl:
+            eng.train_step(ib if resident else ib.to_host_batch(src), 0.05)
+            m = eng.read_metrics()
+            losses.append(m[0] / m[3])
+        outs.append((losses, evm))
+        eng.close()
+    (la, ea), (lb, eb) = outs
+    r['eval_logits_bit_identical'] = {'ok': all(torch.equal(x[0], y[0]) for x, y in zip(ea, eb))}
+    same_counts = all(x[1][1:] == y[1][1:] for x, y in zip(ea, eb))             # top-1, top-5, counted samples
+    same_loss = all(abs(x[1][0] - y[1][0]) <= 1e-9 * max(1.0, abs(y[1][0])) for x, y in zip(ea, eb))   # fp64 atomics
+    r['eval_metrics_identical'] = {'ok': same_counts and same_loss and sum(x[1][3] for x in ea) == 66,
+                                   'counted': [x[1][3] for x in ea]}
+    r['train_losses_close'] = {'ok': all(abs(x - y) <= 2e-2 * max(1.0, abs(y)) for x, y in zip(la, lb)) and len(la) == 3,
+                               'resident': la, 'host': lb}
+    r['ok'] = all(v['ok'] for v in r.values())
+    return r
+
+
 CASES['engine_eval_logits_resnet18'] = lambda: _engine_forward_case(18)
 CASES['engine_eval_logits_resnet50'] = lambda: _engine_forward_case(50)
 CASES['engine_eval_logits_resnet34'] = lambda: _engine_forward_case(34)
 
 
-def _engine_train_case(depth, steps=1, graph=True):
+def _engine_train_case(depth, steps=1, graph=True, batch=32, fixed_floor=False):
     from pmdist.data.loader import augment_cpu
-    model, eng = _mk_engine(depth, 32, graph=graph)
+    model, eng = _mk_engine(depth, batch, graph=graph)
     twin = _torch_twin(model).train()
     twin16 = _torch_twin(model).train()          # calibration: the same step under torch bf16 autocast
     opt = torch.optim.SGD(twin.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=True)
@@ -448,9 +523,9 @@ def _engine_train_case(depth, steps=1, graph=True):
     before = {k: v.detach().clone() for k, v in twin.state_dict().items()}
     losses_ref, losses = [], []
     for s in range(steps):
-        b = _mk_batch(32, train=True, seed=s)
+        b = _mk_batch(batch, train=True, seed=s)
         eng.train_step(b, 0.1)
-        losses.append(eng.read_metrics()[0] / 32)
+        losses.append(eng.read_metrics()[0] / batch)
         x, y = augment_cpu(b.u8, b.aug).cuda(), b.labels.cuda()
         loss = F.cross_entropy(twin(x), y)
         opt.zero_grad()
@@ -491,12 +566,27 @@ def _engine_train_case(depth, steps=1, graph=True):
     r = {'loss': losses, 'loss_ref': losses_ref, 'update_cosine_total': total_cos,
          'update_cosine_of_torch_bf16_autocast': cal_cos, 'worst_tensor_cosine': worst_cos,
          'worst_tensor': worst_name, 'running_mean': rm, 'running_var': rv,
-         'nbt': int(got['bn1.num_batches_tracked']), 'launches_per_step': eng.launches_per_step(32)}
-    # bf16 activations/gradients through BatchNorm's mean-removing backward are noisy at random init; the
-    # bar is "at least as faithful to fp32 as torch's own bf16 autocast step, minus a small margin"
-    stats_ok = (rm['ok'] and rv['ok']) or steps > 1      # after several lr=0.1 steps the trajectories diverge chaotically
-    r['ok'] = (total_cos > min(0.98, cal_cos - 0.03) and abs(losses[0] - losses_ref[0]) < 0.05 and stats_ok
-               and r['nbt'] == steps)
+         'nbt': int(got['bn1.num_batches_tracked']), 'launches_per_step': eng.launches_per_step(batch),
+         'batch': batch, 'steps': steps}
+    if steps > 1:
+        # Running statistics after several lr = 0.1 steps: the stem's (bn1) depend on the stem weights only and must
+        # still agree; the deepest layer's input distribution follows two diverging weight trajectories (bf16 vs fp32
+        # through 12 layers at random init), so its running_var is held to a loose 25 % of the largest entry.
+        rv = _cmp(got['layer4.0.bn2.running_var'], want['layer4.0.bn2.running_var'], 0.25)
+        rm = _cmp(got['bn1.running_mean'], want['bn1.running_mean'], 5e-2)
+        r['running_mean'], r['running_var'] = rm, rv
+    stats_ok = rm['ok'] and rv['ok']
+    if fixed_floor:
+        # the bench configuration (512 images): a fixed bar, no calibration
+        r['ok'] = (total_cos >= 0.985 and abs(losses[0] - losses_ref[0]) < 0.02 and stats_ok and r['nbt'] == steps)
+    else:
+        # bf16 activations/gradients through BatchNorm's mean-removing backward are noisy at random init and batch 32;
+        # the bar is "at least as faithful to fp32 as torch's own bf16 autocast step, minus a small margin"
+        r['ok'] = (total_cos > min(0.98, cal_cos - 0.03) and abs(losses[0] - losses_ref[0]) < 0.05 and stats_ok
+                   and r['nbt'] == steps)
+    print('engine_train_case', json.dumps({k: r[k] for k in ('batch', 'steps', 'loss', 'loss_ref', 'update_cosine_total',
+                                                            'update_cosine_of_torch_bf16_autocast', 'worst_tensor_cosine',
+                                                            'worst_tensor')}), flush=True)
     eng.close()
     return r
 
@@ -505,6 +595,7 @@ CASES['engine_train_step_resnet18_matches_torch'] = lambda: _engine_train_case(1
 CASES['engine_train_3steps_resnet18_graph'] = lambda: _engine_train_case(18, 3)
 CASES['engine_train_step_resnet50_matches_torch'] = lambda: _engine_train_case(50, 1)
 CASES['engine_train_step_resnet34_identity_shortcuts'] = lambda: _engine_train_case(34, 1)
+CASES['engine_train_step_resnet18_batch512_fixed_floor'] = lambda: _engine_train_case(18, 1, batch=512, fixed_floor=True)
 
 
 @case('engine_loss_decreases_and_tail_batch')
@@ -593,8 +684,7 @@ def _bn_multi():
     class Br(C.Structure):
         _fields_ = [('y', C.c_void_p), ('mean', C.c_void_p), ('invstd', C.c_void_p), ('gamma', C.c_void_p),
                     ('sums', C.c_void_p), ('totals', C.c_void_p), ('dy', C.c_void_p), ('dgamma', C.c_void_p),
-                    ('dbeta', C.c_void_p), ('recv_off', C.c_ulonglong), ('totals_out', C.c_void_p),
-                    ('slot', C.c_int), ('pad_', C.c_int)]
+                    ('dbeta', C.c_void_p)]
     lib = _lib.lib()
     Cc, N, H = 128, 8, 8
     rows = N * H * H
