@@ -11,6 +11,16 @@ reference; each patch exists because of one reference line (SURVEY.md Appendix A
       DistributedSampler and DataLoader workers still run on it
   CPU-only mode (REF_CPU=1): .cuda() -> identity, backend -> gloo, no SyncBN, DDP without device_ids
 
+Labelled VARIANTS (never the stock arm; each is named in the JSON line that reports it):
+  REF_GLOBAL_POOL=1       head pools the whole final map (224x224 inputs; ref:model/resnet.py:102 hard-codes 4x4)
+  REF_MODEL=ResNet50      main.py's `resnet.ResNet18()` (ref:main.py:39-40, the only model it can build) resolves to
+                          another factory of the SAME file (ref:model/resnet.py:112-125)
+  REF_NO_AUG=1            RandomCrop / RandomHorizontalFlip become identities and REF_DUMP_INIT=<file> saves rank 0's
+                          initial state_dict right after DDP(model): only tools/parity_vs_reference.py uses them, to feed
+                          both frameworks the same tensors so that their loss curves can be compared number by number
+  REF_AUTOCAST_BF16=1     the reference's model runs under torch.autocast(bf16) with channels_last weights and inputs:
+                          a like-for-like precision baseline for this framework's bf16 path
+
 With REF_TIMING_OUT set, it also records per-iteration timing from OUTSIDE the training loop:
 a CUDA event pair around DDP.forward ... SGD.step (device time of the step) and the wall-clock
 interval between consecutive training forwards (the reference's true end-to-end iteration: its
@@ -72,6 +82,82 @@ if os.environ.get('REF_SHIM') == '1':
             return _avg(x, kernel_size, *a, **k)
 
         _F.avg_pool2d = _avg_pool2d
+
+    if os.environ.get('REF_MODEL'):
+        import importlib.abc
+
+        class _RebindResNet18(importlib.abc.MetaPathFinder):
+            """After the reference's model/resnet.py has been executed, ResNet18 names the requested factory."""
+
+            def find_spec(self, fullname, path, target=None):
+                if fullname != 'model.resnet':
+                    return None
+                for finder in sys.meta_path:
+                    if finder is self or not hasattr(finder, 'find_spec'):
+                        continue
+                    spec = finder.find_spec(fullname, path, target)
+                    if spec is not None and spec.loader is not None:
+                        run = spec.loader.exec_module
+
+                        def exec_module(module, _run=run):
+                            _run(module)
+                            module.ResNet18 = getattr(module, os.environ['REF_MODEL'])
+
+                        spec.loader.exec_module = exec_module
+                        return spec
+                return None
+
+        sys.meta_path.insert(0, _RebindResNet18())
+
+    if os.environ.get('REF_AUTOCAST_BF16') == '1':
+        import torch
+        from torch.nn.parallel import DistributedDataParallel as _DDP
+        _ddp_init0 = _DDP.__init__
+
+        def _ddp_init_cl(self, module, *a, **k):
+            return _ddp_init0(self, module.to(memory_format=torch.channels_last), *a, **k)
+
+        _DDP.__init__ = _ddp_init_cl
+        _ddp_fwd0 = _DDP.forward
+
+        def _ddp_fwd_autocast(self, *a, **k):
+            a = tuple(t.contiguous(memory_format=torch.channels_last) if torch.is_tensor(t) and t.dim() == 4 else t
+                      for t in a)
+            with torch.autocast('cuda', dtype=torch.bfloat16):
+                out = _ddp_fwd0(self, *a, **k)
+            return out.float()
+
+        _DDP.forward = _ddp_fwd_autocast
+
+    if os.environ.get('REF_NO_AUG') == '1':
+        import torchvision.transforms as _T
+
+        class _Identity:
+            def __init__(self, *a, **k):
+                pass
+
+            def __call__(self, img):
+                return img
+
+        import torchvision.transforms.transforms as _TT      # the reference names them transforms.transforms.X
+        for _m in (_T, _TT):                                 # (ref:data.py:12-13)
+            _m.RandomCrop = _Identity
+            _m.RandomHorizontalFlip = _Identity
+
+    if os.environ.get('REF_DUMP_INIT'):
+        import torch
+        from torch.nn.parallel import DistributedDataParallel as _DDP1
+        _ddp_init1 = _DDP1.__init__
+
+        def _ddp_init_dump(self, module, *a, **k):
+            r = _ddp_init1(self, module, *a, **k)        # after the rank-0 broadcast: what every rank starts from
+            import torch.distributed as _dist
+            if _dist.get_rank() == 0:
+                torch.save({kk: v.detach().cpu().clone() for kk, v in self.state_dict().items()},
+                           os.environ['REF_DUMP_INIT'])
+            return r
+
+        _DDP1.__init__ = _ddp_init_dump
 
     if os.environ.get('REF_CPU') == '1':
         import torch

@@ -33,6 +33,21 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 BASELINE_PUBLISHED = None      # BASELINE.json: "published": {} -> vs_baseline is null
+DEPTH_OF = {'res': 18, 'res18': 18, 'resnet18': 18, 'res34': 34, 'resnet34': 34, 'res50': 50, 'resnet50': 50,
+            'res101': 101, 'resnet101': 101, 'res152': 152, 'resnet152': 152}
+REF_FACTORY = {18: 'ResNet18', 34: 'ResNet34', 50: 'ResNet50', 101: 'ResNet101', 152: 'ResNet152'}
+BLOCKS = {18: '[1,1,1,1] BasicBlock', 34: '[3,4,6,3] BasicBlock', 50: '[3,4,6,3] Bottleneck',
+          101: '[3,4,23,3] Bottleneck', 152: '[3,8,36,3] Bottleneck'}
+
+
+def shared_config(depth: int, gb: int, per_gpu: int, image: int, world: int) -> dict:
+    """The workload description both arms print under "config" with identical keys AND values (the driver compares
+    them); what differs between the arms (precision, kernels, transport) goes under "impl_detail"."""
+    return {'model': f'CIFAR ResNet{depth} {BLOCKS[depth]} (model/resnet.py:{"108-109" if depth == 18 else "112-125"})',
+            'global_batch': gb, 'per_gpu_batch': per_gpu, 'seq_len': None, 'image': f'{image}x{image}',
+            'parallelism': f'dp{world}', 'sync_bn': True, 'optimizer': 'SGD-Nesterov lr0.1 m0.9 wd1e-4',
+            'weights': 'random init', 'head': 'avg_pool2d(4)' if image == 32 else 'global average pool (variant: the '
+            'reference head rejects non-32x32 inputs, ref:model/resnet.py:102-104)'}
 
 
 # ----------------------------------------------------------------------------- clocks sampler
@@ -233,12 +248,11 @@ def run_native(a) -> None:
             'unit': 'images/s', 'n_gpus': world, 'steps': a.steps, 'warmup': max(a.warmup, 3),
             'ms_per_step': round(dev_max / a.steps, 4), 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': BASELINE_PUBLISHED, 'dtype': 'bf16', 'data': 'synthetic', 'impl': 'pmdist-native',
-            'config': {'model': f'CIFAR ResNet{depth} from model/resnet.py (ResNet18 = [1,1,1,1] blocks)',
-                       'global_batch': gb, 'per_gpu_batch': B, 'seq_len': None, 'image': f'{a.image_size}x{a.image_size}',
-                       'parallelism': f'dp{world}', 'sync_bn': True, 'optimizer': 'SGD-Nesterov lr0.1 m0.9 wd1e-4',
-                       'grad_allreduce': eng.algo, 'grad_allreduce_choice': eng.algo_source, 'transport': comm.describe(), 'cuda_graph': not a.no_graph,
-                       'l2': 'no flush: per-step working set (~2.7 MB/image of activations+gradients) exceeds the 126 MB L2',
-                       'weights': 'random init'},
+            'config': shared_config(depth, gb, B, a.image_size, world),
+            'impl_detail': {'grad_allreduce': eng.algo, 'grad_allreduce_choice': eng.algo_source, 'transport': comm.describe(),
+                            'cuda_graph': not a.no_graph, 'precision': 'bf16 activations / gradients, fp32 master weights',
+                            'l2': 'no flush: per-step working set (~2.7 MB/image of activations+gradients) exceeds '
+                                  'the 126 MB L2'},
             'clocks': clk.summary(),
             'e2e': {'value': round(gb * a.steps / (e2e_max / 1e3), 1), 'unit': 'images/s',
                     'ms_per_step': round(e2e_max / a.steps, 4),
@@ -298,17 +312,26 @@ def run_reference(a) -> None:
                 'REF_TIMING_OUT': os.path.join(work, 'timing')})
     if a.image_size != 32:
         env['REF_GLOBAL_POOL'] = '1'      # labelled variant: the reference head cannot take non-32x32 inputs
-    if a.model not in ('res', 'res18'):
-        print(json.dumps({'impl': 'reference', 'unavailable':
-                          "the reference's main.py only builds ResNet18 (--model res, ref:main.py:39-40)"}))
-        return
+    depth = DEPTH_OF[a.model]          # (nothing of this framework is imported on the reference arm)
+    variant = []
+    if depth != 18:
+        # the reference CLI can only build ResNet18 (ref:main.py:39-40): labelled variant, same file's other factory
+        env['REF_MODEL'] = REF_FACTORY[depth]
+        variant.append(f'main.py builds resnet.{REF_FACTORY[depth]} instead of ResNet18 (REF_MODEL shim)')
+    if a.image_size != 32:
+        variant.append('global average pool head (REF_GLOBAL_POOL shim)')
+    bf16 = a.impl == 'reference-bf16'
+    if bf16:
+        env['REF_AUTOCAST_BF16'] = '1'
+        variant.append('model under torch.autocast(bf16) + channels_last (REF_AUTOCAST_BF16 shim)')
+    impl_name = 'reference-bf16-autocast' if bf16 else 'reference'
     cmd = [sys.executable, ref_main, '--batch_size', str(gb), '--epochs', '1', '--world_size', str(N),
            '--save_path', os.path.join(work, 'out') + '/', '--print-freq', '1000']
     local = int(os.environ.get('LOCAL_RANK', '0'))
     with ClockSampler(local) as clk:
         r = subprocess.run(cmd, cwd=work, env=env, capture_output=True, text=True, timeout=1500)
     if r.returncode != 0:
-        print(json.dumps({'impl': 'reference', 'unavailable': 'reference run failed: ' + (r.stderr or r.stdout)[-300:].replace('\n', ' ')}))
+        print(json.dumps({'impl': impl_name, 'unavailable': 'reference run failed: ' + (r.stderr or r.stdout)[-300:].replace('\n', ' ')}))
         return
     dev, wall, flags = [], [], {}
     for rk in range(N):
@@ -320,11 +343,14 @@ def run_reference(a) -> None:
     dev_max, e2e_max = max(dev), max(wall)
     out = {'metric': 'ResNet training images/sec (device-timed, max over ranks)', 'value': round(gb * K / (dev_max / 1e3), 1),
            'unit': 'images/s', 'n_gpus': N, 'steps': K, 'warmup': W, 'ms_per_step': round(dev_max / K, 4),
-           'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'fp32 (cuDNN TF32 convs allowed)',
-           'data': 'synthetic', 'impl': 'reference',
-           'config': {'model': 'reference ResNet18 ([1,1,1,1]) via baseline/_ref/main.py, unmodified', 'global_batch': gb,
-                      'per_gpu_batch': B, 'seq_len': None, 'parallelism': f'dp{N} (torch DDP + SyncBatchNorm over NCCL)',
-                      'torch_flags': flags, 'timing': 'CUDA events DDP.forward..SGD.step from baseline/shim/sitecustomize.py'},
+           'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+           'dtype': 'bf16 autocast (fp32 weights, optimizer, BatchNorm)' if bf16 else 'fp32 (cuDNN TF32 convs allowed)',
+           'data': 'synthetic', 'impl': impl_name,
+           'config': shared_config(depth, gb, B, a.image_size, N),
+           'impl_detail': {'source': 'baseline/_ref/main.py (byte-identical copy of /root/reference) through its own CLI',
+                           'stack': 'torch DDP + SyncBatchNorm over NCCL, cuDNN (benchmark=True), cuBLAS',
+                           'variant': variant or 'none: stock reference', 'torch_flags': flags,
+                           'timing': 'CUDA events DDP.forward..SGD.step from baseline/shim/sitecustomize.py'},
            'clocks': clk.summary(),
            'e2e': {'value': round(gb * K / (e2e_max / 1e3), 1), 'unit': 'images/s', 'ms_per_step': round(e2e_max / K, 4),
                    'h2d_bytes_per_step': B * (3 * a.image_size * a.image_size * 4 + 8), 'd2h_bytes_per_step': 8,
@@ -338,7 +364,7 @@ def main() -> None:
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=30)
     ap.add_argument('--warmup', type=int, default=5)
-    ap.add_argument('--impl', default='native', choices=['native', 'reference'])
+    ap.add_argument('--impl', default='native', choices=['native', 'reference', 'reference-bf16'])
     ap.add_argument('--model', default='res18')
     ap.add_argument('--per-gpu-batch', type=int, default=512)
     ap.add_argument('--image-size', type=int, default=32)
@@ -348,7 +374,7 @@ def main() -> None:
     ap.add_argument('--host-dataset', action='store_true', help='e2e: copy every uint8 batch from pinned host memory')
     ap.add_argument('--no-exposed-comm', action='store_true', help='skip the collectives-stubbed timing runs')
     a = ap.parse_args()
-    if a.impl == 'reference':
+    if a.impl in ('reference', 'reference-bf16'):
         run_reference(a)
     else:
         run_native(a)

@@ -2,8 +2,9 @@
 
 Parity target: ref:main.py:21-30.  Every reference command line parses unchanged:
 ``--batch_size`` (global batch, default 64), ``--epochs`` (20), ``--model`` ('res'),
-``--save_path`` ('./test/'), ``--gpu`` ('7'; parsed and ignored by the reference, here it selects
-CUDA_VISIBLE_DEVICES only when it is a comma list as long as world_size), ``--print-freq/-p`` (10),
+``--save_path`` ('./test/'), ``--gpu`` ('7'; parsed and ignored by the reference; here a comma list with
+exactly world_size distinct device ordinals binds rank i to the i-th of them, train.gpu_list, anything else is
+ignored), ``--print-freq/-p`` (10),
 ``--world_size`` (2).
 
 Unlike the reference, flags are parsed inside ``parse_args`` (not at import), travel to the ranks
@@ -26,7 +27,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--model', default='res', type=str,
                    help='res|res18|res34|res50|res101|res152 (res == the reference ResNet18 [1,1,1,1])')
     p.add_argument('--save_path', default='./test/', type=str, help='Savefiles directory')
-    p.add_argument('--gpu', default='7', type=str, help='accepted for compatibility (see module doc)')
+    p.add_argument('--gpu', default='7', type=str, help='"4,5,6,7" (world_size entries): device of each rank; otherwise ignored like the reference does')
     p.add_argument('--print-freq', '-p', default=10, type=int, metavar='N', help='print frequency')
     p.add_argument('--world_size', default=2, type=int, help='number of GPUs / processes')
     # --- optimiser (reference values hard-coded at ref:main.py:51-59)
@@ -37,7 +38,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--milestones', default='60,80', type=str)
     p.add_argument('--gamma', default=0.1, type=float)
     # --- data (ref:data.py)
-    p.add_argument('--data', default='auto', choices=['auto', 'cifar10', 'synthetic'],
+    p.add_argument('--data', default='auto', choices=['auto', 'cifar10', 'synthetic', 'ref-fake'],
                    help="auto = CIFAR-10 from --data-root if present, else synthetic")
     p.add_argument('--data-root', default='./cifar10_data', type=str)
     p.add_argument('--image-size', default=32, type=int, help='synthetic image side (32 or 224)')
@@ -61,6 +62,11 @@ def build_parser() -> argparse.ArgumentParser:
                    help='gradient all-reduce algorithm of the native engine')
     # --- run control
     p.add_argument('--seed', default=0, type=int)
+    p.add_argument('--init-from', default='', type=str,
+                   help='initial weights from a state_dict file (reference key names); epoch numbering starts at 1')
+    p.add_argument('--no-augment', action='store_true', help='training batches without random crop / flip')
+    p.add_argument('--no-reshuffle', action='store_true',
+                   help='same sample order every epoch, as the reference (it never calls set_epoch; SURVEY.md D4)')
     p.add_argument('--resume', default='', type=str, help='model_E.pth or a run directory')
     p.add_argument('--save-every', default=0, type=int, help='checkpoint every N epochs (0 = last only)')
     p.add_argument('--compat-metrics', action='store_true',

@@ -80,6 +80,7 @@ class IndexBatch:
     train: bool
     seed: int
     epoch: int
+    draw: bool = True          # crop / flip are drawn (training with augmentation)
 
     @property
     def indices(self) -> torch.Tensor:
@@ -95,7 +96,7 @@ class IndexBatch:
         from .philox import aug_params
         idx = self.indices
         return Batch(source.images.index_select(0, idx), source.labels.index_select(0, idx), self.valid.clone(),
-                     aug_params(idx.numpy(), self.seed, self.epoch, self.train), self.train)
+                     aug_params(idx.numpy(), self.seed, self.epoch, self.train and self.draw), self.train)
 
 
 class DeviceBatchLoader:
@@ -105,10 +106,12 @@ class DeviceBatchLoader:
 
     SLOTS = 4      # pinned slots in rotation: a slot is rewritten SLOTS steps after its H2D copy was enqueued
 
-    def __init__(self, source: ImageSource, sampler: ShardSampler, batch_size: int, train: bool, seed: int = 0) -> None:
+    def __init__(self, source: ImageSource, sampler: ShardSampler, batch_size: int, train: bool, seed: int = 0,
+                 augment: bool = True) -> None:
         if batch_size <= 0:
             raise ValueError('per-rank batch size must be positive (global batch smaller than world size?)')
         self.source, self.sampler, self.batch_size, self.train, self.seed = source, sampler, batch_size, train, seed
+        self.augment = augment
         self.epoch = 0
         slots = torch.empty((self.SLOTS, 4 + batch_size), dtype=torch.int32)
         self._slots = slots.pin_memory() if torch.cuda.is_available() else slots
@@ -129,22 +132,24 @@ class DeviceBatchLoader:
         from .philox import AUG_STREAM
         idx, valid = self.sampler.indices_and_mask()
         enc = torch.where(valid, idx, ~idx).to(torch.int32)
-        hdr = torch.tensor([self.seed & 0x7FFFFFFF, AUG_STREAM, self.epoch, int(self.train)], dtype=torch.int32)
+        draw = self.train and self.augment           # header word 3: draw crop / flip (else centre crop, no flip)
+        hdr = torch.tensor([self.seed & 0x7FFFFFFF, AUG_STREAM, self.epoch, int(draw)], dtype=torch.int32)
         for s in range(0, enc.numel(), self.batch_size):
             n = min(self.batch_size, enc.numel() - s)
             slot = self._slots[self._next % self.SLOTS]
             self._next += 1
             slot[:4] = hdr
             slot[4:4 + n] = enc[s:s + n]
-            yield IndexBatch(slot, n, self.train, self.seed & 0x7FFFFFFF, self.epoch)
+            yield IndexBatch(slot, n, self.train, self.seed & 0x7FFFFFFF, self.epoch, draw)
 
 
 class BatchLoader:
     def __init__(self, source: ImageSource, sampler: ShardSampler, batch_size: int, train: bool,
-                 seed: int = 0, pin: bool = False) -> None:
+                 seed: int = 0, pin: bool = False, augment: bool = True) -> None:
         if batch_size <= 0:
             raise ValueError('per-rank batch size must be positive '
                              '(global batch smaller than world size?)')
+        self.augment = augment          # False: training batches with the centre crop, no flip (parity runs)
         self.source = source
         self.sampler = sampler
         self.batch_size = batch_size
@@ -187,26 +192,26 @@ class BatchLoader:
             else:
                 u8 = self.source.images.index_select(0, sel)
                 lb = self.source.labels.index_select(0, sel)
-            yield Batch(u8, lb, valid[s:s + n], draw_aug_params(n, self.train, gen), self.train)
+            yield Batch(u8, lb, valid[s:s + n], draw_aug_params(n, self.train and self.augment, gen), self.train)
 
 
 def make_loaders(train_src: ImageSource, test_src: ImageSource, global_batch: int, world_size: int,
-                 rank: int, seed: int = 0, pin: bool = False, compat_eval_shuffle: bool = False):
+                 rank: int, seed: int = 0, pin: bool = False, compat_eval_shuffle: bool = False, augment: bool = True):
     """(train_loader, test_loader) for one rank (ref:data.py:31-53)."""
     from .sampler import per_rank_batch
     bs = per_rank_batch(global_batch, world_size)
-    tr = BatchLoader(train_src, ShardSampler(len(train_src), world_size, rank, True, seed), bs, True, seed, pin)
+    tr = BatchLoader(train_src, ShardSampler(len(train_src), world_size, rank, True, seed), bs, True, seed, pin, augment)
     te = BatchLoader(test_src, ShardSampler(len(test_src), world_size, rank, compat_eval_shuffle, seed),
                      bs, False, seed, pin)
     return tr, te
 
 
 def make_device_loaders(train_src: ImageSource, test_src: ImageSource, global_batch: int, world_size: int,
-                        rank: int, seed: int = 0, compat_eval_shuffle: bool = False):
+                        rank: int, seed: int = 0, compat_eval_shuffle: bool = False, augment: bool = True):
     """Index-only loaders for datasets resident in GPU memory (same sharding as make_loaders)."""
     from .sampler import per_rank_batch
     bs = per_rank_batch(global_batch, world_size)
-    tr = DeviceBatchLoader(train_src, ShardSampler(len(train_src), world_size, rank, True, seed), bs, True, seed)
+    tr = DeviceBatchLoader(train_src, ShardSampler(len(train_src), world_size, rank, True, seed), bs, True, seed, augment)
     te = DeviceBatchLoader(test_src, ShardSampler(len(test_src), world_size, rank, compat_eval_shuffle, seed),
                            bs, False, seed)
     return tr, te

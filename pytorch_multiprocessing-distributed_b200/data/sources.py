@@ -54,6 +54,15 @@ def synthetic_source(n: int, hw: int = 32, num_classes: int = 10, seed: int = 0,
                        f'synthetic-{hw}x{hw}')
 
 
+def ref_fake_source(n: int, hw: int = 32, train: bool = True) -> ImageSource:
+    """The exact tensors of baseline/shim/ref_fake_cifar.py (the synthetic CIFAR10 stand-in the reference baseline
+    harness trains on): same generator, same call order -- for loss-curve parity runs (tools/parity_vs_reference.py)."""
+    rng = np.random.default_rng(0 if train else 1)
+    imgs = rng.integers(0, 256, size=(n, hw, hw, 3), dtype=np.uint8)
+    labels = np.asarray(rng.integers(0, 10, size=n), dtype=np.int64)
+    return ImageSource(torch.from_numpy(imgs), torch.from_numpy(labels), 10, f'ref-fake-{hw}x{hw}')
+
+
 def cifar10_source(root: str = './cifar10_data', train: bool = True) -> ImageSource:
     """CIFAR-10 python pickles under ``root/cifar-10-batches-py`` (the on-disk layout torchvision's
     ``CIFAR10(download=False)`` expects, ref:data.py:21-28). No torchvision dependency."""
@@ -79,6 +88,8 @@ def make_sources(kind: str, root: str, hw: int, train_size: int, test_size: int,
                  num_classes: int = 10, seed: int = 0) -> Tuple[ImageSource, ImageSource]:
     if kind == 'cifar10':
         return cifar10_source(root, True), cifar10_source(root, False)
+    if kind == 'ref-fake':
+        return ref_fake_source(train_size, hw, True), ref_fake_source(test_size, hw, False)
     if kind == 'synthetic':
         return (synthetic_source(train_size, hw, num_classes, seed),
                 synthetic_source(test_size, hw, num_classes, seed + 1))

@@ -56,7 +56,7 @@ class PmdEngineBuffers(C.Structure):
 
 def heap_bytes_for(num_params: int) -> int:
     """fp32 param + grad + momentum, bf16 copy, BN partials, SyncBN push-exchange receive areas, scratch."""
-    return int(num_params * 14 * 1.02) + 96 * MiB
+    return int(num_params * 14 * 1.02) + 160 * MiB
 
 
 def _arr(ctype, values):
@@ -173,7 +173,7 @@ class NativeEngine:
             algo = 'twoshot'
         from .tuning import choose_bucket_algos
         self.bucket_algos, self.bucket_blocks, self.algo_source = choose_bucket_algos(
-            comm.world_size, [nn_ * 4 for nn_ in numels], bool(comm.info.multicast_mapped), algo, comm_blocks)
+            comm.world_size, [nn_ * 4 for nn_ in numels], bool(comm.info.multicast_mapped), algo, comm_blocks, comm=comm)
         self.algo = '+'.join(sorted(set(self.bucket_algos)))
         cfg.algo, cfg.comm_blocks = ALGOS[self.bucket_algos[0]], comm_blocks
         cfg.bucket_algo = arr(C.c_int, [ALGOS[a_] for a_ in self.bucket_algos])

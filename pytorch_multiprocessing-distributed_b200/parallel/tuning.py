@@ -50,14 +50,73 @@ class AllreduceTable:
         return best
 
 
+def measure_bucket_algos(comm, bucket_bytes: List[int], multicast: bool, iters: int = 20):
+    """Bring-up microbenchmark (SURVEY.md N2'): times every all-reduce algorithm x CTA count on THIS box for the
+    model's real bucket sizes (CUDA events, device barrier before, max over ranks) and returns the fastest per
+    bucket.  Used when no committed table matches the world size (or PMDIST_TUNE=1).  ~50 ms for ResNet18."""
+    import ctypes as C
+    import struct
+
+    import torch
+
+    from ..ops import _lib
+    from ..ops._lib import check
+    from .peer import ALGOS
+    big = max(bucket_bytes)
+    try:
+        in_off, out_off = comm.alloc(big + 64), comm.alloc(big + 64)
+    except Exception:
+        return None                                  # heap too small for scratch: fall back to the table / heuristic
+    lib = _lib.lib()
+    algos = ['oneshot', 'twoshot'] + (['nvls'] if multicast else [])
+    pick_a, pick_b, notes = [], [], []
+    cache = {}
+    for nbytes in bucket_bytes:
+        n = nbytes // 16 * 4
+        if n in cache:
+            a_, b_, us_ = cache[n]
+        else:
+            best = None
+            for algo in algos:
+                for blocks in ((8, 32) if nbytes <= (1 << 20) else (32, 96)):
+                    def fn():
+                        check(lib.pmd_allreduce_f32(C.byref(comm.sym), C.c_ulonglong(in_off), C.c_ulonglong(out_off),
+                                                    C.c_longlong(n), C.c_int(ALGOS[algo]), C.c_int(blocks), C.c_int(2000),
+                                                    _lib.stream_ptr()))
+                    for _ in range(3):
+                        fn()
+                    torch.cuda.synchronize()
+                    comm.barrier()
+                    comm.device_barrier()
+                    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    t0.record()
+                    for _ in range(iters):
+                        fn()
+                    t1.record()
+                    torch.cuda.synchronize()
+                    us = t0.elapsed_time(t1) * 1e3 / iters
+                    us = max(struct.unpack('d', v)[0] for v in comm.all_gather_bytes(struct.pack('d', us)))
+                    if best is None or us < best[2]:
+                        best = (algo, blocks, us)        # every rank sees the same max, hence the same choice
+            a_, b_, us_ = cache[n] = best
+        pick_a.append(a_)
+        pick_b.append(b_)
+        notes.append('%d B: %s x%d %.1f us' % (nbytes, a_, b_, us_))
+    return pick_a, pick_b, '; '.join(notes)
+
+
 def choose_bucket_algos(world: int, bucket_bytes: List[int], multicast: bool, forced: str = 'auto',
-                        default_blocks: int = 32) -> Tuple[List[str], List[int], str]:
+                        default_blocks: int = 32, comm=None) -> Tuple[List[str], List[int], str]:
     """Per-bucket (algo, CTAs).  `forced` in {'oneshot','twoshot','nvls'} overrides the table."""
     if world == 1:
         return ['oneshot'] * len(bucket_bytes), [default_blocks] * len(bucket_bytes), 'single rank'
     if forced != 'auto':
         return [forced] * len(bucket_bytes), [default_blocks] * len(bucket_bytes), f'forced {forced}'
     tab = AllreduceTable.load(world)
+    if (tab is None or os.environ.get('PMDIST_TUNE', '0') == '1') and comm is not None:
+        measured = measure_bucket_algos(comm, bucket_bytes, multicast)
+        if measured is not None:
+            return measured[0], measured[1], 'measured at bring-up (%s)' % measured[2]
     if tab is None:
         # no measurement for this world size: latency-optimal one-shot below 256 KB, owner-computes above
         algos = ['oneshot' if b < (256 << 10) else ('nvls' if multicast else 'twoshot') for b in bucket_bytes]

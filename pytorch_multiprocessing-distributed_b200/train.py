@@ -35,13 +35,25 @@ from .utils.meters import AverageMeter, Logger
 from .utils.schedule import SGDConfig
 
 
+def gpu_list(spec: str, world_size: int):
+    """``--gpu 4,5,6,7`` with exactly world_size entries names the device of every rank; anything else (the
+    reference's default '7' included) is ignored, as the reference ignores the flag entirely (ref:main.py:26)."""
+    parts = [p.strip() for p in str(spec).split(',') if p.strip() != '']
+    if len(parts) != world_size or not all(p.isdigit() for p in parts) or len(set(parts)) != len(parts):
+        return None
+    return [int(p) for p in parts]
+
+
 def resolve_device(args, rank: int) -> torch.device:
     want = args.device
     if want == 'auto':
         want = 'cuda' if torch.cuda.is_available() else 'cpu'
     if want == 'cuda':
-        torch.cuda.set_device(rank % max(torch.cuda.device_count(), 1))
-        return torch.device('cuda', rank % max(torch.cuda.device_count(), 1))
+        n = max(torch.cuda.device_count(), 1)
+        ids = gpu_list(getattr(args, 'gpu', ''), int(getattr(args, 'world_size', 0) or 0))
+        index = ids[rank] if ids is not None and all(i < n for i in ids) else rank % n
+        torch.cuda.set_device(index)
+        return torch.device('cuda', index)
     return torch.device('cpu')
 
 
@@ -188,23 +200,27 @@ def worker(rank: int, world_size: int, args) -> None:
                         tuple(args.milestones), args.gamma)
         start_epoch = 1
         resume_state = None
+        if args.init_from:
+            model.load_state_dict(ckpt.load_model(args.init_from))
         if args.resume:
             mpth, spth, e = ckpt.find_resume(args.resume)
             model.load_state_dict(ckpt.load_model(mpth))
             start_epoch = e + 1
             if spth:
-                resume_state = torch.load(spth, map_location='cpu', weights_only=False)
+                resume_state = ckpt.load_train_state(spth)
         engine = build_engine(args, model, comm, device, sgd)
         if engine.kind == 'native' and not args.host_dataset:
             # both datasets live in GPU memory (CIFAR-10: 180 MB of 180 GB); a step's input is its index vector
             train_loader, test_loader = make_device_loaders(train_src, test_src, args.batch_size, world_size, rank,
-                                                            args.seed, compat_eval_shuffle=args.compat_metrics)
+                                                            args.seed, compat_eval_shuffle=args.compat_metrics,
+                                                            augment=not args.no_augment)
         else:
             pin = device.type == 'cuda'
             if pin:
                 train_src.pin(); test_src.pin()
             train_loader, test_loader = make_loaders(train_src, test_src, args.batch_size, world_size, rank,
-                                                     args.seed, pin, compat_eval_shuffle=args.compat_metrics)
+                                                     args.seed, pin, compat_eval_shuffle=args.compat_metrics,
+                                                     augment=not args.no_augment)
         if resume_state is not None:
             engine.load_optimizer_state(resume_state['optimizer'])
 
@@ -215,7 +231,7 @@ def worker(rank: int, world_size: int, args) -> None:
 
         for epoch in range(start_epoch, args.epochs + 1):
             lr = sgd.lr_at(epoch)
-            train_loader.set_epoch(epoch)
+            train_loader.set_epoch(0 if args.no_reshuffle else epoch)
             test_loader.set_epoch(0)
             train_epoch(engine, train_loader, epoch, lr, args, rank, train_logger, comm)
             validate(engine, test_loader, epoch, args, rank, test_logger, comm, 'test')

@@ -46,10 +46,26 @@ def save_model(save_path: str, epoch: int, model_state: Dict[str, torch.Tensor])
     return path
 
 
+def _plain(v):
+    """Only tensors, numbers, strings, None and lists / dicts of those go into a state file, so that it loads with
+    torch's restricted unpickler (``weights_only=True``): a checkpoint directory is data, not code."""
+    if isinstance(v, torch.Tensor) or v is None or isinstance(v, (bool, int, float, str)):
+        return v
+    if isinstance(v, dict):
+        return {str(k): _plain(x) for k, x in v.items()}
+    if isinstance(v, (list, tuple)):
+        return [_plain(x) for x in v]
+    return repr(v)
+
+
 def save_train_state(save_path: str, epoch: int, optimizer_state: dict, extra: Optional[dict] = None) -> str:
     path = state_path(save_path, epoch)
-    torch.save({'epoch': epoch, 'optimizer': optimizer_state, 'extra': extra or {}}, path)
+    torch.save(_plain({'epoch': epoch, 'optimizer': optimizer_state, 'extra': extra or {}}), path)
     return path
+
+
+def load_train_state(path: str) -> dict:
+    return torch.load(path, map_location='cpu', weights_only=True)
 
 
 def load_model(path: str) -> 'OrderedDict[str, torch.Tensor]':
@@ -74,6 +90,9 @@ def find_resume(path: str) -> Tuple[str, Optional[str], int]:
         mp = model_path(path, e)
     else:
         mp = path
-        e = int(os.path.basename(path)[len('model_'):-len('.pth')])
+        name = os.path.basename(path)
+        if not (name.startswith('model_') and name.endswith('.pth') and name[len('model_'):-len('.pth')].isdigit()):
+            raise ValueError(f"--resume expects a run directory or a file named model_<epoch>.pth, got '{path}'")
+        e = int(name[len('model_'):-len('.pth')])
     sp = state_path(os.path.dirname(mp) or '.', e)
     return mp, (sp if os.path.exists(sp) else None), e

@@ -19,3 +19,58 @@ def test_two_rank_collectives_and_engine(tmp_path):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     s = json.load(open(tmp_path / 'summary.json'))
     assert s['ok'], s
+
+
+def _train_until_killed(rank, world):
+    """Both ranks train ResNet18 through the native engine; rank 1 SIGKILLs itself mid-epoch."""
+    import signal
+
+    import torch
+    from pmdist.data.loader import DeviceBatchLoader
+    from pmdist.data.sampler import ShardSampler
+    from pmdist.data.sources import synthetic_source
+    from pmdist.models.resnet import build_resnet
+    from pmdist.parallel.engine import NativeEngine, heap_bytes_for
+    from pmdist.parallel.peer import PeerComm
+    from pmdist.utils.schedule import SGDConfig
+    torch.cuda.set_device(rank)
+    dev = torch.device('cuda', rank)
+    model = build_resnet(18)
+    comm = PeerComm(rank, world, dev, heap_bytes_for(sum(p.numel() for p in model.parameters())))
+    eng = NativeEngine(model, comm, SGDConfig(), dev, 64, 32)
+    src = synthetic_source(64 * 400, 32, seed=1)
+    eng.attach_dataset(src)
+    dl = DeviceBatchLoader(src, ShardSampler(len(src), world, rank, True, 0), 64, True)
+    for i, b in enumerate(dl):
+        eng.train_step(b, 0.05)
+        if i % 10 == 0:
+            eng.read_metrics()
+        if rank == 1 and i == 37:
+            os.kill(os.getpid(), signal.SIGKILL)          # no clean-up, no traceback: the process just vanishes
+    raise AssertionError('the epoch finished although a peer died')
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_killed_rank_is_reported_and_peers_are_reaped():
+    """Fault tier (the mp.spawn(join=True) contract of ref:main.py:185-188): a rank that dies
+    mid-step while its peer spins in a SyncBatchNorm exchange on the GPU must surface as RankFailure(rank=1) in the
+    parent, and every process of the job must be gone well before the device-side 30 s watchdog would fire."""
+    import time
+
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs 2 GPUs')
+    sys.path.insert(0, ROOT)
+    from pmdist.parallel import launch
+    t0 = time.time()
+    with pytest.raises(launch.RankFailure) as ei:
+        launch.spawn(_train_until_killed, 2, timeout=300)
+    took = time.time() - t0
+    assert ei.value.rank == 1 and ei.value.exitcode == -9, (ei.value.rank, ei.value.exitcode)
+    assert took < 120, took                       # includes two cold `import torch` + engine bring-up
+    import multiprocessing as mp
+    assert not mp.active_children()
+    # the surviving GPU is usable again: its context went away with the killed peer's sibling
+    x = torch.ones(1024, device='cuda:0')
+    assert float(x.sum()) == 1024.0

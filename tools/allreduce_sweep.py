@@ -41,6 +41,22 @@ def _worker(rank: int, world: int, out: str, max_bytes: int) -> None:
     dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
     nccl_buf = torch.randn(big // 4, device=dev)
     algos = ['oneshot', 'twoshot'] + (['nvls'] if comm.info.multicast_mapped else [])
+
+    def time_it_n(fn, iters):
+        for _ in range(10):
+            fn()
+        torch.cuda.synchronize()
+        comm.barrier()
+        comm.device_barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        us = a.elapsed_time(b) * 1e3 / iters
+        return max(struct.unpack('d', v)[0] for v in comm.all_gather_bytes(struct.pack('d', us)))
+
     rows = []
     for nbytes in sizes:
         n = nbytes // 4 // 4 * 4
@@ -82,9 +98,37 @@ def _worker(rank: int, world: int, out: str, max_bytes: int) -> None:
         rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)
+    # ---- SyncBatchNorm push exchange (csrc/comm.cu small_allreduce_push_kernel): the [2C] vectors of the model's
+    # BatchNorm layers, one and two vectors per launch, back-to-back launches (PDL), device time per exchange
+    class SmallX(C.Structure):
+        _fields_ = [('local', C.c_void_p), ('total', C.c_void_p), ('recv_off', C.c_ulonglong), ('n', C.c_int),
+                    ('slot', C.c_int)]
+    push_rows = []
+    for c in (64, 128, 256, 512, 2048):
+        n = 2 * c
+        loc = [torch.randn(n, device=dev) for _ in range(2)]
+        tot = [torch.empty(n, device=dev) for _ in range(2)]
+        recv = [comm.alloc(2 * world * n * 8) for _ in range(2)]
+        for off in recv:
+            comm.view(off, (2 * world * n * 2,), torch.int32).zero_()
+        torch.cuda.synchronize()
+        comm.barrier()
+        xs = (SmallX * 2)(SmallX(loc[0].data_ptr(), tot[0].data_ptr(), recv[0], n, 3000 + 2 * c % 97),
+                          SmallX(loc[1].data_ptr(), tot[1].data_ptr(), recv[1], n, 3100 + 2 * c % 97))
+        row = {'channels': c, 'bytes_per_rank': n * 4}
+        iters = 500
+        for nvec in (1, 2):
+            us = time_it_n(lambda nvec=nvec: check(lib.pmd_small_allreduce_push(C.byref(comm.sym), xs, C.c_int(nvec),
+                                                                               _lib.stream_ptr())), iters)
+            row[f'push_{nvec}vec_us'] = round(us, 2)
+        view = nccl_buf[:n]
+        row['nccl_allreduce_us'] = round(time_it_n(lambda: dist.all_reduce(view), iters), 2)
+        push_rows.append(row)
+        if rank == 0:
+            print(json.dumps(row), flush=True)
     if rank == 0:
         with open(out, 'w') as f:
-            json.dump({'world': world, 'transport': comm.describe(), 'rows': rows}, f, indent=1)
+            json.dump({'world': world, 'transport': comm.describe(), 'rows': rows, 'push_exchange': push_rows}, f, indent=1)
     dist.destroy_process_group()
     comm.close()
 

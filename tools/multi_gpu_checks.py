@@ -25,7 +25,7 @@ def _worker(rank: int, world: int, out_dir: str, quick: bool) -> None:
     torch.cuda.set_device(rank)
     dev = torch.device('cuda', rank)
     res = {'rank': rank, 'world': world}
-    comm = PeerComm(rank, world, dev, heap_bytes=1 << 30)
+    comm = PeerComm(rank, world, dev, heap_bytes=(1 << 30) if quick else (3 << 29))
     res['transport'] = comm.describe()
     lib = _lib.lib()
 
@@ -33,7 +33,8 @@ def _worker(rank: int, world: int, out_dir: str, quick: bool) -> None:
     algos = ['oneshot', 'twoshot'] + (['nvls'] if comm.info.multicast_mapped else [])
     ar = {}
     for algo in algos:
-        for n in (256, 4096, 1 << 20, 5 << 20):
+        # quick: up to 20 MB; full: 1 KB .. 256 MB (collective tier)
+        for n in ((256, 4096, 1 << 20, 5 << 20) if quick else (256, 4096, 65536, 1 << 20, 5 << 20, 1 << 24, 1 << 26)):
             g = torch.Generator(device='cuda').manual_seed(1000 * rank + 7)
             x = torch.randn(n, device=dev, generator=g)
             want = torch.zeros(n, device=dev)
@@ -55,7 +56,7 @@ def _worker(rank: int, world: int, out_dir: str, quick: bool) -> None:
     res['broadcast_ok'] = bool((t == 1.0).all())
 
     # ---- flag / epoch reuse: many back-to-back device barriers and small all-reduces on one slot
-    iters = 300 if quick else 3000
+    iters = 300 if quick else 10000
     t0 = time.time()
     v = torch.ones(256, device=dev)
     for _ in range(iters):
@@ -78,7 +79,7 @@ def _worker(rank: int, world: int, out_dir: str, quick: bool) -> None:
     from pmdist.parallel.comm import SingleComm
     from pmdist.parallel.engine import NativeEngine
     from pmdist.utils.schedule import SGDConfig
-    GB = 16 * world
+    GB = (16 if quick else 512) * world          # full: the bench configuration, 512 images per rank
     src = synthetic_source(GB * 3, 32, seed=11)
     eng_res = {}
     for algo in algos:
