@@ -74,3 +74,18 @@ def test_killed_rank_is_reported_and_peers_are_reaped():
     # the surviving GPU is usable again: its context went away with the killed peer's sibling
     x = torch.ones(1024, device='cuda:0')
     assert float(x.sum()) == 1024.0
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_loss_curve_parity_with_the_reference(tmp_path):
+    """End-to-end tier: the unmodified reference (DDP + SyncBatchNorm + NCCL) and this framework
+    (fp32 torch twin over NCCL, then the native bf16 engine) on the same data, initial weights and sample order;
+    per-epoch train losses must agree (tools/parity_vs_reference.py; measured deltas: profiles/r2_parity_*.json)."""
+    if not os.path.exists(os.path.join(ROOT, 'baseline', '_ref', 'main.py')):
+        pytest.skip('baseline/_ref not installed (baseline/install_reference.sh)')
+    r = subprocess.run([sys.executable, os.path.join(ROOT, 'tools', 'parity_vs_reference.py'), '--gpus', '2', '--epochs', '2',
+                        '--out', str(tmp_path)], capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    s = json.load(open(tmp_path / 'summary.json'))
+    assert s['ok'] and s['host_fp32_nccl_ok'] and s['native_bf16_ok'], s
