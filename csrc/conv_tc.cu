@@ -84,9 +84,19 @@ struct RedExtra {          // extra shared state of the RED (dgrad + BatchNorm-b
   float sc[BN], sh[BN];
 };
 
-template <int BN, int STAGES, bool B_MN = false, bool RED = false>
+// TWO: CTA-pair form (tcgen05 cta_group::2).  Two CTAs of a cluster -- neighbouring pixel bricks, same channel tile --
+// run ONE 256 x BN MMA per k-step: each stages its own brick (A) and only HALF of the weight slice (BN/2 rows of B),
+// the leader (cluster rank 0) issues the MMAs for both, each CTA's tensor core reads the missing half of B from its
+// partner's shared memory.  Per-CTA operand traffic out of shared memory drops from 4 KB + BN*32 B to 4 KB + BN*16 B
+// per k-step (BN = 128: 128 -> 96 B/clk, under the SM's 128 B/clk) and the weight slice crosses L2 -> SM once per
+// pair instead of once per CTA.  Epilogues stay per CTA (each holds its 128 accumulator rows in its own TMEM).
+template <int BN, int STAGES, bool B_MN = false, bool RED = false, bool TWO = false>
 __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
-  constexpr int kStageBytes = kABytes + BN * 128;
+  constexpr int kBBytes = (TWO ? BN / 2 : BN) * 128;      // this CTA's share of the weight slice
+  constexpr int kStageBytes = kABytes + kBBytes;
+  static_assert(!TWO || BN >= 128, "CTA pairs need at least 64 weight rows per CTA");
+  const bool leader = !TWO || cluster_ctarank() == 0;
+  const int half = TWO ? static_cast<int>(cluster_ctarank()) : 0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
   PipeBars<STAGES>* bars = reinterpret_cast<PipeBars<STAGES>*>(smem + STAGES * kStageBytes);
@@ -117,9 +127,11 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
     prefetch_tmap(&p.b[0]);
     prefetch_tmap(&p.out[cls]);
   }
-  if (warp == 1) tmem_alloc<BN>(&bars->tmem_base);
+  if (warp == 1) {
+    if (TWO) tmem_alloc_pair<BN>(&bars->tmem_base); else tmem_alloc<BN>(&bars->tmem_base);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (TWO) cluster_sync_all(); else __syncthreads();     // pair: the partner's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
   if (threadIdx.x == 0) trace_mark(p, kTrSetup);
@@ -142,6 +154,23 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         const KBlock kb = p.kb[kb0 + i];
         uint8_t* sa = smem + s * kStageBytes;
         uint8_t* sb = sa + kABytes;
+        if (TWO) {
+          // the leader's barrier counts the bytes of BOTH CTAs' loads; each CTA fills its own shared memory
+          if (leader) mbar_expect_tx(&bars->full[s], 2 * kStageBytes);
+          tma_load_4d_pair(&p.a[kb.a_map], &bars->full[s], sa, kb.a_ch, w0 + kb.dw, h0 + kb.dh, n0);
+          if (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BN / 128; ++j)
+              tma_load_3d_pair(&p.b[kb.b_map], &bars->full[s], sb + j * 8192, ntile * BN + (half * (BN / 128) + j) * 64,
+                               kb.tap, kb.b_c0);
+          } else if (p.b_tap_last) {
+            tma_load_3d_pair(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, ntile * BN + half * (BN / 2), kb.tap);
+          } else {
+            tma_load_3d_pair(&p.b[kb.b_map], &bars->full[s], sb, kb.b_c0, kb.tap, ntile * BN + half * (BN / 2));
+          }
+          if (i == 0) trace_mark(p, kTrFirstLoad);
+          continue;
+        }
         mbar_expect_tx(&bars->full[s], kStageBytes);
         tma_load_4d(&p.a[kb.a_map], &bars->full[s], sa, kb.a_ch, w0 + kb.dw, h0 + kb.dh, n0);
         if (B_MN) {
@@ -158,8 +187,8 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, B_MN);
+    if (lane == 0 && leader) {
+      constexpr uint32_t idesc = make_idesc_bf16(TWO ? 256 : 128, BN, false, B_MN);
       for (int i = 0; i < nkb; ++i) {
         const int s = i % STAGES;
         const uint32_t ph = (i / STAGES) & 1;
@@ -172,11 +201,16 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         for (int k = 0; k < 4; ++k) {   // 64-deep reduction chunk = 4 x (K = 16)
           const uint64_t bdesc = B_MN ? make_smem_desc_sw128(b_addr + k * 2048, 8192, 1024)
                                       : make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-          umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 32, 16, 1024), bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+          const uint64_t adesc = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+          if (TWO) umma_bf16_pair(tmem_base, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+          else umma_bf16(tmem_base, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
         }
-        umma_commit(&bars->empty[s]);   // frees the smem slot once these MMAs have read it
+        // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
+        if (TWO) umma_commit_pair(&bars->empty[s]); else umma_commit(&bars->empty[s]);
       }
-      if (nkb > 0) umma_commit(&bars->tmem_full);
+      if (nkb > 0) {
+        if (TWO) umma_commit_pair(&bars->tmem_full); else umma_commit(&bars->tmem_full);
+      }
       trace_mark(p, kTrMmaIssued);
     }
   } else {
@@ -329,9 +363,11 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
     if (et == 0) trace_mark(p, kTrEpiDone);
   }
   tc_fence_before();
-  __syncthreads();
+  if (TWO) cluster_sync_all(); else __syncthreads();     // pair: neither CTA leaves (or frees TMEM) while its partner works
   if (threadIdx.x == 0) trace_mark(p, kTrExit);
-  if (warp == 1) tmem_dealloc<BN>(tmem_base);
+  if (warp == 1) {
+    if (TWO) tmem_dealloc_pair<BN>(tmem_base); else tmem_dealloc<BN>(tmem_base);
+  }
 }
 
 constexpr int kColPatchBytes = 8 * 18 * 128;      // 18432: one 8 x 18-pixel column patch (64 channels)
@@ -932,6 +968,14 @@ static int pick_bn_tile(int out_channels, int pixel_tiles, int classes) {
   return out_channels % 128 == 0 ? 128 : 64;
 }
 
+// CTA pairs (cta_group::2) for 128- and 256-wide channel tiles when the pixel tiles pair up: PMD_GEMM_2CTA=1.
+// Off by default: correct, but measured no faster than one CTA per tile (profiles/r2_conv_cta_pairs.md).
+static int pick_two_cta(int bn_tile, int pixel_tiles) {
+  const char* v = getenv("PMD_GEMM_2CTA");
+  const bool on = v != nullptr && atoi(v) != 0;
+  return (on && bn_tile >= 128 && pixel_tiles % 2 == 0) ? 1 : 0;
+}
+
 int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
                        ConvGemmParams* out) {
   PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
@@ -950,6 +994,7 @@ int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc,
   p.b_tap_last = 0;
   p.out_channels = s.K;
   p.bn_tile = pick_bn_tile(s.K, p.tiles_w * p.tiles_h * p.tiles_n, 1);
+  p.two_cta = pick_two_cta(p.bn_tile, p.tiles_w * p.tiles_h * p.tiles_n);
   p.stats = stats;
   p.addend = nullptr;
   if (s.stride == 1) {
@@ -962,7 +1007,7 @@ int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc,
   {
     const uint64_t dims[3] = {(uint64_t)s.C, (uint64_t)RS, (uint64_t)s.K};
     const uint64_t strides[2] = {(uint64_t)s.C * 2, (uint64_t)RS * s.C * 2};
-    const uint32_t box[3] = {64u, 1u, (uint32_t)p.bn_tile};
+    const uint32_t box[3] = {64u, 1u, (uint32_t)(p.two_cta ? p.bn_tile / 2 : p.bn_tile)};
     if (encode_map(&p.b[0], w_krsc, 3, dims, strides, box)) return -1;
   }
   if (act_map(&p.out[0], y, s.N, Ho, Wo, s.K, 1, 0, 0, p.w_box, p.h_box, p.n_box)) return -1;
@@ -1029,6 +1074,7 @@ int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck
   p.b_tap_last = 1;
   p.out_channels = s.C;
   p.bn_tile = pick_bn_tile(s.C, p.tiles_w * p.tiles_h * p.tiles_n, st * st);
+  p.two_cta = pick_two_cta(p.bn_tile, p.tiles_w * p.tiles_h * p.tiles_n);
   p.stats = nullptr;
   p.addend = static_cast<const __nv_bfloat16*>(addend);
   // A operands: the output-gradient tensors on the (Ho, Wo) grid
@@ -1045,7 +1091,7 @@ int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck
     }
     const uint64_t dims[3] = {(uint64_t)cs.K, (uint64_t)cs.C, (uint64_t)(cs.R * cs.R)};
     const uint64_t strides[2] = {(uint64_t)cs.K * 2, (uint64_t)cs.C * cs.K * 2};
-    const uint32_t box[3] = {64u, (uint32_t)p.bn_tile, 1u};
+    const uint32_t box[3] = {64u, (uint32_t)(p.two_cta ? p.bn_tile / 2 : p.bn_tile), 1u};
     return encode_map(m, w, 3, dims, strides, box);
   };
   if (wmap(&p.b[0], w_rsck, s)) return -1;
@@ -1276,20 +1322,23 @@ static int conv_resident_mode() {
   static const int mode = getenv("PMD_CONV_RESIDENT") == nullptr ? 2 : atoi(getenv("PMD_CONV_RESIDENT"));
   return mode;
 }
-bool conv_resident_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 2; }
+bool conv_resident_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 2 || conv_resident_mode() == 4; }
 bool conv_resident_dgrad_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 3; }
+// mode 4: fprop + only the dgrads that carry no BatchNorm-backward reduction (a block's first convolution)
+bool conv_resident_block_dgrad_enabled() { return conv_resident_dgrad_enabled() || conv_resident_mode() == 4; }
 
-template <int BN, int ST, bool B_MN = false, bool RED = false>
+template <int BN, int ST, bool B_MN = false, bool RED = false, bool TWO = false>
 static int launch_conv_gemm_t(const ConvGemmParams& p, const dim3& grid, cudaStream_t stream) {
-  constexpr int smem = ST * (kABytes + BN * 128) + sizeof(PipeBars<ST>) + 16 + (RED ? sizeof(RedExtra<BN>) : 0) + 1024;
+  constexpr int smem =
+      ST * (kABytes + (TWO ? BN / 2 : BN) * 128) + sizeof(PipeBars<ST>) + 16 + (RED ? sizeof(RedExtra<BN>) : 0) + 1024;
   static PerDevice<bool> ready;
   bool* once = ready.get();
   if (once == nullptr) return -1;
   if (!*once) {
-    if (set_smem(conv_gemm_kernel<BN, ST, B_MN, RED>, smem)) return -1;
+    if (set_smem(conv_gemm_kernel<BN, ST, B_MN, RED, TWO>, smem)) return -1;
     *once = true;
   }
-  PMD_CHECK_CUDA(launch_pdl(conv_gemm_kernel<BN, ST, B_MN, RED>, grid, dim3(kThreads), smem, stream, p));
+  PMD_CHECK_CUDA(launch_pdl_cluster(conv_gemm_kernel<BN, ST, B_MN, RED, TWO>, grid, dim3(kThreads), smem, stream, TWO ? 2 : 1, p));
   return 0;
 }
 
@@ -1337,7 +1386,24 @@ int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
   // shapes, profiles/r1_conv_variants.md, and was removed).  PMD_GEMM64_STAGES / PMD_GEMM128_STAGES in {2,3,4}.
   static const int st64 = stages_from_env("PMD_GEMM64_STAGES", 2), st128 = stages_from_env("PMD_GEMM128_STAGES", 3);
   int rc;
-  if (p.b_mn_major && p.bn_reduce) {
+  if (p.two_cta) {           // CTA pairs: 128- / 256-wide tiles, pixel tiles in pairs along grid.x
+    PMD_REQUIRE(grid.x % 2 == 0 && p.bn_tile >= 128, "internal: CTA-pair kernel needs an even pixel-tile count");
+    // a pair stage is 8 KB (BN = 128) / 16 KB (BN = 256) smaller than a single-CTA stage: room for a deeper ring
+    const int s128 = stages_from_env("PMD_GEMM2_STAGES128", 3), s256 = stages_from_env("PMD_GEMM2_STAGES256", 2);
+    if (p.b_mn_major && p.bn_reduce)
+      rc = s128 == 4 ? launch_conv_gemm_t<128, 4, true, true, true>(p, grid, stream)
+                     : launch_conv_gemm_t<128, 3, true, true, true>(p, grid, stream);
+    else if (p.b_mn_major)
+      rc = p.bn_tile == 128 ? (s128 == 4 ? launch_conv_gemm_t<128, 4, true, false, true>(p, grid, stream)
+                                         : launch_conv_gemm_t<128, 3, true, false, true>(p, grid, stream))
+                            : (s256 == 3 ? launch_conv_gemm_t<256, 3, true, false, true>(p, grid, stream)
+                                         : launch_conv_gemm_t<256, 2, true, false, true>(p, grid, stream));
+    else
+      rc = p.bn_tile == 128 ? (s128 == 4 ? launch_conv_gemm_t<128, 4, false, false, true>(p, grid, stream)
+                                         : launch_conv_gemm_t<128, 3, false, false, true>(p, grid, stream))
+                            : (s256 == 3 ? launch_conv_gemm_t<256, 3, false, false, true>(p, grid, stream)
+                                         : launch_conv_gemm_t<256, 2, false, false, true>(p, grid, stream));
+  } else if (p.b_mn_major && p.bn_reduce) {
     rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true, true>(p, grid, stream)
                          : launch_conv_gemm_t<128, 3, true, true>(p, grid, stream);
   } else if (p.b_mn_major) {

@@ -35,7 +35,8 @@ struct ConvGemmParams {
   int b_tap_last;            // weight-map coordinate order: 0 = (c, tap, n) [KRSC], 1 = (c, n, tap) [RSCK]
   int b_mn_major;            // dgrad straight from KRSC weights: B tile = [64 k][64 c] boxes, MN-major descriptors
   int out_channels;          // total channels of the output tensor
-  int bn_tile;               // 64 or 128
+  int bn_tile;               // 64, 128 or 256
+  int two_cta;               // CTA-pair kernel (tcgen05 cta_group::2): the weight map's box holds bn_tile / 2 rows
   float* stats;              // optional [2 * out_channels]
   const __nv_bfloat16* addend;  // optional NHWC tensor shaped like the (single-class) output
   long long* trace;          // optional [trace_cap][kTraceSlots] per-CTA timestamps (pmd_conv_set_trace), else null
@@ -128,7 +129,8 @@ inline bool conv_resident_supported(const PmdConvShape& s) {
   return conv_tc_supported(s) && s.R == 3 && s.stride == 1 && s.W % 8 == 0 && s.H % 16 == 0 && s.C == 64 && s.K == 64;
 }
 bool conv_resident_enabled();        // fprop
-bool conv_resident_dgrad_enabled();  // dgrad (PMD_CONV_RESIDENT: 2 fprop only [default], 1 both, 0 off, 3 dgrad only)
+bool conv_resident_dgrad_enabled();
+bool conv_resident_block_dgrad_enabled();   // mode 4: also a block's first-convolution dgrad (no fused BN reduction)  // dgrad (PMD_CONV_RESIDENT: 2 fprop only [default], 1 both, 0 off, 3 dgrad only)
 int build_fprop_resident_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
                                 ConvResidentParams* out);
 int build_dgrad_resident_params(const PmdConvShape& s, const void* dy, const void* w_krsc, const void* addend, void* dx,

@@ -408,7 +408,7 @@ Plan* get_plan(PmdEngine* e, int n) {
       if (build_dgrad_params(s0, c0.dy, e->wbf16 + c0.w_off, nullptr, nullptr, nullptr, b.g_out, b.dz_in,
                              &pl->block_dgrad[bi], true))
         return nullptr;
-      if (resident_dgrad && conv_resident_supported(s0)) {
+      if (conv_resident_block_dgrad_enabled() && conv_resident_supported(s0)) {
         if (build_dgrad_resident_params(s0, c0.dy, e->wbf16 + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_r[bi]))
           return nullptr;
         pl->block_resident[bi] = 1;

@@ -244,6 +244,39 @@ CASES['bench512_dgrad_bn_reduce_layer3_conv2'] = lambda: _dgrad_bn_reduce_case(5
 CASES['bench512_dgrad_bn_reduce_layer4_conv2'] = lambda: _dgrad_bn_reduce_case(512, 4, 512, 512, 3)
 
 
+def _with_env(fn, **env):
+    """Runs a case with kernel switches set (the convolution builders read them per call)."""
+    import os
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update({k: str(v) for k, v in env.items()})
+    try:
+        return fn()
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+# CTA-pair kernels (tcgen05 cta_group::2, opt-in with PMD_GEMM_2CTA=1): 128- and 256-wide tiles, K-major and MN-major B,
+# with the fused BatchNorm-backward reduction, stride 1 and 2, small and bench-size grids
+CASES['pair_fprop_layer2_conv2_n512'] = lambda: _with_env(lambda: _fprop_case(512, 16, 128, 128, 3, 1), PMD_GEMM_2CTA=1)
+CASES['pair_fprop_layer3_conv2_n512_bn256'] = lambda: _with_env(lambda: _fprop_case(512, 8, 256, 256, 3, 1), PMD_GEMM_2CTA=1)
+CASES['pair_fprop_layer4_conv1_s2_n512'] = lambda: _with_env(lambda: _fprop_case(512, 8, 256, 512, 3, 2), PMD_GEMM_2CTA=1)
+CASES['pair_fprop_c128_k128_h16_n4'] = lambda: _with_env(lambda: _fprop_case(4, 16, 128, 128, 3, 1), PMD_GEMM_2CTA=1)
+CASES['pair_dgrad_layer3_conv1_shortcut_n512'] = lambda: _with_env(
+    lambda: _dgrad_case(512, 16, 128, 256, 3, 2, 256, krsc=True), PMD_GEMM_2CTA=1)
+CASES['pair_dgrad_krsc_bn256_layer4_conv2_n512'] = lambda: _with_env(
+    lambda: _dgrad_case(512, 4, 512, 512, 3, 1, krsc=True), PMD_GEMM_2CTA=1)
+CASES['pair_dgrad_rsck_c128_h16_addend'] = lambda: _with_env(
+    lambda: _dgrad_case(4, 16, 128, 128, 3, 1, 0, True), PMD_GEMM_2CTA=1)
+CASES['pair_dgrad_bn_reduce_layer2_conv2_n512'] = lambda: _with_env(
+    lambda: _dgrad_bn_reduce_case(512, 16, 128, 128, 3), PMD_GEMM_2CTA=1)
+CASES['pair_dgrad_bn_reduce_deep_ring'] = lambda: _with_env(
+    lambda: _dgrad_bn_reduce_case(16, 8, 256, 256, 3), PMD_GEMM_2CTA=1, PMD_GEMM2_STAGES128=4)
+
+
 # ------------------------------------------------------------------ BatchNorm
 @case('bn_train_forward_backward_c64')
 def _bn_case(C=64, N=8, H=16, relu=True, with_res=True):
