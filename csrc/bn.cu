@@ -77,15 +77,17 @@ __device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
                                             pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
 }
 
-__global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ y, long long rows, int C, float* stats) {
+__global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ y, long long rows, int C, float* stats,
+                                const float* __restrict__ pivot) {
   column_reduce2(
       [&](long long r, int c0, float(&a0)[8], float(&a1)[8]) {
         float v[8];
         load8(y + r * C + c0, v);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          a0[i] += v[i];
-          a1[i] += v[i] * v[i];
+          const float d = v[i] - (pivot != nullptr ? __ldg(pivot + c0 + i) : 0.f);     // sums around the pivot (bn_math.cuh)
+          a0[i] += d;
+          a1[i] += d * d;
         }
       },
       rows, C, stats, stats + C);
@@ -94,7 +96,8 @@ __global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ y, long long r
 __global__ void bn_finalize_kernel(const float* const* __restrict__ stats_ranks, int world, float count_per_rank,
                                    int C, const float* __restrict__ gamma, const float* __restrict__ beta,
                                    float* running_mean, float* running_var, long long* num_batches, float momentum,
-                                   float eps, float* scale, float* shift, float* save_mean, float* save_invstd) {
+                                   float eps, float* scale, float* shift, float* save_mean, float* save_invstd,
+                                   const float* pivot, float* pivot_new) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c == 0 && num_batches != nullptr) *num_batches += 1;
   if (c >= C) return;
@@ -104,20 +107,8 @@ __global__ void bn_finalize_kernel(const float* const* __restrict__ stats_ranks,
     s1 += st[c];
     s2 += st[C + c];
   }
-  const float n = count_per_rank * world;
-  const float mean = s1 / n;
-  const float var = fmaxf(s2 / n - mean * mean, 0.f);
-  const float invstd = rsqrtf(var + eps);
-  const float a = gamma[c] * invstd;
-  scale[c] = a;
-  shift[c] = beta[c] - mean * a;
-  save_mean[c] = mean;
-  save_invstd[c] = invstd;
-  if (running_mean != nullptr) {
-    const float unbiased = var * (n / fmaxf(n - 1.f, 1.f));
-    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
-  }
+  bn_finalize_channel(c, s1, s2, count_per_rank * world, pivot, pivot_new, gamma, beta, running_mean, running_var, momentum,
+                      eps, scale, shift, save_mean, save_invstd);
 }
 
 __global__ void bn_eval_affine_kernel(int C, const float* gamma, const float* beta, const float* rm, const float* rv,
@@ -215,6 +206,8 @@ struct BnFinalizeDev {
   float* running_var;
   long long* nbt;
   float *scale, *shift, *mean, *invstd;
+  const float* pivot;      // statistics were taken around this (null = 0)
+  float* pivot_new;        // receives the batch mean (null: not kept)
 };
 
 template <int RES>
@@ -232,8 +225,9 @@ __global__ void bn_finalize_apply_kernel(BnFinalizeDev f0, BnFinalizeDev f1, flo
     for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) tot[c] = f.stats[c];
     __syncthreads();
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      const float mean = tot[c] / n;
-      const float var = fmaxf(tot[C + c] / n - mean * mean, 0.f);
+      const float d = tot[c] / n;
+      const float mean = (f.pivot != nullptr ? f.pivot[c] : 0.f) + d;        // sums around the pivot (bn_math.cuh)
+      const float var = fmaxf(tot[C + c] / n - d * d, 0.f);
       const float invstd = rsqrtf(var + eps);
       const float a = f.gamma[c] * invstd;
       const float sh = f.beta[c] - mean * a;
@@ -244,6 +238,7 @@ __global__ void bn_finalize_apply_kernel(BnFinalizeDev f0, BnFinalizeDev f1, flo
         f.shift[c] = sh;
         f.mean[c] = mean;
         f.invstd[c] = invstd;
+        if (f.pivot_new != nullptr) f.pivot_new[c] = mean;   // a different array: the other blocks still read f.pivot
         if (f.running_mean != nullptr) {
           const float unbiased = var * (n / fmaxf(n - 1.f, 1.f));
           f.running_mean[c] = (1.f - momentum) * f.running_mean[c] + momentum * mean;
@@ -316,6 +311,8 @@ struct BnBranchDev {
   __nv_bfloat16* dy;
   float* dgamma;
   float* dbeta;
+  float* pivot;             // next step's statistics pivot := pivot_new (this step's batch mean); both may be null
+  const float* pivot_new;
 };
 
 template <int NB, int MASK>
@@ -442,6 +439,8 @@ __global__ void __launch_bounds__(kBlock, NB == 1 ? 3 : 2) bn_bwd_apply_multi_ke
         br.dbeta[c] += br.sums[c];
         br.dgamma[c] += br.sums[C + c];
       }
+      // forward of this step is over and the next one has not begun: the only moment nobody reads the pivot
+      if (blockIdx.x == 0 && br.pivot != nullptr) br.pivot[c] = br.pivot_new[c];
     }
     if (MASK == 2) {
       coef[NB * 3 * C + c] = mscale[c];
@@ -538,28 +537,44 @@ using namespace pmd;
 
 #define BN_CHECK_C(C) PMD_REQUIRE((C) % 8 == 0 && (C) >= 8 && (C) <= 2048, "BatchNorm channel count must be a multiple of 8 in [8, 2048]")
 
+static int bn_stats_impl(const void* d_y, long long rows, int C, float* d_stats, const float* d_pivot, void* stream);
 extern "C" PMD_API int pmd_bn_stats(const void* d_y, long long rows, int C, float* d_stats, void* stream) {
+  return bn_stats_impl(d_y, rows, C, d_stats, nullptr, stream);
+}
+extern "C" PMD_API int pmd_bn_stats_pivot(const void* d_y, long long rows, int C, float* d_stats, const float* d_pivot,
+                                          void* stream) {
+  return bn_stats_impl(d_y, rows, C, d_stats, d_pivot, stream);
+}
+static int bn_stats_impl(const void* d_y, long long rows, int C, float* d_stats, const float* d_pivot, void* stream) {
   BN_CHECK_C(C);
   const int groups = C / 8, rpi = kBlock / groups > 0 ? kBlock / groups : 1;
   PMD_REQUIRE(groups <= kBlock, "C too large for bn_stats");
   const int smem = 2 * rpi * C * 4;
   bn_stats_kernel<<<grid_for(rows, rpi * 4), kBlock, smem, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(d_y), rows, C, d_stats);
+      static_cast<const __nv_bfloat16*>(d_y), rows, C, d_stats, d_pivot);
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
 }
 
+extern "C" PMD_API int pmd_bn_finalize_pivot(const float* const* d_stats_ranks, int world, float count_per_rank, int C,
+                                             const float* d_gamma, const float* d_beta, float* d_running_mean,
+                                             float* d_running_var, long long* d_num_batches, float momentum, float eps,
+                                             float* d_scale, float* d_shift, float* d_mean, float* d_invstd,
+                                             const float* d_pivot, float* d_pivot_new, void* stream) {
+  bn_finalize_kernel<<<ceil_div(C, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      d_stats_ranks, world, count_per_rank, C, d_gamma, d_beta, d_running_mean, d_running_var, d_num_batches, momentum,
+      eps, d_scale, d_shift, d_mean, d_invstd, d_pivot, d_pivot_new);
+  count_launch();
+  PMD_LAUNCH_CHECK();
+  return 0;
+}
 extern "C" PMD_API int pmd_bn_finalize(const float* const* d_stats_ranks, int world, float count_per_rank, int C,
                                const float* d_gamma, const float* d_beta, float* d_running_mean, float* d_running_var,
                                long long* d_num_batches, float momentum, float eps, float* d_scale, float* d_shift,
                                float* d_mean, float* d_invstd, void* stream) {
-  bn_finalize_kernel<<<ceil_div(C, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      d_stats_ranks, world, count_per_rank, C, d_gamma, d_beta, d_running_mean, d_running_var, d_num_batches, momentum,
-      eps, d_scale, d_shift, d_mean, d_invstd);
-  count_launch();
-  PMD_LAUNCH_CHECK();
-  return 0;
+  return pmd_bn_finalize_pivot(d_stats_ranks, world, count_per_rank, C, d_gamma, d_beta, d_running_mean, d_running_var,
+                               d_num_batches, momentum, eps, d_scale, d_shift, d_mean, d_invstd, nullptr, nullptr, stream);
 }
 
 extern "C" PMD_API int pmd_bn_eval_affine(int C, const float* d_gamma, const float* d_beta, const float* d_running_mean,
@@ -606,6 +621,8 @@ static BnBranchDev to_dev(const PmdBnBranch& b) {
   d.dy = static_cast<__nv_bfloat16*>(b.dy);
   d.dgamma = b.dgamma;
   d.dbeta = b.dbeta;
+  d.pivot = b.pivot_new != nullptr ? b.pivot : nullptr;
+  d.pivot_new = b.pivot_new;
   return d;
 }
 
@@ -723,6 +740,8 @@ static BnFinalizeDev to_dev(const PmdBnFinalize& f) {
   d.shift = f.shift;
   d.mean = f.mean;
   d.invstd = f.invstd;
+  d.pivot = f.pivot;
+  d.pivot_new = f.pivot_new;
   return d;
 }
 

@@ -159,15 +159,15 @@ __global__ void bn_finalize_push_kernel(PmdSym s, int slot, const float* __restr
                                         float count_per_rank, int C, const float* __restrict__ gamma,
                                         const float* __restrict__ beta, float* running_mean, float* running_var,
                                         long long* num_batches, float momentum, float eps, float* scale, float* shift,
-                                        float* save_mean, float* save_invstd) {
+                                        float* save_mean, float* save_invstd, const float* pivot, float* pivot_new) {
   extern __shared__ float tot[];     // [2C]
   pdl_wait();
   ll_exchange_sum(s, slot, stats, 2 * C, recv_off, tot);
   if (threadIdx.x == 0 && num_batches != nullptr) *num_batches += 1;
   const float n = count_per_rank * s.world;
   for (int c = threadIdx.x; c < C; c += blockDim.x)
-    bn_finalize_channel(c, tot[c], tot[C + c], n, gamma, beta, running_mean, running_var, momentum, eps, scale, shift,
-                        save_mean, save_invstd);
+    bn_finalize_channel(c, tot[c], tot[C + c], n, pivot, pivot_new, gamma, beta, running_mean, running_var, momentum, eps,
+                        scale, shift, save_mean, save_invstd);
 }
 
 // One or two vectors exchanged by ONE block: both are pushed before either is awaited, so a projection block's pair
@@ -301,12 +301,12 @@ extern "C" PMD_API int pmd_bn_finalize_push(const PmdSym* sym, int slot, const f
                                             float count_per_rank, int C, const float* d_gamma, const float* d_beta,
                                             float* d_running_mean, float* d_running_var, long long* d_num_batches,
                                             float momentum, float eps, float* d_scale, float* d_shift, float* d_mean,
-                                            float* d_invstd, void* stream) {
+                                            float* d_invstd, const float* d_pivot, float* d_pivot_new, void* stream) {
   SYM_CHECK(sym);
   PMD_REQUIRE(2 * C * 4 <= 48 * 1024, "too many channels for the push exchange");
   PMD_CHECK_CUDA(launch_pdl(bn_finalize_push_kernel, dim3(1), dim3(512), 2 * C * 4, static_cast<cudaStream_t>(stream), *sym,
                             slot, d_stats, recv_off, count_per_rank, C, d_gamma, d_beta, d_running_mean, d_running_var,
-                            d_num_batches, momentum, eps, d_scale, d_shift, d_mean, d_invstd));
+                            d_num_batches, momentum, eps, d_scale, d_shift, d_mean, d_invstd, d_pivot, d_pivot_new));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

@@ -46,6 +46,7 @@ struct PipeBars {
   uint64_t empty[STAGES];
   uint64_t tmem_full;
   uint32_t tmem_base;
+  uint32_t invalid_rows[4];   // per epilogue warp (TMEM lane quarter): rows of the tile outside the tensor (zero-filled)
 };
 
 __device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* raw) {
@@ -309,6 +310,10 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         }
       }
     }
+    if (p.stats != nullptr) {
+      const uint32_t inv = __popc(__ballot_sync(0xffffffffu, !valid));
+      if (lane == 0) bars->invalid_rows[q] = inv;
+    }
     fence_proxy_async_smem();
     asm volatile("bar.sync 1, 128;" ::: "memory");
     const int et = threadIdx.x - 64;
@@ -320,20 +325,25 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
       tma_store_commit();
     }
     if (p.stats != nullptr) {
-      // per-channel sum and sum of squares of the bf16-rounded tile: thread -> (channel, half of the rows)
+      // per-channel sum and sum of squares of the bf16-rounded tile, taken around the channel's pivot (see
+      // ConvGemmParams::stat_pivot): thread -> (channel, half of the rows)
       const int c = et & 63, rh = et >> 6;
+      const float ninv = static_cast<float>(bars->invalid_rows[2 * rh] + bars->invalid_rows[2 * rh + 1]);
 #pragma unroll
       for (int hf = 0; hf < BN / 64; ++hf) {
+        const float piv = p.stat_pivot != nullptr ? p.stat_pivot[ntile * BN + hf * 64 + c] : 0.f;
         float s1 = 0.f, s2 = 0.f;
         const uint8_t* base = stage_out + hf * kABytes;
 #pragma unroll 8
         for (int r = rh * 64; r < rh * 64 + 64; ++r) {
           const __nv_bfloat16 hv =
               *reinterpret_cast<const __nv_bfloat16*>(base + r * 128 + (((c >> 3) ^ (r & 7)) << 4) + (c & 7) * 2);
-          const float f = __bfloat162float(hv);
+          const float f = __bfloat162float(hv) - piv;
           s1 += f;
           s2 += f * f;
         }
+        s1 += ninv * piv;            // zero-filled rows outside the tensor were counted as (0 - pivot)
+        s2 -= ninv * piv * piv;
         red_add_f32(p.stats + ntile * BN + hf * 64 + c, s1);
         red_add_f32(p.stats + p.out_channels + ntile * BN + hf * 64 + c, s2);
       }
@@ -530,9 +540,12 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
     const int et = threadIdx.x - 64 - g * 128;     // 0..127 inside the group
     uint8_t* stage_out = smem_out + g * kABytes;
     const int bar_id = 1 + g;
-    float s1[8], s2[8];
+    float s1[8], s2[8], piv[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) s1[i] = s2[i] = 0.f;
+    for (int i = 0; i < 8; ++i) {
+      s1[i] = s2[i] = 0.f;
+      piv[i] = (p.stats != nullptr && p.stat_pivot != nullptr) ? p.stat_pivot[(et & 7) * 8 + i] : 0.f;
+    }
     uint32_t u = 0;
     bool store_pending = false;
     for (int t = blockIdx.x + g * gridDim.x; t < total_tiles; t += 2 * gridDim.x, ++u) {
@@ -599,7 +612,9 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
           const uint32_t hw[4] = {h4.x, h4.y, h4.z, h4.w};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const float2 f = unpack_bf16x2(hw[e]);
+            float2 f = unpack_bf16x2(hw[e]);
+            f.x -= piv[2 * e];
+            f.y -= piv[2 * e + 1];
             s1[2 * e] += f.x;
             s2[2 * e] += f.x * f.x;
             s1[2 * e + 1] += f.y;

@@ -37,7 +37,10 @@ struct ConvGemmParams {
   int out_channels;          // total channels of the output tensor
   int bn_tile;               // 64, 128 or 256
   int two_cta;               // CTA-pair kernel (tcgen05 cta_group::2): the weight map's box holds bn_tile / 2 rows
-  float* stats;              // optional [2 * out_channels]
+  float* stats;              // optional [2 * out_channels]: per channel sum(y - pivot), sum((y - pivot)^2)
+  // Optional [out_channels] pivot of the statistics (null = 0).  E[y^2] - E[y]^2 in fp32 cancels when |mean| >> std;
+  // sums taken around a pivot near the mean do not.  The engine passes the previous step's batch mean.
+  const float* stat_pivot;
   const __nv_bfloat16* addend;  // optional NHWC tensor shaped like the (single-class) output
   long long* trace;          // optional [trace_cap][kTraceSlots] per-CTA timestamps (pmd_conv_set_trace), else null
   int trace_cap;
@@ -110,6 +113,7 @@ struct ConvResidentParams {
   int b_mn;            // dgrad straight from the KRSC weights (MN-major B operand)
   int out_channels;    // 64
   float* stats;
+  const float* stat_pivot;   // as in ConvGemmParams
   const __nv_bfloat16* addend;
   long long* trace;    // optional [trace_cap][kTraceSlots] per-CTA record (kRt* slots), else null
   int trace_cap;

@@ -42,6 +42,7 @@ struct Conv {
   const bf16* x = nullptr;
   bf16 *y = nullptr, *dy = nullptr;
   float *scale = nullptr, *shift = nullptr, *mean = nullptr, *invstd = nullptr;
+  float *pivot = nullptr, *pivot_new = nullptr;   // statistics pivot (previous step's batch mean) and its successor
   float *stats = nullptr, *sums = nullptr, *sums_total = nullptr, *stats_total = nullptr;
   unsigned long long stats_off = 0, sums_off = 0;
   unsigned long long recv_fwd_off = 0, recv_bwd_off = 0;   // push-exchange receive areas (multi-rank SyncBN)
@@ -261,7 +262,9 @@ int allocate(PmdEngine* e) {
     E_CHECK(e->dalloc(&cv.y, out_elems));
     E_CHECK(e->dalloc(&cv.dy, out_elems));
     float* f = nullptr;
-    E_CHECK(e->dalloc(&f, 8LL * cv.s.K));
+    E_CHECK(e->dalloc(&f, 10LL * cv.s.K));
+    cv.pivot = f + 8 * cv.s.K;       // zero-initialised: the first step takes plain sums
+    cv.pivot_new = f + 9 * cv.s.K;
     cv.scale = f;
     cv.shift = f + cv.s.K;
     cv.mean = f + 2 * cv.s.K;
@@ -347,10 +350,12 @@ Plan* get_plan(PmdEngine* e, int n) {
     s.N = n;
     const bf16* w = cv.stem_col ? e->stem_w_pad : e->wbf16 + cv.w_off;
     if (build_fprop_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop)) return nullptr;
+    pl->conv[i].fprop.stat_pivot = cv.pivot;
     pl->conv[i].fprop_eval = pl->conv[i].fprop;
     pl->conv[i].fprop_eval.stats = nullptr;
     if (!cv.stem_col && resident_on && conv_resident_supported(s)) {
       if (build_fprop_resident_params(s, cv.x, w, cv.y, cv.stats, &pl->conv[i].fprop_r)) return nullptr;
+      pl->conv[i].fprop_r.stat_pivot = cv.pivot;
       pl->conv[i].fprop_eval_r = pl->conv[i].fprop_r;
       pl->conv[i].fprop_eval_r.stats = nullptr;
       pl->conv[i].resident = true;
@@ -473,6 +478,8 @@ PmdBnFinalize bn_desc(PmdEngine* e, int ci) {
   f.shift = cv.shift;
   f.mean = cv.mean;
   f.invstd = cv.invstd;
+  f.pivot = cv.pivot;
+  f.pivot_new = cv.pivot_new;
   return f;
 }
 
@@ -484,7 +491,7 @@ int exchange_forward(PmdEngine* e, int ci, long long rows, cudaStream_t st) {
   const PmdEngineConfig& c = e->cfg;
   return pmd_bn_finalize_push(&e->sym, ci, b.stats, b.recv_fwd_off, static_cast<float>(rows), b.s.K, e->param + b.g_off,
                               e->param + b.b_off, b.rm, b.rv, b.nb, c.bn_momentum, c.bn_eps, b.scale, b.shift, b.mean,
-                              b.invstd, st);
+                              b.invstd, b.pivot, b.pivot_new, st);
 }
 
 // z = relu(BN_ci(y_ci) [+ res | + BN_cres(y_cres)]).  Training, one rank: the statistics are finalised inside the
@@ -536,6 +543,8 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
     br[b].dy = cv.dy;
     br[b].dgamma = e->grad + cv.g_off;
     br[b].dbeta = e->grad + cv.b_off;
+    br[b].pivot = cv.pivot;
+    br[b].pivot_new = cv.pivot_new;
   }
   Conv& c0 = e->convs[ci];
   const int mask = z != nullptr ? 1 : 2;
@@ -575,7 +584,7 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
       PmdConvShape s = cv.s;
       s.N = n;
       E_CHECK(pmd_conv_fprop_direct(&s, cv.x_cstride, cv.x, e->wbf16 + cv.w_off, cv.y, st));
-      if (train) E_CHECK(pmd_bn_stats(cv.y, 1LL * n * cv.Ho * cv.Wo, cv.s.K, cv.stats, st));
+      if (train) E_CHECK(pmd_bn_stats_pivot(cv.y, 1LL * n * cv.Ho * cv.Wo, cv.s.K, cv.stats, cv.pivot, st));
     }
     if (train && sync_bn_active(e)) E_CHECK(exchange_forward(e, ci, 1LL * n * cv.Ho * cv.Wo, st));
     return 0;
@@ -959,6 +968,8 @@ extern "C" PMD_API int pmd_engine_set_comm_stub(PmdEngine* e, int mask) {
   if (mask == e->comm_stub) return 0;
   E_CHECK(drop_plans(e));
   e->comm_stub = mask;
+  // the statistics pivots must be identical on every rank whenever sums are exchanged; ranks diverge under a stub
+  for (Conv& cv : e->convs) PMD_CHECK_CUDA(cudaMemset(cv.pivot, 0, 2 * sizeof(float) * cv.s.K));
   return 0;
 }
 

@@ -80,6 +80,16 @@ int pmd_conv_wgrad_direct(const PmdConvShape* s, int x_cstride, const void* d_x,
  * Replaces torch's SyncBatchNorm kernels (ref:main.py:43). */
 /* per-channel sum / sum-of-squares of a bf16 [rows, C] tensor -> d_stats[2C] (accumulates). */
 int pmd_bn_stats(const void* d_y, long long rows, int C, float* d_stats, void* stream);
+/* The same sums taken around a per-channel pivot P (d_pivot[C], NULL = 0): d_stats[c] += sum(y - P),
+ * d_stats[C + c] += sum((y - P)^2).  With P near the channel mean the variance  s2/n - (s1/n)^2  does not suffer the
+ * fp32 cancellation of E[y^2] - E[y]^2 when |mean| >> std (torch's SyncBatchNorm avoids it with Welford merges).
+ * pmd_bn_finalize_pivot consumes such sums (mean = P + s1/n) and can store the batch mean as the next pivot; the
+ * convolution epilogues (pmd_conv_fprop through the engine) produce them the same way.  All ranks must use the same P. */
+int pmd_bn_stats_pivot(const void* d_y, long long rows, int C, float* d_stats, const float* d_pivot, void* stream);
+int pmd_bn_finalize_pivot(const float* const* d_stats_ranks, int world, float count_per_rank, int C,
+                          const float* d_gamma, const float* d_beta, float* d_running_mean, float* d_running_var,
+                          long long* d_num_batches, float momentum, float eps, float* d_scale, float* d_shift,
+                          float* d_mean, float* d_invstd, const float* d_pivot, float* d_pivot_new, void* stream);
 /* Combine statistics and produce the affine the apply kernel uses.
  *   d_stats_ranks: `world` pointers (device array of float*) to each rank's [2C] sums -- with
  *   world == 1 pass a 1-element table.  count_per_rank = rows each rank contributed.
@@ -135,6 +145,10 @@ typedef struct {
   void* dy;             /* apply only */
   float* dgamma;        /* apply only, may be NULL; += */
   float* dbeta;
+  /* pivot rotation (optional, both NULL = off): at the end of a step's backward pass the statistics pivot of the NEXT
+   * step becomes this step's batch mean (pivot[c] = pivot_new[c]); see pmd_bn_stats_pivot */
+  float* pivot;
+  const float* pivot_new;
 } PmdBnBranch;
 int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z, const float* d_mask_scale, const float* d_mask_shift,
                             int mask_mode, const PmdBnBranch* br, int nb, long long rows, int C, void* stream);
@@ -156,6 +170,8 @@ typedef struct {
   float* running_var;
   long long* num_batches;       /* may be NULL */
   float *scale, *shift, *mean, *invstd; /* [C] outputs */
+  const float* pivot;           /* [C] pivot the statistics were taken around (NULL = 0) */
+  float* pivot_new;             /* [C] receives the batch mean (NULL: not kept); must not alias pivot */
 } PmdBnFinalize;
 int pmd_bn_finalize_apply(const PmdBnFinalize* f, const PmdBnFinalize* f_res, float count, float momentum, float eps,
                           const void* d_y, const void* d_res, int relu, void* d_z, long long rows, int C, void* stream);

@@ -123,11 +123,13 @@ int pmd_broadcast(const PmdSym* sym, unsigned long long off, unsigned long long 
  * (Letting that producer's last CTA do the exchange instead was built and measured slower:
  * profiles/r2_syncbn_exchange_placement.md.) */
 #define PMD_LL_RECV_BYTES(world, n) (2ull * (world) * (n) * 8ull)
-/* forward: exchange [sum, sumsq], then finalize like pmd_bn_finalize over the rank-ordered totals */
+/* forward: exchange [sum, sumsq] (taken around d_pivot, which must be identical on every rank; NULL = 0), then
+ * finalize like pmd_bn_finalize over the rank-ordered totals; d_pivot_new (may be NULL) receives the batch mean */
 int pmd_bn_finalize_push(const PmdSym* sym, int slot, const float* d_stats, unsigned long long recv_off,
                          float count_per_rank, int C, const float* d_gamma, const float* d_beta, float* d_running_mean,
                          float* d_running_var, long long* d_num_batches, float momentum, float eps, float* d_scale,
-                         float* d_shift, float* d_mean, float* d_invstd, void* stream);
+                         float* d_shift, float* d_mean, float* d_invstd, const float* d_pivot, float* d_pivot_new,
+                         void* stream);
 /* backward / generic: total[i] = sum over ranks (in rank order) of local[i]; one or two vectors per launch */
 typedef struct {
   const float* local;          /* this rank's vector (any device pointer) */

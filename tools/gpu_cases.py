@@ -327,6 +327,46 @@ CASES['bn_train_forward_backward_c512_norelu'] = lambda: _bn_case(512, 16, 4, Fa
 CASES['bn_train_forward_backward_c2048'] = lambda: _bn_case(2048, 4, 4, True, True)
 
 
+@case('bn_statistics_large_mean_small_std_pivot')
+def _bn_pivot_stress():
+    """|mean| >> std (mean 30, std 0.05, 524,288 rows: the bench's layer1 row count): E[y^2] - E[y]^2 in fp32 cancels
+    (first step, pivot 0: the variance is off by tens of percent), sums taken around the previous step's batch mean
+    do not.  Oracle: torch.var_mean in fp64 over the bf16-rounded tensor.  Also: the fused finalize+apply kernel on
+    pivoted sums, and the pivot rotation at the end of the backward apply."""
+    import ctypes as C
+    from pmdist.ops import _lib
+    from pmdist.ops._lib import check, ptr, stream_ptr
+    lib = _lib.lib()
+    Cc, rows = 64, 524288
+    g = torch.Generator(device='cuda').manual_seed(77)
+    mean_c = 30.0 + torch.randn(Cc, device='cuda', generator=g)
+    y = (mean_c + 0.05 * torch.randn(rows, Cc, device='cuda', generator=g)).to(torch.bfloat16).view(512, 32, 32, Cc)
+    yd = y.double().view(-1, Cc)
+    var_ref, mean_ref = torch.var_mean(yd, dim=0, unbiased=False)
+    gamma, beta = torch.ones(Cc, device='cuda'), torch.zeros(Cc, device='cuda')
+    r = {}
+    pivot = torch.zeros(Cc, device='cuda')
+    errs = []
+    for step in range(2):
+        stats = torch.zeros(2 * Cc, device='cuda')
+        check(lib.pmd_bn_stats_pivot(ptr(y), C.c_longlong(rows), C.c_int(Cc), ptr(stats), ptr(pivot), stream_ptr()))
+        outs = [torch.empty(Cc, device='cuda') for _ in range(4)]
+        pivot_new = torch.empty(Cc, device='cuda')
+        tab = torch.tensor([stats.data_ptr()], dtype=torch.int64, device='cuda')
+        check(lib.pmd_bn_finalize_pivot(ptr(tab), C.c_int(1), C.c_float(rows), C.c_int(Cc), ptr(gamma), ptr(beta), None, None,
+                                        None, C.c_float(0.1), C.c_float(1e-5), ptr(outs[0]), ptr(outs[1]), ptr(outs[2]),
+                                        ptr(outs[3]), ptr(pivot), ptr(pivot_new), stream_ptr()))
+        torch.cuda.synchronize()
+        var_got = (1.0 / outs[3].double() ** 2) - 1e-5
+        errs.append({'mean_abs_err': float((outs[2].double() - mean_ref).abs().max()),
+                     'var_rel_err': float(((var_got - var_ref).abs() / var_ref).max())})
+        pivot = pivot_new
+    r['first_step_pivot0'] = dict(errs[0], ok=errs[0]['mean_abs_err'] < 1e-3)        # informational: the variance is NOT expected to hold
+    r['second_step_pivot_prev_mean'] = dict(errs[1], ok=errs[1]['mean_abs_err'] < 1e-4 and errs[1]['var_rel_err'] < 2e-3)
+    r['ok'] = r['first_step_pivot0']['ok'] and r['second_step_pivot_prev_mean']['ok']
+    return r
+
+
 @case('bn_two_rank_tables_sum_in_rank_order')
 def _bn_two_rank():
     """world=2 pointer tables on one GPU: statistics of two half-batches must combine to the
@@ -532,7 +572,7 @@ def _engine_resident_dataset():
     (la, ea), (lb, eb) = outs
     r['eval_logits_bit_identical'] = {'ok': all(torch.equal(x[0], y[0]) for x, y in zip(ea, eb))}
     same_counts = all(x[1][1:] == y[1][1:] for x, y in zip(ea, eb))             # top-1, top-5, counted samples
-    same_loss = all(abs(x[1][0] - y[1][0]) <= 1e-9 * max(1.0, abs(y[1][0])) for x, y in zip(ea, eb))   # fp64 atomics
+    same_loss = all(abs(x[1][0] - y[1][0]) <= 1e-5 * max(1.0, abs(y[1][0])) for x, y in zip(ea, eb))   # per-block fp32 atomics
     r['eval_metrics_identical'] = {'ok': same_counts and same_loss and sum(x[1][3] for x in ea) == 66,
                                    'counted': [x[1][3] for x in ea]}
     r['train_losses_close'] = {'ok': all(abs(x - y) <= 2e-2 * max(1.0, abs(y)) for x, y in zip(la, lb)) and len(la) == 3,
@@ -717,7 +757,7 @@ def _bn_multi():
     class Br(C.Structure):
         _fields_ = [('y', C.c_void_p), ('mean', C.c_void_p), ('invstd', C.c_void_p), ('gamma', C.c_void_p),
                     ('sums', C.c_void_p), ('totals', C.c_void_p), ('dy', C.c_void_p), ('dgamma', C.c_void_p),
-                    ('dbeta', C.c_void_p)]
+                    ('dbeta', C.c_void_p), ('pivot', C.c_void_p), ('pivot_new', C.c_void_p)]
     lib = _lib.lib()
     Cc, N, H = 128, 8, 8
     rows = N * H * H
@@ -734,7 +774,7 @@ def _bn_multi():
     brs = (Br * 2)()
     for i in range(2):
         brs[i] = Br(ys[i].data_ptr(), fin[i][2].data_ptr(), fin[i][3].data_ptr(), gam[i].data_ptr(), sums[i].data_ptr(), 0,
-                    dys[i].data_ptr(), dgs[2 * i].data_ptr(), dgs[2 * i + 1].data_ptr())
+                    dys[i].data_ptr(), dgs[2 * i].data_ptr(), dgs[2 * i + 1].data_ptr(), 0, 0)
     check(lib.pmd_bn_bwd_reduce_multi(ptr(dz), ptr(z), None, None, C.c_int(1), brs, C.c_int(2), C.c_longlong(rows),
                                       C.c_int(Cc), stream_ptr()))
     check(lib.pmd_bn_bwd_apply_multi(ptr(dz), ptr(z), None, None, C.c_int(1), brs, C.c_int(2), C.c_float(rows), None,
@@ -756,7 +796,7 @@ def _bn_multi():
     for mode, zz, ss, dd in ((1, z1, sA, dyA), (2, None, sB, dyB)):
         b1 = (Br * 1)()
         b1[0] = Br(ys[0].data_ptr(), fin[0][2].data_ptr(), fin[0][3].data_ptr(), gam[0].data_ptr(), ss.data_ptr(), 0,
-                   dd.data_ptr(), 0, 0)
+                   dd.data_ptr(), 0, 0, 0, 0)
         check(lib.pmd_bn_bwd_reduce_multi(ptr(dz), ptr(zz), ptr(fin[0][0]), ptr(fin[0][1]), C.c_int(mode), b1, C.c_int(1),
                                           C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
         check(lib.pmd_bn_bwd_apply_multi(ptr(dz), ptr(zz), ptr(fin[0][0]), ptr(fin[0][1]), C.c_int(mode), b1, C.c_int(1),
@@ -778,7 +818,7 @@ def _bn_fused_fwd():
     class Fin(C.Structure):
         _fields_ = [('stats', C.c_void_p), ('gamma', C.c_void_p), ('beta', C.c_void_p), ('running_mean', C.c_void_p),
                     ('running_var', C.c_void_p), ('num_batches', C.c_void_p), ('scale', C.c_void_p), ('shift', C.c_void_p),
-                    ('mean', C.c_void_p), ('invstd', C.c_void_p)]
+                    ('mean', C.c_void_p), ('invstd', C.c_void_p), ('pivot', C.c_void_p), ('pivot_new', C.c_void_p)]
     lib = _lib.lib()
     Cc, N, H = 128, 8, 8
     rows = N * H * H
@@ -801,13 +841,13 @@ def _bn_fused_fwd():
     for i in range(2):
         fs.append(Fin(stats[i].data_ptr(), gam[i].data_ptr(), bet[i].data_ptr(), rmB[i].data_ptr(), rvB[i].data_ptr(),
                       nbB[i].data_ptr(), outs[i][0].data_ptr(), outs[i][1].data_ptr(), outs[i][2].data_ptr(),
-                      outs[i][3].data_ptr()))
+                      outs[i][3].data_ptr(), 0, 0))
     z = torch.empty_like(ys[0])
     check(lib.pmd_bn_finalize_apply(C.byref(fs[0]), C.byref(fs[1]), C.c_float(rows), C.c_float(0.1), C.c_float(1e-5),
                                     ptr(ys[0]), ptr(ys[1]), C.c_int(1), ptr(z), C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
     z1 = torch.empty_like(ys[0])          # single BatchNorm, plain residual
     f_single = Fin(stats[0].data_ptr(), gam[0].data_ptr(), bet[0].data_ptr(), 0, 0, 0, outs[0][0].data_ptr(),
-                   outs[0][1].data_ptr(), outs[0][2].data_ptr(), outs[0][3].data_ptr())
+                   outs[0][1].data_ptr(), outs[0][2].data_ptr(), outs[0][3].data_ptr(), 0, 0)
     check(lib.pmd_bn_finalize_apply(C.byref(f_single), None, C.c_float(rows), C.c_float(0.1), C.c_float(1e-5),
                                     ptr(ys[0]), ptr(ys[1]), C.c_int(1), ptr(z1), C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
     torch.cuda.synchronize()
