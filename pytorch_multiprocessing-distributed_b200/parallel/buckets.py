@@ -7,7 +7,7 @@ reference's ResNet18 gives 9,990,184 B + 9,622,784 B (SURVEY.md probe:1).
 
 Here the plan is explicit and drives memory layout: all parameters live in ONE flat slab ordered
 by gradient arrival (last layer first), so every bucket is a contiguous byte range of the
-gradient slab and the fused reduce+SGD kernel (csrc/comm_allreduce_sgd.cu) is launched on a range
+gradient slab and the fused reduce+SGD kernel (allreduce_sgd_kernel, csrc/comm.cu) is launched on a range
 as soon as backward has produced it.  ``parity`` caps reproduce torch's bucket sizes exactly
 (tested); the default caps are smaller because over NVSwitch the cost model is launch latency +
 bytes/900 GB/s, not a ring.

@@ -7,7 +7,7 @@ Two transports implement the same ``Comm`` interface:
   * ``TorchComm``  -- torch.distributed (gloo on CPU, NCCL on GPU).  This is the plumbing /
     baseline / oracle transport (BASELINE.json: "a path that only calls NCCL ... is the baseline").
   * ``PeerComm``   -- parallel/peer.py: the product transport, symmetric peer-mapped buffers over
-    NVLink 5 / NVSwitch driven by hand-written kernels (csrc/comm_*.cu).
+    NVLink 5 / NVSwitch driven by hand-written kernels (csrc/comm.cu, csrc/sym.cuh; host side csrc/runtime.cpp).
 The endpoint comes from the launcher's environment (unique per run) instead of a fixed port.
 """
 from __future__ import annotations

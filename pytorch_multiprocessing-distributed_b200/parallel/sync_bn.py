@@ -5,7 +5,7 @@ function behind it (torch:nn/modules/_functions.py:39-179).  torch's SyncBatchNo
 tensors (torch:nn/parallel/distributed.py:2259-2266), which is why the reference cannot run its
 own plumbing config without a GPU; this version is transport-agnostic (any ``Comm``), so the
 2-process gloo configuration keeps synchronised statistics, and it doubles as the multi-rank
-oracle for the fused sm_100a kernels (csrc/bn_*.cu + csrc/comm_small.cu).
+oracle for the fused sm_100a kernels (csrc/bn.cu + the push-exchange kernels of csrc/comm.cu).
 
 Math (identical to torch): forward all-reduces [sum(x), sum(x^2), n] per channel -> global mean,
 biased var for normalisation, unbiased var for ``running_var`` with momentum 0.1; backward
