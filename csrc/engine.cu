@@ -7,7 +7,7 @@
 //   exchange when SyncBN) -> BN apply (+residual, ReLU)]* -> pool+FC -> CE (+metrics) -> backward
 //   (BN reduce / exchange / apply, wgrad straight into the bucket slab, dgrad with the shortcut
 //   branch fused) -> per bucket, as soon as its last gradient exists: fused all-reduce + SGD on a
-//   side stream -> repack dgrad weights.
+//   side stream.
 #include <cstdlib>
 #include <map>
 #include <memory>

@@ -1,5 +1,5 @@
 // SGD (weight decay, momentum, Nesterov) on flat fp32 slabs with the bf16 working copy written in
-// the same pass, plus weight repacking for dgrad.  Replaces optimizer.zero_grad/step's _foreach
+// the same pass.  Replaces optimizer.zero_grad/step's _foreach
 // kernels (ref:main.py:51-55, 108-110; math torch/optim/sgd.py:343-380).  The
 // multi-GPU build folds this update into the gradient all-reduce kernel (comm.cu); this file is the
 // single-GPU path and the shared device function.
@@ -37,19 +37,6 @@ __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, f
   }
 }
 
-__global__ void repack_kernel(const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ wt,
-                              const PmdRepackEntry* __restrict__ table) {
-  const PmdRepackEntry e = table[blockIdx.y];
-  const long long total = static_cast<long long>(e.K) * e.RS * e.C;
-  for (long long o = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; o < total;
-       o += static_cast<long long>(gridDim.x) * blockDim.x) {
-    // destination index o = (rs * C + c) * K + k  (k fastest -> coalesced stores)
-    const int k = static_cast<int>(o % e.K);
-    const long long rc = o / e.K;
-    const int c = static_cast<int>(rc % e.C), rs = static_cast<int>(rc / e.C);
-    wt[e.dst_off + o] = w[e.src_off + (static_cast<long long>(k) * e.RS + rs) * e.C + c];
-  }
-}
 
 __global__ void cast_kernel(const float* __restrict__ s, __nv_bfloat16* __restrict__ d, long long n) {
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
@@ -75,18 +62,6 @@ extern "C" PMD_API int pmd_sgd_step(float* d_param, const float* d_grad, float* 
   return 0;
 }
 
-extern "C" PMD_API int pmd_repack_dgrad_weights(const void* d_w_bf16, void* d_wt_bf16, const PmdRepackEntry* d_table,
-                                        int n_entries, long long max_elems, void* stream) {
-  if (n_entries == 0) return 0;
-  long long bx = ceil_div_ll(max_elems, 256 * 4);
-  if (bx > 256) bx = 256;
-  if (bx < 1) bx = 1;
-  repack_kernel<<<dim3(static_cast<unsigned>(bx), n_entries), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(d_w_bf16), static_cast<__nv_bfloat16*>(d_wt_bf16), d_table);
-  count_launch();
-  PMD_LAUNCH_CHECK();
-  return 0;
-}
 
 extern "C" PMD_API int pmd_cast_f32_to_bf16(const float* d_src, void* d_dst, long long n, void* stream) {
   long long blocks = ceil_div_ll(n, 256 * 4);

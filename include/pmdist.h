@@ -193,15 +193,6 @@ int pmd_pool_fc_bwd(const float* d_dlogits, const float* d_feat, const float* d_
  * in the same pass (ref:main.py:51-55,110; math = torch/optim/sgd.py). */
 int pmd_sgd_step(float* d_param, const float* d_grad, float* d_mom, void* d_param_bf16, long long n, float lr,
                  float momentum, float weight_decay, int nesterov, float grad_scale, void* stream);
-/* bf16 KRSC -> bf16 RSCK repack of every conv weight in one launch (table of {src, dst, K, RS, C}). */
-typedef struct {
-  long long src_off; /* element offset in the bf16 working slab (KRSC) */
-  long long dst_off; /* element offset in the dgrad weight slab (RSCK) */
-  int K, RS, C;
-  int pad_;
-} PmdRepackEntry;
-int pmd_repack_dgrad_weights(const void* d_w_bf16, void* d_wt_bf16, const PmdRepackEntry* d_table, int n_entries,
-                             long long max_elems, void* stream);
 int pmd_cast_f32_to_bf16(const float* d_src, void* d_dst, long long n, void* stream);
 
 /* ------------------------------------------------------------------ input pipeline (data_aug.cu)

@@ -22,11 +22,6 @@ class PmdConvShape(C.Structure):
                 ('R', C.c_int), ('stride', C.c_int)]
 
 
-class PmdRepackEntry(C.Structure):
-    _fields_ = [('src_off', C.c_longlong), ('dst_off', C.c_longlong), ('K', C.c_int), ('RS', C.c_int),
-                ('C', C.c_int), ('pad_', C.c_int)]
-
-
 class NativeError(RuntimeError):
     pass
 

@@ -23,7 +23,7 @@ SIZES = [1 << 10, 4 << 10, 16 << 10, 64 << 10, 256 << 10, 1 << 20, 4 << 20, 9_62
          19_612_968, 64 << 20, 256 << 20]
 
 
-def _worker(rank: int, world: int, out: str, max_bytes: int) -> None:
+def _worker(rank: int, world: int, out: str, max_bytes: int, nvlink_proof: bool = False) -> None:
     import torch
     import torch.distributed as dist
     from pmdist.ops import _lib
@@ -126,9 +126,44 @@ def _worker(rank: int, world: int, out: str, max_bytes: int) -> None:
         push_rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)
+    # ---- NVLink-side proof: the driver's per-link byte counters of THIS rank's GPU around 1000 launches of the
+    # fused-path collective on the whole ResNet18 gradient slab (19.6 MB); expected traffic per GPU = 2 S (W-1)/W
+    # for the two-shot kernel (NVLS: S (W-1)/W up for the in-switch reduction + the multicast stores)
+    proof = None
+    if nvlink_proof:
+        import subprocess
+
+        def counters():
+            r = subprocess.run(['nvidia-smi', 'nvlink', '-gt', 'd', '-i', str(rank)], capture_output=True, text=True)
+            tx = rx = 0
+            for ln in r.stdout.splitlines():
+                p = ln.replace(':', ' ').split()
+                if 'Tx' in p and 'KiB' in p:
+                    tx += int(p[p.index('KiB') - 1])
+                if 'Rx' in p and 'KiB' in p:
+                    rx += int(p[p.index('KiB') - 1])
+            return tx, rx, r.stdout[-400:]
+        n = 19_612_960 // 16 * 4
+        proof = {'bytes': n * 4, 'launches': 1000}
+        for algo in algos[1:]:                      # twoshot, nvls
+            torch.cuda.synchronize()
+            comm.barrier()
+            t0, r0, _ = counters()
+            for _ in range(1000):
+                check(lib.pmd_allreduce_f32(C.byref(comm.sym), C.c_ulonglong(in_off), C.c_ulonglong(out_off), C.c_longlong(n),
+                                            C.c_int(ALGOS[algo]), C.c_int(32), C.c_int(2000), _lib.stream_ptr()))
+            torch.cuda.synchronize()
+            comm.barrier()
+            t1, r1, tail = counters()
+            proof[algo] = {'tx_KiB': t1 - t0, 'rx_KiB': r1 - r0,
+                           'tx_bytes_per_launch': (t1 - t0) * 1024 / 1000, 'rx_bytes_per_launch': (r1 - r0) * 1024 / 1000,
+                           'expected_two_shot_bytes_per_launch_each_way': 2 * n * 4 * (world - 1) / world}
+            if t1 == t0:
+                proof[algo]['raw_tail'] = tail
     if rank == 0:
         with open(out, 'w') as f:
-            json.dump({'world': world, 'transport': comm.describe(), 'rows': rows, 'push_exchange': push_rows}, f, indent=1)
+            json.dump({'world': world, 'transport': comm.describe(), 'rows': rows, 'push_exchange': push_rows,
+                       'nvlink_counters_rank0': proof}, f, indent=1)
     dist.destroy_process_group()
     comm.close()
 
@@ -138,10 +173,11 @@ def main() -> None:
     ap.add_argument('--gpus', type=int, default=2)
     ap.add_argument('--max-mb', type=int, default=256)
     ap.add_argument('--out', default=os.path.join(ROOT, 'gpurun_out', 'allreduce_sweep.json'))
+    ap.add_argument('--nvlink-proof', action='store_true', help='nvidia-smi nvlink byte counters around 1000 launches')
     a = ap.parse_args()
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     from pmdist.parallel import launch
-    launch.spawn(_worker, a.gpus, args=(a.out, a.max_mb << 20), timeout=1200)
+    launch.spawn(_worker, a.gpus, args=(a.out, a.max_mb << 20, a.nvlink_proof), timeout=1200)
 
 
 if __name__ == '__main__':
