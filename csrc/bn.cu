@@ -131,7 +131,8 @@ template <int RES>   // 0: none, 1: plain residual, 2: residual with its own aff
 __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ scale,
                                 const float* __restrict__ shift, const __nv_bfloat16* __restrict__ res,
                                 const float* __restrict__ rscale, const float* __restrict__ rshift, int relu,
-                                __nv_bfloat16* __restrict__ z, long long total8, int C) {
+                                __nv_bfloat16* __restrict__ z, unsigned char* __restrict__ relu_bits, long long total8,
+                                int C) {
   pdl_wait();
   extern __shared__ float aff[];     // [scale | shift | rscale | rshift], C floats each: 2-4 wide shared loads per
   for (int c = threadIdx.x; c < C; c += blockDim.x) {   // 8 elements instead of 16-32 scalar global loads
@@ -165,6 +166,12 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float
       for (int j = 0; j < 8; ++j) o[j] += rv[j];
     }
     if (relu) {
+      if (relu_bits != nullptr) {        // one byte per 8-channel group: which outputs passed the ReLU (read by backward
+        unsigned bits = 0;               // instead of the 16x larger z tensor)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) bits |= (o[j] > 0.f ? 1u : 0u) << j;
+        relu_bits[i] = static_cast<unsigned char>(bits);
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], 0.f);
     }
@@ -214,7 +221,7 @@ template <int RES>
 __global__ void bn_finalize_apply_kernel(BnFinalizeDev f0, BnFinalizeDev f1, float count_per_rank,
                                          float momentum, float eps, const __nv_bfloat16* __restrict__ y,
                                          const __nv_bfloat16* __restrict__ res, int relu, __nv_bfloat16* __restrict__ z,
-                                         long long total8, int C) {
+                                         unsigned char* __restrict__ relu_bits, long long total8, int C) {
   pdl_wait();
   extern __shared__ float aff[];     // [scale | shift | rscale | rshift] (C each) + totals scratch [2C]
   float* tot = aff + 4 * C;
@@ -271,6 +278,12 @@ __global__ void bn_finalize_apply_kernel(BnFinalizeDev f0, BnFinalizeDev f1, flo
       for (int j = 0; j < 8; ++j) o[j] += rv[j];
     }
     if (relu) {
+      if (relu_bits != nullptr) {        // one byte per 8-channel group: which outputs passed the ReLU (read by backward
+        unsigned bits = 0;               // instead of the 16x larger z tensor)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) bits |= (o[j] > 0.f ? 1u : 0u) << j;
+        relu_bits[i] = static_cast<unsigned char>(bits);
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], 0.f);
     }
@@ -349,11 +362,14 @@ bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bflo
       lds8(msm + c0, ms);
       lds8(msm + C + c0, mh);
     }
-    auto body = [&](const float (&gin)[8], const float (&y0)[8], const float (&zin)[8], const float (&y1)[8]) {
+    const unsigned char* zbits = reinterpret_cast<const unsigned char*>(z);     // MASK == 3: one byte per 8-channel group
+    auto body = [&](const float (&gin)[8], const float (&y0)[8], const float (&zin)[8], const float (&y1)[8],
+                    unsigned bits) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         float gv = gin[i];
         if (MASK == 1) gv = zin[i] > 0.f ? gv : 0.f;
+        if (MASK == 3) gv = ((bits >> i) & 1u) ? gv : 0.f;
         if (MASK == 2) gv = fmaf(y0[i], ms[i], mh[i]) > 0.f ? gv : 0.f;
         sg[i] += gv;
         sgy0[i] = fmaf(gv, y0[i], sgy0[i]);
@@ -375,8 +391,13 @@ bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bflo
         load8(b1.y + r * C + c0, y1a);
         load8(b1.y + (r + stride) * C + c0, y1b);
       }
-      body(ga, ya, za, y1a);
-      body(gb, yb, zb, y1b);
+      unsigned ba = 0, bb = 0;
+      if (MASK == 3) {
+        ba = zbits[r * groups + g];
+        bb = zbits[(r + stride) * groups + g];
+      }
+      body(ga, ya, za, y1a, ba);
+      body(gb, yb, zb, y1b, bb);
     }
     for (; r < rows; r += stride) {
       float ga[8], ya[8], za[8], y1a[8];
@@ -384,7 +405,7 @@ bn_bwd_reduce_multi_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bflo
       load8(b0.y + r * C + c0, ya);
       if (MASK == 1) load8(z + r * C + c0, za);
       if (NB == 2) load8(b1.y + r * C + c0, y1a);
-      body(ga, ya, za, y1a);
+      body(ga, ya, za, y1a, MASK == 3 ? zbits[r * groups + g] : 0u);
     }
     // block reduction scratch: [v][rl][c], v = 0: S_g, 1: S_gy0, 2: S_gy1
 #pragma unroll
@@ -464,9 +485,14 @@ __global__ void __launch_bounds__(kBlock, NB == 1 ? 3 : 2) bn_bwd_apply_multi_ke
     lds8(coef + NB * 3 * C + c0, ms);
     lds8(coef + NB * 3 * C + C + c0, mh);
   }
+  const unsigned char* zbits = reinterpret_cast<const unsigned char*>(z);     // MASK == 3: one byte per 8-channel group
   auto one = [&](long long i, float (&gv)[8], const float (&y0)[8], const float (&zv)[8], const float (&y1)[8]) {
     float o[8];
-    if (MASK == 1) {
+    if (MASK == 3) {
+      const unsigned bits = zbits[i];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) gv[j] = ((bits >> j) & 1u) ? gv[j] : 0.f;
+    } else if (MASK == 1) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) gv[j] = zv[j] > 0.f ? gv[j] : 0.f;
     } else if (MASK == 2) {
@@ -586,28 +612,35 @@ extern "C" PMD_API int pmd_bn_eval_affine(int C, const float* d_gamma, const flo
   return 0;
 }
 
-extern "C" PMD_API int pmd_bn_apply(const void* d_y, const float* d_scale, const float* d_shift, const void* d_res,
-                            const float* d_res_scale, const float* d_res_shift, int relu, void* d_z, long long rows,
-                            int C, void* stream) {
+extern "C" PMD_API int pmd_bn_apply_bits(const void* d_y, const float* d_scale, const float* d_shift, const void* d_res,
+                                         const float* d_res_scale, const float* d_res_shift, int relu, void* d_z,
+                                         void* d_relu_bits, long long rows, int C, void* stream) {
   BN_CHECK_C(C);
   const long long total8 = rows * C / 8;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const __nv_bfloat16* y = static_cast<const __nv_bfloat16*>(d_y);
   const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(d_res);
   __nv_bfloat16* z = static_cast<__nv_bfloat16*>(d_z);
+  unsigned char* bits = static_cast<unsigned char*>(d_relu_bits);
   const int blk = fixed_block(C);
   if (d_res == nullptr)
     PMD_CHECK_CUDA(launch_pdl(bn_apply_kernel<0>, dim3(wave_grid(bn_apply_kernel<0>, blk, 2 * C * 4, total8, blk * 2)), dim3(blk),
-                              2 * C * 4, st, y, d_scale, d_shift, nullptr, nullptr, nullptr, relu, z, total8, C));
+                              2 * C * 4, st, y, d_scale, d_shift, nullptr, nullptr, nullptr, relu, z, bits, total8, C));
   else if (d_res_scale == nullptr)
     PMD_CHECK_CUDA(launch_pdl(bn_apply_kernel<1>, dim3(wave_grid(bn_apply_kernel<1>, blk, 2 * C * 4, total8, blk * 2)), dim3(blk),
-                              2 * C * 4, st, y, d_scale, d_shift, res, nullptr, nullptr, relu, z, total8, C));
+                              2 * C * 4, st, y, d_scale, d_shift, res, nullptr, nullptr, relu, z, bits, total8, C));
   else
     PMD_CHECK_CUDA(launch_pdl(bn_apply_kernel<2>, dim3(wave_grid(bn_apply_kernel<2>, blk, 4 * C * 4, total8, blk * 2)), dim3(blk),
-                              4 * C * 4, st, y, d_scale, d_shift, res, d_res_scale, d_res_shift, relu, z, total8, C));
+                              4 * C * 4, st, y, d_scale, d_shift, res, d_res_scale, d_res_shift, relu, z, bits, total8, C));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" PMD_API int pmd_bn_apply(const void* d_y, const float* d_scale, const float* d_shift, const void* d_res,
+                            const float* d_res_scale, const float* d_res_shift, int relu, void* d_z, long long rows,
+                            int C, void* stream) {
+  return pmd_bn_apply_bits(d_y, d_scale, d_shift, d_res, d_res_scale, d_res_shift, relu, d_z, nullptr, rows, C, stream);
 }
 
 static BnBranchDev to_dev(const PmdBnBranch& b) {
@@ -636,6 +669,7 @@ static cudaError_t launch_reduce(int mask, int smem, cudaStream_t st, const __nv
                     st, dz, z, ms, mh, b0, b1, rows, C)
   if (mask == 0) PMD_RED(0);
   if (mask == 1) PMD_RED(1);
+  if (mask == 3) PMD_RED(3);
   PMD_RED(2);
 #undef PMD_RED
 }
@@ -645,8 +679,8 @@ extern "C" PMD_API int pmd_bn_bwd_reduce_multi(const void* d_dz, const void* d_z
                                                long long rows, int C, void* stream) {
   BN_CHECK_C(C);
   PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
-  PMD_REQUIRE(mask_mode >= 0 && mask_mode <= 2, "mask mode must be 0, 1 or 2");
-  PMD_REQUIRE(mask_mode != 1 || d_z != nullptr, "mask mode 1 needs z");
+  PMD_REQUIRE(mask_mode >= 0 && mask_mode <= 3, "mask mode must be 0, 1, 2 or 3");
+  PMD_REQUIRE((mask_mode != 1 && mask_mode != 3) || d_z != nullptr, "mask modes 1 and 3 need z (mode 3: the ReLU bit array)");
   PMD_REQUIRE(mask_mode != 2 || (d_mask_scale != nullptr && d_mask_shift != nullptr), "mask mode 2 needs the forward affine");
   const int groups = C / 8, rpi = kBlock / groups > 0 ? kBlock / groups : 1;
   PMD_REQUIRE(groups <= kBlock, "C too large for bn_bwd_reduce");
@@ -675,6 +709,7 @@ static cudaError_t launch_apply(int mask, int smem, cudaStream_t st, const __nv_
     cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
     cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
     cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+    cudaFuncSetAttribute(bn_bwd_apply_multi_kernel<NB, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
     *once = true;
   }
   const int blk = fixed_block(C);
@@ -684,6 +719,7 @@ static cudaError_t launch_apply(int mask, int smem, cudaStream_t st, const __nv_
                     dz, z, ms, mh, b0, b1, count, g_out, total8, C)
   if (mask == 0) PMD_APP(0);
   if (mask == 1) PMD_APP(1);
+  if (mask == 3) PMD_APP(3);
   PMD_APP(2);
 #undef PMD_APP
 }
@@ -693,7 +729,8 @@ extern "C" PMD_API int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z,
                                               float count_total, void* d_g_out, long long rows, int C, void* stream) {
   BN_CHECK_C(C);
   PMD_REQUIRE(nb == 1 || nb == 2, "1 or 2 BatchNorm branches");
-  PMD_REQUIRE(mask_mode >= 0 && mask_mode <= 2, "mask mode must be 0, 1 or 2");
+  PMD_REQUIRE(mask_mode >= 0 && mask_mode <= 3, "mask mode must be 0, 1, 2 or 3");
+  PMD_REQUIRE((mask_mode != 1 && mask_mode != 3) || d_z != nullptr, "mask modes 1 and 3 need z (mode 3: the ReLU bit array)");
   const long long total8 = rows * C / 8;
   const BnBranchDev b0 = to_dev(br[0]), b1 = to_dev(br[nb - 1]);
   const int smem = (nb * 3 + 2) * C * 4;
@@ -715,7 +752,8 @@ extern "C" PMD_API int pmd_bn_bwd_apply_multi(const void* d_dz, const void* d_z,
 template <int RES>
 static cudaError_t launch_finalize_apply(int smem, cudaStream_t st, const BnFinalizeDev& f0, const BnFinalizeDev& f1,
                                          float count, float momentum, float eps, const __nv_bfloat16* y,
-                                         const __nv_bfloat16* res, int relu, __nv_bfloat16* z, long long total8, int C) {
+                                         const __nv_bfloat16* res, int relu, __nv_bfloat16* z, unsigned char* bits,
+                                         long long total8, int C) {
   static PerDevice<bool> ready;
   bool* once = ready.get();
   if (once == nullptr) return cudaErrorInvalidDevice;
@@ -725,7 +763,7 @@ static cudaError_t launch_finalize_apply(int smem, cudaStream_t st, const BnFina
   }
   const int blk = fixed_block(C);
   return launch_pdl(bn_finalize_apply_kernel<RES>, dim3(wave_grid(bn_finalize_apply_kernel<RES>, blk, smem, total8, blk * 2)),
-                    dim3(blk), smem, st, f0, f1, count, momentum, eps, y, res, relu, z, total8, C);
+                    dim3(blk), smem, st, f0, f1, count, momentum, eps, y, res, relu, z, bits, total8, C);
 }
 
 static BnFinalizeDev to_dev(const PmdBnFinalize& f) {
@@ -748,6 +786,13 @@ static BnFinalizeDev to_dev(const PmdBnFinalize& f) {
 extern "C" PMD_API int pmd_bn_finalize_apply(const PmdBnFinalize* f, const PmdBnFinalize* f_res, float count,
                                              float momentum, float eps, const void* d_y, const void* d_res, int relu,
                                              void* d_z, long long rows, int C, void* stream) {
+  return pmd_bn_finalize_apply_bits(f, f_res, count, momentum, eps, d_y, d_res, relu, d_z, nullptr, rows, C, stream);
+}
+
+extern "C" PMD_API int pmd_bn_finalize_apply_bits(const PmdBnFinalize* f, const PmdBnFinalize* f_res, float count,
+                                                  float momentum, float eps, const void* d_y, const void* d_res, int relu,
+                                                  void* d_z, void* d_relu_bits, long long rows, int C, void* stream) {
+  unsigned char* bits = static_cast<unsigned char*>(d_relu_bits);
   BN_CHECK_C(C);
   PMD_REQUIRE(f != nullptr, "missing BatchNorm description");
   PMD_REQUIRE(f_res == nullptr || d_res != nullptr, "a residual BatchNorm needs the residual tensor");
@@ -760,11 +805,11 @@ extern "C" PMD_API int pmd_bn_finalize_apply(const PmdBnFinalize* f, const PmdBn
   const BnFinalizeDev f0 = to_dev(*f), f1 = to_dev(f_res != nullptr ? *f_res : *f);
   const int resmode = f_res != nullptr ? 2 : (d_res != nullptr ? 1 : 0);
   if (resmode == 0)
-    PMD_CHECK_CUDA(launch_finalize_apply<0>(smem, st, f0, f1, count, momentum, eps, y, res, relu, z, total8, C));
+    PMD_CHECK_CUDA(launch_finalize_apply<0>(smem, st, f0, f1, count, momentum, eps, y, res, relu, z, bits, total8, C));
   else if (resmode == 1)
-    PMD_CHECK_CUDA(launch_finalize_apply<1>(smem, st, f0, f1, count, momentum, eps, y, res, relu, z, total8, C));
+    PMD_CHECK_CUDA(launch_finalize_apply<1>(smem, st, f0, f1, count, momentum, eps, y, res, relu, z, bits, total8, C));
   else
-    PMD_CHECK_CUDA(launch_finalize_apply<2>(smem, st, f0, f1, count, momentum, eps, y, res, relu, z, total8, C));
+    PMD_CHECK_CUDA(launch_finalize_apply<2>(smem, st, f0, f1, count, momentum, eps, y, res, relu, z, bits, total8, C));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

@@ -1370,7 +1370,7 @@ static int stages_from_env(const char* name, int dflt) {
 int attach_bn_reduce(ConvGemmParams* p, const PmdConvShape& s, const void* y, const float* scale, const float* shift,
                      const float* mean, const float* invstd, float* sums) {
   static const bool on = getenv("PMD_DGRAD_BN_REDUCE") == nullptr || atoi(getenv("PMD_DGRAD_BN_REDUCE")) != 0;
-  if (!on || !p->b_mn_major || p->n_classes != 1 || p->addend != nullptr || s.stride != 1) return 0;
+  if (!on || !p->b_mn_major || p->n_classes != 1 || s.stride != 1) return 0;   // (an addend is summed in before the mask)
   if (p->out_channels % 256 == 0 && p->bn_tile == 256) {
     // the y tile does not fit beside a 256-wide output staging area: fall back to 128-wide tiles for this dgrad
     p->bn_tile = 128;
@@ -1531,15 +1531,23 @@ extern "C" PMD_API int pmd_conv_dgrad_krsc(const PmdConvShape* s, const void* d_
   return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
 }
 
-extern "C" PMD_API int pmd_conv_dgrad_bn_reduce(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const void* d_y_prev,
-                                                const float* d_scale, const float* d_shift, const float* d_mean,
-                                                const float* d_invstd, float* d_sums, void* d_dz, void* stream) {
+extern "C" PMD_API int pmd_conv_dgrad_bn_reduce_addend(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc,
+                                                       const void* d_addend, const void* d_y_prev, const float* d_scale,
+                                                       const float* d_shift, const float* d_mean, const float* d_invstd,
+                                                       float* d_sums, void* d_dz, void* stream) {
   ConvGemmParams p;
-  if (build_dgrad_params(*s, d_dy, d_w_krsc, nullptr, nullptr, nullptr, nullptr, d_dz, &p, true)) return -1;
+  if (build_dgrad_params(*s, d_dy, d_w_krsc, nullptr, nullptr, nullptr, d_addend, d_dz, &p, true)) return -1;
   const int rc = attach_bn_reduce(&p, *s, d_y_prev, d_scale, d_shift, d_mean, d_invstd, d_sums);
   if (rc < 0) return -1;
   PMD_REQUIRE(rc == 1, "this dgrad cannot carry the BatchNorm reduction (needs stride 1, C % 64 == 0, and the fusion enabled)");
   return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" PMD_API int pmd_conv_dgrad_bn_reduce(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const void* d_y_prev,
+                                                const float* d_scale, const float* d_shift, const float* d_mean,
+                                                const float* d_invstd, float* d_sums, void* d_dz, void* stream) {
+  return pmd_conv_dgrad_bn_reduce_addend(s, d_dy, d_w_krsc, nullptr, d_y_prev, d_scale, d_shift, d_mean, d_invstd, d_sums, d_dz,
+                                         stream);
 }
 
 extern "C" PMD_API int pmd_conv_wgrad(const PmdConvShape* s, const void* d_x, const void* d_dy, float* d_dw_krsc, int split_k,

@@ -59,6 +59,7 @@ struct Block {
   bf16* z_mid[2] = {nullptr, nullptr};
   bf16* dz_mid[2] = {nullptr, nullptr};
   bf16 *z_out = nullptr, *dz_out = nullptr, *g_out = nullptr;
+  unsigned char* zbits = nullptr;   // ReLU bit array of z_out (one bit per element): backward's mask instead of z_out
   int Hin = 0, Hout = 0, Cin = 0, Cout = 0;
 };
 
@@ -78,6 +79,7 @@ struct Plan {
   std::vector<ConvResidentParams> block_dgrad_r, inner_dgrad_r;
   std::vector<char> block_resident, inner_resident;
   std::vector<char> inner_reduced;          // inner dgrad also does the BatchNorm-backward reduction of the layer below
+  bool stem_reduced = false;                // the first block's dgrad does it for the stem's BatchNorm
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_launches = 0, eval_launches = 0;
   bool train_warm = false, eval_warm = false;
@@ -153,6 +155,8 @@ struct PmdEngine {
 };
 
 namespace {
+
+bool relu_bits_enabled();
 
 int build_topology(PmdEngine* e) {
   const PmdEngineConfig& c = e->cfg;
@@ -318,10 +322,18 @@ int allocate(PmdEngine* e) {
     E_CHECK(e->dalloc(&b.z_out, oel));
     E_CHECK(e->dalloc(&b.dz_out, oel));
     if (b.sc < 0) E_CHECK(e->dalloc(&b.g_out, oel));
+    if (relu_bits_enabled()) E_CHECK(e->dalloc(&b.zbits, oel / 8));
     z_prev = b.z_out;
     dz_prev = b.dz_out;
   }
   return 0;
+}
+
+// PMD_BN_RELU_BITS=0: the block-output BatchNorm backward reads z (16 bits per element) for its ReLU mask instead of
+// the bit array the forward apply leaves behind (1 bit per element).
+bool relu_bits_enabled() {
+  static const bool on = getenv("PMD_BN_RELU_BITS") == nullptr || atoi(getenv("PMD_BN_RELU_BITS")) != 0;
+  return on;
 }
 
 // Multi-rank SyncBatchNorm is in effect (and not stubbed out for a communication-free timing run).
@@ -417,6 +429,14 @@ Plan* get_plan(PmdEngine* e, int n) {
         if (build_dgrad_resident_params(s0, c0.dy, e->wbf16 + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_r[bi]))
           return nullptr;
         pl->block_resident[bi] = 1;
+      } else if (bi == 0) {
+        // dz_stem is consumed only by the stem's BatchNorm backward (mask recomputed from y_stem): this dgrad's
+        // epilogue (accumulator + identity-shortcut addend) masks it and accumulates the two channel sums
+        Conv& stem = e->convs[0];
+        const int rc = attach_bn_reduce(&pl->block_dgrad[bi], s0, stem.y, stem.scale, stem.shift, stem.mean, stem.invstd,
+                                        stem.sums);
+        if (rc < 0) return nullptr;
+        pl->stem_reduced = rc == 1;
       }
     }
   }
@@ -497,15 +517,17 @@ int exchange_forward(PmdEngine* e, int ci, long long rows, cudaStream_t st) {
 // z = relu(BN_ci(y_ci) [+ res | + BN_cres(y_cres)]).  Training, one rank: the statistics are finalised inside the
 // apply kernel.  Training, multi-rank SyncBatchNorm: exchange_forward() has finalised them, only the plain apply
 // remains.  Evaluation uses the running statistics.
-int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long long rows, bool train, cudaStream_t st) {
+int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long long rows, bool train, cudaStream_t st,
+                  unsigned char* bits = nullptr) {
+  if (!train) bits = nullptr;
   Conv& cv = e->convs[ci];
   const PmdEngineConfig& c = e->cfg;
   if (train && !sync_bn_active(e)) {
     const PmdBnFinalize f = bn_desc(e, ci);
     PmdBnFinalize fr{};
     if (cres >= 0) fr = bn_desc(e, cres);
-    return pmd_bn_finalize_apply(&f, cres >= 0 ? &fr : nullptr, static_cast<float>(rows), c.bn_momentum, c.bn_eps, cv.y,
-                                 cres >= 0 ? e->convs[cres].y : res, 1, z, rows, cv.s.K, st);
+    return pmd_bn_finalize_apply_bits(&f, cres >= 0 ? &fr : nullptr, static_cast<float>(rows), c.bn_momentum, c.bn_eps, cv.y,
+                                      cres >= 0 ? e->convs[cres].y : res, 1, z, bits, rows, cv.s.K, st);
   }
   if (!train) {
     E_CHECK(pmd_bn_eval_affine(cv.s.K, e->param + cv.g_off, e->param + cv.b_off, cv.rm, cv.rv, c.bn_eps, cv.scale, cv.shift, st));
@@ -516,9 +538,9 @@ int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long
   }
   if (cres >= 0) {
     Conv& cr = e->convs[cres];
-    return pmd_bn_apply(cv.y, cv.scale, cv.shift, cr.y, cr.scale, cr.shift, 1, z, rows, cv.s.K, st);
+    return pmd_bn_apply_bits(cv.y, cv.scale, cv.shift, cr.y, cr.scale, cr.shift, 1, z, bits, rows, cv.s.K, st);
   }
-  return pmd_bn_apply(cv.y, cv.scale, cv.shift, res, nullptr, nullptr, 1, z, rows, cv.s.K, st);
+  return pmd_bn_apply_bits(cv.y, cv.scale, cv.shift, res, nullptr, nullptr, 1, z, bits, rows, cv.s.K, st);
 }
 
 // BatchNorm backward of conv `ci` (and, for a projection block's output, of the shortcut conv `cj`
@@ -526,7 +548,7 @@ int bn_apply_step(PmdEngine* e, int ci, int cres, const bf16* res, bf16* z, long
 // (block outputs, where a residual was added before the ReLU) or is recomputed from y (z == nullptr).
 // already_reduced: the dgrad that produced dz accumulated the sums (and masked dz) in its epilogue.
 int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, long long rows, bf16* g_out,
-                cudaStream_t st, bool already_reduced = false) {
+                cudaStream_t st, bool already_reduced = false, const unsigned char* zbits = nullptr) {
   const bool sync = sync_bn_active(e);
   const int nb = cj >= 0 ? 2 : 1;
   PmdBnBranch br[2];
@@ -547,7 +569,11 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
     br[b].pivot_new = cv.pivot_new;
   }
   Conv& c0 = e->convs[ci];
-  const int mask = z != nullptr ? 1 : 2;
+  int mask = z != nullptr ? 1 : 2;
+  if (zbits != nullptr) {        // the forward apply recorded which outputs passed the ReLU: 1/16 of the bytes of z
+    mask = 3;
+    z = reinterpret_cast<const bf16*>(zbits);
+  }
   if (!already_reduced) E_CHECK(pmd_bn_bwd_reduce_multi(dz, z, c0.scale, c0.shift, mask, br, nb, rows, c0.s.K, st));
   if (sync) {
     // one push-exchange kernel; a projection block's two [2C] vectors leave in the same NVLink trip
@@ -615,7 +641,7 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
     if (sc_done != nullptr) PMD_CHECK_CUDA(cudaStreamWaitEvent(st, sc_done, 0));
     Conv& last = e->convs[b.main[b.n_main - 1]];
     E_CHECK(bn_apply_step(e, b.main[b.n_main - 1], b.sc, b.sc >= 0 ? nullptr : b.z_in, b.z_out,
-                          1LL * n * last.Ho * last.Wo, train, st));
+                          1LL * n * last.Ho * last.Wo, train, st, b.zbits));
   }
   Block& lb = e->blocks.back();
   E_CHECK(pmd_pool_fc_fwd(lb.z_out, n, lb.Hout * lb.Hout, lb.Cout, e->param + c.fc_w_off, e->param + c.fc_b_off,
@@ -678,7 +704,7 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     Block& b = e->blocks[bi];
     const int last = b.main[b.n_main - 1];
     const long long rows_out = 1LL * n * b.Hout * b.Hout;
-    E_CHECK(bn_backward(e, last, b.sc, b.dz_out, b.z_out, rows_out, b.g_out, st));
+    E_CHECK(bn_backward(e, last, b.sc, b.dz_out, b.z_out, rows_out, b.g_out, st, false, b.zbits));
     E_CHECK(bn_done(last));
     if (b.sc >= 0) E_CHECK(bn_done(b.sc));
     for (int j = b.n_main - 1; j >= 1; --j) {
@@ -716,7 +742,7 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
   }
   {
     Conv& cv = e->convs[0];
-    E_CHECK(bn_backward(e, 0, -1, e->dz_stem, nullptr, 1LL * n * cv.Ho * cv.Wo, nullptr, st));
+    E_CHECK(bn_backward(e, 0, -1, e->dz_stem, nullptr, 1LL * n * cv.Ho * cv.Wo, nullptr, st, pl->stem_reduced));
     E_CHECK(bn_done(0));
     E_CHECK(dy_ready());
     E_CHECK(wgrad(0));

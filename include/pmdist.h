@@ -56,6 +56,11 @@ int pmd_conv_dgrad_krsc(const PmdConvShape* s, const void* d_dy, const void* d_w
 int pmd_conv_dgrad_bn_reduce(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const void* d_y_prev,
                              const float* d_scale, const float* d_shift, const float* d_mean, const float* d_invstd,
                              float* d_sums, void* d_dz, void* stream);
+/* The same with an addend tensor (an identity shortcut's gradient, shaped like d_dz) summed in before the mask:
+ * the first residual block's dgrad, whose output feeds only the stem's BatchNorm backward. */
+int pmd_conv_dgrad_bn_reduce_addend(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const void* d_addend,
+                                    const void* d_y_prev, const float* d_scale, const float* d_shift, const float* d_mean,
+                                    const float* d_invstd, float* d_sums, void* d_dz, void* stream);
 /* dw (fp32, KRSC) += x^T * dy, reduction over all N*Ho*Wo pixels split over `split_k` CTAs per
  * output tile (0 = choose); partial tiles are added with red.global.add.f32, so d_dw is an
  * accumulator the caller zeroes (it is a slice of the flat gradient bucket slab). */
@@ -106,6 +111,12 @@ int pmd_bn_eval_affine(int C, const float* d_gamma, const float* d_beta, const f
 int pmd_bn_apply(const void* d_y, const float* d_scale, const float* d_shift, const void* d_res,
                  const float* d_res_scale, const float* d_res_shift, int relu, void* d_z, long long rows, int C,
                  void* stream);
+/* The same, also recording WHICH outputs passed the ReLU: d_relu_bits = uint8 [rows * C / 8], bit j of byte i set iff
+ * element 8 i + j was > 0 before clamping.  The backward kernels take this array as their mask (mask_mode 3) instead of
+ * reading the 16x larger z tensor (threshold_backward fused into the BatchNorm backward). */
+int pmd_bn_apply_bits(const void* d_y, const float* d_scale, const float* d_shift, const void* d_res,
+                      const float* d_res_scale, const float* d_res_shift, int relu, void* d_z, void* d_relu_bits,
+                      long long rows, int C, void* stream);
 /* backward reduce: g = dz * (z > 0 if relu); d_sums[0..C) += sum(g), d_sums[C..2C) += sum(g * xhat),
  * xhat = (y - mean) * invstd. */
 int pmd_bn_bwd_reduce(const void* d_dz, const void* d_z, const void* d_y, const float* d_mean, const float* d_invstd,
@@ -134,7 +145,8 @@ int pmd_bn_bwd_apply_static(const void* d_dz, const void* d_z, const void* d_y, 
 
 /* One or two BatchNorms that share the incoming gradient dz and its ReLU mask (a residual block's last
  * main-path BN and its projection-shortcut BN) handled in one pass each.  mask_mode: 0 none, 1 z > 0,
- * 2 recomputed as mask_scale*y0 + mask_shift > 0 from branch 0's forward affine (no read of z). */
+ * 2 recomputed as mask_scale*y0 + mask_shift > 0 from branch 0's forward affine (no read of z),
+ * 3 d_z is the ReLU bit array written by pmd_bn_apply_bits / pmd_bn_finalize_apply_bits (uint8 [rows * C / 8]). */
 typedef struct {
   const void* y;        /* conv output this BN normalised (bf16 NHWC) */
   const float* mean;
@@ -175,6 +187,9 @@ typedef struct {
 } PmdBnFinalize;
 int pmd_bn_finalize_apply(const PmdBnFinalize* f, const PmdBnFinalize* f_res, float count, float momentum, float eps,
                           const void* d_y, const void* d_res, int relu, void* d_z, long long rows, int C, void* stream);
+int pmd_bn_finalize_apply_bits(const PmdBnFinalize* f, const PmdBnFinalize* f_res, float count, float momentum, float eps,
+                               const void* d_y, const void* d_res, int relu, void* d_z, void* d_relu_bits, long long rows,
+                               int C, void* stream);   /* + ReLU bit array, see pmd_bn_apply_bits */
 
 /* ------------------------------------------------------------------ head + loss (head.cu)
  * Global average pool + Linear, cross-entropy with top-1/top-5 counters (ref:model/resnet.py:102-104,

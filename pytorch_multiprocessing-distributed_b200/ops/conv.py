@@ -73,14 +73,14 @@ def conv_dgrad(dy: torch.Tensor, w: torch.Tensor, x_shape: Tuple[int, int, int, 
 
 def conv_dgrad_bn_reduce(dy: torch.Tensor, w_krsc: torch.Tensor, y_prev: torch.Tensor, scale: torch.Tensor,
                          shift: torch.Tensor, mean: torch.Tensor, invstd: torch.Tensor,
-                         sums: torch.Tensor) -> torch.Tensor:
+                         sums: torch.Tensor, addend: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Stride-1 dgrad whose epilogue applies the ReLU mask of the layer below and accumulates that layer's
     BatchNorm-backward sums (``pmd_conv_dgrad_bn_reduce``).  ``y_prev`` is that layer's pre-BN output [N,H,W,C]."""
     K, R = w_krsc.shape[0], w_krsc.shape[1]
     dz = torch.empty_like(y_prev)
     s = _shape(tuple(y_prev.shape), K, R, 1)
-    check(_lib.lib().pmd_conv_dgrad_bn_reduce(C.byref(s), ptr(dy), ptr(w_krsc), ptr(y_prev), ptr(scale), ptr(shift), ptr(mean),
-                                              ptr(invstd), ptr(sums), ptr(dz), stream_ptr()))
+    check(_lib.lib().pmd_conv_dgrad_bn_reduce_addend(C.byref(s), ptr(dy), ptr(w_krsc), ptr(addend), ptr(y_prev), ptr(scale),
+                                                     ptr(shift), ptr(mean), ptr(invstd), ptr(sums), ptr(dz), stream_ptr()))
     return dz
 
 

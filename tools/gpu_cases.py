@@ -153,7 +153,7 @@ for _name, _args in {
                                                 addend=(a[7] if len(a) > 7 else False), krsc=True))
 
 
-def _dgrad_bn_reduce_case(N, H, C, K, R):
+def _dgrad_bn_reduce_case(N, H, C, K, R, addend=False):
     """dgrad + BatchNorm-backward reduction in one kernel vs plain PyTorch fp32: masked dz and both channel sums."""
     from pmdist.ops import conv as cv
     dy = _rand_bf16(N, H, H, K, seed=11)
@@ -165,9 +165,12 @@ def _dgrad_bn_reduce_case(N, H, C, K, R):
     mean = torch.randn(C, device='cuda', generator=g) * 0.1
     invstd = torch.rand(C, device='cuda', generator=g) + 0.5
     sums = torch.zeros(2 * C, device='cuda')
-    dz = cv.conv_dgrad_bn_reduce(dy, cv.krsc_from_torch(w), y_prev, scale, shift, mean, invstd, sums)
+    add = _rand_bf16(N, H, H, C, seed=15) if addend else None
+    dz = cv.conv_dgrad_bn_reduce(dy, cv.krsc_from_torch(w), y_prev, scale, shift, mean, invstd, sums, addend=add)
     torch.cuda.synchronize()
     ref = _dgrad_ref(dy, w, (N, H, H, C), 1)
+    if addend:
+        ref = ref + add.float()
     yf = y_prev.float()
     mask = (yf * scale + shift) > 0
     ref = torch.where(mask, ref, torch.zeros_like(ref))
@@ -238,6 +241,8 @@ CASES['bench512_dgrad_layer2_conv1_shortcut'] = lambda: _dgrad_case(512, 32, 64,
 CASES['bench512_dgrad_layer3_conv1_shortcut'] = lambda: _dgrad_case(512, 16, 128, 256, 3, 2, 256, krsc=True)
 CASES['bench512_dgrad_layer4_conv1_shortcut'] = lambda: _dgrad_case(512, 8, 256, 512, 3, 2, 512, krsc=True)
 # inner dgrads (conv2 of every block) also do the BatchNorm-backward reduction of bn1
+CASES['bench512_dgrad_bn_reduce_addend_layer1_conv1_stem'] = lambda: _dgrad_bn_reduce_case(512, 32, 64, 64, 3, addend=True)
+CASES['dgrad_bn_reduce_addend_c128_h16_n3'] = lambda: _dgrad_bn_reduce_case(3, 16, 128, 128, 3, addend=True)
 CASES['bench512_dgrad_bn_reduce_layer1_conv2'] = lambda: _dgrad_bn_reduce_case(512, 32, 64, 64, 3)
 CASES['bench512_dgrad_bn_reduce_layer2_conv2'] = lambda: _dgrad_bn_reduce_case(512, 16, 128, 128, 3)
 CASES['bench512_dgrad_bn_reduce_layer3_conv2'] = lambda: _dgrad_bn_reduce_case(512, 8, 256, 256, 3)
@@ -364,6 +369,62 @@ def _bn_pivot_stress():
     r['first_step_pivot0'] = dict(errs[0], ok=errs[0]['mean_abs_err'] < 1e-3)        # informational: the variance is NOT expected to hold
     r['second_step_pivot_prev_mean'] = dict(errs[1], ok=errs[1]['mean_abs_err'] < 1e-4 and errs[1]['var_rel_err'] < 2e-3)
     r['ok'] = r['first_step_pivot0']['ok'] and r['second_step_pivot_prev_mean']['ok']
+    return r
+
+
+@case('bn_relu_bits_mask_equals_z_mask')
+def _bn_relu_bits():
+    """The forward apply's ReLU bit array (1 bit per element) must be exactly (z > 0), and the backward kernels must
+    produce the same sums and gradients from it (mask_mode 3) as from z (mask_mode 1), for one and two branches."""
+    import ctypes as C
+    from pmdist.ops import _lib, nn as nk
+    from pmdist.ops._lib import check, ptr, stream_ptr
+
+    class Br(C.Structure):
+        _fields_ = [('y', C.c_void_p), ('mean', C.c_void_p), ('invstd', C.c_void_p), ('gamma', C.c_void_p),
+                    ('sums', C.c_void_p), ('totals', C.c_void_p), ('dy', C.c_void_p), ('dgamma', C.c_void_p),
+                    ('dbeta', C.c_void_p), ('pivot', C.c_void_p), ('pivot_new', C.c_void_p)]
+    lib = _lib.lib()
+    r = {}
+    for Cc, N, H, nb in ((64, 16, 32, 1), (128, 8, 16, 2), (512, 8, 4, 2)):
+        rows = N * H * H
+        ys = [(_rand_bf16(N, H, H, Cc, seed=50 + i) * 1.3 + 0.2).to(torch.bfloat16) for i in range(2)]
+        gam = [torch.rand(Cc, device='cuda') + 0.5 for _ in range(2)]
+        bet = [torch.randn(Cc, device='cuda') * 0.1 for _ in range(2)]
+        fin = [nk.bn_finalize([nk.bn_stats(y)], float(rows), g, b, None, None, None) for y, g, b in zip(ys, gam, bet)]
+        z = torch.empty_like(ys[0])
+        bits = torch.zeros(rows * Cc // 8, dtype=torch.uint8, device='cuda')
+        if nb == 2:
+            check(lib.pmd_bn_apply_bits(ptr(ys[0]), ptr(fin[0][0]), ptr(fin[0][1]), ptr(ys[1]), ptr(fin[1][0]), ptr(fin[1][1]),
+                                        C.c_int(1), ptr(z), ptr(bits), C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
+        else:
+            check(lib.pmd_bn_apply_bits(ptr(ys[0]), ptr(fin[0][0]), ptr(fin[0][1]), ptr(ys[1]), None, None,
+                                        C.c_int(1), ptr(z), ptr(bits), C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
+        torch.cuda.synchronize()
+        want = ((z.view(-1, 8) > 0).to(torch.int32) << torch.arange(8, device='cuda', dtype=torch.int32)).sum(1).to(torch.uint8)
+        tag = f'c{Cc}_nb{nb}'
+        r[f'bits_exact_{tag}'] = {'ok': bool(torch.equal(bits, want))}
+        dz = _rand_bf16(N, H, H, Cc, seed=60)
+        outs = {}
+        for mode, mask_src in ((1, z), (3, bits)):
+            sums = [torch.zeros(2 * Cc, device='cuda') for _ in range(nb)]
+            dys = [torch.empty_like(ys[0]) for _ in range(nb)]
+            gout = torch.empty_like(ys[0])
+            brs = (Br * nb)()
+            for i in range(nb):
+                brs[i] = Br(ys[i].data_ptr(), fin[i][2].data_ptr(), fin[i][3].data_ptr(), gam[i].data_ptr(), sums[i].data_ptr(), 0,
+                            dys[i].data_ptr(), 0, 0, 0, 0)
+            check(lib.pmd_bn_bwd_reduce_multi(ptr(dz), ptr(mask_src), None, None, C.c_int(mode), brs, C.c_int(nb),
+                                              C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
+            check(lib.pmd_bn_bwd_apply_multi(ptr(dz), ptr(mask_src), None, None, C.c_int(mode), brs, C.c_int(nb),
+                                             C.c_float(rows), ptr(gout), C.c_longlong(rows), C.c_int(Cc), stream_ptr()))
+            torch.cuda.synchronize()
+            outs[mode] = (sums, dys, gout)
+        r[f'g_out_exact_{tag}'] = {'ok': bool(torch.equal(outs[1][2], outs[3][2]))}
+        for i in range(nb):
+            r[f'sums{i}_{tag}'] = _cmp(outs[3][0][i], outs[1][0][i], 1e-5)
+            r[f'dy{i}_{tag}'] = _cmp(outs[3][1][i], outs[1][1][i], 1e-3)
+    r['ok'] = all(v['ok'] for v in r.values())
     return r
 
 
