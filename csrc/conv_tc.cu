@@ -91,7 +91,11 @@ struct RedExtra {          // extra shared state of the RED (dgrad + BatchNorm-b
 // partner's shared memory.  Per-CTA operand traffic out of shared memory drops from 4 KB + BN*32 B to 4 KB + BN*16 B
 // per k-step (BN = 128: 128 -> 96 B/clk, under the SM's 128 B/clk) and the weight slice crosses L2 -> SM once per
 // pair instead of once per CTA.  Epilogues stay per CTA (each holds its 128 accumulator rows in its own TMEM).
-template <int BN, int STAGES, bool B_MN = false, bool RED = false, bool TWO = false>
+// RED: 0 plain; 1 = the dgrad also does the BatchNorm-backward reduction of the layer below, ReLU mask recomputed from
+// that layer's y (inner BatchNorms); 2 = the same for a residual block's OUTPUT BatchNorm(s): the mask comes from the
+// ReLU bit array the forward apply recorded, one or two branches (main path + projection shortcut) share it, and the
+// dgrad may be strided (one parity view of y per class).
+template <int BN, int STAGES, bool B_MN = false, int RED = 0, bool TWO = false>
 __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
   constexpr int kBBytes = (TWO ? BN / 2 : BN) * 128;      // this CTA's share of the weight slice
   constexpr int kStageBytes = kABytes + kBBytes;
@@ -102,7 +106,8 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
   uint8_t* smem = align_smem_1024(smem_raw);
   PipeBars<STAGES>* bars = reinterpret_cast<PipeBars<STAGES>*>(smem + STAGES * kStageBytes);
   RedExtra<BN>* rx = reinterpret_cast<RedExtra<BN>*>(reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBars<STAGES>) + 15) & ~15));
-  static_assert(!RED || STAGES * kStageBytes >= 2 * (BN / 64) * kABytes, "y tile does not fit beside the output staging");
+  static_assert(RED == 0 || STAGES * kStageBytes >= (RED + 1) * (BN / 64) * kABytes,
+                "the y tile(s) do not fit beside the output staging");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cls = blockIdx.z, ntile = blockIdx.y;
@@ -137,7 +142,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
   const uint32_t tmem_base = bars->tmem_base;
   if (threadIdx.x == 0) trace_mark(p, kTrSetup);
   pdl_wait();        // everything above is private to this CTA; operands below come from the previous kernel
-  if (RED) {
+  if (RED == 1) {
     for (int c = threadIdx.x; c < BN; c += kThreads) {
       rx->sc[c] = p.red_scale[ntile * BN + c];
       rx->sh[c] = p.red_shift[ntile * BN + c];
@@ -234,14 +239,27 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
     if (threadIdx.x == 64) trace_mark(p, kTrAccReady);
     uint8_t* stage_out = smem;           // pipeline buffers are idle now: reuse them as the store staging
     uint8_t* stage_y = smem + (BN / 64) * kABytes;
+    uint8_t* stage_y2 = stage_y + (BN / 64) * kABytes;   // RED == 2 with two branches: the shortcut conv's y tile
+    const int red_nb = RED == 2 ? p.red_nb : 1;
     if (RED) {
-      if (threadIdx.x == 64) {           // every MMA has completed (tmem_full): the ring can take the y tile
-        mbar_expect_tx(&rx->y_full, (BN / 64) * kABytes);
+      if (threadIdx.x == 64) {           // every MMA has completed (tmem_full): the ring can take the y tile(s)
+        mbar_expect_tx(&rx->y_full, red_nb * (BN / 64) * kABytes);
 #pragma unroll
         for (int hf = 0; hf < BN / 64; ++hf)
-          tma_load_4d(&p.ymap, &rx->y_full, stage_y + hf * kABytes, ntile * BN + hf * 64, w0, h0, n0);
+          tma_load_4d(&p.ymap[RED == 2 ? cls : 0], &rx->y_full, stage_y + hf * kABytes, ntile * BN + hf * 64, w0, h0, n0);
+        if (RED == 2 && red_nb == 2) {
+#pragma unroll
+          for (int hf = 0; hf < BN / 64; ++hf)
+            tma_load_4d(&p.ymap2[cls], &rx->y_full, stage_y2 + hf * kABytes, ntile * BN + hf * 64, w0, h0, n0);
+        }
       }
       mbar_wait(&rx->y_full, 0);
+    }
+    const unsigned char* bits_row = nullptr;   // RED == 2: this row's bytes of the ReLU bit array (full-resolution pixel)
+    if (RED == 2 && valid) {
+      const int st = p.red_stride, ph = cls / st, pw = cls % st;
+      const long long pix = (static_cast<long long>(n0 + ni) * p.red_H + (st * (h0 + hi) + ph)) * p.red_W + (st * (w0 + wi) + pw);
+      bits_row = p.red_bits + (pix * p.out_channels + ntile * BN) / 8;
     }
 #pragma unroll
     for (int hf = 0; hf < BN / 64; ++hf) {
@@ -274,7 +292,18 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
           for (int j = 0; j < 16; ++j)
             packed[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
         }
-        if (RED) {
+        if (RED == 2) {
+          // ReLU mask of the block output this gradient belongs to: 32 channels = 4 bytes of the bit array
+          const uint32_t m = bits_row != nullptr ? *reinterpret_cast<const uint32_t*>(bits_row + (hf * 64 + cc * 32) / 8) : 0u;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            float2 gf = unpack_bf16x2(packed[j]);
+            if (!((m >> (2 * j)) & 1u)) gf.x = 0.f;
+            if (!((m >> (2 * j + 1)) & 1u)) gf.y = 0.f;
+            packed[j] = pack_bf16x2(gf.x, gf.y);
+          }
+        }
+        if (RED == 1) {
           // ReLU mask of the layer below, recomputed from its pre-activation y: g = (scale*y + shift > 0) ? dz : 0
           const uint8_t* yrow = stage_y + hf * kABytes + row * 128;
 #pragma unroll
@@ -353,9 +382,10 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
       const int c = et & 63, rh = et >> 6;
 #pragma unroll
       for (int hf = 0; hf < BN / 64; ++hf) {
-        float s1 = 0.f, s2 = 0.f;
+        float s1 = 0.f, s2 = 0.f, s3 = 0.f;
         const uint8_t* gb = stage_out + hf * kABytes;
         const uint8_t* yb = stage_y + hf * kABytes;
+        const uint8_t* yb2 = stage_y2 + hf * kABytes;
 #pragma unroll 8
         for (int r = rh * 64; r < rh * 64 + 64; ++r) {
           const int off = r * 128 + (((c >> 3) ^ (r & 7)) << 4) + (c & 7) * 2;
@@ -363,10 +393,16 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
           const float yv = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(yb + off));
           s1 += g;
           s2 = fmaf(g, yv, s2);
+          if (RED == 2 && red_nb == 2)
+            s3 = fmaf(g, __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(yb2 + off)), s3);
         }
         const int ch = ntile * BN + hf * 64 + c;
         red_add_f32(p.red_sums + ch, s1);
         red_add_f32(p.red_sums + p.out_channels + ch, (s2 - p.red_mean[ch] * s1) * p.red_invstd[ch]);
+        if (RED == 2 && red_nb == 2) {
+          red_add_f32(p.red_sums2 + ch, s1);
+          red_add_f32(p.red_sums2 + p.out_channels + ch, (s3 - p.red_mean2[ch] * s1) * p.red_invstd2[ch]);
+        }
       }
     }
     if (et == 0) tma_store_wait_read0();
@@ -1342,7 +1378,7 @@ bool conv_resident_dgrad_enabled() { return conv_resident_mode() == 1 || conv_re
 // mode 4: fprop + only the dgrads that carry no BatchNorm-backward reduction (a block's first convolution)
 bool conv_resident_block_dgrad_enabled() { return conv_resident_dgrad_enabled() || conv_resident_mode() == 4; }
 
-template <int BN, int ST, bool B_MN = false, bool RED = false, bool TWO = false>
+template <int BN, int ST, bool B_MN = false, int RED = 0, bool TWO = false>
 static int launch_conv_gemm_t(const ConvGemmParams& p, const dim3& grid, cudaStream_t stream) {
   constexpr int smem =
       ST * (kABytes + (TWO ? BN / 2 : BN) * 128) + sizeof(PipeBars<ST>) + 16 + (RED ? sizeof(RedExtra<BN>) : 0) + 1024;
@@ -1378,13 +1414,43 @@ int attach_bn_reduce(ConvGemmParams* p, const PmdConvShape& s, const void* y, co
   if (p->bn_tile != 64 && p->bn_tile != 128) return 0;
   for (int i = 0; i < p->kb_count[0]; ++i)
     if (p->kb[p->kb_begin[0] + i].a_map != 0) return 0;    // fused shortcut branch: two A tensors, not handled
-  if (act_map(&p->ymap, y, s.N, s.H, s.W, s.C, 1, 0, 0, p->w_box, p->h_box, p->n_box)) return -1;
+  if (act_map(&p->ymap[0], y, s.N, s.H, s.W, s.C, 1, 0, 0, p->w_box, p->h_box, p->n_box)) return -1;
   p->red_scale = scale;
   p->red_shift = shift;
   p->red_mean = mean;
   p->red_invstd = invstd;
   p->red_sums = sums;
   p->bn_reduce = 1;
+  return 1;
+}
+
+int attach_block_bn_reduce(ConvGemmParams* p, const PmdConvShape& s, const unsigned char* relu_bits, int nb, const void* y0,
+                           const float* mean0, const float* invstd0, float* sums0, const void* y1, const float* mean1,
+                           const float* invstd1, float* sums1) {
+  static const bool on = getenv("PMD_DGRAD_BN_REDUCE") == nullptr || atoi(getenv("PMD_DGRAD_BN_REDUCE")) != 0;
+  if (!on || !p->b_mn_major || relu_bits == nullptr || (nb != 1 && nb != 2) || s.C % 64 != 0) return 0;
+  if (p->out_channels % 256 == 0 && p->bn_tile == 256) p->bn_tile = 128;   // staging + y tile(s) must fit the ring
+  if (p->bn_tile != 64 && p->bn_tile != 128) return 0;
+  p->two_cta = 0;
+  const int st = s.stride;
+  for (int ph = 0; ph < st; ++ph)
+    for (int pw = 0; pw < st; ++pw) {
+      if (act_map(&p->ymap[ph * st + pw], y0, s.N, s.H, s.W, s.C, st, ph, pw, p->w_box, p->h_box, p->n_box)) return -1;
+      if (nb == 2 && act_map(&p->ymap2[ph * st + pw], y1, s.N, s.H, s.W, s.C, st, ph, pw, p->w_box, p->h_box, p->n_box)) return -1;
+    }
+  p->red_nb = nb;
+  p->red_stride = st;
+  p->red_H = s.H;
+  p->red_W = s.W;
+  p->red_bits = relu_bits;
+  p->red_mean = mean0;
+  p->red_invstd = invstd0;
+  p->red_sums = sums0;
+  p->red_mean2 = mean1;
+  p->red_invstd2 = invstd1;
+  p->red_sums2 = sums1;
+  p->red_scale = p->red_shift = nullptr;
+  p->bn_reduce = 2;
   return 1;
 }
 
@@ -1406,21 +1472,24 @@ int launch_conv_gemm(const ConvGemmParams& p_in, cudaStream_t stream) {
     // a pair stage is 8 KB (BN = 128) / 16 KB (BN = 256) smaller than a single-CTA stage: room for a deeper ring
     const int s128 = stages_from_env("PMD_GEMM2_STAGES128", 3), s256 = stages_from_env("PMD_GEMM2_STAGES256", 2);
     if (p.b_mn_major && p.bn_reduce)
-      rc = s128 == 4 ? launch_conv_gemm_t<128, 4, true, true, true>(p, grid, stream)
-                     : launch_conv_gemm_t<128, 3, true, true, true>(p, grid, stream);
+      rc = s128 == 4 ? launch_conv_gemm_t<128, 4, true, 1, true>(p, grid, stream)
+                     : launch_conv_gemm_t<128, 3, true, 1, true>(p, grid, stream);
     else if (p.b_mn_major)
-      rc = p.bn_tile == 128 ? (s128 == 4 ? launch_conv_gemm_t<128, 4, true, false, true>(p, grid, stream)
-                                         : launch_conv_gemm_t<128, 3, true, false, true>(p, grid, stream))
-                            : (s256 == 3 ? launch_conv_gemm_t<256, 3, true, false, true>(p, grid, stream)
-                                         : launch_conv_gemm_t<256, 2, true, false, true>(p, grid, stream));
+      rc = p.bn_tile == 128 ? (s128 == 4 ? launch_conv_gemm_t<128, 4, true, 0, true>(p, grid, stream)
+                                         : launch_conv_gemm_t<128, 3, true, 0, true>(p, grid, stream))
+                            : (s256 == 3 ? launch_conv_gemm_t<256, 3, true, 0, true>(p, grid, stream)
+                                         : launch_conv_gemm_t<256, 2, true, 0, true>(p, grid, stream));
     else
-      rc = p.bn_tile == 128 ? (s128 == 4 ? launch_conv_gemm_t<128, 4, false, false, true>(p, grid, stream)
-                                         : launch_conv_gemm_t<128, 3, false, false, true>(p, grid, stream))
-                            : (s256 == 3 ? launch_conv_gemm_t<256, 3, false, false, true>(p, grid, stream)
-                                         : launch_conv_gemm_t<256, 2, false, false, true>(p, grid, stream));
+      rc = p.bn_tile == 128 ? (s128 == 4 ? launch_conv_gemm_t<128, 4, false, 0, true>(p, grid, stream)
+                                         : launch_conv_gemm_t<128, 3, false, 0, true>(p, grid, stream))
+                            : (s256 == 3 ? launch_conv_gemm_t<256, 3, false, 0, true>(p, grid, stream)
+                                         : launch_conv_gemm_t<256, 2, false, 0, true>(p, grid, stream));
+  } else if (p.b_mn_major && p.bn_reduce == 2) {
+    rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true, 2>(p, grid, stream)
+                         : launch_conv_gemm_t<128, 3, true, 2>(p, grid, stream);
   } else if (p.b_mn_major && p.bn_reduce) {
-    rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true, true>(p, grid, stream)
-                         : launch_conv_gemm_t<128, 3, true, true>(p, grid, stream);
+    rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true, 1>(p, grid, stream)
+                         : launch_conv_gemm_t<128, 3, true, 1>(p, grid, stream);
   } else if (p.b_mn_major) {
     rc = p.bn_tile == 64 ? launch_conv_gemm_t<64, 2, true>(p, grid, stream)
                          : (p.bn_tile == 128 ? launch_conv_gemm_t<128, 3, true>(p, grid, stream)
@@ -1548,6 +1617,21 @@ extern "C" PMD_API int pmd_conv_dgrad_bn_reduce(const PmdConvShape* s, const voi
                                                 const float* d_invstd, float* d_sums, void* d_dz, void* stream) {
   return pmd_conv_dgrad_bn_reduce_addend(s, d_dy, d_w_krsc, nullptr, d_y_prev, d_scale, d_shift, d_mean, d_invstd, d_sums, d_dz,
                                          stream);
+}
+
+extern "C" PMD_API int pmd_conv_dgrad_block_bn_reduce(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc,
+                                                      const PmdConvShape* s2, const void* d_dy2, const void* d_w2_krsc,
+                                                      const void* d_addend, const unsigned char* d_relu_bits, int nb,
+                                                      const void* d_y0, const float* d_mean0, const float* d_invstd0,
+                                                      float* d_sums0, const void* d_y1, const float* d_mean1,
+                                                      const float* d_invstd1, float* d_sums1, void* d_dx, void* stream) {
+  ConvGemmParams p;
+  if (build_dgrad_params(*s, d_dy, d_w_krsc, s2, d_dy2, d_w2_krsc, d_addend, d_dx, &p, true)) return -1;
+  const int rc = attach_block_bn_reduce(&p, *s, d_relu_bits, nb, d_y0, d_mean0, d_invstd0, d_sums0, d_y1, d_mean1, d_invstd1,
+                                        d_sums1);
+  if (rc < 0) return -1;
+  PMD_REQUIRE(rc == 1, "this dgrad cannot carry the block-output BatchNorm reduction");
+  return launch_conv_gemm(p, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" PMD_API int pmd_conv_wgrad(const PmdConvShape* s, const void* d_x, const void* d_dy, float* d_dw_krsc, int split_k,

@@ -48,11 +48,19 @@ struct ConvGemmParams {
   // layer's activation z = relu(BN(y)).  The epilogue loads the y tile, applies the ReLU mask to dz before storing
   // it and accumulates per channel  sum(g), sum(g * xhat)  into red_sums -- exactly what the stand-alone
   // bn_bwd_reduce kernel would compute from a second pass over dz and y.
-  int bn_reduce;
-  CUtensorMap ymap;                      // y of that BatchNorm, same shape and box as the output
+  int bn_reduce;                         // 0 off, 1 inner BatchNorm (mask from y), 2 block-output BatchNorm(s) (mask from bits)
+  CUtensorMap ymap[4];                   // y of that BatchNorm, same shape and box as the output (mode 2: one parity view per class)
   const float *red_scale, *red_shift;    // forward affine (mask = scale*y + shift > 0)
   const float *red_mean, *red_invstd;
   float* red_sums;                       // [2 * out_channels], accumulated with red.global.add
+  // mode 2 (attach_block_bn_reduce): the gradient this dgrad produces is dL/dz of a residual block's output
+  // z = relu(BN(y) + BN_sc(y_sc) | + identity); its mask is the ReLU bit array of z, and up to two BatchNorms reduce it
+  int red_nb;                            // 1 or 2 branches
+  int red_stride, red_H, red_W;          // output (= z) geometry: class (ph, pw) pixel (h, w) is z pixel (stride*h + ph, stride*w + pw)
+  const unsigned char* red_bits;         // uint8 [N * red_H * red_W * out_channels / 8]
+  CUtensorMap ymap2[4];                  // the shortcut convolution's y (second branch)
+  const float *red_mean2, *red_invstd2;
+  float* red_sums2;
 };
 
 // Per-CTA trace record written by the fprop/dgrad kernels when tracing is on (tools/conv_trace.py decodes it).
@@ -153,6 +161,11 @@ int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, flo
 // Returns 1 if attached, 0 if this dgrad cannot take it (the caller then runs the stand-alone reduce), -1 on error.
 int attach_bn_reduce(ConvGemmParams* p, const PmdConvShape& s, const void* y, const float* scale, const float* shift,
                      const float* mean, const float* invstd, float* sums);
+// The same for the BatchNorm(s) that produced a residual block's OUTPUT, fused into the dgrad of the NEXT block's first
+// convolution (any stride, with or without a fused projection-shortcut dgrad / addend).  nb = 1: y1 etc. null.
+int attach_block_bn_reduce(ConvGemmParams* p, const PmdConvShape& s, const unsigned char* relu_bits, int nb, const void* y0,
+                           const float* mean0, const float* invstd0, float* sums0, const void* y1, const float* mean1,
+                           const float* invstd1, float* sums1);
 int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream);
 int launch_wgrad(const WgradParams& p, cudaStream_t stream);
 

@@ -80,6 +80,7 @@ struct Plan {
   std::vector<char> block_resident, inner_resident;
   std::vector<char> inner_reduced;          // inner dgrad also does the BatchNorm-backward reduction of the layer below
   bool stem_reduced = false;                // the first block's dgrad does it for the stem's BatchNorm
+  std::vector<char> out_reduced;            // per block: the NEXT block's dgrad does it for this block's output BatchNorm(s)
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_launches = 0, eval_launches = 0;
   bool train_warm = false, eval_warm = false;
@@ -353,6 +354,7 @@ Plan* get_plan(PmdEngine* e, int n) {
   pl->block_resident.assign(e->blocks.size(), 0);
   pl->inner_resident.assign(e->convs.size(), 0);
   pl->inner_reduced.assign(e->convs.size(), 0);
+  pl->out_reduced.assign(e->blocks.size(), 0);
   // C = K = 64 3x3 layers: weight-resident persistent kernel
   const bool resident_on = conv_resident_enabled(), resident_dgrad = conv_resident_dgrad_enabled();
   for (size_t i = 0; i < e->convs.size(); ++i) {
@@ -439,6 +441,27 @@ Plan* get_plan(PmdEngine* e, int n) {
         pl->stem_reduced = rc == 1;
       }
     }
+  }
+  // The dgrad of block bi's first convolution produces dL/dz of block bi-1's output: let its epilogue mask that gradient
+  // with the output's ReLU bits and reduce it for the output BatchNorm(s) of block bi-1 (no stand-alone reduce pass).
+  // Not when two kernels write dz_in (Bottleneck stage entry with a strided projection) or the resident kernel runs.
+  for (size_t bi = 1; bi < e->blocks.size(); ++bi) {
+    Block& b = e->blocks[bi];
+    Block& pb = e->blocks[bi - 1];
+    const bool two_writers = b.sc >= 0 && e->convs[b.sc].s.stride != e->convs[b.main[0]].s.stride;
+    // PMD_BLOCK_REDUCE: bit (bi - 1) enables the fusion for the output of block bi - 1 (default: see below)
+    static const int sel = getenv("PMD_BLOCK_REDUCE") == nullptr ? 0 : atoi(getenv("PMD_BLOCK_REDUCE"));
+    if (pb.zbits == nullptr || two_writers || pl->block_resident[bi] || ((sel >> (bi - 1)) & 1) == 0) continue;
+    Conv& c0 = e->convs[b.main[0]];
+    PmdConvShape s0 = c0.s;
+    s0.N = n;
+    Conv& l0 = e->convs[pb.main[pb.n_main - 1]];
+    Conv* l1 = pb.sc >= 0 ? &e->convs[pb.sc] : nullptr;
+    const int rc = attach_block_bn_reduce(&pl->block_dgrad[bi], s0, pb.zbits, l1 != nullptr ? 2 : 1, l0.y, l0.mean, l0.invstd,
+                                          l0.sums, l1 != nullptr ? l1->y : nullptr, l1 != nullptr ? l1->mean : nullptr,
+                                          l1 != nullptr ? l1->invstd : nullptr, l1 != nullptr ? l1->sums : nullptr);
+    if (rc < 0) return nullptr;
+    pl->out_reduced[bi - 1] = static_cast<char>(rc);
   }
   Plan* raw = pl.get();
   e->plans[n] = std::move(pl);
@@ -704,7 +727,7 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     Block& b = e->blocks[bi];
     const int last = b.main[b.n_main - 1];
     const long long rows_out = 1LL * n * b.Hout * b.Hout;
-    E_CHECK(bn_backward(e, last, b.sc, b.dz_out, b.z_out, rows_out, b.g_out, st, false, b.zbits));
+    E_CHECK(bn_backward(e, last, b.sc, b.dz_out, b.z_out, rows_out, b.g_out, st, pl->out_reduced[bi] != 0, b.zbits));
     E_CHECK(bn_done(last));
     if (b.sc >= 0) E_CHECK(bn_done(b.sc));
     for (int j = b.n_main - 1; j >= 1; --j) {

@@ -61,6 +61,16 @@ int pmd_conv_dgrad_bn_reduce(const PmdConvShape* s, const void* d_dy, const void
 int pmd_conv_dgrad_bn_reduce_addend(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const void* d_addend,
                                     const void* d_y_prev, const float* d_scale, const float* d_shift, const float* d_mean,
                                     const float* d_invstd, float* d_sums, void* d_dz, void* stream);
+/* dgrad of a residual block's FIRST convolution (optionally with the projection shortcut's dgrad fused as s2 / d_dy2 /
+ * d_w2_krsc, or an identity shortcut's gradient as d_addend) that also does the BatchNorm-backward reduction of the
+ * PREVIOUS block's output: d_dx = dL/dz_prev is masked with that output's ReLU bit array (pmd_bn_apply_bits) and, per
+ * channel, sum(g) and sum(g * xhat) are accumulated for nb = 1 (main path) or 2 (main path + projection shortcut)
+ * BatchNorms -- what pmd_bn_bwd_reduce_multi would compute from a second pass over d_dx, y0, y1 and z.  Any stride. */
+int pmd_conv_dgrad_block_bn_reduce(const PmdConvShape* s, const void* d_dy, const void* d_w_krsc, const PmdConvShape* s2,
+                                   const void* d_dy2, const void* d_w2_krsc, const void* d_addend,
+                                   const unsigned char* d_relu_bits, int nb, const void* d_y0, const float* d_mean0,
+                                   const float* d_invstd0, float* d_sums0, const void* d_y1, const float* d_mean1,
+                                   const float* d_invstd1, float* d_sums1, void* d_dx, void* stream);
 /* dw (fp32, KRSC) += x^T * dy, reduction over all N*Ho*Wo pixels split over `split_k` CTAs per
  * output tile (0 = choose); partial tiles are added with red.global.add.f32, so d_dw is an
  * accumulator the caller zeroes (it is a slice of the flat gradient bucket slab). */

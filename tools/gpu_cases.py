@@ -194,6 +194,63 @@ for _name, _args in {
     CASES[_name] = (lambda a=_args: _dgrad_bn_reduce_case(*a))
 
 
+def _dgrad_block_bn_reduce_case(N, H, C, K, R, stride, shortcut_K=0, addend=False, nb=1):
+    """Block dgrad (+ fused projection dgrad / identity addend) that also masks its output with the previous block's
+    ReLU bits and accumulates that block's BatchNorm-backward sums (1 or 2 branches) -- vs plain PyTorch fp32."""
+    import ctypes as C_
+    from pmdist.ops import _lib, conv as cv
+    from pmdist.ops._lib import PmdConvShape, check, ptr, stream_ptr
+    Ho = cv.out_dim(H, R, stride)
+    dy = _rand_bf16(N, Ho, Ho, K, seed=21)
+    w = _rand_bf16(K, C, R, R, scale=1.0 / math.sqrt(K * R * R), seed=22)
+    ref = _dgrad_ref(dy, w, (N, H, H, C), stride)
+    s2 = dy2 = w2k = None
+    if shortcut_K:
+        dy2 = _rand_bf16(N, Ho, Ho, shortcut_K, seed=23)
+        w2 = _rand_bf16(shortcut_K, C, 1, 1, scale=1.0 / math.sqrt(shortcut_K), seed=24)
+        ref = ref + _dgrad_ref(dy2, w2, (N, H, H, C), stride)
+        w2k = cv.krsc_from_torch(w2)
+        s2 = PmdConvShape(N, H, H, C, shortcut_K, 1, stride)
+    add = None
+    if addend:
+        add = _rand_bf16(N, H, H, C, seed=25)
+        ref = ref + add.float()
+    g = torch.Generator(device='cuda').manual_seed(26)
+    keep = torch.rand(N, H, H, C, device='cuda', generator=g) > 0.4                      # the block output's ReLU mask
+    bits = ((keep.view(-1, 8).to(torch.int32) << torch.arange(8, device='cuda', dtype=torch.int32)).sum(1)).to(torch.uint8)
+    ys = [_rand_bf16(N, H, H, C, seed=27 + i) for i in range(nb)]
+    means = [torch.randn(C, device='cuda', generator=g) * 0.1 for _ in range(nb)]
+    invs = [torch.rand(C, device='cuda', generator=g) + 0.5 for _ in range(nb)]
+    sums = [torch.zeros(2 * C, device='cuda') for _ in range(nb)]
+    dx = torch.empty(N, H, H, C, dtype=torch.bfloat16, device='cuda')
+    s = PmdConvShape(N, H, H, C, K, R, stride)
+    wk = cv.krsc_from_torch(w)
+    check(_lib.lib().pmd_conv_dgrad_block_bn_reduce(
+        C_.byref(s), ptr(dy), ptr(wk), C_.byref(s2) if s2 is not None else None, ptr(dy2), ptr(w2k), ptr(add), ptr(bits),
+        C_.c_int(nb), ptr(ys[0]), ptr(means[0]), ptr(invs[0]), ptr(sums[0]), ptr(ys[1]) if nb == 2 else None,
+        ptr(means[1]) if nb == 2 else None, ptr(invs[1]) if nb == 2 else None, ptr(sums[1]) if nb == 2 else None, ptr(dx),
+        stream_ptr()))
+    torch.cuda.synchronize()
+    ref = torch.where(keep, ref, torch.zeros_like(ref))
+    res = _cmp(dx, ref, 2e-2)
+    gf = dx.float()
+    for i in range(nb):
+        r1 = _cmp(sums[i][:C], gf.sum((0, 1, 2)), 2e-3)
+        r2 = _cmp(sums[i][C:], (gf * (ys[i].float() - means[i]) * invs[i]).sum((0, 1, 2)), 2e-3)
+        res[f'sum_g_rel_{i}'], res[f'sum_gx_rel_{i}'] = r1['rel_to_max'], r2['rel_to_max']
+        res['ok'] = res['ok'] and r1['ok'] and r2['ok']
+    return res
+
+
+CASES['dgrad_block_bn_reduce_s2_shortcut_nb2_c128_k256'] = lambda: _dgrad_block_bn_reduce_case(4, 16, 128, 256, 3, 2, 256, nb=2)
+CASES['dgrad_block_bn_reduce_s2_shortcut_nb1_c64_k128'] = lambda: _dgrad_block_bn_reduce_case(4, 32, 64, 128, 3, 2, 128, nb=1)
+CASES['dgrad_block_bn_reduce_s1_addend_nb1_c128'] = lambda: _dgrad_block_bn_reduce_case(3, 16, 128, 128, 3, 1, 0, True, nb=1)
+CASES['dgrad_block_bn_reduce_s2_nb2_c256_k512_n3'] = lambda: _dgrad_block_bn_reduce_case(3, 8, 256, 512, 3, 2, 512, nb=2)
+CASES['bench512_dgrad_block_bn_reduce_layer2_conv1'] = lambda: _dgrad_block_bn_reduce_case(512, 32, 64, 128, 3, 2, 128, nb=1)
+CASES['bench512_dgrad_block_bn_reduce_layer3_conv1'] = lambda: _dgrad_block_bn_reduce_case(512, 16, 128, 256, 3, 2, 256, nb=2)
+CASES['bench512_dgrad_block_bn_reduce_layer4_conv1'] = lambda: _dgrad_block_bn_reduce_case(512, 8, 256, 512, 3, 2, 512, nb=2)
+
+
 # ------------------------------------------------------------------ wgrad
 def _wgrad_case(N, H, C, K, R, stride, split=0, direct=False):
     from pmdist.ops import conv as cv
