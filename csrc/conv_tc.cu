@@ -232,6 +232,13 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
       const long long pix = (static_cast<long long>(n0 + ni) * p.GH[cls] + (h0 + hi)) * p.GW[cls] + (w0 + wi);
       add_row = p.addend + pix * p.out_channels + ntile * BN;
     }
+    if (add_row != nullptr) {
+      // the epilogue warps idle while the MMAs run: pull this row's addend (BN * 2 bytes) towards the SM now, so the
+      // loads in the epilogue hit cache instead of paying a DRAM round trip each
+#pragma unroll
+      for (int b = 0; b < BN * 2; b += 128)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(add_row) + b));
+    }
     if (nkb > 0) {
       mbar_wait(&bars->tmem_full, 0);
       tc_fence_after();

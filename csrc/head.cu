@@ -41,6 +41,39 @@ __global__ void pool_fc_fwd_kernel(const __nv_bfloat16* __restrict__ z, int HW, 
   }
 }
 
+// Large final maps (224x224 inputs: 28x28x2048 per image): one block per image walking HW pixels serially leaves the
+// GPU idle (32 blocks).  Split: pool_partial_kernel sums slices of the map with many blocks (atomics into the zeroed
+// feature vector), fc_kernel finishes.
+__global__ void pool_partial_kernel(const __nv_bfloat16* __restrict__ z, int HW, int C, int slices, float* __restrict__ feat) {
+  pdl_wait();
+  const int n = blockIdx.x / slices, sl = blockIdx.x % slices;
+  const int p0 = static_cast<int>(static_cast<long long>(HW) * sl / slices), p1 = static_cast<int>(static_cast<long long>(HW) * (sl + 1) / slices);
+  const __nv_bfloat16* zn = z + static_cast<long long>(n) * HW * C;
+  const float inv = 1.f / HW;
+  for (int c2 = threadIdx.x; c2 < C / 2; c2 += blockDim.x) {
+    float s0 = 0.f, s1 = 0.f;
+    for (int p = p0; p < p1; ++p) {
+      const float2 f = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(zn + static_cast<long long>(p) * C + 2 * c2));
+      s0 += f.x;
+      s1 += f.y;
+    }
+    atomicAdd(feat + static_cast<long long>(n) * C + 2 * c2, s0 * inv);
+    atomicAdd(feat + static_cast<long long>(n) * C + 2 * c2 + 1, s1 * inv);
+  }
+}
+__global__ void fc_kernel(const float* __restrict__ feat, int C, const float* __restrict__ w, const float* __restrict__ b,
+                          int classes, float* __restrict__ logits) {
+  pdl_wait();
+  const int n = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (int j = warp; j < classes; j += nwarps) {
+    float acc = 0.f;
+    for (int c = lane; c < C; c += 32) acc += feat[static_cast<long long>(n) * C + c] * __ldg(w + static_cast<long long>(j) * C + c);
+    acc = warp_sum(acc);
+    if (lane == 0) logits[static_cast<long long>(n) * classes + j] = acc + b[j];
+  }
+}
+
 // one warp per sample
 __global__ void ce_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
                           const unsigned char* __restrict__ valid, int N, int classes, float grad_scale,
@@ -135,8 +168,23 @@ using namespace pmd;
 extern "C" PMD_API int pmd_pool_fc_fwd(const void* d_z, int N, int HW, int C, const float* d_w, const float* d_b, int classes,
                                float* d_feat, float* d_logits, void* stream) {
   PMD_REQUIRE(C % 2 == 0, "feature width must be even");
-  PMD_CHECK_CUDA(launch_pdl(pool_fc_fwd_kernel, dim3(N), dim3(256), C * 4, static_cast<cudaStream_t>(stream),
-                            static_cast<const __nv_bfloat16*>(d_z), HW, C, d_w, d_b, classes, d_feat, d_logits));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long work = static_cast<long long>(HW) * C;
+  if (HW >= 64 && N * 8 < 148 * 4 && work >= (1 << 18)) {
+    // few images with large final maps: pool with (N x slices) blocks, then the tiny FC
+    int slices = (148 * 4 + N - 1) / N;
+    if (slices > HW / 8) slices = HW / 8;
+    PMD_CHECK_CUDA(cudaMemsetAsync(d_feat, 0, static_cast<size_t>(N) * C * sizeof(float), st));
+    PMD_CHECK_CUDA(launch_pdl(pool_partial_kernel, dim3(N * slices), dim3(256), 0, st, static_cast<const __nv_bfloat16*>(d_z), HW,
+                              C, slices, d_feat));
+    PMD_CHECK_CUDA(launch_pdl(fc_kernel, dim3(N), dim3(256), 0, st, static_cast<const float*>(d_feat), C, d_w, d_b, classes,
+                              d_logits));
+    count_launch(2);
+    PMD_LAUNCH_CHECK();
+    return 0;
+  }
+  PMD_CHECK_CUDA(launch_pdl(pool_fc_fwd_kernel, dim3(N), dim3(256), C * 4, st, static_cast<const __nv_bfloat16*>(d_z), HW, C, d_w,
+                            d_b, classes, d_feat, d_logits));
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;

@@ -532,9 +532,8 @@ def _bn_res_affine():
 
 # ------------------------------------------------------------------ head / loss / optimiser / aug
 @case('pool_fc_ce_forward_backward')
-def _head_case():
+def _head_case(N=32, H=4, C=512, classes=10):
     from pmdist.ops import nn as nk
-    N, H, C, classes = 32, 4, 512, 10
     z = _rand_bf16(N, H, H, C, seed=17).abs().to(torch.bfloat16)
     w = torch.randn(classes, C, device='cuda') * 0.05
     b = torch.randn(classes, device='cuda') * 0.1
@@ -557,6 +556,9 @@ def _head_case():
                           and m[2] == float(top.sum()) and m[3] == N)
     r['ok'] = all(v['ok'] for v in r.values())
     return r
+
+
+CASES['head_pool_fc_ce_large_map_28x28_c2048_split_pool'] = lambda: _head_case(8, 28, 2048, 10)
 
 
 @case('ce_valid_mask_excludes_padding')

@@ -21,9 +21,11 @@ OUT = os.path.join(ROOT, 'profiles', 'sass')
 
 # output file -> substring that selects the (mangled) kernel name
 KERNELS = {
-    'conv_gemm_kernel_128_3_fprop': 'conv_gemm_kernelILi128ELi3ELb0ELb0EE',
-    'conv_gemm_kernel_256_2_dgrad_krsc': 'conv_gemm_kernelILi256ELi2ELb1ELb0EE',
-    'conv_gemm_kernel_128_3_dgrad_bn_reduce': 'conv_gemm_kernelILi128ELi3ELb1ELb1EE',
+    'conv_gemm_kernel_128_3_fprop': 'conv_gemm_kernelILi128ELi3ELb0ELi0ELb0EE',
+    'conv_gemm_kernel_256_2_dgrad_krsc': 'conv_gemm_kernelILi256ELi2ELb1ELi0ELb0EE',
+    'conv_gemm_kernel_128_3_dgrad_bn_reduce': 'conv_gemm_kernelILi128ELi3ELb1ELi1ELb0EE',
+    'conv_gemm_kernel_128_3_dgrad_block_bn_reduce': 'conv_gemm_kernelILi128ELi3ELb1ELi2ELb0EE',
+    'conv_gemm_kernel_128_3_fprop_cta_pair': 'conv_gemm_kernelILi128ELi3ELb0ELi0ELb1EE',
     'conv_wgrad_kernel_256_3_2': 'conv_wgrad_kernelILi256ELi3ELi2EE',
     'conv_wgrad_patch_kernel_4': 'conv_wgrad_patch_kernelILi4EE',
     'conv3x3_resident_kernel_fprop': 'conv3x3_resident_kernelILb0EE',
