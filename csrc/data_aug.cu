@@ -84,7 +84,8 @@ __global__ void augment_kernel(const unsigned char* __restrict__ u8, const int* 
 // of the stem weight) padded with zeros to 64 columns.  The stem conv (ref:model/resnet.py:79-80) then is
 // a 64-wide 1x1 convolution the tcgen05 path handles, and so is its weight gradient.  Positions outside
 // the image are the convolution's zero padding (0), positions inside the image but outside the crop are
-// torchvision's pre-normalisation zero pad (-1 after Normalize).
+// torchvision's pre-normalisation zero pad (-1 after Normalize).  Only columns 0..31 of a pixel are written (27 values
+// + 5 zeros); columns 32..63 must be zero in the caller's buffer and stay untouched.
 template <bool GATHER>
 __global__ void augment_im2col_kernel(const unsigned char* __restrict__ u8, const int* __restrict__ aug, GatherSrc g, int N,
                                       int H, int W, int pad, __nv_bfloat16* __restrict__ out) {
@@ -139,11 +140,7 @@ __global__ void augment_im2col_kernel(const unsigned char* __restrict__ u8, cons
     o[2] = make_uint4(pack_bf16x2(v[16], v[17]), pack_bf16x2(v[18], v[19]), pack_bf16x2(v[20], v[21]),
                       pack_bf16x2(v[22], v[23]));
     o[3] = make_uint4(pack_bf16x2(v[24], v[25]), pack_bf16x2(v[26], v[27]), 0u, 0u);
-    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-    o[4] = z;
-    o[5] = z;
-    o[6] = z;
-    o[7] = z;
+    // columns 32..63 are never written: they are zero from the buffer's allocation on (half the store traffic)
   }
 }
 

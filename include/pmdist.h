@@ -229,7 +229,8 @@ int pmd_augment(const unsigned char* d_u8, const int* d_aug, int N, int H, int W
 /* Same augmentation fused with the stem convolution's im2col: out is [N, H, W, 64] bf16 whose first 27
  * columns are the 3x3x3 neighbourhood ((r*3+s)*3 + c order, zero outside the image), the rest zero.  The
  * 3->64 stem conv (ref:model/resnet.py:79-80) and its weight gradient then run as 64-wide 1x1
- * convolutions on the tensor-core path; pmd_pad_stem_weight makes the matching [K][64] weight. */
+ * convolutions on the tensor-core path; pmd_pad_stem_weight makes the matching [K][64] weight.
+ * d_out must be ZERO-INITIALISED once by the caller: the kernel writes columns 0..31 of every pixel only. */
 int pmd_augment_im2col(const unsigned char* d_u8, const int* d_aug, int N, int H, int W, int pad, void* d_out,
                        void* stream);
 /* The same kernel fed from a dataset that is RESIDENT in device memory (replaces the DataLoader workers, the pinned

@@ -845,7 +845,7 @@ def _stem_im2col():
     aug = draw_aug_params(N, True, torch.Generator().manual_seed(2))
     x = augment_cpu(src.images, aug).cuda().to(torch.bfloat16).float()                # NCHW, bf16-rounded
     w = _rand_bf16(64, 3, 3, 3, scale=0.2, seed=22)
-    col = torch.empty((N, H, H, 64), dtype=torch.bfloat16, device='cuda')
+    col = torch.zeros((N, H, H, 64), dtype=torch.bfloat16, device='cuda')     # columns 32..63 stay as allocated
     lib = _lib.lib()
     u8_dev, aug_dev = src.images.cuda(), aug.cuda()      # keep both alive: a freed temporary's block is reused at once
     check(lib.pmd_augment_im2col(ptr(u8_dev), ptr(aug_dev), C.c_int(N), C.c_int(H), C.c_int(H), C.c_int(8),
