@@ -228,9 +228,11 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
     const int ni = row / (p.w_box * p.h_box);
     const bool valid = (w0 + wi < p.GW[cls]) && (h0 + hi < p.GH[cls]) && (n0 + ni < p.N);
     const __nv_bfloat16* add_row = nullptr;
+    const unsigned char* add_bits = nullptr;   // optional ReLU bits of the addend (see ConvGemmParams::addend_bits)
     if (p.addend != nullptr && valid) {
       const long long pix = (static_cast<long long>(n0 + ni) * p.GH[cls] + (h0 + hi)) * p.GW[cls] + (w0 + wi);
       add_row = p.addend + pix * p.out_channels + ntile * BN;
+      if (p.addend_bits != nullptr) add_bits = p.addend_bits + (pix * p.out_channels + ntile * BN) / 8;
     }
     if (add_row != nullptr) {
       // the epilogue warps idle while the MMAs run: pull this row's addend (BN * 2 bytes) towards the SM now, so the
@@ -283,13 +285,17 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
         uint32_t packed[16];
         if (add_row != nullptr) {
           const uint4* ap = reinterpret_cast<const uint4*>(add_row + hf * 64 + cc * 32);
+          const uint32_t am = add_bits != nullptr ? *reinterpret_cast<const uint32_t*>(add_bits + (hf * 64 + cc * 32) / 8)
+                                                  : 0xffffffffu;
 #pragma unroll
           for (int jj = 0; jj < 4; ++jj) {
             const uint4 a4 = ap[jj];   // plain load: the addend may alias the output (in-place accumulate)
             const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              const float2 af = unpack_bf16x2(aw[e]);
+              float2 af = unpack_bf16x2(aw[e]);
+              if (!((am >> (jj * 8 + e * 2)) & 1u)) af.x = 0.f;
+              if (!((am >> (jj * 8 + e * 2 + 1)) & 1u)) af.y = 0.f;
               packed[jj * 4 + e] = pack_bf16x2(__uint_as_float(v[jj * 8 + e * 2]) + af.x,
                                                __uint_as_float(v[jj * 8 + e * 2 + 1]) + af.y);
             }

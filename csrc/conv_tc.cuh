@@ -42,6 +42,10 @@ struct ConvGemmParams {
   // sums taken around a pivot near the mean do not.  The engine passes the previous step's batch mean.
   const float* stat_pivot;
   const __nv_bfloat16* addend;  // optional NHWC tensor shaped like the (single-class) output
+  // Optional ReLU bit array of the addend (uint8 [pixels * out_channels / 8], pmd_bn_apply_bits): elements whose bit is
+  // clear count as zero.  An identity shortcut's gradient is dz_out masked by the block output's ReLU: with the bits the
+  // dgrad reads dz_out directly and the BatchNorm backward need not write the masked copy.
+  const unsigned char* addend_bits;
   long long* trace;          // optional [trace_cap][kTraceSlots] per-CTA timestamps (pmd_conv_set_trace), else null
   int trace_cap;
   // dgrad + BatchNorm-backward reduction in one kernel (attach_bn_reduce): the output dz = dL/dz of the previous

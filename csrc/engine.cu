@@ -80,6 +80,7 @@ struct Plan {
   std::vector<char> block_resident, inner_resident;
   std::vector<char> inner_reduced;          // inner dgrad also does the BatchNorm-backward reduction of the layer below
   bool stem_reduced = false;                // the first block's dgrad does it for the stem's BatchNorm
+  std::vector<char> g_out_unused;           // per identity block: the dgrad masks dz_out itself (ReLU bits), g_out is not written
   std::vector<char> out_reduced;            // per block: the NEXT block's dgrad does it for this block's output BatchNorm(s)
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_launches = 0, eval_launches = 0;
@@ -355,6 +356,7 @@ Plan* get_plan(PmdEngine* e, int n) {
   pl->inner_resident.assign(e->convs.size(), 0);
   pl->inner_reduced.assign(e->convs.size(), 0);
   pl->out_reduced.assign(e->blocks.size(), 0);
+  pl->g_out_unused.assign(e->blocks.size(), 0);
   // C = K = 64 3x3 layers: weight-resident persistent kernel
   const bool resident_on = conv_resident_enabled(), resident_dgrad = conv_resident_dgrad_enabled();
   for (size_t i = 0; i < e->convs.size(); ++i) {
@@ -424,9 +426,14 @@ Plan* get_plan(PmdEngine* e, int n) {
                              &pl->block_dgrad[bi], true))
         return nullptr;
     } else {
-      if (build_dgrad_params(s0, c0.dy, e->wbf16 + c0.w_off, nullptr, nullptr, nullptr, b.g_out, b.dz_in,
-                             &pl->block_dgrad[bi], true))
+      // identity shortcut: its gradient is dz_out under the block output's ReLU mask -- read straight from dz_out with
+      // the ReLU bits when they exist (the BatchNorm backward then does not write the masked copy g_out)
+      const bool masked_addend = b.zbits != nullptr && !(conv_resident_block_dgrad_enabled() && conv_resident_supported(s0));
+      if (build_dgrad_params(s0, c0.dy, e->wbf16 + c0.w_off, nullptr, nullptr, nullptr, masked_addend ? b.dz_out : b.g_out,
+                             b.dz_in, &pl->block_dgrad[bi], true))
         return nullptr;
+      if (masked_addend) pl->block_dgrad[bi].addend_bits = b.zbits;
+      pl->g_out_unused[bi] = masked_addend ? 1 : 0;
       if (conv_resident_block_dgrad_enabled() && conv_resident_supported(s0)) {
         if (build_dgrad_resident_params(s0, c0.dy, e->wbf16 + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_r[bi]))
           return nullptr;
@@ -727,7 +734,8 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     Block& b = e->blocks[bi];
     const int last = b.main[b.n_main - 1];
     const long long rows_out = 1LL * n * b.Hout * b.Hout;
-    E_CHECK(bn_backward(e, last, b.sc, b.dz_out, b.z_out, rows_out, b.g_out, st, pl->out_reduced[bi] != 0, b.zbits));
+    E_CHECK(bn_backward(e, last, b.sc, b.dz_out, b.z_out, rows_out, pl->g_out_unused[bi] ? nullptr : b.g_out, st,
+                        pl->out_reduced[bi] != 0, b.zbits));
     E_CHECK(bn_done(last));
     if (b.sc >= 0) E_CHECK(bn_done(b.sc));
     for (int j = b.n_main - 1; j >= 1; --j) {
