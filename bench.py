@@ -203,7 +203,7 @@ def run_native(a) -> None:
     for _ in range(a.steps):
         eng.train_step(nxt, lr)                  # H2D of this step's batch from pinned memory + one graph launch
         if async_metrics:
-            f2 = eng.read_metrics_async()        # D2H of this step's metrics, enqueued behind the step
+            f2 = eng.read_metrics_async(reset=False)   # D2H of the (cumulative) metrics, enqueued behind this step
             nxt = next(it)
             if fut is not None:
                 m = fut.result()                 # the previous step's loss / accuracy, on the host by now
@@ -215,6 +215,8 @@ def run_native(a) -> None:
         m = fut.result()
     torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - t0) * 1e3
+    if async_metrics:
+        m = eng.read_metrics()                   # (outside the timed region) totals of the K steps; clears the accumulators
     comm.barrier()
 
     # ---- exposed communication: the same K steps with the collectives stubbed out (BatchNorm statistics and

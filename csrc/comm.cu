@@ -161,11 +161,47 @@ __global__ void bn_finalize_push_kernel(PmdSym s, int slot, const float* __restr
                                         long long* num_batches, float momentum, float eps, float* scale, float* shift,
                                         float* save_mean, float* save_invstd, const float* pivot, float* pivot_new) {
   extern __shared__ float tot[];     // [2C]
+  __shared__ uint32_t epoch_s;
+  // Everything that does not depend on the producer of `stats` happens BEFORE the grid-dependency wait, while that
+  // producer is still running: the exchange's epoch counter (private to this slot), and gamma / beta / pivot /
+  // running statistics of the first channel this thread finalises (written by earlier steps only).  What remains on
+  // the critical path behind the producer is: read sums -> push -> poll -> finalize from registers.
+  const uint32_t epoch = ll_next_epoch(s, slot, &epoch_s);
+  const int c0 = threadIdx.x;
+  float g0 = 0.f, b0 = 0.f, p0 = 0.f, rm0 = 0.f, rv0 = 0.f;
+  if (c0 < C) {
+    g0 = gamma[c0];
+    b0 = beta[c0];
+    p0 = pivot != nullptr ? pivot[c0] : 0.f;
+    if (running_mean != nullptr) {
+      rm0 = running_mean[c0];
+      rv0 = running_var[c0];
+    }
+  }
   pdl_wait();
-  ll_exchange_sum(s, slot, stats, 2 * C, recv_off, tot);
+  ll_push(s, stats, 2 * C, recv_off, epoch);
+  ll_poll_sum(s, slot, stats, 2 * C, recv_off, epoch, tot);
+  __syncthreads();
   if (threadIdx.x == 0 && num_batches != nullptr) *num_batches += 1;
   const float n = count_per_rank * s.world;
-  for (int c = threadIdx.x; c < C; c += blockDim.x)
+  if (c0 < C) {        // same arithmetic as bn_finalize_channel, operands already in registers
+    const float d = tot[c0] / n;
+    const float mean = p0 + d;
+    const float var = fmaxf(tot[C + c0] / n - d * d, 0.f);
+    const float invstd = rsqrtf(var + eps);
+    const float a = g0 * invstd;
+    if (pivot_new != nullptr) pivot_new[c0] = mean;
+    scale[c0] = a;
+    shift[c0] = b0 - mean * a;
+    save_mean[c0] = mean;
+    save_invstd[c0] = invstd;
+    if (running_mean != nullptr) {
+      const float unbiased = var * (n / fmaxf(n - 1.f, 1.f));
+      running_mean[c0] = (1.f - momentum) * rm0 + momentum * mean;
+      running_var[c0] = (1.f - momentum) * rv0 + momentum * unbiased;
+    }
+  }
+  for (int c = c0 + blockDim.x; c < C; c += blockDim.x)       // C > 512 (Bottleneck stages)
     bn_finalize_channel(c, tot[c], tot[C + c], n, pivot, pivot_new, gamma, beta, running_mean, running_var, momentum, eps,
                         scale, shift, save_mean, save_invstd);
 }
@@ -181,9 +217,10 @@ struct SmallExchangeDev {
 __global__ void small_allreduce_push_kernel(PmdSym s, SmallExchangeDev x0, SmallExchangeDev x1, int nvec) {
   extern __shared__ float tot[];     // [x0.n + x1.n]
   __shared__ uint32_t ep_s[2];
-  pdl_wait();
+  // the epoch counters are private to these slots: advance them while the producer of the vectors is still running
   const uint32_t e0 = ll_next_epoch(s, x0.slot, &ep_s[0]);
   const uint32_t e1 = nvec > 1 ? ll_next_epoch(s, x1.slot, &ep_s[1]) : 0u;
+  pdl_wait();
   ll_push(s, x0.local, x0.n, x0.recv_off, e0);
   if (nvec > 1) ll_push(s, x1.local, x1.n, x1.recv_off, e1);
   ll_poll_sum(s, x0.slot, x0.local, x0.n, x0.recv_off, e0, tot);

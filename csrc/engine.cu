@@ -796,15 +796,24 @@ int run_eval(PmdEngine* e, Plan* pl, cudaStream_t st) {
   return pmd_ce_fwd_bwd(e->logits, e->in_labels, e->in_valid, pl->n, e->cfg.num_classes, 0.f, nullptr, e->metrics, st);
 }
 
+int enter(PmdEngine* e, cudaStream_t user);
+int leave(PmdEngine* e, cudaStream_t user);
+
+// Eager (first call per batch size, or graphs off): the body runs on the engine's stream `st`, bracketed by events that
+// order it after the caller's pending work and the caller's later work after it.  Replay: the graph was captured on
+// `st` but is LAUNCHED ON THE CALLER'S STREAM -- its input copy, the step and the metric read-back then sit in one
+// stream and no cross-stream event hop separates them (each hop costs microseconds of idle GPU per step).
 template <typename Body>
-int run_or_replay(PmdEngine* e, cudaGraphExec_t* graph, bool* warm, int* launches, cudaStream_t st, Body body) {
+int run_or_replay(PmdEngine* e, cudaGraphExec_t* graph, bool* warm, int* launches, cudaStream_t st, cudaStream_t user,
+                  Body body) {
   if (!e->cfg.use_graph || !*warm) {
+    E_CHECK(enter(e, user));
     // first call for this batch size runs eagerly: surfaces errors, sets function attributes, counts launches
     const unsigned long long before = g_launch_count;
     E_CHECK(body());
     *launches = static_cast<int>(g_launch_count - before);
     *warm = true;
-    return 0;
+    return leave(e, user);
   }
   if (*graph == nullptr) {
     cudaGraph_t g = nullptr;
@@ -820,9 +829,9 @@ int run_or_replay(PmdEngine* e, cudaGraphExec_t* graph, bool* warm, int* launche
     PMD_CHECK_CUDA(ce);
     PMD_CHECK_CUDA(cudaGraphInstantiate(graph, g, 0));
     cudaGraphDestroy(g);
-    PMD_CHECK_CUDA(cudaGraphUpload(*graph, st));   // device-side set-up of the graph now, not inside its first launch
+    PMD_CHECK_CUDA(cudaGraphUpload(*graph, user));   // device-side set-up of the graph now, not inside its first launch
   }
-  PMD_CHECK_CUDA(cudaGraphLaunch(*graph, st));
+  PMD_CHECK_CUDA(cudaGraphLaunch(*graph, user));
   count_launch(*launches);
   return 0;
 }
@@ -942,30 +951,32 @@ extern "C" PMD_API int pmd_engine_sync_params(PmdEngine* e, int broadcast_from_r
 // The step runs on the engine's own stream (the caller's may be the legacy default stream, which
 // cannot be captured); events order it after the caller's pending work (the H2D copies of this
 // step's inputs) and order the caller's later work (metric reads) after it.
-static int enter(PmdEngine* e, cudaStream_t user) {
+namespace {
+int enter(PmdEngine* e, cudaStream_t user) {
   PMD_CHECK_CUDA(cudaEventRecord(e->ev_in, user));
   PMD_CHECK_CUDA(cudaStreamWaitEvent(e->main_stream, e->ev_in, 0));
   return 0;
 }
-static int leave(PmdEngine* e, cudaStream_t user) {
+int leave(PmdEngine* e, cudaStream_t user) {
   PMD_CHECK_CUDA(cudaEventRecord(e->ev_out, e->main_stream));
   PMD_CHECK_CUDA(cudaStreamWaitEvent(user, e->ev_out, 0));
   return 0;
 }
+}  // namespace
 
 extern "C" PMD_API int pmd_engine_train_step(PmdEngine* e, int n, float lr, void* stream) {
   PMD_REQUIRE(n >= 1 && n <= e->cfg.max_batch, "batch size outside [1, max_batch]");
   cudaStream_t user = static_cast<cudaStream_t>(stream), st = e->main_stream;
   Plan* pl = get_plan(e, n);
   if (pl == nullptr) return -1;
-  E_CHECK(enter(e, user));
   if (lr != e->last_lr) {
-    PMD_CHECK_CUDA(cudaMemcpyAsync(e->d_lr, &lr, sizeof(float), cudaMemcpyHostToDevice, st));
+    // rare (LR milestones): a synchronous copy keeps it ordered with whichever stream runs the next step
+    PMD_CHECK_CUDA(cudaDeviceSynchronize());
+    PMD_CHECK_CUDA(cudaMemcpy(e->d_lr, &lr, sizeof(float), cudaMemcpyHostToDevice));
     e->last_lr = lr;
   }
-  E_CHECK(run_or_replay(e, &pl->train_graph, &pl->train_warm, &pl->train_launches, st,
-                        [&]() { return run_train(e, pl, lr, st); }));
-  return leave(e, user);
+  return run_or_replay(e, &pl->train_graph, &pl->train_warm, &pl->train_launches, st, user,
+                       [&]() { return run_train(e, pl, lr, st); });
 }
 
 extern "C" PMD_API int pmd_engine_eval_step(PmdEngine* e, int n, void* stream) {
@@ -973,10 +984,8 @@ extern "C" PMD_API int pmd_engine_eval_step(PmdEngine* e, int n, void* stream) {
   cudaStream_t user = static_cast<cudaStream_t>(stream), st = e->main_stream;
   Plan* pl = get_plan(e, n);
   if (pl == nullptr) return -1;
-  E_CHECK(enter(e, user));
-  E_CHECK(run_or_replay(e, &pl->eval_graph, &pl->eval_warm, &pl->eval_launches, st,
-                        [&]() { return run_eval(e, pl, st); }));
-  return leave(e, user);
+  return run_or_replay(e, &pl->eval_graph, &pl->eval_warm, &pl->eval_launches, st, user,
+                       [&]() { return run_eval(e, pl, st); });
 }
 
 extern "C" PMD_API int pmd_engine_read_metrics(PmdEngine* e, int reduce_over_ranks, int reset, double* out4,
@@ -1012,8 +1021,9 @@ extern "C" PMD_API int pmd_engine_set_dataset(PmdEngine* e, const void* d_images
   if (on) {
     const unsigned long long desc[2] = {reinterpret_cast<unsigned long long>(d_images_u8),
                                         reinterpret_cast<unsigned long long>(d_labels)};
-    // ordered behind the steps already enqueued on the engine's stream (pageable source: copied before returning)
-    PMD_CHECK_CUDA(cudaMemcpyAsync(e->d_ds, desc, sizeof(desc), cudaMemcpyHostToDevice, e->main_stream));
+    // twice per epoch (train <-> test): synchronous, so it is ordered with every stream that has run or will run steps
+    PMD_CHECK_CUDA(cudaDeviceSynchronize());
+    PMD_CHECK_CUDA(cudaMemcpy(e->d_ds, desc, sizeof(desc), cudaMemcpyHostToDevice));
   }
   e->ds_on = on;
   e->ds_count = on ? count : 0;

@@ -79,10 +79,13 @@ int pmd_engine_sync_params(PmdEngine* e, int broadcast_from_rank0, void* stream)
  * memory owned by the caller (must outlive the engine or a later call with NULL).  While attached, a step takes its
  * batch from `in_index` (header + dataset indices, ~2 KB of H2D per step) instead of in_u8 / in_aug / in_labels:
  * gather, crop/flip (in-kernel Philox), normalise and stem im2col run in one kernel (pmd_augment_im2col_gather).
- * Passing d_images == NULL detaches.  Switching between resident datasets (train / test) is a 16-byte descriptor
- * update on the engine's stream; only attaching / detaching re-captures the CUDA graphs. */
+ * Passing d_images == NULL detaches.  Switching between resident datasets (train / test) is a synchronous 16-byte
+ * descriptor update (twice per epoch); only attaching / detaching re-captures the CUDA graphs. */
 int pmd_engine_set_dataset(PmdEngine* e, const void* d_images_u8, const long long* d_labels, long long count);
-/* One training step on the n <= max_batch samples currently in the staging buffers. */
+/* One training step on the n <= max_batch samples currently in the staging buffers.  `stream` is the caller's stream:
+ * the step is ordered after the work already enqueued there (the input copy) and before what is enqueued next (the
+ * metric read-back).  Replays launch the captured CUDA graph directly INTO that stream (no cross-stream hop per step);
+ * the first call per batch size runs eagerly on the engine's own streams, bracketed by events. */
 int pmd_engine_train_step(PmdEngine* e, int n, float lr, void* stream);
 /* Forward + loss/metrics only, BatchNorm in evaluation mode. */
 int pmd_engine_eval_step(PmdEngine* e, int n, void* stream);
