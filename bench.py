@@ -197,10 +197,25 @@ def run_native(a) -> None:
     # With PMD_BENCH_ASYNC_METRICS=1 the read of step i's metrics is enqueued right behind step i but consumed on
     # the host after step i+1 has been launched (NativeEngine.read_metrics_async), so the launch leaves the critical path.
     async_metrics = os.environ.get('PMD_BENCH_ASYNC_METRICS', '1') != '0'
+    pipelined = async_metrics and not a.host_dataset and os.environ.get('PMD_BENCH_PIPELINED', '1') != '0'
     nxt = next(it)
     fut = None
+    if pipelined:
+        eng.train_step_pipelined(nxt, lr).result()       # (untimed) creates the copy streams, captures the slot-1 graph
+        eng.train_step_pipelined(next(it), lr).result()
+        nxt = next(it)
+        torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(a.steps):
+        if pipelined:
+            # H2D of this step's index vector on a copy stream (overlapping the previous step), one graph launch, D2H of
+            # this step's metric snapshot on a second copy stream (overlapping the next step)
+            f2 = eng.train_step_pipelined(nxt, lr)
+            nxt = next(it)
+            if fut is not None:
+                m = fut.result()                 # the previous step's cumulative loss / accuracy, on the host by now
+            fut = f2
+            continue
         eng.train_step(nxt, lr)                  # H2D of this step's batch from pinned memory + one graph launch
         if async_metrics:
             f2 = eng.read_metrics_async(reset=False)   # D2H of the (cumulative) metrics, enqueued behind this step
@@ -262,8 +277,10 @@ def run_native(a) -> None:
                     'path': ('BatchLoader(pinned uint8 batch) -> NativeEngine.train_step -> read_metrics' if a.host_dataset else
                              'DeviceBatchLoader(pinned header + index vector; dataset resident in HBM, in-kernel gather + '
                              'Philox crop/flip) -> NativeEngine.train_step -> read_metrics') +
-                            (' (every step\'s metrics copied D2H into a pinned slot behind the step, consumed on the host one step '
-                             'later: read_metrics_async)' if async_metrics else '')},
+                            (' (train_step_pipelined: index H2D on a copy stream during the previous step, metric snapshot D2H on '
+                             'a second copy stream during the next step, consumed on the host one step later)' if pipelined else
+                             (' (every step\'s metrics copied D2H into a pinned slot behind the step, consumed on the host one step '
+                              'later: read_metrics_async)' if async_metrics else ''))},
             'exposed_comm_ms': (round((dev_max - stub_max['no_comm']) / a.steps, 4) if stub_max else
                                 (0.0 if world == 1 else None)),
             'exposed_comm': ({'ms_per_step_full': round(dev_max / a.steps, 4),

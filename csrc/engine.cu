@@ -83,6 +83,7 @@ struct Plan {
   std::vector<char> g_out_unused;           // per identity block: the dgrad masks dz_out itself (ReLU bits), g_out is not written
   std::vector<char> out_reduced;            // per block: the NEXT block's dgrad does it for this block's output BatchNorm(s)
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
+  cudaGraphExec_t train_graph_alt = nullptr;   // the same step reading input slot 1 / writing metric snapshot 1
   int train_launches = 0, eval_launches = 0;
   bool train_warm = false, eval_warm = false;
 };
@@ -117,7 +118,9 @@ struct PmdEngine {
   bf16* stem_w_pad = nullptr;         // [64][64] zero-padded stem weight
   unsigned char *in_u8 = nullptr, *in_valid = nullptr;
   int* in_aug = nullptr;
-  int* in_index = nullptr;            // [4 + max_batch]: Philox header + dataset indices (resident-dataset mode)
+  int* in_index = nullptr;            // [2][4 + max_batch]: Philox header + dataset indices (resident-dataset mode);
+  int in_slot = 0;                    // two slots, so step i+1's indices can be copied in while step i runs
+  double* metrics_snap = nullptr;     // [2][4]: the cumulative metrics as of the end of the last step of each slot
   unsigned long long* d_ds = nullptr; // device {images address, labels address} of the active resident dataset
   bool ds_on = false;
   long long ds_count = 0;
@@ -251,7 +254,8 @@ int allocate(PmdEngine* e) {
   E_CHECK(e->dalloc(&e->stem_w_pad, 64 * 64));
   E_CHECK(e->dalloc(&e->in_u8, 1LL * B * c.image_hw * c.image_hw * 3));
   E_CHECK(e->dalloc(&e->in_aug, 3LL * B));
-  E_CHECK(e->dalloc(&e->in_index, 4LL + B));
+  E_CHECK(e->dalloc(&e->in_index, 2 * (4LL + B)));
+  E_CHECK(e->dalloc(&e->metrics_snap, 8));
   E_CHECK(e->dalloc(&e->d_ds, 2));
   E_CHECK(e->dalloc(&e->in_labels, B));
   E_CHECK(e->dalloc(&e->in_valid, B));
@@ -625,10 +629,11 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
 int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
   const PmdEngineConfig& c = e->cfg;
   const int n = pl->n;
-  if (e->ds_on)
-    E_CHECK(pmd_augment_im2col_gather(e->d_ds, e->in_index, e->in_index + 4, n, c.image_hw, c.image_hw, 8, e->x0,
-                                      e->in_labels, e->in_valid, st));
-  else
+  if (e->ds_on) {
+    const int* idx = e->in_index + e->in_slot * (4 + c.max_batch);
+    E_CHECK(pmd_augment_im2col_gather(e->d_ds, idx, idx + 4, n, c.image_hw, c.image_hw, 8, e->x0, e->in_labels, e->in_valid,
+                                      st));
+  } else
     E_CHECK(pmd_augment_im2col(e->in_u8, e->in_aug, n, c.image_hw, c.image_hw, 8, e->x0, st));
   auto conv_fwd = [&](int ci, cudaStream_t st) -> int {
     Conv& cv = e->convs[ci];
@@ -900,6 +905,7 @@ extern "C" PMD_API int pmd_engine_destroy(PmdEngine* e) {
   cudaDeviceSynchronize();
   for (auto& kv : e->plans) {
     if (kv.second->train_graph) cudaGraphExecDestroy(kv.second->train_graph);
+    if (kv.second->train_graph_alt) cudaGraphExecDestroy(kv.second->train_graph_alt);
     if (kv.second->eval_graph) cudaGraphExecDestroy(kv.second->eval_graph);
   }
   for (void* p : e->owned) cudaFree(p);
@@ -926,6 +932,7 @@ extern "C" PMD_API int pmd_engine_buffers(PmdEngine* e, PmdEngineBuffers* o) {
   o->in_labels = reinterpret_cast<unsigned long long>(e->in_labels);
   o->in_valid = reinterpret_cast<unsigned long long>(e->in_valid);
   o->in_index = reinterpret_cast<unsigned long long>(e->in_index);
+  o->metrics_snap = reinterpret_cast<unsigned long long>(e->metrics_snap);
   o->logits = reinterpret_cast<unsigned long long>(e->logits);
   o->metrics = reinterpret_cast<unsigned long long>(e->metrics);
   o->slab_elems = e->cfg.slab_elems;
@@ -965,7 +972,14 @@ int leave(PmdEngine* e, cudaStream_t user) {
 }  // namespace
 
 extern "C" PMD_API int pmd_engine_train_step(PmdEngine* e, int n, float lr, void* stream) {
+  return pmd_engine_train_step_slot(e, n, lr, 0, stream);
+}
+
+extern "C" PMD_API int pmd_engine_train_step_slot(PmdEngine* e, int n, float lr, int slot, void* stream) {
   PMD_REQUIRE(n >= 1 && n <= e->cfg.max_batch, "batch size outside [1, max_batch]");
+  PMD_REQUIRE(slot == 0 || slot == 1, "input slot must be 0 or 1");
+  PMD_REQUIRE(slot == 0 || e->ds_on, "input slot 1 exists for the device-resident dataset path only");
+  e->in_slot = slot;
   cudaStream_t user = static_cast<cudaStream_t>(stream), st = e->main_stream;
   Plan* pl = get_plan(e, n);
   if (pl == nullptr) return -1;
@@ -975,12 +989,20 @@ extern "C" PMD_API int pmd_engine_train_step(PmdEngine* e, int n, float lr, void
     PMD_CHECK_CUDA(cudaMemcpy(e->d_lr, &lr, sizeof(float), cudaMemcpyHostToDevice));
     e->last_lr = lr;
   }
-  return run_or_replay(e, &pl->train_graph, &pl->train_warm, &pl->train_launches, st, user,
-                       [&]() { return run_train(e, pl, lr, st); });
+  // one captured graph per input slot (they differ in the index vector the first kernel reads and in the metric
+  // snapshot the last node writes)
+  return run_or_replay(e, slot == 0 ? &pl->train_graph : &pl->train_graph_alt, &pl->train_warm, &pl->train_launches, st, user,
+                       [&]() {
+                         E_CHECK(run_train(e, pl, lr, st));
+                         PMD_CHECK_CUDA(cudaMemcpyAsync(e->metrics_snap + 4 * slot, e->metrics, 4 * sizeof(double),
+                                                        cudaMemcpyDeviceToDevice, st));
+                         return 0;
+                       });
 }
 
 extern "C" PMD_API int pmd_engine_eval_step(PmdEngine* e, int n, void* stream) {
   PMD_REQUIRE(n >= 1 && n <= e->cfg.max_batch, "batch size outside [1, max_batch]");
+  e->in_slot = 0;
   cudaStream_t user = static_cast<cudaStream_t>(stream), st = e->main_stream;
   Plan* pl = get_plan(e, n);
   if (pl == nullptr) return -1;
@@ -1006,6 +1028,7 @@ static int drop_plans(PmdEngine* e) {
   PMD_CHECK_CUDA(cudaDeviceSynchronize());
   for (auto& kv : e->plans) {       // plans (tensor maps, captured graphs) bake in the pointers and switches
     if (kv.second->train_graph) cudaGraphExecDestroy(kv.second->train_graph);
+    if (kv.second->train_graph_alt) cudaGraphExecDestroy(kv.second->train_graph_alt);
     if (kv.second->eval_graph) cudaGraphExecDestroy(kv.second->eval_graph);
   }
   e->plans.clear();

@@ -61,7 +61,8 @@ typedef struct {
 typedef struct {
   unsigned long long param, grad, mom, bf16; /* device addresses of the flat slabs (in the symmetric heap) */
   unsigned long long in_u8, in_aug, in_labels, in_valid; /* device staging of one step's inputs */
-  unsigned long long in_index; /* int32 [4 + max_batch]: {seed, stream, epoch, train} + dataset indices (resident mode) */
+  unsigned long long in_index; /* int32 [2][4 + max_batch]: per input slot {seed, stream, epoch, train} + dataset indices (resident mode) */
+  unsigned long long metrics_snap; /* double [2][4]: cumulative metrics as of the end of the last step run with each slot */
   unsigned long long logits;                 /* fp32 [max_batch, classes] of the last step */
   unsigned long long metrics;                /* double[4] running {loss sum, top1, top5, count} */
   long long slab_elems;
@@ -87,6 +88,11 @@ int pmd_engine_set_dataset(PmdEngine* e, const void* d_images_u8, const long lon
  * metric read-back).  Replays launch the captured CUDA graph directly INTO that stream (no cross-stream hop per step);
  * the first call per batch size runs eagerly on the engine's own streams, bracketed by events. */
 int pmd_engine_train_step(PmdEngine* e, int n, float lr, void* stream);
+/* The same on input slot 0 or 1 of `in_index` (device-resident dataset only).  Two slots let a caller copy step i+1's
+ * index vector (on its own copy stream) while step i runs, and read step i's metric snapshot (metrics_snap[slot], written
+ * by the step's last node) while step i+1 runs: consecutive steps then run back to back on the GPU although every step
+ * has a host->device input copy and a device->host result read.  pmd_engine_train_step == slot 0. */
+int pmd_engine_train_step_slot(PmdEngine* e, int n, float lr, int slot, void* stream);
 /* Forward + loss/metrics only, BatchNorm in evaluation mode. */
 int pmd_engine_eval_step(PmdEngine* e, int n, void* stream);
 /* Copies the (optionally cross-rank reduced) metric accumulators to the host and optionally clears them. */

@@ -49,7 +49,8 @@ class PmdEngineConfig(C.Structure):
 class PmdEngineBuffers(C.Structure):
     _fields_ = [('param', C.c_ulonglong), ('grad', C.c_ulonglong), ('mom', C.c_ulonglong), ('bf16', C.c_ulonglong),
                 ('in_u8', C.c_ulonglong), ('in_aug', C.c_ulonglong), ('in_labels', C.c_ulonglong),
-                ('in_valid', C.c_ulonglong), ('in_index', C.c_ulonglong), ('logits', C.c_ulonglong),
+                ('in_valid', C.c_ulonglong), ('in_index', C.c_ulonglong), ('metrics_snap', C.c_ulonglong),
+                ('logits', C.c_ulonglong),
                 ('metrics', C.c_ulonglong),
                 ('slab_elems', C.c_longlong), ('activation_bytes', C.c_longlong), ('heap_bytes_used', C.c_longlong)]
 
@@ -192,7 +193,11 @@ class NativeEngine:
         self.in_aug = alias_tensor(bufs.in_aug, per_rank_batch * 12, device).view(torch.int32).view(per_rank_batch, 3)
         self.in_labels = alias_tensor(bufs.in_labels, per_rank_batch * 8, device).view(torch.int64)
         self.in_valid = alias_tensor(bufs.in_valid, per_rank_batch, device)
-        self.in_index = alias_tensor(bufs.in_index, (4 + per_rank_batch) * 4, device).view(torch.int32)
+        both = alias_tensor(bufs.in_index, 2 * (4 + per_rank_batch) * 4, device).view(torch.int32).view(2, 4 + per_rank_batch)
+        self.in_index_slots = both                   # two input slots (train_step_pipelined alternates between them)
+        self.in_index = both[0]
+        self.metrics_snap = alias_tensor(bufs.metrics_snap, 64, device).view(torch.float64).view(2, 4)
+        self._pipe = None                            # lazily created state of train_step_pipelined
         self._datasets: Dict[int, tuple] = {}      # id(source) -> (images, labels) resident in device memory
         self._attached: Optional[int] = None
         self.logits = alias_tensor(bufs.logits, per_rank_batch * spec.num_classes * 4, device).view(torch.float32).view(
@@ -283,6 +288,53 @@ class NativeEngine:
         n = self._stage_index(batch) if isinstance(batch, IndexBatch) else self._stage(batch, False)
         check(self.lib.pmd_engine_train_step(self._h, C.c_int(n), C.c_float(lr), _lib.stream_ptr()))
         self.step_count += 1
+
+    def train_step_pipelined(self, batch: IndexBatch, lr: float) -> 'MetricsFuture':
+        """One training step whose host<->device traffic is taken off the GPU's critical path (device-resident dataset):
+
+        * the step's index vector is copied host->device on a COPY stream into one of two device slots, as soon as the
+          step that last used that slot has finished -- i.e. while the previous step is still running;
+        * the step itself (one CUDA-graph launch) goes to the current stream right behind the previous step;
+        * its result -- the cumulative ``[loss_sum, top1, top5, count]`` as of the end of THIS step, snapshotted by the
+          step's last graph node -- is copied device->host into a pinned slot on a second copy stream while the next
+          step runs.  The returned future's ``result()`` waits for just that copy.
+
+        Every step still has its H2D input copy and its D2H result read; consecutive steps nevertheless run back to back
+        on the GPU.  Metrics are cumulative here (difference two results for per-step values; ``read_metrics()`` clears)."""
+        if self._attached is None:
+            raise RuntimeError('train_step_pipelined needs a device-resident dataset: call attach_dataset(source) first')
+        n = batch.n
+        if n > self.max_batch:
+            raise ValueError(f'batch of {n} exceeds the engine capacity {self.max_batch}')
+        if self._pipe is None:
+            self._pipe = {'h2d': torch.cuda.Stream(self.device), 'd2h': torch.cuda.Stream(self.device), 'step': 0,
+                          'slot_free': [None, None],
+                          'host': [torch.empty(4, dtype=torch.float64).pin_memory() for _ in range(4)]}
+        p = self._pipe
+        slot = p['step'] & 1
+        cur = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(p['h2d']):
+            if p['slot_free'][slot] is not None:
+                p['h2d'].wait_event(p['slot_free'][slot])            # the step two back has consumed this slot
+            else:
+                p['h2d'].wait_stream(cur)                            # first use: behind whatever ran before (set-up, warm-up)
+            self.in_index_slots[slot, :4 + n].copy_(batch.packed[:4 + n], non_blocking=True)
+            copied = torch.cuda.Event()
+            copied.record(p['h2d'])
+        cur.wait_event(copied)
+        check(self.lib.pmd_engine_train_step_slot(self._h, C.c_int(n), C.c_float(lr), C.c_int(slot), _lib.stream_ptr()))
+        done = torch.cuda.Event()
+        done.record(cur)
+        p['slot_free'][slot] = done
+        out = p['host'][p['step'] % len(p['host'])]
+        with torch.cuda.stream(p['d2h']):
+            p['d2h'].wait_event(done)
+            out.copy_(self.metrics_snap[slot], non_blocking=True)
+            landed = torch.cuda.Event()
+            landed.record(p['d2h'])
+        p['step'] += 1
+        self.step_count += 1
+        return MetricsFuture(out, landed)
 
     def train_step_staged(self, n: int, lr: float) -> None:
         """Step on whatever is already in the device staging buffers (kernel-only benchmarking)."""
