@@ -880,7 +880,7 @@ def _engine_ckpt():
 
 # ------------------------------------------------------------------ v2 kernels: im2col stem, two-branch BN backward
 @case('stem_im2col_conv_matches_conv3x3')
-def _stem_im2col():
+def _stem_im2col(N=8, H=32):
     """augment_im2col + 64-wide 1x1 tensor-core conv == augment + 3x3 conv (pad 1) of the RGB image;
     its tensor-core wgrad lands in the [K][27] KRSC stem gradient."""
     import ctypes as C
@@ -888,7 +888,6 @@ def _stem_im2col():
     from pmdist.data.sources import synthetic_source
     from pmdist.ops import _lib, conv as cv
     from pmdist.ops._lib import check, ptr, stream_ptr, PmdConvShape
-    N, H = 8, 32
     src = synthetic_source(N, H, seed=21)
     aug = draw_aug_params(N, True, torch.Generator().manual_seed(2))
     x = augment_cpu(src.images, aug).cuda().to(torch.bfloat16).float()                # NCHW, bf16-rounded
@@ -914,6 +913,9 @@ def _stem_im2col():
     r['wgrad_pad_cols_zero'] = {'ok': bool((dw.view(64, 64)[:, 27:] == 0).all())}
     r['ok'] = all(v['ok'] for v in r.values())
     return r
+
+
+CASES['stem_im2col_conv_matches_conv3x3_odd_size_h20'] = lambda: _stem_im2col(5, 20)   # partial tiles of the 4 x 32 augmentation blocks
 
 
 @case('bn_bwd_two_branch_and_mask_from_y')
