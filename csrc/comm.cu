@@ -103,6 +103,30 @@ __global__ void __launch_bounds__(512) allreduce_sgd_kernel(PmdSym s, PmdAllredu
   rank_barrier(s, slot, ALGO != PMD_ALGO_ONESHOT);
 }
 
+// Small ranges (the step's last bucket: nothing is left to overlap it, so its LATENCY is exposed): push protocol instead
+// of barrier + peer loads + barrier.  Single block; every rank ends up with identical sums (rank order) and applies the
+// identical update to the whole range, so weights stay bitwise equal and momentum is replicated.
+__global__ void __launch_bounds__(512) allreduce_sgd_ll_kernel(PmdSym s, PmdAllreduceSgd a, int slot) {
+  __shared__ uint32_t epoch_s;
+  const SgdHyper h{a.d_lr != nullptr ? *a.d_lr : a.lr, a.momentum, a.weight_decay, 1.0f / s.world, a.nesterov};
+  const uint32_t epoch = ll_next_epoch(s, slot, &epoch_s);
+  const int n = static_cast<int>(a.n);
+  const float* g = heap_ptr<const float>(s, s.rank, a.grad_off) + a.first;
+  float* p = heap_ptr<float>(s, s.rank, a.param_off) + a.first;
+  float* m = heap_ptr<float>(s, s.rank, a.mom_off) + a.first;
+  __nv_bfloat16* pb = heap_ptr<__nv_bfloat16>(s, s.rank, a.bf16_off) + a.first;
+  ll_push(s, g, n, a.recv_off, epoch);
+  const uint2* mine = heap_ptr<const uint2>(s, s.rank, a.recv_off) + static_cast<long long>(epoch & 1) * s.world * n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float sum = ll_poll_sum_one(s, mine, n, i, __ldcg(g + i), epoch, slot);
+    float pv = p[i], mv = m[i];
+    sgd_update(pv, sum, mv, h);
+    p[i] = pv;
+    m[i] = mv;
+    pb[i] = __float2bfloat16_rn(pv);
+  }
+}
+
 // ------------------------------------------------------------------ plain all-reduce (sweep primitive)
 template <int ALGO>
 __global__ void __launch_bounds__(512) allreduce_f32_kernel(PmdSym s, unsigned long long in_off,
@@ -274,6 +298,13 @@ extern "C" PMD_API int pmd_allreduce_sgd(const PmdSym* sym, const PmdAllreduceSg
   if (sym->world == 1) algo = PMD_ALGO_ONESHOT;
   if (algo == PMD_ALGO_AUTO) algo = PMD_ALGO_TWOSHOT;
   if (algo == PMD_ALGO_NVLS && sym->mc_base == 0) algo = PMD_ALGO_TWOSHOT;
+  if (algo == PMD_ALGO_LL) {
+    PMD_REQUIRE(a->n <= PMD_LL_MAX_ELEMS && a->recv_off != 0, "the LL all-reduce needs n <= PMD_LL_MAX_ELEMS and a receive area");
+    allreduce_sgd_ll_kernel<<<1, 512, 0, static_cast<cudaStream_t>(stream)>>>(*sym, *a, slot);
+    count_launch();
+    PMD_LAUNCH_CHECK();
+    return 0;
+  }
   const long long work4 = algo == PMD_ALGO_ONESHOT ? a->n / 4 : ceil_div_ll(a->n / 4, sym->world);
   PmdAllreduceSgd aa = *a;
   aa.blocks = clamp_blocks(a->blocks, work4);

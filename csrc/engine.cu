@@ -100,6 +100,7 @@ struct PmdEngine {
   std::vector<long long> bucket_start, bucket_numel;
   std::vector<int> bucket_params;     // number of parameter tensors per bucket
   std::vector<int> bucket_algo, bucket_blocks;
+  std::vector<unsigned long long> bucket_recv;   // per bucket: receive area of the push (LL) all-reduce, or 0
   int sm_count = 148;
   // slabs (symmetric heap)
   unsigned long long param_off = 0, grad_off = 0, mom_off = 0, bf16_off = 0, metrics_off = 0, bnpart_off = 0;
@@ -511,6 +512,7 @@ struct BucketTracker {
     const bool local = e->sym.world == 1 || (e->comm_stub & 2) != 0;
     a.blocks = local ? 4 * e->sm_count : e->bucket_blocks[bkt];
     a.d_lr = e->d_lr;
+    a.recv_off = e->bucket_recv[bkt];
     const int slot = 2 * static_cast<int>(e->convs.size()) + 8 + bkt * 128;
     E_CHECK(pmd_allreduce_sgd(local ? &e->sym_local : &e->sym, &a, slot, e->comm_stream));
     ++launched;
@@ -865,6 +867,17 @@ extern "C" PMD_API int pmd_engine_create(const PmdEngineConfig* cfg, PmdComm* co
               "too many gradient buckets for the signal pad (raise --bucket-mb)");
   E_CHECK(build_topology(e));
   E_CHECK(allocate(e));
+  e->bucket_recv.assign(cfg->n_buckets, 0);
+  for (int b = 0; b < cfg->n_buckets; ++b) {
+    if (e->bucket_algo[b] != PMD_ALGO_LL) continue;
+    if (e->sym.world == 1 || e->bucket_numel[b] > PMD_LL_MAX_ELEMS) {      // not applicable: fall back
+      e->bucket_algo[b] = PMD_ALGO_ONESHOT;
+      continue;
+    }
+    const unsigned long long bytes = PMD_LL_RECV_BYTES(e->sym.world, e->bucket_numel[b]);
+    E_CHECK(e->halloc(&e->bucket_recv[b], bytes));
+    PMD_CHECK_CUDA(cudaMemset(e->hptr<char>(e->bucket_recv[b]), 0, bytes));
+  }
   e->bucket_params.assign(cfg->n_buckets, 0);
   for (Conv& cv : e->convs) {
     e->bucket_params[cv.w_bkt]++;

@@ -30,7 +30,7 @@ extern "C" {
 
 enum { PMD_TRANSPORT_SINGLE = 0, PMD_TRANSPORT_VMM = 1, PMD_TRANSPORT_IPC = 2 };
 enum { PMD_COMM_FORCE_IPC = 1, PMD_COMM_NO_MULTICAST = 2 };
-enum { PMD_ALGO_AUTO = 0, PMD_ALGO_ONESHOT = 1, PMD_ALGO_TWOSHOT = 2, PMD_ALGO_NVLS = 3 };
+enum { PMD_ALGO_AUTO = 0, PMD_ALGO_ONESHOT = 1, PMD_ALGO_TWOSHOT = 2, PMD_ALGO_NVLS = 3, PMD_ALGO_LL = 4 };
 
 typedef struct PmdRendezvous PmdRendezvous;
 typedef struct PmdComm PmdComm;
@@ -92,6 +92,10 @@ int pmd_dev_barrier(const PmdSym* sym, int slot, void* stream);
  *   TWOSHOT: rank r reduces and updates slice r, then stores the new fp32 + bf16 weights into every
  *            peer's heap (owner-computes; momentum for slice r lives on rank r only).
  *   NVLS:    as TWOSHOT with multimem.ld_reduce / multimem.st through the NVSwitch.
+ *   LL:      for ranges of at most PMD_LL_MAX_ELEMS elements (the step's LAST, un-overlappable bucket): every rank pushes
+ *            its gradients into every peer's receive area as {value, epoch} words (a->recv_off, PMD_LL_RECV_BYTES(world,
+ *            n) bytes, zero-initialised, owned by this range), polls its own, and updates the whole range itself -- one
+ *            one-way NVLink trip and no cross-rank barrier (the barrier-based kernels floor at ~16 us at 8 GPUs).
  * All offsets are byte offsets into the symmetric heap; `n` elements starting at element `first`. */
 typedef struct {
   unsigned long long param_off, grad_off, mom_off, bf16_off;
@@ -101,7 +105,9 @@ typedef struct {
   int algo;   /* PMD_ALGO_* (AUTO resolved by the caller) */
   int blocks; /* CTAs (== flag slots used) */
   const float* d_lr; /* if non-NULL the learning rate is read from device memory (CUDA-graph replays) */
+  unsigned long long recv_off; /* PMD_ALGO_LL only: heap offset of the range's receive area */
 } PmdAllreduceSgd;
+#define PMD_LL_MAX_ELEMS 16384
 int pmd_allreduce_sgd(const PmdSym* sym, const PmdAllreduceSgd* a, int slot, void* stream);
 
 /* Plain all-reduce (sum) of n floats: out[i] = sum over ranks of in_w[i], delivered to every rank's

@@ -68,10 +68,13 @@ def arrival_order(params: Sequence[ParamInfo]) -> List[ParamInfo]:
 
 
 def plan_buckets(params: Sequence[ParamInfo], first_cap_bytes: int, cap_bytes: int,
-                 itemsize: int = 4, align_elems: int = 1) -> Tuple[List[Bucket], int]:
+                 itemsize: int = 4, align_elems: int = 1, tail_cap_bytes: int = 0) -> Tuple[List[Bucket], int]:
     """Greedy assignment in arrival order: a bucket closes as soon as its size reaches its cap
     (the first bucket uses ``first_cap_bytes``).  ``align_elems`` pads every tensor's slab offset
     (the native path uses 64 elements = 256 B so vector loads and per-peer slices stay aligned).
+    ``tail_cap_bytes`` > 0 splits the LAST gradients to arrive (the stem) off into a final bucket of at most that many
+    bytes (slab span, alignment padding included): nothing is left to overlap the step's last all-reduce, so its
+    latency is exposed, and a tiny range can use the barrier-free push all-reduce (csrc/comm.cu allreduce_sgd_ll_kernel).
     Returns (buckets, total slab elements)."""
     order = arrival_order(params)
     buckets: List[Bucket] = []
@@ -93,6 +96,17 @@ def plan_buckets(params: Sequence[ParamInfo], first_cap_bytes: int, cap_bytes: i
             cur, cur_payload, cap = [], 0, cap_bytes
     if cur:
         buckets.append(Bucket(cur_start, off - cur_start, tuple(cur)))
+    if tail_cap_bytes > 0 and buckets and len(buckets[-1].entries) > 1:
+        last = buckets[-1]
+        end = last.start + last.numel
+        if last.numel * itemsize > tail_cap_bytes:        # (a last bucket that already fits IS the tail)
+            k = len(last.entries)                         # entries[k:] will form the tail bucket
+            while k - 1 >= 1 and (end - last.entries[k - 1].offset) * itemsize <= tail_cap_bytes:
+                k -= 1
+            if k < len(last.entries):
+                split_at = last.entries[k].offset
+                buckets[-1] = Bucket(last.start, split_at - last.start, last.entries[:k])
+                buckets.append(Bucket(split_at, end - split_at, last.entries[k:]))
     if align_elems > 1:
         off = (off + align_elems - 1) // align_elems * align_elems
     return buckets, off

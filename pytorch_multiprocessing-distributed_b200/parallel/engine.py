@@ -24,6 +24,7 @@ from .peer import ALGOS, PeerComm
 
 MiB = 1 << 20
 MAX_BUCKETS = 24
+LL_MAX_ELEMS = 16384           # PMD_LL_MAX_ELEMS (include/pmdist_comm.h)
 ALIGN = 64
 
 
@@ -106,8 +107,13 @@ class NativeEngine:
         comm.verify_same('model structure', repr([(i.name, i.numel) for i in infos]).encode())
 
         first_cap, cap = (1 * MiB, 4 * MiB) if bucket_mb <= 0 else (int(bucket_mb * MiB),) * 2
+        # multi-rank: the last gradients to arrive (the stem) get a bucket of their own, small enough for the barrier-free
+        # push all-reduce -- nothing is left to overlap the step's final all-reduce, so its latency is what is exposed
+        import os
+        tail_ll = comm.world_size > 1 and os.environ.get('PMD_TAIL_LL', '1') != '0' and algo == 'auto'
         while True:
-            buckets, total = plan_buckets(infos, first_cap, cap, align_elems=ALIGN)
+            buckets, total = plan_buckets(infos, first_cap, cap, align_elems=ALIGN,
+                                          tail_cap_bytes=LL_MAX_ELEMS * 4 if tail_ll else 0)
             if len(buckets) <= MAX_BUCKETS:
                 break
             first_cap, cap = first_cap * 2, cap * 2
@@ -175,6 +181,10 @@ class NativeEngine:
         from .tuning import choose_bucket_algos
         self.bucket_algos, self.bucket_blocks, self.algo_source = choose_bucket_algos(
             comm.world_size, [nn_ * 4 for nn_ in numels], bool(comm.info.multicast_mapped), algo, comm_blocks, comm=comm)
+        if tail_ll and numels[-1] <= LL_MAX_ELEMS:
+            self.bucket_algos[-1] = 'll'
+            self.bucket_blocks[-1] = 1
+            self.algo_source += '; last bucket (%d B): push all-reduce' % (numels[-1] * 4)
         self.algo = '+'.join(sorted(set(self.bucket_algos)))
         cfg.algo, cfg.comm_blocks = ALGOS[self.bucket_algos[0]], comm_blocks
         cfg.bucket_algo = arr(C.c_int, [ALGOS[a_] for a_ in self.bucket_algos])
@@ -401,12 +411,12 @@ class NativeEngine:
         bucket current; collect the live slices from the peers' heaps (collective: all ranks call)."""
         w = self.comm.world_size
         m = self.flat_m.clone()
-        if w == 1 or all(a == 'oneshot' for a in self.bucket_algos):
+        if w == 1 or all(a in ('oneshot', 'll') for a in self.bucket_algos):
             return m
         self.comm.barrier()
         mom_off = self.bufs.mom - self.comm.info.local_base
         for b, b_algo in zip(self.buckets, self.bucket_algos):
-            if b_algo == 'oneshot':
+            if b_algo in ('oneshot', 'll'):
                 continue            # every rank updated the whole bucket: momentum is replicated
             n4 = ((b.numel + ALIGN - 1) // ALIGN * ALIGN) // 4
             per = (n4 + w - 1) // w

@@ -19,7 +19,7 @@ from .comm import Comm
 
 MAX_RANKS = 8
 MAX_SLOTS = 4096
-ALGOS = {'auto': 0, 'oneshot': 1, 'twoshot': 2, 'nvls': 3}
+ALGOS = {'auto': 0, 'oneshot': 1, 'twoshot': 2, 'nvls': 3, 'll': 4}
 TRANSPORTS = {0: 'single', 1: 'vmm', 2: 'cuda-ipc'}
 
 

@@ -126,3 +126,24 @@ def test_bucket_algorithm_selector_uses_measured_table(tmp_path, monkeypatch):
     monkeypatch.delenv('PMDIST_ALLREDUCE_TABLE')
     assert AllreduceTable.load(7) is None
     assert choose_bucket_algos(7, [1024, 64 << 20], True)[0] == ['oneshot', 'nvls']     # heuristic fallback
+
+
+def test_tail_bucket_split_keeps_layout_and_isolates_the_last_gradients():
+    """tail_cap_bytes splits the last-arriving gradients (the stem) into a final small bucket for the push all-reduce:
+    same slab layout (offsets, total), contiguous buckets, tail within the cap; a last bucket that already fits is left."""
+    from pmdist.models.resnet import build_resnet
+    from pmdist.parallel.buckets import params_of, plan_buckets
+    MiB = 1 << 20
+    for depth, expect_split in ((18, True), (34, True), (50, False)):
+        infos = params_of(build_resnet(depth))
+        base, total0 = plan_buckets(infos, MiB, 4 * MiB, align_elems=64)
+        tail, total1 = plan_buckets(infos, MiB, 4 * MiB, align_elems=64, tail_cap_bytes=64 << 10)
+        assert total0 == total1
+        assert [(e.name, e.offset) for b in base for e in b.entries] == [(e.name, e.offset) for b in tail for e in b.entries]
+        assert (len(tail) == len(base) + 1) == expect_split
+        pos = tail[0].start
+        for b in tail:
+            assert b.start == pos
+            pos = b.start + b.numel
+        assert tail[-1].numel * 4 <= 64 << 10
+        assert tail[-1].entries[-1].name == 'conv1.weight'          # the stem's weight gradient arrives last

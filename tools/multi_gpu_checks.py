@@ -82,7 +82,7 @@ def _worker(rank: int, world: int, out_dir: str, quick: bool) -> None:
     GB = (16 if quick else 512) * world          # full: the bench configuration, 512 images per rank
     src = synthetic_source(GB * 3, 32, seed=11)
     eng_res = {}
-    for algo in algos:
+    for algo in algos + ['auto']:               # auto = measured table per bucket + push all-reduce for the tail bucket
         torch.manual_seed(100 + rank)            # deliberately different initial weights per rank (D12)
         model = build_resnet(18)
         eng = NativeEngine(model, comm, SGDConfig(), dev, GB // world, 32, algo=algo)
