@@ -1020,6 +1020,11 @@ void choose_brick(int P, int GW, int GH, int* w_box, int* h_box, int* n_box) {
 
 }  // namespace
 
+int encode_tiled_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box) {
+  return encode_map(m, base, rank, dims, strides_bytes, box);
+}
+
 // Output-channel tile of the fprop/dgrad GEMM.  256-wide tiles halve the A traffic and take an N=256 MMA under the
 // shared-memory operand limit (96 B/clk instead of 128), but leave half as many CTAs; PMD_GEMM_BN256: 0 never,
 // 1 whenever the channel count allows, 2 (default) only when at least `148` CTAs remain.

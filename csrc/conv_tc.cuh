@@ -173,5 +173,39 @@ int attach_block_bn_reduce(ConvGemmParams* p, const PmdConvShape& s, const unsig
 int launch_conv_gemm(const ConvGemmParams& p, cudaStream_t stream);
 int launch_wgrad(const WgradParams& p, cudaStream_t stream);
 
+// Tiled bf16 tensor map with 128-byte swizzle (the encoder behind every map in this file), for kernels in other files.
+int encode_tiled_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box);
+
+// stem_fused_kernel (csrc/stem_fused.cu): gather + crop/flip + normalise + im2col + the 3->64 stem convolution + its
+// BatchNorm statistics in ONE persistent kernel.  Builder warps write the 27-column patches of 128 consecutive pixels
+// straight into the swizzled shared-memory A tile (and, for the weight gradient, into x0); no im2col read-back.
+struct StemFusedParams {
+  CUtensorMap w;       // padded stem weight [64 k][64 c], box 64 x 64
+  CUtensorMap out;     // y viewed as [M pixels][64], box 64 x 128
+  CUtensorMap x0m;     // x0 viewed as [M pixels][32 of 64 columns] (or all 64), box 64 x 128: store of an A slot
+  int x0_tma;          // x0m is valid: x0 leaves through TMA; 0 = per-thread stores
+  // batch source: resident dataset (desc/hdr/idx, see pmd_augment_im2col_gather) or staged uint8 images + crop/flip
+  const unsigned long long* ds;
+  const int* hdr;
+  const int* idx;
+  const unsigned char* u8;
+  const int* aug;
+  long long* labels_out;
+  unsigned char* valid_out;
+  int N, H, W, pad;
+  __nv_bfloat16* x0;         // optional [M][64]: columns 0..31 written (the stem wgrad's operand); null = not needed
+  float* stats;              // optional [128]: per channel sum(y - pivot), sum((y - pivot)^2)
+  const float* stat_pivot;   // optional [64]
+};
+inline bool stem_fused_supported(int N, int H, int W) {
+  // W % 4: image rows are copied as 32-bit words; W <= 336: the (at most four, for W >= 128) stored rows one 128-pixel
+  // tile reads fit its 4 KB stage
+  return (H * W) % 128 == 0 && W % 4 == 0 && W <= 336 && static_cast<long long>(N) * H * W < (1LL << 31);
+}
+bool stem_fused_enabled();   // PMD_STEM_FUSED (default 1)
+// x0 (may be null) = the [M][64] im2col buffer a training launch fills; a launch uses it only if its p.x0 is set.
+int build_stem_fused_params(int N, int H, int W, int pad, const void* w_pad, void* x0, void* y, StemFusedParams* out);
+int launch_stem_fused(const StemFusedParams& p, cudaStream_t stream);
 
 }  // namespace pmd

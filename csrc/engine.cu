@@ -80,6 +80,8 @@ struct Plan {
   std::vector<char> block_resident, inner_resident;
   std::vector<char> inner_reduced;          // inner dgrad also does the BatchNorm-backward reduction of the layer below
   bool stem_reduced = false;                // the first block's dgrad does it for the stem's BatchNorm
+  bool stem_fused = false;                  // input pipeline + stem convolution + statistics in one kernel (stem_fused.cu)
+  StemFusedParams stem_f;
   std::vector<char> g_out_unused;           // per identity block: the dgrad masks dz_out itself (ReLU bits), g_out is not written
   std::vector<char> out_reduced;            // per block: the NEXT block's dgrad does it for this block's output BatchNorm(s)
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
@@ -385,6 +387,10 @@ Plan* get_plan(PmdEngine* e, int n) {
                            cv.stem_col ? cv.real_rsc : 0, cv.stem_col ? cv.real_rsc : 64))
       return nullptr;
   }
+  if (e->convs[0].stem_col && e->convs[0].tc && stem_fused_enabled() && stem_fused_supported(n, e->cfg.image_hw, e->cfg.image_hw)) {
+    if (build_stem_fused_params(n, e->cfg.image_hw, e->cfg.image_hw, 8, e->stem_w_pad, e->x0, e->convs[0].y, &pl->stem_f)) return nullptr;
+    pl->stem_fused = true;
+  }
   for (size_t bi = 0; bi < e->blocks.size(); ++bi) {
     Block& b = e->blocks[bi];
     for (int j = 1; j < b.n_main; ++j) {
@@ -631,7 +637,25 @@ int bn_backward(PmdEngine* e, int ci, int cj, const bf16* dz, const bf16* z, lon
 int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
   const PmdEngineConfig& c = e->cfg;
   const int n = pl->n;
-  if (e->ds_on) {
+  if (pl->stem_fused) {
+    // gather / crop / flip / normalise + stem convolution + its statistics: one persistent kernel
+    StemFusedParams sp = pl->stem_f;
+    if (e->ds_on) {
+      const int* idx = e->in_index + e->in_slot * (4 + c.max_batch);
+      sp.ds = e->d_ds;
+      sp.hdr = idx;
+      sp.idx = idx + 4;
+      sp.labels_out = e->in_labels;
+      sp.valid_out = e->in_valid;
+    } else {
+      sp.u8 = e->in_u8;
+      sp.aug = e->in_aug;
+    }
+    sp.x0 = train ? e->x0 : nullptr;      // only the weight gradient reads the im2col rows
+    sp.stats = train ? e->convs[0].stats : nullptr;
+    sp.stat_pivot = e->convs[0].pivot;
+    E_CHECK(launch_stem_fused(sp, st));
+  } else if (e->ds_on) {
     const int* idx = e->in_index + e->in_slot * (4 + c.max_batch);
     E_CHECK(pmd_augment_im2col_gather(e->d_ds, idx, idx + 4, n, c.image_hw, c.image_hw, 8, e->x0, e->in_labels, e->in_valid,
                                       st));
@@ -652,7 +676,8 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
     if (train && sync_bn_active(e)) E_CHECK(exchange_forward(e, ci, 1LL * n * cv.Ho * cv.Wo, st));
     return 0;
   };
-  E_CHECK(conv_fwd(0, st));
+  if (!pl->stem_fused) E_CHECK(conv_fwd(0, st));
+  else if (train && sync_bn_active(e)) E_CHECK(exchange_forward(e, 0, 1LL * n * e->convs[0].Ho * e->convs[0].Wo, st));
   {
     Conv& cv = e->convs[0];
     E_CHECK(bn_apply_step(e, 0, -1, nullptr, e->z_stem, 1LL * n * cv.Ho * cv.Wo, train, st));

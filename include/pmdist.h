@@ -246,6 +246,29 @@ int pmd_augment_im2col_gather(const unsigned long long* d_dataset_desc, const in
                               void* stream);
 int pmd_pad_stem_weight(const void* d_w_k_rsc, void* d_w_padded_k64, int K, int rsc, void* stream);
 
+/* The whole first layer in one persistent kernel (csrc/stem_fused.cu): batch gather (resident dataset: d_dataset_desc,
+ * d_hdr, d_idx, d_labels_out, d_valid_out as in pmd_augment_im2col_gather) or staged images (d_u8 [N,H,W,3], d_aug
+ * [N,3]), crop/flip/normalise, the 3x3 3->64 stem convolution against the padded weight of pmd_pad_stem_weight, bf16
+ * output y [N,H,W,64] and, when stats != NULL, its BatchNorm statistics around stat_pivot (may be NULL).  x0 != NULL
+ * additionally receives the im2col rows (columns 0..31; the rest of the buffer must be zero) for the weight gradient.
+ * Needs H*W % 128 == 0, W % 4 == 0, W <= 336.  Bit-identical to pmd_augment_im2col[_gather] followed by pmd_conv_fprop on x0. */
+typedef struct PmdStemFused {
+  const unsigned long long* d_dataset_desc;
+  const int* d_hdr;
+  const int* d_idx;
+  long long* d_labels_out;
+  unsigned char* d_valid_out;
+  const unsigned char* d_u8;
+  const int* d_aug;
+  int N, H, W, pad;
+  const void* w_pad;
+  void* x0;
+  void* y;
+  float* stats;
+  const float* stat_pivot;
+} PmdStemFused;
+int pmd_stem_fused(const PmdStemFused* a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

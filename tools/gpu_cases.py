@@ -918,6 +918,141 @@ def _stem_im2col(N=8, H=32):
 CASES['stem_im2col_conv_matches_conv3x3_odd_size_h20'] = lambda: _stem_im2col(5, 20)   # partial tiles of the 4 x 32 augmentation blocks
 
 
+def _stem_fused(N=8, H=32, timed=0):
+    """stem_fused_kernel (gather/crop/flip/normalise + stem conv + BN statistics in one persistent kernel) against the
+    two-kernel form it replaces: y and x0 bit-identical, statistics equal up to summation order, labels/valid equal;
+    both batch sources (staged images + parameters, resident dataset + Philox)."""
+    import ctypes as C
+    from pmdist.data.loader import draw_aug_params
+    from pmdist.data.sources import synthetic_source
+    from pmdist.ops import _lib, conv as cv
+    from pmdist.ops._lib import check, ptr, stream_ptr
+
+    class SF(C.Structure):
+        _fields_ = [('ds', C.c_void_p), ('hdr', C.c_void_p), ('idx', C.c_void_p), ('labels', C.c_void_p), ('valid', C.c_void_p),
+                    ('u8', C.c_void_p), ('aug', C.c_void_p), ('N', C.c_int), ('H', C.c_int), ('W', C.c_int), ('pad', C.c_int),
+                    ('w_pad', C.c_void_p), ('x0', C.c_void_p), ('y', C.c_void_p), ('stats', C.c_void_p), ('pivot', C.c_void_p)]
+    lib = _lib.lib()
+    M = 16384 if timed else max(2 * N, 16)      # timed: a dataset larger than a few MB, so the gather misses L2 like a real one
+    src = synthetic_source(M, H, seed=31)
+    w = _rand_bf16(64, 3, 3, 3, scale=0.2, seed=32)
+    wk = cv.krsc_from_torch(w).reshape(64, 27).contiguous()
+    wp = torch.empty((64, 64), dtype=torch.bfloat16, device='cuda')
+    check(lib.pmd_pad_stem_weight(ptr(wk), ptr(wp), C.c_int(64), C.c_int(27), stream_ptr()))
+    pivot = (torch.randn(64, device='cuda') * 0.1).contiguous()
+    images, labels = src.images.cuda(), src.labels.cuda().long()
+    r = {}
+    # (a) staged images + host-drawn parameters
+    aug = draw_aug_params(N, True, torch.Generator().manual_seed(4)).cuda()
+    u8 = images[:N].contiguous()
+    col_a = torch.zeros((N, H, H, 64), dtype=torch.bfloat16, device='cuda')
+    check(lib.pmd_augment_im2col(ptr(u8), ptr(aug), C.c_int(N), C.c_int(H), C.c_int(H), C.c_int(8), ptr(col_a), stream_ptr()))
+    st_a = torch.zeros(128, device='cuda')
+    y_a = torch.empty((N, H, H, 64), dtype=torch.bfloat16, device='cuda')
+    from pmdist.ops._lib import PmdConvShape
+    shp = PmdConvShape(N, H, H, 64, 64, 1, 1)
+    # statistics of the two-kernel form around the same pivot: computed here from y (fp32)
+    check(lib.pmd_conv_fprop(C.byref(shp), ptr(col_a), ptr(wp), ptr(y_a), None, stream_ptr()))
+    col_f = torch.zeros_like(col_a)
+    y_f = torch.empty_like(y_a)
+    st_f = torch.zeros(128, device='cuda')
+    a = SF(0, 0, 0, 0, 0, u8.data_ptr(), aug.data_ptr(), N, H, H, 8, wp.data_ptr(), col_f.data_ptr(), y_f.data_ptr(),
+           st_f.data_ptr(), pivot.data_ptr())
+    check(lib.pmd_stem_fused(C.byref(a), stream_ptr()))
+    torch.cuda.synchronize()
+    yf = y_a.float().reshape(-1, 64) - pivot
+    st_ref = torch.cat([yf.sum(0), (yf * yf).sum(0)])
+    r['staged_y_bitwise'] = {'ok': bool(torch.equal(y_f, y_a))}
+    r['staged_x0_bitwise'] = {'ok': bool(torch.equal(col_f, col_a))}
+    r['staged_stats'] = _cmp(st_f, st_ref, 1e-4)
+    # (b) resident dataset + in-kernel Philox; one wrap-around duplicate (~index)
+    desc = torch.tensor([images.data_ptr(), labels.data_ptr()], dtype=torch.int64, device='cuda')
+    hdr = torch.tensor([1234, 0x5EED0A06, 3, 1], dtype=torch.int64).to(torch.int32).cuda()
+    idx = torch.randperm(M, generator=torch.Generator().manual_seed(6))[:N].to(torch.int32)
+    idx[N - 1] = ~idx[N - 1]
+    idx = idx.cuda()
+    col_g = torch.zeros_like(col_a)
+    lab_g = torch.zeros(N, dtype=torch.int64, device='cuda')
+    val_g = torch.zeros(N, dtype=torch.uint8, device='cuda')
+    check(lib.pmd_augment_im2col_gather(ptr(desc), ptr(hdr), ptr(idx), C.c_int(N), C.c_int(H), C.c_int(H), C.c_int(8),
+                                        ptr(col_g), ptr(lab_g), ptr(val_g), stream_ptr()))
+    y_g = torch.empty_like(y_a)
+    check(lib.pmd_conv_fprop(C.byref(shp), ptr(col_g), ptr(wp), ptr(y_g), None, stream_ptr()))
+    col_h = torch.zeros_like(col_a)
+    y_h = torch.empty_like(y_a)
+    lab_h = torch.zeros_like(lab_g)
+    val_h = torch.zeros_like(val_g)
+    st_h = torch.zeros(128, device='cuda')
+    b = SF(desc.data_ptr(), hdr.data_ptr(), idx.data_ptr(), lab_h.data_ptr(), val_h.data_ptr(), 0, 0, N, H, H, 8, wp.data_ptr(),
+           col_h.data_ptr(), y_h.data_ptr(), st_h.data_ptr(), 0)
+    check(lib.pmd_stem_fused(C.byref(b), stream_ptr()))
+    torch.cuda.synchronize()
+    yg = y_g.float().reshape(-1, 64)
+    r['gather_y_bitwise'] = {'ok': bool(torch.equal(y_h, y_g))}
+    r['gather_x0_bitwise'] = {'ok': bool(torch.equal(col_h, col_g))}
+    r['gather_stats_no_pivot'] = _cmp(st_h, torch.cat([yg.sum(0), (yg * yg).sum(0)]), 1e-4)
+    r['gather_labels_valid'] = {'ok': bool(torch.equal(lab_h, lab_g) and torch.equal(val_h, val_g) and int(val_h[-1]) == 0)}
+    # (c) evaluation form: no x0, no statistics
+    hdr[3] = 0
+    b.x0, b.stats = 0, 0
+    y_e = torch.empty_like(y_a)
+    b.y = y_e.data_ptr()
+    check(lib.pmd_stem_fused(C.byref(b), stream_ptr()))
+    check(lib.pmd_augment_im2col_gather(ptr(desc), ptr(hdr), ptr(idx), C.c_int(N), C.c_int(H), C.c_int(H), C.c_int(8),
+                                        ptr(col_g), ptr(lab_g), ptr(val_g), stream_ptr()))
+    check(lib.pmd_conv_fprop(C.byref(shp), ptr(col_g), ptr(wp), ptr(y_g), None, stream_ptr()))
+    torch.cuda.synchronize()
+    r['eval_y_bitwise'] = {'ok': bool(torch.equal(y_e, y_g))}
+    if timed:
+        b.x0, b.stats, b.y = col_h.data_ptr(), st_h.data_ptr(), y_h.data_ptr()
+        hdr[3] = 1
+        st_x = torch.zeros(128, device='cuda')
+
+        def two():
+            check(lib.pmd_augment_im2col_gather(ptr(desc), ptr(hdr), ptr(idx), C.c_int(N), C.c_int(H), C.c_int(H), C.c_int(8),
+                                                ptr(col_g), ptr(lab_g), ptr(val_g), stream_ptr()))
+            check(lib.pmd_conv_fprop(C.byref(shp), ptr(col_g), ptr(wp), ptr(y_g), ptr(st_x), stream_ptr()))
+
+        def one():
+            check(lib.pmd_stem_fused(C.byref(b), stream_ptr()))
+        b_eval = SF(desc.data_ptr(), hdr.data_ptr(), idx.data_ptr(), lab_h.data_ptr(), val_h.data_ptr(), 0, 0, N, H, H, 8,
+                    wp.data_ptr(), 0, y_h.data_ptr(), 0, 0)
+
+        def one_eval():
+            check(lib.pmd_stem_fused(C.byref(b_eval), stream_ptr()))
+        b_x0 = SF(desc.data_ptr(), hdr.data_ptr(), idx.data_ptr(), lab_h.data_ptr(), val_h.data_ptr(), 0, 0, N, H, H, 8,
+                  wp.data_ptr(), col_h.data_ptr(), y_h.data_ptr(), 0, 0)
+        b_st = SF(desc.data_ptr(), hdr.data_ptr(), idx.data_ptr(), lab_h.data_ptr(), val_h.data_ptr(), 0, 0, N, H, H, 8,
+                  wp.data_ptr(), 0, y_h.data_ptr(), st_h.data_ptr(), 0)
+
+        def one_x0():
+            check(lib.pmd_stem_fused(C.byref(b_x0), stream_ptr()))
+
+        def one_st():
+            check(lib.pmd_stem_fused(C.byref(b_st), stream_ptr()))
+        for name, fn in (('two_kernels_us', two), ('fused_us', one), ('fused_no_x0_no_stats_us', one_eval),
+                         ('fused_x0_only_us', one_x0), ('fused_stats_only_us', one_st)):
+            for _ in range(5):
+                fn()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(timed):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            r[name] = {'ok': True, 'value': e0.elapsed_time(e1) * 1000.0 / timed}
+    r['ok'] = all(v['ok'] for v in r.values())
+    return r
+
+
+CASES['stem_fused_matches_two_kernel_form'] = lambda: _stem_fused(8, 32)
+CASES['stem_fused_matches_two_kernel_form_h48_n3'] = lambda: _stem_fused(3, 48)
+CASES['stem_fused_matches_two_kernel_form_w160_row_tiles'] = lambda: _stem_fused(2, 160)   # tiles inside one image row and straddling two
+CASES['stem_fused_matches_two_kernel_form_224'] = lambda: _stem_fused(2, 224)
+CASES['bench512_stem_fused'] = lambda: _stem_fused(512, 32, timed=50)
+
+
 @case('bn_bwd_two_branch_and_mask_from_y')
 def _bn_multi():
     import ctypes as C
