@@ -462,7 +462,11 @@ struct ResBars {
 };
 constexpr int kResSmem = kResWBytes + kResSlots * kColPatchBytes + 2 * kABytes + sizeof(ResBars) + 1024;
 
-template <bool B_MN>
+// RED (dgrad only): the BatchNorm-backward reduction of the layer below in the epilogue.  The tile is staged unmasked;
+// a second pass in the statistics mapping (thread = 8 channels x 8 rows) reads the matching cells of y straight from
+// global memory (coalesced 16-byte loads issued before the accumulator wait), masks, accumulates sum(g) and sum(g*y) in
+// registers and writes the masked cells back before the TMA store: no y tile in shared memory.
+template <bool B_MN, bool RED = false>
 __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __grid_constant__ ConvResidentParams p,
                                                                        int total_tiles) {
   extern __shared__ uint8_t smem_raw[];
@@ -595,15 +599,35 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
       s1[i] = s2[i] = 0.f;
       piv[i] = (p.stats != nullptr && p.stat_pivot != nullptr) ? p.stat_pivot[(et & 7) * 8 + i] : 0.f;
     }
+    float rsc[8], rsh[8];       // RED: scale / shift of this thread's 8 channels (et & 7)
+    if (RED) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        rsc[i] = p.red_scale[(et & 7) * 8 + i];
+        rsh[i] = p.red_shift[(et & 7) * 8 + i];
+      }
+    }
     uint32_t u = 0;
     bool store_pending = false;
     for (int t = blockIdx.x + g * gridDim.x; t < total_tiles; t += 2 * gridDim.x, ++u) {
       const int n0 = t / tiles_per_img, r = t % tiles_per_img;
       const int h0 = (r / p.tiles_w) * 16, w0 = (r % p.tiles_w) * 8;
       const __nv_bfloat16* add_row = nullptr;
+      const unsigned char* add_bits = nullptr;
       if (p.addend != nullptr) {
         const long long pix = (static_cast<long long>(n0) * p.GH + (h0 + hi)) * p.GW + (w0 + wi);
         add_row = p.addend + pix * 64;
+        if (p.addend_bits != nullptr) add_bits = p.addend_bits + pix * 8;
+      }
+      uint4 yv[8];
+      if (RED) {
+        // this thread's cells of the y tile: 8 channels (et & 7) of rows (et >> 3) + 16 i; a warp reads whole 128-byte lines
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = (et >> 3) + 16 * i;
+          const long long pix = (static_cast<long long>(n0) * p.GH + (h0 + (rr >> 3))) * p.GW + (w0 + (rr & 7));
+          yv[i] = __ldg(reinterpret_cast<const uint4*>(p.red_y + pix * 64 + (et & 7) * 8));
+        }
       }
       RT_WAIT(w0c, mbar_wait(&bars->tmem_full[g], u & 1));
       tc_fence_after();
@@ -619,13 +643,16 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
         uint32_t packed[16];
         if (add_row != nullptr) {
           const uint4* ap = reinterpret_cast<const uint4*>(add_row + cc * 32);
+          const uint32_t am = add_bits != nullptr ? *reinterpret_cast<const uint32_t*>(add_bits + cc * 4) : 0xffffffffu;
 #pragma unroll
           for (int jj = 0; jj < 4; ++jj) {
             const uint4 a4 = ap[jj];
             const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              const float2 af = unpack_bf16x2(aw[e]);
+              float2 af = unpack_bf16x2(aw[e]);
+              if (!((am >> (jj * 8 + e * 2)) & 1u)) af.x = 0.f;
+              if (!((am >> (jj * 8 + e * 2 + 1)) & 1u)) af.y = 0.f;
               packed[jj * 4 + e] = pack_bf16x2(__uint_as_float(v[jj * 8 + e * 2]) + af.x,
                                                __uint_as_float(v[jj * 8 + e * 2 + 1]) + af.y);
             }
@@ -644,6 +671,31 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
       }
       tc_fence_before();
       mbar_arrive(&bars->tmem_empty[g]);          // this thread's TMEM reads are complete: accumulator g is free
+      if (RED) {
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");     // the whole tile is staged
+        const int cg = et & 7;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = (et >> 3) + 16 * i;
+          uint4* cell = reinterpret_cast<uint4*>(stage_out + rr * 128 + ((cg ^ (rr & 7)) << 4));
+          const uint4 g4 = *cell;
+          uint32_t gw[4] = {g4.x, g4.y, g4.z, g4.w};
+          const uint32_t yw[4] = {yv[i].x, yv[i].y, yv[i].z, yv[i].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float2 gf = unpack_bf16x2(gw[e]);
+            const float2 yf = unpack_bf16x2(yw[e]);
+            if (!(fmaf(yf.x, rsc[2 * e], rsh[2 * e]) > 0.f)) gf.x = 0.f;
+            if (!(fmaf(yf.y, rsc[2 * e + 1], rsh[2 * e + 1]) > 0.f)) gf.y = 0.f;
+            s1[2 * e] += gf.x;
+            s2[2 * e] = fmaf(gf.x, yf.x, s2[2 * e]);
+            s1[2 * e + 1] += gf.y;
+            s2[2 * e + 1] = fmaf(gf.y, yf.y, s2[2 * e + 1]);
+            gw[e] = pack_bf16x2(gf.x, gf.y);
+          }
+          *cell = make_uint4(gw[0], gw[1], gw[2], gw[3]);
+        }
+      }
       fence_proxy_async_smem();
       asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
       if (et == 0) {
@@ -679,7 +731,7 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
       trec[kRtEpiBusy] = w2c;
     }
     if (et == 0 && store_pending) tma_store_wait_read0();
-    if (p.stats != nullptr) {
+    if (p.stats != nullptr || RED) {
       // lanes with equal (lane & 7) hold the same channel group: fold 4 lanes, then the 4 warps via shared memory
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -699,7 +751,15 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
         }
       }
       asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-      red_add_f32(p.stats + (et < 64 ? et : p.out_channels + et - 64), part[et]);
+      if (RED) {
+        // S_g = sum(g), S_gy = sum(g*y): sum(g*xhat) = (S_gy - mean*S_g)*invstd is linear in them
+        if (et < 64) {
+          red_add_f32(p.red_sums + et, part[et]);
+          red_add_f32(p.red_sums + 64 + et, (part[64 + et] - p.red_mean[et] * part[et]) * p.red_invstd[et]);
+        }
+      } else {
+        red_add_f32(p.stats + (et < 64 ? et : p.out_channels + et - 64), part[et]);
+      }
     }
   }
 #undef RT_WAIT
@@ -1353,20 +1413,30 @@ int build_dgrad_resident_params(const PmdConvShape& s, const void* dy, const voi
   return 0;
 }
 
-template <bool B_MN>
+void attach_bn_reduce_resident(ConvResidentParams* p, const void* y, const float* scale, const float* shift,
+                               const float* mean, const float* invstd, float* sums) {
+  p->red_y = static_cast<const __nv_bfloat16*>(y);
+  p->red_scale = scale;
+  p->red_shift = shift;
+  p->red_mean = mean;
+  p->red_invstd = invstd;
+  p->red_sums = sums;
+}
+
+template <bool B_MN, bool RED = false>
 static int launch_conv_resident_t(const ConvResidentParams& p, cudaStream_t stream) {
   static PerDevice<int> sms_of;      // also marks "shared-memory attribute set on this device"
   int* sms = sms_of.get();
   if (sms == nullptr) return -1;
   if (*sms == 0) {
-    if (set_smem(conv3x3_resident_kernel<B_MN>, kResSmem)) return -1;
+    if (set_smem(conv3x3_resident_kernel<B_MN, RED>, kResSmem)) return -1;
     int dev = 0;
     PMD_CHECK_CUDA(cudaGetDevice(&dev));
     PMD_CHECK_CUDA(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, dev));
   }
   const int total = p.tiles_w * p.tiles_h * p.N;
   const int grid = total < *sms ? total : *sms;
-  PMD_CHECK_CUDA(launch_pdl(conv3x3_resident_kernel<B_MN>, dim3(grid), dim3(kResThreads), kResSmem, stream, p, total));
+  PMD_CHECK_CUDA(launch_pdl(conv3x3_resident_kernel<B_MN, RED>, dim3(grid), dim3(kResThreads), kResSmem, stream, p, total));
   return 0;
 }
 
@@ -1378,21 +1448,27 @@ int launch_conv_resident(const ConvResidentParams& p_in, cudaStream_t stream) {
     p_traced.trace_cap = g_trace_cap;
   }
   const ConvResidentParams& p = g_trace_buf != nullptr ? p_traced : p_in;
-  if ((p.b_mn ? launch_conv_resident_t<true>(p, stream) : launch_conv_resident_t<false>(p, stream)) != 0) return -1;
+  PMD_REQUIRE(p.red_y == nullptr || p.b_mn, "the fused BatchNorm-backward reduction belongs to the dgrad form");
+  const int rc = p.red_y != nullptr ? launch_conv_resident_t<true, true>(p, stream)
+                 : p.b_mn         ? launch_conv_resident_t<true>(p, stream)
+                                  : launch_conv_resident_t<false>(p, stream);
+  if (rc != 0) return -1;
   count_launch();
   PMD_LAUNCH_CHECK();
   return 0;
 }
 
-// PMD_CONV_RESIDENT: 2 (default) fprop only, 1 fprop and dgrad, 0 off, 3 dgrad only.  In the training step the
-// dgrad runs beside the wgrad of the same layer (side stream); a CTA that owns a whole SM's shared memory cannot
-// share SMs with those, and the lost overlap costs more than the faster kernel gains (1.941 vs 1.918 ms/step).
+// PMD_CONV_RESIDENT: 5 (default) fprop and every 64-channel dgrad, the dgrads with their fused BatchNorm-backward
+// reduction / ReLU-bit addend; 2 fprop only; 1 fprop and dgrad without the fused reduction; 3 dgrad only; 4 fprop + a
+// block's first-convolution dgrad; 0 off.  Without the fused reduction the resident dgrads lose (an extra reduce pass
+// per layer: 1.479 / 1.471 ms/step for modes 1 / 4 against 1.461 for mode 2); with it they win (1.433).  Leaving SMs to
+// the weight-gradient stream (fewer CTAs) does not help (1.438 / 1.443 at 140 / 128 CTAs).
 static int conv_resident_mode() {
-  static const int mode = getenv("PMD_CONV_RESIDENT") == nullptr ? 2 : atoi(getenv("PMD_CONV_RESIDENT"));
-  return mode;
+  return getenv("PMD_CONV_RESIDENT") == nullptr ? 5 : atoi(getenv("PMD_CONV_RESIDENT"));   // read per call (plan builders, tests)
 }
-bool conv_resident_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 2 || conv_resident_mode() == 4; }
-bool conv_resident_dgrad_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 3; }
+bool conv_resident_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 2 || conv_resident_mode() >= 4; }
+bool conv_resident_dgrad_enabled() { return conv_resident_mode() == 1 || conv_resident_mode() == 3 || conv_resident_mode() == 5; }
+bool conv_resident_red_enabled() { return conv_resident_mode() == 5; }
 // mode 4: fprop + only the dgrads that carry no BatchNorm-backward reduction (a block's first convolution)
 bool conv_resident_block_dgrad_enabled() { return conv_resident_dgrad_enabled() || conv_resident_mode() == 4; }
 
@@ -1622,6 +1698,12 @@ extern "C" PMD_API int pmd_conv_dgrad_bn_reduce_addend(const PmdConvShape* s, co
                                                        const void* d_addend, const void* d_y_prev, const float* d_scale,
                                                        const float* d_shift, const float* d_mean, const float* d_invstd,
                                                        float* d_sums, void* d_dz, void* stream) {
+  if (conv_resident_red_enabled() && conv_resident_supported(*s)) {
+    ConvResidentParams hp;
+    if (build_dgrad_resident_params(*s, d_dy, d_w_krsc, d_addend, d_dz, &hp)) return -1;
+    attach_bn_reduce_resident(&hp, d_y_prev, d_scale, d_shift, d_mean, d_invstd, d_sums);
+    return launch_conv_resident(hp, static_cast<cudaStream_t>(stream));
+  }
   ConvGemmParams p;
   if (build_dgrad_params(*s, d_dy, d_w_krsc, nullptr, nullptr, nullptr, d_addend, d_dz, &p, true)) return -1;
   const int rc = attach_bn_reduce(&p, *s, d_y_prev, d_scale, d_shift, d_mean, d_invstd, d_sums);

@@ -127,6 +127,12 @@ struct ConvResidentParams {
   float* stats;
   const float* stat_pivot;   // as in ConvGemmParams
   const __nv_bfloat16* addend;
+  const unsigned char* addend_bits;   // optional ReLU bits of the addend (as ConvGemmParams::addend_bits)
+  // Fused BatchNorm-backward reduction of the layer below (dgrad only; as RED == 1 of conv_gemm_kernel): the output is
+  // masked with (red_scale * y + red_shift > 0) and red_sums[c] += sum(g), red_sums[64 + c] += sum(g * xhat).
+  const __nv_bfloat16* red_y;
+  const float *red_scale, *red_shift, *red_mean, *red_invstd;
+  float* red_sums;
   long long* trace;    // optional [trace_cap][kTraceSlots] per-CTA record (kRt* slots), else null
   int trace_cap;
 };
@@ -146,11 +152,15 @@ inline bool conv_resident_supported(const PmdConvShape& s) {
 }
 bool conv_resident_enabled();        // fprop
 bool conv_resident_dgrad_enabled();
-bool conv_resident_block_dgrad_enabled();   // mode 4: also a block's first-convolution dgrad (no fused BN reduction)  // dgrad (PMD_CONV_RESIDENT: 2 fprop only [default], 1 both, 0 off, 3 dgrad only)
+bool conv_resident_red_enabled();           // mode 5: every 64-channel dgrad resident, with the fused reductions
+bool conv_resident_block_dgrad_enabled();   // a block's first-convolution dgrad (modes 1, 3, 4, 5; see conv_resident_mode in conv_tc.cu)
 int build_fprop_resident_params(const PmdConvShape& s, const void* x, const void* w_krsc, void* y, float* stats,
                                 ConvResidentParams* out);
 int build_dgrad_resident_params(const PmdConvShape& s, const void* dy, const void* w_krsc, const void* addend, void* dx,
                                 ConvResidentParams* out);
+// The layer below's BatchNorm-backward reduction in a resident dgrad's epilogue (see ConvResidentParams::red_y).
+void attach_bn_reduce_resident(ConvResidentParams* p, const void* y, const float* scale, const float* shift,
+                               const float* mean, const float* invstd, float* sums);
 int launch_conv_resident(const ConvResidentParams& p, cudaStream_t stream);
 
 // Builders return 0 / -1 (error text via pmd_last_error()).

@@ -405,6 +405,11 @@ Plan* get_plan(PmdEngine* e, int n) {
                                         &pl->inner_dgrad_r[b.main[j]]))
           return nullptr;
         pl->inner_resident[b.main[j]] = 1;
+        if (conv_resident_red_enabled()) {
+          Conv& pv = e->convs[b.main[j - 1]];
+          attach_bn_reduce_resident(&pl->inner_dgrad_r[b.main[j]], pv.y, pv.scale, pv.shift, pv.mean, pv.invstd, pv.sums);
+          pl->inner_reduced[b.main[j]] = 1;
+        }
       } else {
         // dz_mid[j-1] is consumed only by the BatchNorm backward of conv j-1: let the dgrad epilogue do its reduction
         const int prev = b.main[j - 1];
@@ -439,16 +444,24 @@ Plan* get_plan(PmdEngine* e, int n) {
     } else {
       // identity shortcut: its gradient is dz_out under the block output's ReLU mask -- read straight from dz_out with
       // the ReLU bits when they exist (the BatchNorm backward then does not write the masked copy g_out)
-      const bool masked_addend = b.zbits != nullptr && !(conv_resident_block_dgrad_enabled() && conv_resident_supported(s0));
+      const bool res_block = conv_resident_block_dgrad_enabled() && conv_resident_supported(s0);
+      const bool masked_addend = b.zbits != nullptr && (!res_block || conv_resident_red_enabled());
       if (build_dgrad_params(s0, c0.dy, e->wbf16 + c0.w_off, nullptr, nullptr, nullptr, masked_addend ? b.dz_out : b.g_out,
                              b.dz_in, &pl->block_dgrad[bi], true))
         return nullptr;
       if (masked_addend) pl->block_dgrad[bi].addend_bits = b.zbits;
       pl->g_out_unused[bi] = masked_addend ? 1 : 0;
-      if (conv_resident_block_dgrad_enabled() && conv_resident_supported(s0)) {
-        if (build_dgrad_resident_params(s0, c0.dy, e->wbf16 + c0.w_off, b.g_out, b.dz_in, &pl->block_dgrad_r[bi]))
+      if (res_block) {
+        if (build_dgrad_resident_params(s0, c0.dy, e->wbf16 + c0.w_off, masked_addend ? b.dz_out : b.g_out, b.dz_in,
+                                        &pl->block_dgrad_r[bi]))
           return nullptr;
+        if (masked_addend) pl->block_dgrad_r[bi].addend_bits = b.zbits;
         pl->block_resident[bi] = 1;
+        if (bi == 0 && conv_resident_red_enabled()) {
+          Conv& stem = e->convs[0];
+          attach_bn_reduce_resident(&pl->block_dgrad_r[bi], stem.y, stem.scale, stem.shift, stem.mean, stem.invstd, stem.sums);
+          pl->stem_reduced = true;
+        }
       } else if (bi == 0) {
         // dz_stem is consumed only by the stem's BatchNorm backward (mask recomputed from y_stem): this dgrad's
         // epilogue (accumulator + identity-shortcut addend) masks it and accumulates the two channel sums

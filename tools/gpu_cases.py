@@ -321,6 +321,14 @@ def _with_env(fn, **env):
                 os.environ[k] = v
 
 
+# weight-resident dgrad with the fused BatchNorm-backward reduction (PMD_CONV_RESIDENT=5)
+CASES['resident_dgrad_bn_reduce_layer1_conv2_n512'] = lambda: _with_env(
+    lambda: _dgrad_bn_reduce_case(512, 32, 64, 64, 3), PMD_CONV_RESIDENT=5)
+CASES['resident_dgrad_bn_reduce_addend_layer1_conv1_n96'] = lambda: _with_env(
+    lambda: _dgrad_bn_reduce_case(96, 32, 64, 64, 3, addend=True), PMD_CONV_RESIDENT=5)
+CASES['resident_dgrad_bn_reduce_h16_n7'] = lambda: _with_env(
+    lambda: _dgrad_bn_reduce_case(7, 16, 64, 64, 3), PMD_CONV_RESIDENT=5)
+
 # CTA-pair kernels (tcgen05 cta_group::2, opt-in with PMD_GEMM_2CTA=1): 128- and 256-wide tiles, K-major and MN-major B,
 # with the fused BatchNorm-backward reduction, stride 1 and 2, small and bench-size grids
 CASES['pair_fprop_layer2_conv2_n512'] = lambda: _with_env(lambda: _fprop_case(512, 16, 128, 128, 3, 1), PMD_GEMM_2CTA=1)
@@ -837,6 +845,13 @@ CASES['engine_train_3steps_resnet18_graph'] = lambda: _engine_train_case(18, 3)
 CASES['engine_train_step_resnet50_matches_torch'] = lambda: _engine_train_case(50, 1)
 CASES['engine_train_step_resnet34_identity_shortcuts'] = lambda: _engine_train_case(34, 1)
 CASES['engine_train_step_resnet18_batch512_fixed_floor'] = lambda: _engine_train_case(18, 1, batch=512, fixed_floor=True)
+
+
+# every 64-channel dgrad on the weight-resident kernel: fused reductions, ReLU-bit addend (identity shortcuts)
+CASES['engine_train_step_resnet18_batch512_resident_dgrads'] = lambda: _with_env(
+    lambda: _engine_train_case(18, 1, batch=512, fixed_floor=True), PMD_CONV_RESIDENT=5)
+CASES['engine_train_step_resnet34_resident_dgrads'] = lambda: _with_env(lambda: _engine_train_case(34, 1), PMD_CONV_RESIDENT=5)
+CASES['engine_train_3steps_resnet18_graph_resident_dgrads'] = lambda: _with_env(lambda: _engine_train_case(18, 3), PMD_CONV_RESIDENT=5)
 
 
 @case('engine_loss_decreases_and_tail_batch')
