@@ -618,6 +618,8 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
         const long long pix = (static_cast<long long>(n0) * p.GH + (h0 + hi)) * p.GW + (w0 + wi);
         add_row = p.addend + pix * 64;
         if (p.addend_bits != nullptr) add_bits = p.addend_bits + pix * 8;
+        // this row's addend (128 bytes) is read after the accumulator wait: pull its line towards the SM now
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(add_row));
       }
       uint4 yv[8];
       if (RED) {

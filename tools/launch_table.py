@@ -1,6 +1,7 @@
 """Turns an ncu per-launch CSV (--metrics gpu__time_duration.sum --csv) of `bench.py --no-graph` into the per-kernel
 table of ONE training step kept under profiles/.  A step is the launch range from an augmentation kernel to the
-following stem-weight re-pad (the first and last kernels the engine enqueues per step).
+following stem-weight re-pad (the first and last kernels the engine enqueues per step; the first is the fused stem
+kernel, or the augmentation kernel of the two-kernel form).
 
     ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file gpurun_out/l.csv \
         python bench.py --no-graph --steps 1 --warmup 3
@@ -27,7 +28,7 @@ def main():
         if r.get('Metric Name') != 'gpu__time_duration.sum':
             continue
         rows.append((short(r['Kernel Name']), float(r['Metric Value'].replace(',', '')) / 1e3, r['Grid Size']))
-    starts = [i for i, r in enumerate(rows) if r[0].startswith('augment')]
+    starts = [i for i, r in enumerate(rows) if r[0].startswith('augment') or r[0].startswith('stem_fused')]
     ends = [i for i, r in enumerate(rows) if r[0].startswith('pad_stem_weight')]
     step = None
     for s in reversed(starts):
