@@ -1091,6 +1091,10 @@ int encode_tiled_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t
 // shared-memory operand limit (96 B/clk instead of 128), but leave half as many CTAs; PMD_GEMM_BN256: 0 never,
 // 1 whenever the channel count allows, 2 (default) only when at least `148` CTAs remain.
 static int pick_bn_tile(int out_channels, int pixel_tiles, int classes) {
+  if (const char* f = getenv("PMD_GEMM_BN")) {      // experiments: force the tile width where the channel count allows it
+    const int bn = atoi(f);
+    if ((bn == 64 || bn == 128 || bn == 256) && out_channels % bn == 0) return bn;
+  }
   static const int mode = getenv("PMD_GEMM_BN256") == nullptr ? 2 : atoi(getenv("PMD_GEMM_BN256"));
   if (out_channels % 256 == 0 && mode != 0) {
     const int ctas = pixel_tiles * (out_channels / 256) * classes;

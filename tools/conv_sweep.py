@@ -15,6 +15,8 @@ from pmdist.ops import conv as cv  # noqa: E402
 LAYERS = {'layer2_conv2': (16, 128, 128, 3, 1), 'layer3_conv2': (8, 256, 256, 3, 1), 'layer4_conv2': (4, 512, 512, 3, 1),
           'layer2_conv1': (32, 64, 128, 3, 2), 'layer3_conv1': (16, 128, 256, 3, 2), 'layer4_conv1': (8, 256, 512, 3, 2)}
 SETTINGS = [{'PMD_GEMM_2CTA': '0'}, {'PMD_GEMM_2CTA': '1'}, {'PMD_GEMM_2CTA': '1', 'PMD_GEMM2_STAGES128': '4', 'PMD_GEMM2_STAGES256': '3'}]
+if os.environ.get('PMD_SWEEP') == 'bn':      # tile width instead of CTA pairs
+    SETTINGS = [{}, {'PMD_GEMM_BN': '64'}, {'PMD_GEMM_BN': '128'}, {'PMD_GEMM_BN': '256'}]
 N = 512
 flush = torch.empty(512 << 20, dtype=torch.uint8, device='cuda')
 
@@ -40,7 +42,7 @@ for name, (h, c, k, r, st) in LAYERS.items():
     dy = torch.randn(N, ho, ho, k, device='cuda').to(torch.bfloat16)
     stats = torch.zeros(2 * k, device='cuda')
     for setting in SETTINGS:
-        for kk in ('PMD_GEMM_2CTA', 'PMD_GEMM2_STAGES128', 'PMD_GEMM2_STAGES256'):
+        for kk in ('PMD_GEMM_2CTA', 'PMD_GEMM2_STAGES128', 'PMD_GEMM2_STAGES256', 'PMD_GEMM_BN'):
             os.environ.pop(kk, None)
         os.environ.update(setting)
         f = timed(lambda: cv.conv_fprop(x, w, st, stats))
