@@ -28,7 +28,10 @@ KERNELS = {
     'conv_gemm_kernel_128_3_fprop_cta_pair': 'conv_gemm_kernelILi128ELi3ELb0ELi0ELb1EE',
     'conv_wgrad_kernel_256_3_2': 'conv_wgrad_kernelILi256ELi3ELi2EE',
     'conv_wgrad_patch_kernel_4': 'conv_wgrad_patch_kernelILi4EE',
-    'conv3x3_resident_kernel_fprop': 'conv3x3_resident_kernelILb0EE',
+    'conv3x3_resident_kernel_fprop': 'conv3x3_resident_kernelILb0ELb0EE',
+    'conv3x3_resident_kernel_dgrad_bn_reduce': 'conv3x3_resident_kernelILb1ELb1EE',
+    'stem_fused_kernel_gather_4groups': 'stem_fused_kernelILb1ELi4EE',
+    'allreduce_sgd_ll_kernel': 'allreduce_sgd_ll_kernel',
     'allreduce_sgd_kernel_nvls': 'allreduce_sgd_kernelILi3EE',
     'allreduce_sgd_kernel_twoshot': 'allreduce_sgd_kernelILi2EE',
     'small_allreduce_push_kernel': 'small_allreduce_push_kernel',
