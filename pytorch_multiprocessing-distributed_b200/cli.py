@@ -53,6 +53,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--device', default='auto', choices=['auto', 'cuda', 'cpu'])
     p.add_argument('--no-sync-bn', action='store_true', help='per-rank BatchNorm statistics')
     p.add_argument('--no-graph', action='store_true', help='native engine: do not capture CUDA graphs')
+    p.add_argument('--deterministic', action='store_true',
+                   help='bitwise-reproducible runs: the torch-autograd engine under torch.use_deterministic_algorithms '
+                        '(cuDNN deterministic, fixed cuBLAS workspace), NCCL / gloo all-reduce; the native engine '
+                        'accumulates split-K and BatchNorm partial sums with fp32 atomics and is not offered here')
     p.add_argument('--host-dataset', action='store_true',
                    help='native engine: keep the dataset in pinned host memory and copy every batch (default: the '
                         'dataset is uploaded once and lives in GPU memory; a step copies only its indices)')

@@ -57,6 +57,23 @@ def resolve_device(args, rank: int) -> torch.device:
     return torch.device('cpu')
 
 
+def apply_deterministic(args) -> None:
+    """--deterministic: the same command line twice gives bit-identical checkpoints (the reference leaves
+    cudnn.benchmark on and is not reproducible, ref:main.py:45).  Only the torch-autograd engine qualifies: the native
+    kernels reduce split-K and statistics partials with fp32 atomics, whose order varies from run to run."""
+    if not getattr(args, 'deterministic', False):
+        return
+    if args.engine == 'native':
+        raise SystemExit('--deterministic needs the torch-autograd engine (--engine host or auto)')
+    args.engine = 'host'
+    if args.backend in ('auto', 'p2p'):
+        args.backend = 'auto_host'
+    os.environ.setdefault('CUBLAS_WORKSPACE_CONFIG', ':4096:8')      # before the first cuBLAS call of this process
+    torch.use_deterministic_algorithms(True, warn_only=True)
+    torch.backends.cudnn.deterministic = True
+    torch.backends.cudnn.benchmark = False
+
+
 def build_engine(args, model, comm, device, sgd):
     engine = args.engine
     if engine == 'auto':
@@ -75,6 +92,8 @@ def build_engine(args, model, comm, device, sgd):
 
 def _make_comm(args, rank, world_size, device):
     backend = args.backend
+    if backend == 'auto_host':        # --deterministic: library all-reduce (fixed ring order), no peer-memory kernels
+        backend = ('nccl' if device.type == 'cuda' else 'gloo') if world_size > 1 else 'single'
     if backend == 'auto':
         backend = ('p2p' if device.type == 'cuda' else 'gloo') if world_size > 1 else 'single'
     if backend == 'p2p':
@@ -176,6 +195,7 @@ def validate(engine, loader, epoch: int, args, rank: int, logger: Optional[Logge
 
 def worker(rank: int, world_size: int, args) -> None:
     """ref:main.py:32-84, one call per rank."""
+    apply_deterministic(args)
     torch.manual_seed(args.seed)
     device = resolve_device(args, rank)
     if device.type == 'cpu':

@@ -70,3 +70,16 @@ def test_cli_host_engine_nccl_baseline_two_gpus(tmp_path):
               '--test-size', '32', '--save_path', out, '--print-freq', '1', '--engine', 'host', '--backend', 'nccl'])
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert os.path.exists(os.path.join(out, 'model_1.pth'))
+
+
+@pytest.mark.gpu
+def test_cli_deterministic_flag_gives_bit_identical_checkpoints_on_gpu(tmp_path):
+    """--deterministic selects the torch-autograd engine under deterministic algorithms: two runs, identical bytes."""
+    sds = []
+    for i in range(2):
+        out = str(tmp_path / f'det{i}') + '/'
+        r = _run(['--world_size', '1', '--epochs', '1', '--batch_size', '32', '--data', 'synthetic', '--train-size', '96',
+                  '--test-size', '32', '--save_path', out, '--deterministic'])
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        sds.append(torch.load(out + 'model_1.pth', weights_only=True))
+    assert all(torch.equal(sds[0][k], sds[1][k]) for k in sds[0])

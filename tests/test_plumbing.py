@@ -129,3 +129,16 @@ def _hanging_worker(rank, world):
 def test_watchdog_timeout():
     with pytest.raises(TimeoutError):
         launch.spawn(_hanging_worker, 2, timeout=3)
+
+
+def test_deterministic_flag_gives_bit_identical_checkpoints(tmp_path):
+    """--deterministic: the same command twice -> the same bytes in every tensor of the checkpoint."""
+    sds = []
+    for i in range(2):
+        out = str(tmp_path / f'run{i}') + '/'
+        r = _run(['--world_size', '2', '--epochs', '1', '--batch_size', '16', '--data', 'synthetic', '--train-size', '32',
+                  '--test-size', '16', '--save_path', out, '--device', 'cpu', '--deterministic'])
+        assert r.returncode == 0, r.stdout + r.stderr
+        sds.append(torch.load(out + 'model_1.pth', weights_only=True))
+    assert sds[0].keys() == sds[1].keys()
+    assert all(torch.equal(sds[0][k], sds[1][k]) for k in sds[0])
