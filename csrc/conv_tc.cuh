@@ -191,7 +191,9 @@ int encode_tiled_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t
 // BatchNorm statistics in ONE persistent kernel.  Builder warps write the 27-column patches of 128 consecutive pixels
 // straight into the swizzled shared-memory A tile (and, for the weight gradient, into x0); no im2col read-back.
 struct StemFusedParams {
-  CUtensorMap w;       // padded stem weight [64 k][64 c], box 64 x 64
+  CUtensorMap w;       // padded stem weight [64 k][64 c], box 64 x 64 (used when w_raw is null)
+  const __nv_bfloat16* w_raw;   // or the KRSC stem weight [64][w_rsc] itself: the kernel pads it into shared memory
+  int w_rsc;
   CUtensorMap out;     // y viewed as [M pixels][64], box 64 x 128
   CUtensorMap x0m;     // x0 viewed as [M pixels][32 of 64 columns] (or all 64), box 64 x 128: store of an A slot
   int x0_tma;          // x0m is valid: x0 leaves through TMA; 0 = per-thread stores

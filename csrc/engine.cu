@@ -667,6 +667,8 @@ int run_forward(PmdEngine* e, Plan* pl, bool train, cudaStream_t st) {
     sp.x0 = train ? e->x0 : nullptr;      // only the weight gradient reads the im2col rows
     sp.stats = train ? e->convs[0].stats : nullptr;
     sp.stat_pivot = e->convs[0].pivot;
+    sp.w_raw = e->wbf16 + e->convs[0].w_off;      // the optimizer's bf16 copy; padded inside the kernel
+    sp.w_rsc = e->convs[0].real_rsc;
     E_CHECK(launch_stem_fused(sp, st));
   } else if (e->ds_on) {
     const int* idx = e->in_index + e->in_slot * (4 + c.max_batch);
@@ -730,9 +732,10 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
   PMD_CHECK_CUDA(cudaMemsetAsync(e->grad, 0, c.slab_elems * 4, st));
   PMD_CHECK_CUDA(cudaMemsetAsync(e->hptr<char>(e->bnpart_off), 0, e->bnpart_bytes, st));
   E_CHECK(run_forward(e, pl, true, st));
-  E_CHECK(pmd_ce_fwd_bwd(e->logits, e->in_labels, nullptr, n, c.num_classes, 1.0f / n, e->dlogits, e->metrics, st));
   BucketTracker bt{e, st, e->bucket_params, 0, lr};
   Block& lb = e->blocks.back();
+  // (head forward / loss / backward stay three launches: one kernel per image doing all three was 6 us per step slower)
+  E_CHECK(pmd_ce_fwd_bwd(e->logits, e->in_labels, nullptr, n, c.num_classes, 1.0f / n, e->dlogits, e->metrics, st));
   E_CHECK(pmd_pool_fc_bwd(e->dlogits, e->feat, e->param + c.fc_w_off, n, lb.Hout * lb.Hout, lb.Cout, c.num_classes,
                           e->grad + c.fc_w_off, e->grad + c.fc_b_off, lb.dz_out, st));
   E_CHECK(bt.done(c.fc_b_bucket));
@@ -832,7 +835,8 @@ int run_train(PmdEngine* e, Plan* pl, float lr, cudaStream_t st) {
     PMD_CHECK_CUDA(cudaEventRecord(ev, e->wg_stream));
     PMD_CHECK_CUDA(cudaStreamWaitEvent(st, ev, 0));
   }
-  E_CHECK(pmd_pad_stem_weight(e->wbf16 + e->convs[0].w_off, e->stem_w_pad, 64, e->convs[0].real_rsc, st));
+  if (!pl->stem_fused)      // the two-kernel stem reads a padded copy; the fused kernel pads in shared memory
+    E_CHECK(pmd_pad_stem_weight(e->wbf16 + e->convs[0].w_off, e->stem_w_pad, 64, e->convs[0].real_rsc, st));
   return 0;
 }
 

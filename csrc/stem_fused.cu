@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(sf_threads(GROUPS), 1) stem_fused_kernel(const
       mbar_init(&bars->a_full[s], 128);
       mbar_init(&bars->a_empty[s], 1);
     }
-    mbar_init(&bars->w_full, 1);
+    mbar_init(&bars->w_full, p.w_raw != nullptr ? 256 : 1);
     mbar_init(&bars->tmem_full[0], 1);
     mbar_init(&bars->tmem_full[1], 1);
     mbar_init(&bars->tmem_empty[0], 128);
@@ -118,8 +118,10 @@ __global__ void __launch_bounds__(sf_threads(GROUPS), 1) stem_fused_kernel(const
   if (warp == 0) {
     // ------------------------------------------------------------------ weights + MMA issuer
     if (lane == 0) {
-      mbar_expect_tx(&bars->w_full, kSfWBytes);
-      tma_load_2d(&p.w, &bars->w_full, smem_w, 0, 0);
+      if (p.w_raw == nullptr) {
+        mbar_expect_tx(&bars->w_full, kSfWBytes);
+        tma_load_2d(&p.w, &bars->w_full, smem_w, 0, 0);
+      }
       constexpr uint32_t idesc = make_idesc_bf16(128, 64, false, false);
       const uint32_t w_addr = smem_u32(smem_w);
       mbar_wait(&bars->w_full, 0);
@@ -268,6 +270,23 @@ __global__ void __launch_bounds__(sf_threads(GROUPS), 1) stem_fused_kernel(const
     const int et = static_cast<int>(threadIdx.x) - 32 * kSfEpiWarp0 - g * 128;
     uint8_t* stage_out = smem_out + g * kSfTileBytes;
     const int bar_id = 1 + g;
+    if (p.w_raw != nullptr) {
+      // the [64][rsc] weight as the optimizer left it -> K-major SW128 tile, columns rsc..31 zero (no re-pad kernel at the
+      // end of every step): 256 threads x 8 elements, one 16-byte chunk each
+      const int wt = et + g * 128;                   // 0..255
+      const int k = wt >> 2, c0 = (wt & 3) * 8;
+      uint32_t w4[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int c = c0 + 2 * e;
+        const unsigned short lo = c < p.w_rsc ? *reinterpret_cast<const unsigned short*>(p.w_raw + k * p.w_rsc + c) : 0;
+        const unsigned short hi = c + 1 < p.w_rsc ? *reinterpret_cast<const unsigned short*>(p.w_raw + k * p.w_rsc + c + 1) : 0;
+        w4[e] = static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+      }
+      *reinterpret_cast<uint4*>(smem_w + k * 128 + (((c0 >> 3) ^ (k & 7)) << 4)) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+      fence_proxy_async_smem();
+      mbar_arrive(&bars->w_full);
+    }
     float s1[8], s2[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) s1[i] = s2[i] = 0.f;
@@ -378,7 +397,7 @@ int build_stem_fused_params(int N, int H, int W, int pad, const void* w_pad, voi
     const uint64_t dims[2] = {64ull, 64ull};
     const uint64_t strides[1] = {128ull};
     const uint32_t box[2] = {64u, 64u};
-    if (encode_tiled_bf16(&p.w, w_pad, 2, dims, strides, box)) return -1;
+    if (w_pad != nullptr && encode_tiled_bf16(&p.w, w_pad, 2, dims, strides, box)) return -1;
   }
   const uint64_t dims[2] = {64ull, static_cast<uint64_t>(N) * H * W};
   const uint64_t strides[1] = {128ull};
@@ -436,6 +455,7 @@ using namespace pmd;
 
 extern "C" PMD_API int pmd_stem_fused(const PmdStemFused* a, void* stream) {
   PMD_REQUIRE(a != nullptr && a->w_pad != nullptr && a->y != nullptr, "weights and output are required");
+  PMD_REQUIRE(a->w_rsc >= 0 && a->w_rsc <= 32, "w_rsc must be 0 (padded [64][64] weight) or the row length of the raw weight (<= 32)");
   StemFusedParams p;
   if (build_stem_fused_params(a->N, a->H, a->W, a->pad, a->w_pad, a->x0, a->y, &p)) return -1;
   p.ds = a->d_dataset_desc;
@@ -448,5 +468,9 @@ extern "C" PMD_API int pmd_stem_fused(const PmdStemFused* a, void* stream) {
   p.x0 = static_cast<__nv_bfloat16*>(a->x0);
   p.stats = a->stats;
   p.stat_pivot = a->stat_pivot;
+  if (a->w_rsc > 0) {
+    p.w_raw = static_cast<const __nv_bfloat16*>(a->w_pad);
+    p.w_rsc = a->w_rsc;
+  }
   return launch_stem_fused(p, static_cast<cudaStream_t>(stream));
 }

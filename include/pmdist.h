@@ -261,11 +261,12 @@ typedef struct PmdStemFused {
   const unsigned char* d_u8;
   const int* d_aug;
   int N, H, W, pad;
-  const void* w_pad;
+  const void* w_pad;   /* padded [64][64] weight (w_rsc == 0), or the raw KRSC weight [64][w_rsc] (w_rsc = 27) */
   void* x0;
   void* y;
   float* stats;
   const float* stat_pivot;
+  int w_rsc;
 } PmdStemFused;
 int pmd_stem_fused(const PmdStemFused* a, void* stream);
 

@@ -567,6 +567,7 @@ def _head_case(N=32, H=4, C=512, classes=10):
 
 
 CASES['head_pool_fc_ce_large_map_28x28_c2048_split_pool'] = lambda: _head_case(8, 28, 2048, 10)
+CASES['head_pool_fc_ce_n512'] = lambda: _head_case(512, 4, 512, 10)
 
 
 @case('ce_valid_mask_excludes_padding')
@@ -946,7 +947,8 @@ def _stem_fused(N=8, H=32, timed=0):
     class SF(C.Structure):
         _fields_ = [('ds', C.c_void_p), ('hdr', C.c_void_p), ('idx', C.c_void_p), ('labels', C.c_void_p), ('valid', C.c_void_p),
                     ('u8', C.c_void_p), ('aug', C.c_void_p), ('N', C.c_int), ('H', C.c_int), ('W', C.c_int), ('pad', C.c_int),
-                    ('w_pad', C.c_void_p), ('x0', C.c_void_p), ('y', C.c_void_p), ('stats', C.c_void_p), ('pivot', C.c_void_p)]
+                    ('w_pad', C.c_void_p), ('x0', C.c_void_p), ('y', C.c_void_p), ('stats', C.c_void_p), ('pivot', C.c_void_p),
+                    ('w_rsc', C.c_int)]
     lib = _lib.lib()
     M = 16384 if timed else max(2 * N, 16)      # timed: a dataset larger than a few MB, so the gather misses L2 like a real one
     src = synthetic_source(M, H, seed=31)
@@ -998,8 +1000,9 @@ def _stem_fused(N=8, H=32, timed=0):
     lab_h = torch.zeros_like(lab_g)
     val_h = torch.zeros_like(val_g)
     st_h = torch.zeros(128, device='cuda')
-    b = SF(desc.data_ptr(), hdr.data_ptr(), idx.data_ptr(), lab_h.data_ptr(), val_h.data_ptr(), 0, 0, N, H, H, 8, wp.data_ptr(),
-           col_h.data_ptr(), y_h.data_ptr(), st_h.data_ptr(), 0)
+    # this form takes the raw [64][27] weight and pads it in shared memory (what the engine does)
+    b = SF(desc.data_ptr(), hdr.data_ptr(), idx.data_ptr(), lab_h.data_ptr(), val_h.data_ptr(), 0, 0, N, H, H, 8, wk.data_ptr(),
+           col_h.data_ptr(), y_h.data_ptr(), st_h.data_ptr(), 0, 27)
     check(lib.pmd_stem_fused(C.byref(b), stream_ptr()))
     torch.cuda.synchronize()
     yg = y_g.float().reshape(-1, 64)
