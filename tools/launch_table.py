@@ -1,7 +1,6 @@
 """Turns an ncu per-launch CSV (--metrics gpu__time_duration.sum --csv) of `bench.py --no-graph` into the per-kernel
-table of ONE training step kept under profiles/.  A step is the launch range from an augmentation kernel to the
-following stem-weight re-pad (the first and last kernels the engine enqueues per step; the first is the fused stem
-kernel, or the augmentation kernel of the two-kernel form).
+table of ONE training step kept under profiles/.  A step is the launch range from the engine's first kernel (the fused
+stem kernel, or the augmentation kernel of the two-kernel form) to just before the next step's first kernel.
 
     ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file gpurun_out/l.csv \
         python bench.py --no-graph --steps 1 --warmup 3
@@ -29,14 +28,13 @@ def main():
             continue
         rows.append((short(r['Kernel Name']), float(r['Metric Value'].replace(',', '')) / 1e3, r['Grid Size']))
     starts = [i for i, r in enumerate(rows) if r[0].startswith('augment') or r[0].startswith('stem_fused')]
-    ends = [i for i, r in enumerate(rows) if r[0].startswith('pad_stem_weight')]
     step = None
-    for s in reversed(starts):
-        e = next((x for x in ends if x > s), None)
-        if e is not None:
-            step = rows[s:e + 1]
-            break
-    if step is None:
+    if len(starts) >= 2:            # the last complete step: from one first kernel to just before the next
+        step = rows[starts[-2]:starts[-1]]
+        while step and not (step[-1][0].startswith('allreduce') or step[-1][0].startswith('pad_stem_weight') or
+                            step[-1][0].startswith('conv_wgrad')):
+            step.pop()              # host-side torch kernels between steps (metric reads, copies) are not part of it
+    if not step:
         step = rows
     agg = OrderedDict()
     for name, us, _ in step:
