@@ -62,8 +62,25 @@ __device__ __forceinline__ void column_reduce2(F f, long long rows, int C, float
   }
 }
 
+// Streaming read: every BatchNorm pass touches its inputs once, so they are loaded with an L2 evict-first policy -- the
+// tensor the pass WRITES (read next by a convolution) then survives in the 126 MB L2 instead of being pushed out by them.
+// Same box, same run: 1.4437 -> 1.4155 ms/step together with the convolutions' operand hints (conv_l2_hint_mask).
+#ifndef PMD_BN_STREAM      // -DPMD_BN_STREAM=0 builds the plain-load variant (A/B: PMDIST_LIB=<that library>)
+#define PMD_BN_STREAM 1
+#endif
+__device__ __forceinline__ uint4 ld_stream16(const void* p) {
+  uint4 u;
+  if (!PMD_BN_STREAM) return *reinterpret_cast<const uint4*>(p);
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  asm volatile("ld.global.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+               : "l"(p), "l"(pol)
+               : "memory");
+  return u;
+}
 __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
-  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const uint4 u = ld_stream16(p);
   const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -946,3 +963,4 @@ extern "C" PMD_API int pmd_bn_bwd_apply_static(const void* d_dz, const void* d_z
   b.dbeta = d_dbeta;
   return pmd_bn_bwd_apply_multi(d_dz, d_z, nullptr, nullptr, relu ? 1 : 0, &b, 1, count_total, d_g_out, rows, C, stream);
 }
+

@@ -49,6 +49,17 @@ struct PipeBars {
   uint32_t invalid_rows[4];   // per epilogue warp (TMEM lane quarter): rows of the tile outside the tensor (zero-filled)
 };
 
+__device__ __forceinline__ uint4 ld_stream16(const void* p) {     // 16-byte global load, L2 evict-first
+  uint4 u;
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  asm volatile("ld.global.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+               : "l"(p), "l"(pol)
+               : "memory");
+  return u;
+}
+
 __device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* raw) {
   const uint32_t s = smem_u32(raw);
   return raw + ((1024u - (s & 1023u)) & 1023u);
@@ -178,7 +189,10 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const __grid_consta
           continue;
         }
         mbar_expect_tx(&bars->full[s], kStageBytes);
-        tma_load_4d(&p.a[kb.a_map], &bars->full[s], sa, kb.a_ch, w0 + kb.dw, h0 + kb.dh, n0);
+        if ((p.l2_hint & (B_MN ? 4 : 2)) != 0)
+          tma_load_4d_stream(&p.a[kb.a_map], &bars->full[s], sa, kb.a_ch, w0 + kb.dw, h0 + kb.dh, n0);
+        else
+          tma_load_4d(&p.a[kb.a_map], &bars->full[s], sa, kb.a_ch, w0 + kb.dw, h0 + kb.dh, n0);
         if (B_MN) {
 #pragma unroll
           for (int j = 0; j < BN / 64; ++j)   // KRSC map (c, tap, k): 64 output channels x 64 reduction rows per box
@@ -538,7 +552,10 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
           const int s = it % kResSlots;
           RT_WAIT(w0c, mbar_wait(&bars->a_empty[s], ((it / kResSlots) & 1) ^ 1u));
           mbar_expect_tx(&bars->a_full[s], kColPatchBytes);
-          tma_load_4d(&p.a, &bars->a_full[s], smem_a + s * kColPatchBytes, 0, w0 + q - 1, h0 - 1, n0);
+          if ((p.l2_hint & (B_MN ? 4 : 1)) != 0)
+            tma_load_4d_stream(&p.a, &bars->a_full[s], smem_a + s * kColPatchBytes, 0, w0 + q - 1, h0 - 1, n0);
+          else
+            tma_load_4d(&p.a, &bars->a_full[s], smem_a + s * kColPatchBytes, 0, w0 + q - 1, h0 - 1, n0);
         }
       }
       if (tracing) trec[kRtProdWaitEmpty] = w0c;
@@ -628,7 +645,8 @@ __global__ void __launch_bounds__(kResThreads) conv3x3_resident_kernel(const __g
         for (int i = 0; i < 8; ++i) {
           const int rr = (et >> 3) + 16 * i;
           const long long pix = (static_cast<long long>(n0) * p.GH + (h0 + (rr >> 3))) * p.GW + (w0 + (rr & 7));
-          yv[i] = __ldg(reinterpret_cast<const uint4*>(p.red_y + pix * 64 + (et & 7) * 8));
+          const uint4* yp = reinterpret_cast<const uint4*>(p.red_y + pix * 64 + (et & 7) * 8);
+          yv[i] = (p.l2_hint & 32) != 0 ? ld_stream16(yp) : __ldg(yp);
         }
       }
       RT_WAIT(w0c, mbar_wait(&bars->tmem_full[g], u & 1));
@@ -830,10 +848,14 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_kernel(const __grid_const
         mbar_expect_tx(&bars->full[s], kStageBytes);
 #pragma unroll
         for (int j = 0; j < kABox; ++j)
-          tma_load_4d(&p.x[bx[j].a_map], &bars->full[s], sa + j * kBoxBytes, bx[j].a_ch, w0 + bx[j].dw, h0 + bx[j].dh, n0);
+          if ((p.l2_hint & 8) != 0)
+            tma_load_4d_stream(&p.x[bx[j].a_map], &bars->full[s], sa + j * kBoxBytes, bx[j].a_ch, w0 + bx[j].dw, h0 + bx[j].dh, n0);
+          else
+            tma_load_4d(&p.x[bx[j].a_map], &bars->full[s], sa + j * kBoxBytes, bx[j].a_ch, w0 + bx[j].dw, h0 + bx[j].dh, n0);
 #pragma unroll
         for (int j = 0; j < BNW / 64; ++j)
-          tma_load_4d(&p.dy, &bars->full[s], sb + j * kBoxBytes, k0 + j * 64, w0, h0, n0);
+          if ((p.l2_hint & 16) != 0) tma_load_4d_stream(&p.dy, &bars->full[s], sb + j * kBoxBytes, k0 + j * 64, w0, h0, n0);
+          else tma_load_4d(&p.dy, &bars->full[s], sb + j * kBoxBytes, k0 + j * 64, w0, h0, n0);
       }
     }
   } else if (warp == 1) {
@@ -952,8 +974,10 @@ __global__ void __launch_bounds__(kThreads) conv_wgrad_patch_kernel(const __grid
         mbar_expect_tx(&bars->full[s], kWPatchStage);
 #pragma unroll
         for (int q = 0; q < 3; ++q)
-          tma_load_4d(&p.x[0], &bars->full[s], sa + q * kWPatchBytes, c0, w0 + q - 1, h0 - 1, n0);
-        tma_load_4d(&p.dy, &bars->full[s], sa + 3 * kWPatchBytes, k0, w0, h0, n0);
+          if ((p.l2_hint & 8) != 0) tma_load_4d_stream(&p.x[0], &bars->full[s], sa + q * kWPatchBytes, c0, w0 + q - 1, h0 - 1, n0);
+          else tma_load_4d(&p.x[0], &bars->full[s], sa + q * kWPatchBytes, c0, w0 + q - 1, h0 - 1, n0);
+        if ((p.l2_hint & 16) != 0) tma_load_4d_stream(&p.dy, &bars->full[s], sa + 3 * kWPatchBytes, k0, w0, h0, n0);
+        else tma_load_4d(&p.dy, &bars->full[s], sa + 3 * kWPatchBytes, k0, w0, h0, n0);
       }
     }
   } else if (warp == 1) {
@@ -1082,6 +1106,11 @@ void choose_brick(int P, int GW, int GH, int* w_box, int* h_box, int* n_box) {
 
 }  // namespace
 
+int conv_l2_hint_mask() {
+  static const int mask = getenv("PMD_L2_HINT") == nullptr ? 27 : atoi(getenv("PMD_L2_HINT"));
+  return mask;
+}
+
 int encode_tiled_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                       const uint32_t* box) {
   return encode_map(m, base, rank, dims, strides_bytes, box);
@@ -1116,6 +1145,7 @@ int build_fprop_params(const PmdConvShape& s, const void* x, const void* w_krsc,
   PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
   ConvGemmParams& p = *out;
   memset(&p, 0, sizeof(p));
+  p.l2_hint = conv_l2_hint_mask();
   const int pad = s.R / 2, RS = s.R * s.R;
   const int Ho = conv_out_dim(s.H, s.R, s.stride), Wo = conv_out_dim(s.W, s.R, s.stride);
   choose_brick(128, Wo, Ho, &p.w_box, &p.h_box, &p.n_box);
@@ -1183,6 +1213,7 @@ int build_dgrad_params(const PmdConvShape& s, const void* dy, const void* w_rsck
   PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
   ConvGemmParams& p = *out;
   memset(&p, 0, sizeof(p));
+  p.l2_hint = conv_l2_hint_mask();
   const int Ho = conv_out_dim(s.H, s.R, s.stride), Wo = conv_out_dim(s.W, s.R, s.stride);
   if (s2 != nullptr) {
     PMD_REQUIRE(conv_tc_supported(*s2) && s2->N == s.N && s2->H == s.H && s2->W == s.W && s2->C == s.C &&
@@ -1272,6 +1303,7 @@ int build_wgrad_params(const PmdConvShape& s, const void* x, const void* dy, flo
   PMD_REQUIRE(conv_tc_supported(s), "conv shape not supported by the tensor-core path");
   WgradParams& p = *out;
   memset(&p, 0, sizeof(p));
+  p.l2_hint = conv_l2_hint_mask();
   const int pad = s.R / 2, RS = s.R * s.R;
   const int Ho = conv_out_dim(s.H, s.R, s.stride), Wo = conv_out_dim(s.W, s.R, s.stride);
   {
@@ -1388,6 +1420,7 @@ static int build_resident_common(const PmdConvShape& s, const void* in, const vo
   PMD_REQUIRE(conv_resident_supported(s), "shape not eligible for the weight-resident 3x3 kernel");
   ConvResidentParams& p = *o;
   memset(&p, 0, sizeof(p));
+  p.l2_hint = conv_l2_hint_mask();
   p.tiles_w = s.W / 8;
   p.tiles_h = s.H / 16;
   p.N = s.N;

@@ -23,6 +23,7 @@ struct KBlock {
 };
 
 struct ConvGemmParams {
+  int l2_hint;               // L2 eviction hints of the operand loads (set at launch from PMD_L2_HINT, see conv_l2_hint_mask)
   CUtensorMap a[4];
   CUtensorMap b[2];
   CUtensorMap out[4];
@@ -93,6 +94,7 @@ struct WBox {
 };
 
 struct WgradParams {
+  int l2_hint;
   CUtensorMap x[4];
   CUtensorMap dy;
   WBox box[kMaxWBoxes];
@@ -117,6 +119,7 @@ inline bool conv_tc_supported(const PmdConvShape& s) {
 // conv3x3_resident_kernel -- persistent, weights resident in shared memory, activations as three column patches
 // per tile (L2->SM activation traffic 2.7x lower than per-tap boxes).
 struct ConvResidentParams {
+  int l2_hint;
   CUtensorMap a;       // input, box (64 ch, 8, 18, 1): one column patch
   CUtensorMap b;       // KRSC weights (c, tap, k), box 64 x 1 x 64
   CUtensorMap out;     // output, box (64 ch, 8, 16, 1)
@@ -150,6 +153,12 @@ enum {
 inline bool conv_resident_supported(const PmdConvShape& s) {
   return conv_tc_supported(s) && s.R == 3 && s.stride == 1 && s.W % 8 == 0 && s.H % 16 == 0 && s.C == 64 && s.K == 64;
 }
+// PMD_L2_HINT bit mask: operand loads issued with an L2 evict-first policy (the tensor is not read again soon, so it should
+// not push out the one being written for the next kernel): 1 resident fprop activations, 2 per-tap fprop activations,
+// 4 dgrad dy, 8 wgrad x, 16 wgrad dy, 32 the y cells of the resident dgrad reduction.  Default 27 (1 + 2 + 8 + 16): measured on
+// one box in one run, ms/step: 0 -> 1.4531, 19 -> 1.4437, 19 + BatchNorm streaming loads (csrc/bn.cu) -> 1.4155; on another
+// box 19 -> 1.4252, 27 -> 1.4185, 51 -> 1.4271, 59 -> 1.4205; bit 4 (dy is read by the dgrad AND the wgrad) costs ~10 us.
+int conv_l2_hint_mask();
 bool conv_resident_enabled();        // fprop
 bool conv_resident_dgrad_enabled();
 bool conv_resident_red_enabled();           // mode 5: every 64-channel dgrad resident, with the fused reductions

@@ -12,7 +12,7 @@ import sys
 from typing import Optional
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), '_lib', 'libpmdist.so')
+LIB_PATH = os.environ.get('PMDIST_LIB') or os.path.join(os.path.dirname(_HERE), '_lib', 'libpmdist.so')   # PMDIST_LIB: A/B builds
 REPO_ROOT = os.path.dirname(os.path.dirname(_HERE))
 _lib: Optional[C.CDLL] = None
 
